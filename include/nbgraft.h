@@ -1,0 +1,245 @@
+/*
+ * nbgraft.h — C ABI of libnbgraft.so: batched desired-vs-live "needs update"
+ * predicates and the culler's idleness decision, as sm_100a CUDA kernels.
+ *
+ * The reference (harshad16/odh-kubeflow) is a Go controller with no FFI; the
+ * calls this library replaces are ordinary in-process Go calls, one object at
+ * a time.  Each entry point below cites the reference function it batches.
+ * Path abbreviations (all under the reference tree):
+ *   COMMON = components/common/reconcilehelper/util.go
+ *   NBCTL  = components/notebook-controller/controllers/notebook_controller.go
+ *   CULL   = components/notebook-controller/controllers/culling_controller.go
+ *
+ * Conventions
+ *   - every buffer is caller-allocated, borrowed for the duration of the call,
+ *     and is a flat array of fixed-width integers: no pointers inside buffers
+ *     (cgo pointer-passing rules are satisfied by construction);
+ *   - status is an int: 0 = OK, negative = error (nbg_strerror); nothing
+ *     aborts or throws across this boundary;
+ *   - there is NO CPU fallback: without a usable CUDA device nbg_init fails
+ *     with NBG_E_NODEVICE and nothing else can be called;
+ *   - a context may be used from several OS threads at once (the reference
+ *     has up to two concurrent callers, the "notebook" and "Culler"
+ *     controllers); host-buffer calls serialise per device inside the library.
+ *   - strings never cross the boundary: the host packs them as 64-bit hashes
+ *     (nbg_hash64; the empty / missing string is 0, no other string is 0).
+ */
+#ifndef NBGRAFT_H
+#define NBGRAFT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NBG_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+#define NBG_OK              0
+#define NBG_E_NODEVICE    (-1) /* no CUDA device / driver: there is no CPU path   */
+#define NBG_E_INVAL       (-2) /* null pointer, bad size, bad parameter           */
+#define NBG_E_NOMEM       (-3) /* device or pinned-host allocation failed         */
+#define NBG_E_CUDA        (-4) /* a CUDA call failed; nbg_last_cuda_error()       */
+#define NBG_E_NILREPLICAS (-5) /* an object had a nil Spec.Replicas: the Go code
+                                  would panic at COMMON:123; reason bit7 marks it */
+#define NBG_E_RANGE       (-6) /* CSR offsets not monotone or past the entry array */
+#define NBG_E_TOOBIG      (-7) /* batch exceeds a documented maximum              */
+
+/* ---- schema constants (frozen; tests/test_abi.py checks them) ---------- */
+#define NBG_POD_SLOTS   192u  /* u64 slots per PodSpec tile  (1536 B per side)   */
+#define NBG_SVC_SLOTS    16u  /* u64 slots per Service ports tile (128 B)        */
+#define NBG_VS_SLOTS      8u  /* u64 slots per VirtualService spec tile (64 B)   */
+#define NBG_REPLICAS_NIL INT32_MIN /* marks a nil *int32 Replicas pointer        */
+#define NBG_ARGMAX_NONE 0xFFFFFFFFu
+
+/* one map entry: key hash, value hash ("" == 0). Entries of one object are
+ * sorted by key; duplicate keys cannot occur (they are Go map keys). */
+typedef struct nbg_kv { uint64_t key; uint64_t val; } nbg_kv;
+
+/* CSR of per-object string maps (labels, annotations, selector, headers):
+ * object i owns ent[off[i] .. off[i+1]).  off has n+1 elements, off[0] may be
+ * non-zero (a slice of a larger batch). */
+typedef struct nbg_kvmap { const uint32_t* off; const nbg_kv* ent; } nbg_kvmap;
+
+/* ---- reason bits ------------------------------------------------------- */
+/* StatefulSet (COMMON:107-134 + caller pre-step NBCTL:188-194) */
+#define NBG_STS_LABELS      0x01u /* L: live label whose desired value differs (COMMON:109-113) */
+#define NBG_STS_ANNOTATIONS 0x02u /* A: same on annotations (COMMON:116-120)                    */
+#define NBG_STS_REPLICAS    0x04u /* R: *from.Spec.Replicas != *to.Spec.Replicas (COMMON:123)   */
+#define NBG_STS_PODSPEC     0x08u /* P: !reflect.DeepEqual(PodSpec, PodSpec) (COMMON:128)       */
+#define NBG_STS_TMPL_LABELS 0x10u /* D1': caller copied template labels (NBCTL:190-194); NOT part
+                                     of the returned bool                                       */
+#define NBG_STS_NILREPLICAS 0x80u /* object would panic in Go; other bits are still valid except R */
+#define NBG_STS_UPDATE_MASK 0x0Fu
+/* Service (COMMON:166-195) */
+#define NBG_SVC_LABELS      0x01u
+#define NBG_SVC_ANNOTATIONS 0x02u
+#define NBG_SVC_SELECTOR    0x04u /* S: !DeepEqual(to.Spec.Selector, from.Spec.Selector) (COMMON:184) */
+#define NBG_SVC_PORTS       0x08u /* Pt: !DeepEqual(to.Spec.Ports, from.Spec.Ports) (COMMON:189)       */
+#define NBG_SVC_UPDATE_MASK 0x0Fu
+/* VirtualService (COMMON:199-219) */
+#define NBG_VS_SPEC_DIFFERS 0x01u /* both specs present and !DeepEqual (COMMON:214)              */
+#define NBG_VS_TO_MISSING   0x02u /* to.spec missing or not a map: copied, returns true (:209-212) */
+#define NBG_VS_FROM_MISSING 0x04u /* from.spec missing or not a map: returns false (:200-206)     */
+/* bool returned by Go = (reason & FROM_MISSING) ? 0 : (reason & 3) != 0 */
+
+/* flags byte shared by the diff batches (one per object) */
+#define NBG_F_FROM_SEL_NIL   0x01u /* Service: from.Spec.Selector is a nil map (vs empty)   */
+#define NBG_F_TO_SEL_NIL     0x02u
+#define NBG_F_FROM_SPEC_MISS 0x04u /* VS: NestedMap(from,"spec") not found / not a map     */
+#define NBG_F_TO_SPEC_MISS   0x08u
+#define NBG_F_FROM_HDR_NIL   0x10u /* VS: headers.request.set absent (vs empty map)        */
+#define NBG_F_TO_HDR_NIL     0x20u
+
+/* ---- batches ----------------------------------------------------------- */
+/* StatefulSet desired ("from") vs live ("to") pairs. */
+typedef struct nbg_sts_batch {
+  const int32_t*  replicas_from;   /* n; NBG_REPLICAS_NIL = nil pointer            */
+  const int32_t*  replicas_to;     /* n                                            */
+  const uint64_t* tmpl_from;       /* n; digest of Spec.Template.Labels (nil != {}) */
+  const uint64_t* tmpl_to;         /* n                                            */
+  const uint64_t* pod_from;        /* n * NBG_POD_SLOTS, object-major              */
+  const uint64_t* pod_to;          /* n * NBG_POD_SLOTS                            */
+  nbg_kvmap labels_from, labels_to; /* ObjectMeta.Labels                            */
+  nbg_kvmap ann_from, ann_to;       /* ObjectMeta.Annotations                       */
+} nbg_sts_batch;
+
+typedef struct nbg_svc_batch {
+  const uint8_t*  flags;           /* n; NBG_F_*_SEL_NIL                           */
+  const uint64_t* ports_from;      /* n * NBG_SVC_SLOTS                            */
+  const uint64_t* ports_to;
+  nbg_kvmap labels_from, labels_to;
+  nbg_kvmap ann_from, ann_to;
+  nbg_kvmap sel_from, sel_to;      /* Spec.Selector                                */
+} nbg_svc_batch;
+
+typedef struct nbg_vs_batch {
+  const uint8_t*  flags;           /* n; NBG_F_*_SPEC_MISS, NBG_F_*_HDR_NIL        */
+  const uint64_t* spec_from;       /* n * NBG_VS_SLOTS                             */
+  const uint64_t* spec_to;
+  nbg_kvmap hdr_from, hdr_to;      /* spec.http[0].headers.request.set             */
+} nbg_vs_batch;
+
+/* Culler inputs.  An instant is (sec since Unix epoch, nsec) as Go's time.Time
+ * holds it after time.Parse; *_nsf words carry nsec in bits 0..29 and two flags. */
+#define NBG_NSEC_MASK     0x3FFFFFFFu
+#define NBG_REC_PARSE_OK  0x40000000u /* last_activity parsed as RFC3339 (CULL:332,339) */
+#define NBG_REC_IDLE      0x80000000u /* execution_state == "idle" (CULL:320); terminals: unused */
+#define NBG_ANN_PARSE_OK  0x40000000u /* last-activity annotation parsed (CULL:229,353)  */
+#define NBG_ANN_STOP_SET  0x80000000u /* kubeflow-resource-stopped key present (CULL:493-502) */
+#define NBG_CHK_PARSE_OK  0x40000000u /* check-timestamp parsed (CULL:212; failure => zero Time) */
+#define NBG_CHK_PRESENT   0x80000000u /* check-timestamp key present (CULL:208)           */
+#define NBG_NB_LA_PRESENT  0x01u      /* last-activity key present (CULL:442, annotationsExist) */
+#define NBG_NB_POD_MISSING 0x02u      /* pod "<name>-0" not found (CULL:121-135); flow mode only */
+
+typedef struct nbg_cull_batch {
+  const uint32_t* k_off;   /* n+1: kernels of notebook i are records k_off[i]..k_off[i+1) */
+  const int64_t*  k_sec;   /* K                                                          */
+  const uint32_t* k_nsf;   /* K                                                          */
+  const uint32_t* t_off;   /* n+1: terminals                                             */
+  const int64_t*  t_sec;   /* T                                                          */
+  const uint32_t* t_nsf;   /* T                                                          */
+  const int64_t*  ann_sec; /* n: last-activity annotation                                */
+  const uint32_t* ann_nsf; /* n                                                          */
+  const int64_t*  chk_sec; /* n: last_activity_check_timestamp annotation                */
+  const uint32_t* chk_nsf; /* n                                                          */
+  const uint8_t*  nb_flags;/* n                                                          */
+} nbg_cull_batch;
+
+typedef struct nbg_cull_params {
+  int64_t now_sec;           /* time.Now(): one instant for the whole batch            */
+  int32_t now_nsec;          /* 0..999999999                                            */
+  int32_t cull_idle_min;     /* CULL_IDLE_TIME (CULL:37,525-558), minutes               */
+  int32_t check_period_min;  /* IDLENESS_CHECK_PERIOD (CULL:39), minutes                */
+  int32_t mode;              /* NBG_CULL_PREDICATES or NBG_CULL_RECONCILE               */
+} nbg_cull_params;
+#define NBG_CULL_PREDICATES 0 /* C4,C5,C7,C8 evaluated unconditionally on every notebook */
+#define NBG_CULL_RECONCILE  1 /* the decision flow of CullingReconciler.Reconcile, CULL:86-203 */
+#define NBG_CULL_MAX_MINUTES 100000000 /* |minutes| bound so minutes*60e9 ns fits Go's int64 Duration */
+
+/* action byte written per notebook */
+#define NBG_ACT_SRC_MASK   0x03u /* new last-activity: 0 unchanged, 1 now (CULL:386), 2 kernels[argmax]
+                                    (CULL:399), 3 terminals[argmax] (CULL:425)                      */
+#define NBG_ACT_PERIOD     0x04u /* cullingCheckPeriodHasPassed (CULL:207-217)                      */
+#define NBG_ACT_CULL       0x08u /* notebookIsIdle after the updates (CULL:220-241) => setStopAnnotation */
+#define NBG_ACT_STOPPED    0x10u /* StopAnnotationIsSet at entry (CULL:104): annotations removed     */
+#define NBG_ACT_INIT       0x20u /* !annotationsExist (CULL:141): both annotations := now            */
+#define NBG_ACT_NOPOD      0x40u /* pod missing (CULL:121): annotations removed                      */
+
+/* ---- context ----------------------------------------------------------- */
+typedef struct nbg_ctx nbg_ctx;
+
+/* Create a context on the listed CUDA devices (n_devices >= 1; devices may be
+ * NULL meaning {0}).  One stream, one event pair and grow-only staging buffers
+ * per device.  Replaces nothing in the reference (there is no device there). */
+int nbg_init(const int* devices, int n_devices, nbg_ctx** out);
+void nbg_destroy(nbg_ctx* ctx);
+const char* nbg_strerror(int status);
+/* text of the last CUDA error seen on this thread ("" if none) */
+const char* nbg_last_cuda_error(void);
+int nbg_abi_version(void);
+int nbg_device_count(const nbg_ctx* ctx);
+
+/* Pinned host memory for batch buffers (faster H2D; optional). */
+void* nbg_alloc_pinned(size_t bytes);
+void  nbg_free_pinned(void* p);
+
+/* ---- hashing / sharding (host side, pure) ------------------------------ */
+/* 64-bit string hash used by every packer: "" -> 0, nothing else -> 0. */
+uint64_t nbg_hash64(const void* data, size_t len);
+/* namespace -> shard (GPU) map, the batch analogue of the per-namespace List
+ * at NBCTL:159: shard = mix64(ns_hash) % n_shards. */
+uint32_t nbg_shard_of(uint64_t ns_hash, uint32_t n_shards);
+
+/* ---- host-buffer entry points (H2D + kernel + D2H inside the call) ----- */
+/* Batched CopyStatefulSetFields (COMMON:107-134) with the caller's template-
+ * label pre-step (NBCTL:188-194).  reason[i] = NBG_STS_* bits;
+ * bitmap bit i (word i/64, bit i%64) = (reason[i] & NBG_STS_UPDATE_MASK) != 0,
+ * i.e. the bool the Go function returns.  bitmap has ceil(n/64) words. */
+int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n,
+                 uint8_t* reason, uint64_t* bitmap);
+/* Batched CopyServiceFields (COMMON:166-195). */
+int nbg_diff_svc(nbg_ctx* ctx, const nbg_svc_batch* in, uint64_t n,
+                 uint8_t* reason, uint64_t* bitmap);
+/* Batched CopyVirtualService (COMMON:199-219). */
+int nbg_diff_vs(nbg_ctx* ctx, const nbg_vs_batch* in, uint64_t n,
+                uint8_t* reason, uint64_t* bitmap);
+/* Batched culler decision: allKernelsAreIdle, getNotebookRecentTime,
+ * compareAnnotationTimeToResource, updateTimestampFrom{Kernels,Terminals}Activity,
+ * notebookIsIdle, cullingCheckPeriodHasPassed (CULL:207-241,315-428).
+ * action[i] = NBG_ACT_* bits; argmax[i] = index (within the notebook's own
+ * list) of the record that supplies the new last-activity for src 2/3, else
+ * NBG_ARGMAX_NONE; cull_bitmap bit i = NBG_ACT_CULL; period_bitmap bit i =
+ * NBG_ACT_PERIOD. */
+int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n,
+             const nbg_cull_params* params,
+             uint8_t* action, uint32_t* argmax,
+             uint64_t* cull_bitmap, uint64_t* period_bitmap);
+
+/* ---- device-pointer entry points (asynchronous, no copies) ------------- */
+/* Same kernels on buffers already resident in HBM.  Every pointer inside the
+ * batch and every output is a DEVICE pointer on `device` (an index into the
+ * list given to nbg_init); `stream` is a cudaStream_t (NULL = the context's
+ * own stream).  The call only enqueues work.  CSR offsets are NOT validated
+ * here (the host-buffer calls validate them before upload). */
+int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
+                        uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_diff_svc_device(nbg_ctx* ctx, int device, const nbg_svc_batch* in, uint64_t n,
+                        uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_diff_vs_device(nbg_ctx* ctx, int device, const nbg_vs_batch* in, uint64_t n,
+                       uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_cull_device(nbg_ctx* ctx, int device, const nbg_cull_batch* in, uint64_t n,
+                    const nbg_cull_params* params,
+                    uint8_t* action, uint32_t* argmax,
+                    uint64_t* cull_bitmap, uint64_t* period_bitmap, void* stream);
+/* Block until everything enqueued on the context's own stream of `device` is done. */
+int nbg_sync(nbg_ctx* ctx, int device);
+/* Number of kernels this library has launched since nbg_init (all devices). */
+uint64_t nbg_launch_count(const nbg_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBGRAFT_H */

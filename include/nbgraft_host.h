@@ -1,0 +1,129 @@
+/*
+ * nbgraft_host.h — C ABI of libnbgraft_host.so: the HOST side of the graft.
+ *
+ * In the reference this work is done by ordinary Go code before the predicates
+ * run: decoding objects from the API server, building the desired objects
+ * (generateStatefulSet/Service/VirtualService, NBCTL:433-658) and, in this
+ * build, flattening them into the structure-of-arrays batches that
+ * libnbgraft.so consumes.  No Go toolchain exists in the build image, so the
+ * host side is C++ behind this C ABI (a Go packer would produce byte-identical
+ * batches from the same objects; INTEGRATION.md shows the cgo binding).
+ * Nothing here touches CUDA; the library loads on a machine without a GPU.
+ *
+ * Handles are opaque and owned by the caller (free with the matching *_free).
+ * Functions returning int return 0 on success, -1 on failure with a message
+ * in `err` (if err != NULL and errlen > 0).
+ */
+#ifndef NBGRAFT_HOST_H
+#define NBGRAFT_HOST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "nbgraft.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nbh_obj nbh_obj;     /* one decoded object (a Go value tree)          */
+typedef struct nbh_sts nbh_sts;     /* packed StatefulSet pairs  -> nbg_sts_batch    */
+typedef struct nbh_svc nbh_svc;     /* packed Service pairs      -> nbg_svc_batch    */
+typedef struct nbh_vs nbh_vs;       /* packed VirtualService pairs -> nbg_vs_batch   */
+typedef struct nbh_cull nbh_cull;   /* packed culler inputs      -> nbg_cull_batch   */
+typedef struct nbh_fleet nbh_fleet; /* seeded synthetic Notebook fleet (diff side)   */
+typedef struct nbh_cullfleet nbh_cullfleet; /* seeded synthetic culler fleet         */
+
+/* ---- objects ----------------------------------------------------------- */
+/* type: "Notebook", "StatefulSet", "Service", "PodSpec", ... or "Unstructured"
+ * (untyped JSON, what CopyVirtualService receives). */
+int nbh_obj_from_json(const char* type, const char* json, nbh_obj** out, char* err, size_t errlen);
+void nbh_obj_free(nbh_obj* o);
+/* Debug rendering of the value tree as JSON (Ptr -> its pointee, Null -> null);
+ * caller frees with nbh_str_free. */
+char* nbh_obj_to_json(const nbh_obj* o);
+void nbh_str_free(char* s);
+/* Copy of the sub-object at a dotted field path ("spec.template.spec"); -1 if absent. */
+int nbh_obj_get(const nbh_obj* o, const char* dotted_path, nbh_obj** out);
+/* canonical digest of the whole value: equal digests <=> reflect.DeepEqual (mod 2^-64) */
+uint64_t nbh_obj_digest(const nbh_obj* o);
+
+/* ---- desired-object builders ------------------------------------------- */
+typedef struct nbh_env {
+  int add_fsgroup;             /* ADD_FSGROUP unset or "true" (NBCTL:514)      */
+  const char* cluster_domain;  /* CLUSTER_DOMAIN; NULL = "cluster.local"       */
+  const char* istio_host;      /* ISTIO_HOST; NULL or "" = "*"                 */
+  const char* istio_gateway;   /* ISTIO_GATEWAY; NULL or "" = kubeflow/kubeflow-gateway */
+} nbh_env;
+/* generateStatefulSet (NBCTL:433-523); env may be NULL for the defaults */
+int nbh_generate_statefulset(const nbh_obj* notebook, const nbh_env* env, nbh_obj** out, char* err, size_t errlen);
+/* generateService (NBCTL:525-552) */
+int nbh_generate_service(const nbh_obj* notebook, nbh_obj** out, char* err, size_t errlen);
+/* generateVirtualService (NBCTL:558-658) */
+int nbh_generate_virtualservice(const nbh_obj* notebook, const nbh_env* env, nbh_obj** out, char* err, size_t errlen);
+/* ODH mutating-webhook injections (ODHWH:105-114,177-326,666-781; notebook_runtime.go:216-285;
+ * notebook_dspa_secret.go:375-450) applied in place. flags: 1 lock, 2 CA bundle,
+ * 4 runtime images, 8 elyra secret, 16 kube-rbac-proxy. */
+int nbh_odh_mutate(nbh_obj* notebook, int flags);
+
+/* ---- packed batches ---------------------------------------------------- */
+nbh_sts* nbh_sts_new(void);
+void nbh_sts_free(nbh_sts* b);
+int nbh_sts_add(nbh_sts* b, const nbh_obj* from, const nbh_obj* to);
+uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out);   /* returns n; pointers live as long as b is unchanged */
+
+nbh_svc* nbh_svc_new(void);
+void nbh_svc_free(nbh_svc* b);
+int nbh_svc_add(nbh_svc* b, const nbh_obj* from, const nbh_obj* to);
+uint64_t nbh_svc_view(const nbh_svc* b, nbg_svc_batch* out);
+
+nbh_vs* nbh_vs_new(void);
+void nbh_vs_free(nbh_vs* b);
+int nbh_vs_add(nbh_vs* b, const nbh_obj* from, const nbh_obj* to);
+uint64_t nbh_vs_view(const nbh_vs* b, nbg_vs_batch* out);
+
+/* One notebook as the culler sees it, as JSON:
+ *   {"annotations": {..}|null, "pod_missing": bool,
+ *    "kernels": [{"last_activity": "...", "execution_state": "..."}],
+ *    "terminals": [{"last_activity": "..."}]}
+ * Timestamps are parsed as Go's time.Parse(time.RFC3339, ...) would (CULL:212,229,332,339). */
+nbh_cull* nbh_cull_new(void);
+void nbh_cull_free(nbh_cull* b);
+int nbh_cull_add_json(nbh_cull* b, const char* json, char* err, size_t errlen);
+uint64_t nbh_cull_view(const nbh_cull* b, nbg_cull_batch* out);
+/* number of kernel / terminal records */
+uint64_t nbh_cull_records(const nbh_cull* b, uint64_t* kernels, uint64_t* terminals);
+/* The new last-activity annotation value for notebook i given the kernel's
+ * outputs (what CULL:386,399,425 would have written); "" when unchanged.
+ * Writes a NUL-terminated string into buf; returns its length or -1. */
+int nbh_cull_new_last_activity(const nbh_cull* b, uint64_t i, uint8_t action, uint32_t argmax,
+                               int64_t now_sec, int32_t now_offset_sec, char* buf, size_t buflen);
+
+/* time.Parse(time.RFC3339, s): 1 if it parses, else 0 */
+int nbh_parse_rfc3339(const char* s, int64_t* sec, int32_t* nsec, int32_t* offset_sec);
+/* t.Format(time.RFC3339) */
+int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_t buflen);
+
+/* ---- synthetic fleets ------------------------------------- */
+/* kind: 2 = Kubeflow loadtest-shaped notebooks (configs #2/#5), 4 = ODH-webhook-shaped (#4) */
+nbh_fleet* nbh_fleet_new(int kind, uint64_t seed, uint64_t n, uint32_t n_namespaces);
+void nbh_fleet_free(nbh_fleet* f);
+/* which: 0 notebook, 1 sts desired, 2 sts live, 3 svc desired, 4 svc live, 5 vs desired, 6 vs live */
+int nbh_fleet_get(const nbh_fleet* f, uint64_t i, int which, nbh_obj** out);
+int nbh_fleet_drift_class(const nbh_fleet* f, uint64_t i);
+uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i);   /* nbg_hash64(namespace name) */
+/* Pack objects idx[0..m) (idx == NULL: the range [i0, i0+m)) with all host threads. */
+int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                   nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
+
+nbh_cullfleet* nbh_cullfleet_new(uint64_t seed, uint64_t n, int64_t now_sec, int32_t now_nsec, double mean_kernels);
+void nbh_cullfleet_free(nbh_cullfleet* f);
+char* nbh_cullfleet_json(const nbh_cullfleet* f, uint64_t i);  /* free with nbh_str_free */
+int nbh_cullfleet_pack(const nbh_cullfleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_cull** out);
+
+int nbh_threads(void);  /* host threads the packers use */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBGRAFT_HOST_H */

@@ -1,0 +1,209 @@
+"""ctypes bindings of the two in-tree shared libraries.
+
+libnbgraft.so       kernels + C ABI (include/nbgraft.h)
+libnbgraft_host.so  host packer / builders / fleets (include/nbgraft_host.h)
+
+There is no Python or CPU fallback for the kernels: if libnbgraft.so is missing
+the import fails loudly, and without a CUDA device ``nbg_init`` returns
+NBG_E_NODEVICE, which ``Context`` turns into an exception.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class NativeLibraryMissing(ImportError):
+    pass
+
+
+def _load(name):
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        raise NativeLibraryMissing(
+            f"{path} is not built. Run `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"(or `make -C odh-kubeflow_b200/csrc`). There is no Python fallback for the CUDA path.")
+    return C.CDLL(path)
+
+
+u8p, u32p, u64p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+i32p, i64p = C.POINTER(C.c_int32), C.POINTER(C.c_int64)
+
+
+class nbg_kv(C.Structure):
+    _fields_ = [("key", C.c_uint64), ("val", C.c_uint64)]
+
+
+class nbg_kvmap(C.Structure):
+    _fields_ = [("off", u32p), ("ent", C.POINTER(nbg_kv))]
+
+
+class nbg_sts_batch(C.Structure):
+    _fields_ = [("replicas_from", i32p), ("replicas_to", i32p), ("tmpl_from", u64p), ("tmpl_to", u64p),
+                ("pod_from", u64p), ("pod_to", u64p),
+                ("labels_from", nbg_kvmap), ("labels_to", nbg_kvmap),
+                ("ann_from", nbg_kvmap), ("ann_to", nbg_kvmap)]
+
+
+class nbg_svc_batch(C.Structure):
+    _fields_ = [("flags", u8p), ("ports_from", u64p), ("ports_to", u64p),
+                ("labels_from", nbg_kvmap), ("labels_to", nbg_kvmap),
+                ("ann_from", nbg_kvmap), ("ann_to", nbg_kvmap),
+                ("sel_from", nbg_kvmap), ("sel_to", nbg_kvmap)]
+
+
+class nbg_vs_batch(C.Structure):
+    _fields_ = [("flags", u8p), ("spec_from", u64p), ("spec_to", u64p),
+                ("hdr_from", nbg_kvmap), ("hdr_to", nbg_kvmap)]
+
+
+class nbg_cull_batch(C.Structure):
+    _fields_ = [("k_off", u32p), ("k_sec", i64p), ("k_nsf", u32p),
+                ("t_off", u32p), ("t_sec", i64p), ("t_nsf", u32p),
+                ("ann_sec", i64p), ("ann_nsf", u32p), ("chk_sec", i64p), ("chk_nsf", u32p),
+                ("nb_flags", u8p)]
+
+
+class nbg_cull_params(C.Structure):
+    _fields_ = [("now_sec", C.c_int64), ("now_nsec", C.c_int32), ("cull_idle_min", C.c_int32),
+                ("check_period_min", C.c_int32), ("mode", C.c_int32)]
+
+
+class nbh_env(C.Structure):
+    _fields_ = [("add_fsgroup", C.c_int), ("cluster_domain", C.c_char_p), ("istio_host", C.c_char_p),
+                ("istio_gateway", C.c_char_p)]
+
+
+# constants of include/nbgraft.h
+NBG_OK, NBG_E_NODEVICE, NBG_E_INVAL, NBG_E_NOMEM, NBG_E_CUDA = 0, -1, -2, -3, -4
+NBG_E_NILREPLICAS, NBG_E_RANGE, NBG_E_TOOBIG = -5, -6, -7
+NBG_POD_SLOTS, NBG_SVC_SLOTS, NBG_VS_SLOTS = 192, 16, 8
+NBG_REPLICAS_NIL = -(2 ** 31)
+NBG_ARGMAX_NONE = 0xFFFFFFFF
+STS_LABELS, STS_ANNOTATIONS, STS_REPLICAS, STS_PODSPEC, STS_TMPL_LABELS, STS_NILREPLICAS = 1, 2, 4, 8, 16, 0x80
+SVC_LABELS, SVC_ANNOTATIONS, SVC_SELECTOR, SVC_PORTS = 1, 2, 4, 8
+VS_SPEC_DIFFERS, VS_TO_MISSING, VS_FROM_MISSING = 1, 2, 4
+ACT_SRC_MASK, ACT_PERIOD, ACT_CULL, ACT_STOPPED, ACT_INIT, ACT_NOPOD = 3, 4, 8, 16, 32, 64
+CULL_PREDICATES, CULL_RECONCILE = 0, 1
+
+NBG_SYMBOLS = [
+    "nbg_init", "nbg_destroy", "nbg_strerror", "nbg_last_cuda_error", "nbg_abi_version", "nbg_device_count",
+    "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of",
+    "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull",
+    "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
+    "nbg_sync", "nbg_launch_count",
+]
+
+_vp = C.c_void_p
+
+
+def _bind_nbg(lib):
+    lib.nbg_init.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(_vp)]
+    lib.nbg_init.restype = C.c_int
+    lib.nbg_destroy.argtypes = [_vp]
+    lib.nbg_destroy.restype = None
+    lib.nbg_strerror.argtypes = [C.c_int]
+    lib.nbg_strerror.restype = C.c_char_p
+    lib.nbg_last_cuda_error.restype = C.c_char_p
+    lib.nbg_abi_version.restype = C.c_int
+    lib.nbg_device_count.argtypes = [_vp]
+    lib.nbg_alloc_pinned.argtypes = [C.c_size_t]
+    lib.nbg_alloc_pinned.restype = _vp
+    lib.nbg_free_pinned.argtypes = [_vp]
+    lib.nbg_free_pinned.restype = None
+    lib.nbg_hash64.argtypes = [C.c_char_p, C.c_size_t]
+    lib.nbg_hash64.restype = C.c_uint64
+    lib.nbg_shard_of.argtypes = [C.c_uint64, C.c_uint32]
+    lib.nbg_shard_of.restype = C.c_uint32
+    for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch)):
+        f = getattr(lib, name)
+        f.argtypes = [_vp, C.POINTER(bt), C.c_uint64, _vp, _vp]
+        f.restype = C.c_int
+        g = getattr(lib, name + "_device")
+        g.argtypes = [_vp, C.c_int, C.POINTER(bt), C.c_uint64, _vp, _vp, _vp]
+        g.restype = C.c_int
+    lib.nbg_cull.argtypes = [_vp, C.POINTER(nbg_cull_batch), C.c_uint64, C.POINTER(nbg_cull_params), _vp, _vp, _vp, _vp]
+    lib.nbg_cull.restype = C.c_int
+    lib.nbg_cull_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_cull_batch), C.c_uint64, C.POINTER(nbg_cull_params),
+                                    _vp, _vp, _vp, _vp, _vp]
+    lib.nbg_cull_device.restype = C.c_int
+    lib.nbg_sync.argtypes = [_vp, C.c_int]
+    lib.nbg_sync.restype = C.c_int
+    lib.nbg_launch_count.argtypes = [_vp]
+    lib.nbg_launch_count.restype = C.c_uint64
+    return lib
+
+
+def _bind_nbh(lib):
+    cp, sz = C.c_char_p, C.c_size_t
+    P = C.POINTER
+    sig = {
+        "nbh_obj_from_json": ([cp, cp, P(_vp), cp, sz], C.c_int),
+        "nbh_obj_free": ([_vp], None),
+        "nbh_obj_to_json": ([_vp], _vp),
+        "nbh_str_free": ([_vp], None),
+        "nbh_obj_get": ([_vp, cp, P(_vp)], C.c_int),
+        "nbh_obj_digest": ([_vp], C.c_uint64),
+        "nbh_generate_statefulset": ([_vp, P(nbh_env), P(_vp), cp, sz], C.c_int),
+        "nbh_generate_service": ([_vp, P(_vp), cp, sz], C.c_int),
+        "nbh_generate_virtualservice": ([_vp, P(nbh_env), P(_vp), cp, sz], C.c_int),
+        "nbh_odh_mutate": ([_vp, C.c_int], C.c_int),
+        "nbh_sts_new": ([], _vp), "nbh_sts_free": ([_vp], None),
+        "nbh_sts_add": ([_vp, _vp, _vp], C.c_int), "nbh_sts_view": ([_vp, P(nbg_sts_batch)], C.c_uint64),
+        "nbh_svc_new": ([], _vp), "nbh_svc_free": ([_vp], None),
+        "nbh_svc_add": ([_vp, _vp, _vp], C.c_int), "nbh_svc_view": ([_vp, P(nbg_svc_batch)], C.c_uint64),
+        "nbh_vs_new": ([], _vp), "nbh_vs_free": ([_vp], None),
+        "nbh_vs_add": ([_vp, _vp, _vp], C.c_int), "nbh_vs_view": ([_vp, P(nbg_vs_batch)], C.c_uint64),
+        "nbh_cull_new": ([], _vp), "nbh_cull_free": ([_vp], None),
+        "nbh_cull_add_json": ([_vp, cp, cp, sz], C.c_int), "nbh_cull_view": ([_vp, P(nbg_cull_batch)], C.c_uint64),
+        "nbh_cull_records": ([_vp, P(C.c_uint64), P(C.c_uint64)], C.c_uint64),
+        "nbh_cull_new_last_activity": ([_vp, C.c_uint64, C.c_uint8, C.c_uint32, C.c_int64, C.c_int32, cp, sz], C.c_int),
+        "nbh_parse_rfc3339": ([cp, P(C.c_int64), P(C.c_int32), P(C.c_int32)], C.c_int),
+        "nbh_format_rfc3339": ([C.c_int64, C.c_int32, cp, sz], C.c_int),
+        "nbh_fleet_new": ([C.c_int, C.c_uint64, C.c_uint64, C.c_uint32], _vp), "nbh_fleet_free": ([_vp], None),
+        "nbh_fleet_get": ([_vp, C.c_uint64, C.c_int, P(_vp)], C.c_int),
+        "nbh_fleet_drift_class": ([_vp, C.c_uint64], C.c_int),
+        "nbh_fleet_ns_hash": ([_vp, C.c_uint64], C.c_uint64),
+        "nbh_fleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
+        "nbh_cullfleet_new": ([C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_double], _vp),
+        "nbh_cullfleet_free": ([_vp], None),
+        "nbh_cullfleet_json": ([_vp, C.c_uint64], _vp),
+        "nbh_cullfleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp)], C.c_int),
+        "nbh_threads": ([], C.c_int),
+    }
+    for name, (args, res) in sig.items():
+        f = getattr(lib, name)
+        f.argtypes = args
+        f.restype = res
+    return lib
+
+
+NBH_SYMBOLS = [
+    "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_digest",
+    "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate",
+    "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
+    "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_cull_new", "nbh_cull_free",
+    "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
+    "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
+    "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
+    "nbh_cullfleet_pack", "nbh_threads",
+]
+
+_nbg = None
+_nbh = None
+
+
+def nbg():
+    """libnbgraft.so (kernels + C ABI)."""
+    global _nbg
+    if _nbg is None:
+        _nbg = _bind_nbg(_load("libnbgraft.so"))
+    return _nbg
+
+
+def nbh():
+    """libnbgraft_host.so (host packer)."""
+    global _nbh
+    if _nbh is None:
+        _nbh = _bind_nbh(_load("libnbgraft_host.so"))
+    return _nbh

@@ -1,0 +1,525 @@
+// capi.cu — the C ABI of libnbgraft.so (include/nbgraft.h).
+//
+// Host-buffer entry points run a two-slot pipeline per device: chunk c+1 is
+// copied host->device on the copy stream while chunk c is compared on the run
+// stream, and the (tiny) results return on the run stream.  Device staging is
+// a grow-only arena per slot, so steady-state calls allocate nothing.
+// There is no CPU fallback anywhere in this file: without a device nbg_init
+// fails and every other entry point rejects the null context.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../../include/nbgraft.h"
+#include "../hash.h"
+
+extern "C" {
+cudaError_t nbg_launch_cull(const nbg_cull_batch*, unsigned long long, const nbg_cull_params*,
+                            unsigned, unsigned, uint8_t*, uint32_t*, uint64_t*, uint64_t*,
+                            cudaStream_t);
+cudaError_t nbg_launch_diff_sts(const nbg_sts_batch*, unsigned long long, const unsigned*, uint8_t*,
+                                uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const unsigned*, uint8_t*,
+                                uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
+                               uint64_t*, cudaStream_t);
+}
+
+namespace {
+
+thread_local char g_cuda_err[256] = "";
+
+bool cuda_ok(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return true;
+  snprintf(g_cuda_err, sizeof g_cuda_err, "%s: %s", what, cudaGetErrorString(e));
+  return false;
+}
+#define CU(call) do { if (!cuda_ok((call), #call)) return NBG_E_CUDA; } while (0)
+
+struct Slot {
+  char* dev = nullptr;
+  size_t cap = 0;
+  cudaEvent_t in_done = nullptr, free_ev = nullptr;
+  bool used = false;
+};
+
+struct Dev {
+  int id = 0;
+  cudaStream_t s_in = nullptr, s_run = nullptr;
+  Slot slot[2];
+  std::mutex mu;
+};
+
+}  // namespace
+
+struct nbg_ctx {
+  std::vector<Dev*> devs;
+  std::atomic<uint64_t> launches{0};
+};
+
+namespace {
+
+constexpr size_t kAlign = 256;
+size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+// Lay out one chunk in a slot's arena.
+struct Layout {
+  struct In { const void* host; size_t bytes; size_t off; };
+  struct Out { void* host; size_t bytes; size_t off; };
+  std::vector<In> ins;
+  std::vector<Out> outs;
+  size_t total = 0;
+  size_t in(const void* host, size_t bytes) {
+    const size_t off = total;
+    ins.push_back({host, bytes, off});
+    total += align_up(bytes ? bytes : 1);
+    return off;
+  }
+  size_t out(void* host, size_t bytes) {
+    const size_t off = total;
+    outs.push_back({host, bytes, off});
+    total += align_up(bytes ? bytes : 1);
+    return off;
+  }
+};
+
+int slot_reserve(Slot& sl, size_t bytes) {
+  if (sl.cap >= bytes) return NBG_OK;
+  if (sl.used) CU(cudaEventSynchronize(sl.free_ev));
+  if (sl.dev) { CU(cudaFree(sl.dev)); sl.dev = nullptr; sl.cap = 0; }
+  const size_t want = bytes + bytes / 4;
+  if (cudaMalloc(&sl.dev, want) != cudaSuccess) {
+    cudaGetLastError();
+    if (!cuda_ok(cudaMalloc(&sl.dev, bytes), "cudaMalloc(staging)")) { sl.dev = nullptr; return NBG_E_NOMEM; }
+    sl.cap = bytes;
+  } else {
+    sl.cap = want;
+  }
+  return NBG_OK;
+}
+
+int slot_upload(Dev& d, Slot& sl, const Layout& lay) {
+  if (int rc = slot_reserve(sl, lay.total)) return rc;
+  if (sl.used) CU(cudaStreamWaitEvent(d.s_in, sl.free_ev, 0));
+  for (const auto& in : lay.ins)
+    if (in.bytes) CU(cudaMemcpyAsync(sl.dev + in.off, in.host, in.bytes, cudaMemcpyHostToDevice, d.s_in));
+  CU(cudaEventRecord(sl.in_done, d.s_in));
+  CU(cudaStreamWaitEvent(d.s_run, sl.in_done, 0));
+  return NBG_OK;
+}
+
+int slot_download(Dev& d, Slot& sl, const Layout& lay) {
+  for (const auto& o : lay.outs)
+    if (o.bytes) CU(cudaMemcpyAsync(o.host, sl.dev + o.off, o.bytes, cudaMemcpyDeviceToHost, d.s_run));
+  CU(cudaEventRecord(sl.free_ev, d.s_run));
+  sl.used = true;
+  return NBG_OK;
+}
+
+bool csr_ok(const nbg_kvmap& m, uint64_t n) {
+  if (!m.off) return false;
+  for (uint64_t i = 0; i < n; ++i)
+    if (m.off[i] > m.off[i + 1]) return false;
+  if (m.off[n] > m.off[0] && !m.ent) return false;
+  return true;
+}
+bool off_ok(const uint32_t* off, uint64_t n) {
+  if (!off) return false;
+  for (uint64_t i = 0; i < n; ++i)
+    if (off[i] > off[i + 1]) return false;
+  return true;
+}
+
+// Upload rows [i0,i1) of a CSR map; returns device pointers and the base offset.
+struct CsrDev { size_t off_at, ent_at; unsigned base; };
+CsrDev csr_in(Layout& lay, const nbg_kvmap& m, uint64_t i0, uint64_t i1) {
+  CsrDev c;
+  c.base = m.off[i0];
+  c.off_at = lay.in(m.off + i0, (i1 - i0 + 1) * sizeof(uint32_t));
+  const size_t cnt = m.off[i1] - m.off[i0];
+  c.ent_at = lay.in(cnt ? m.ent + m.off[i0] : nullptr, cnt * sizeof(nbg_kv));
+  return c;
+}
+nbg_kvmap csr_ptr(const Slot& sl, const CsrDev& c) {
+  nbg_kvmap m;
+  m.off = reinterpret_cast<const uint32_t*>(sl.dev + c.off_at);
+  m.ent = reinterpret_cast<const nbg_kv*>(sl.dev + c.ent_at);
+  return m;
+}
+
+// Contiguous, 64-aligned split of [0,n) over the context's devices.
+void device_range(uint64_t n, int ndev, int d, uint64_t* lo, uint64_t* hi) {
+  const uint64_t words = (n + 63) / 64;
+  const uint64_t w_lo = words * d / ndev, w_hi = words * (d + 1) / ndev;
+  *lo = w_lo * 64 < n ? w_lo * 64 : n;
+  *hi = w_hi * 64 < n ? w_hi * 64 : n;
+}
+
+template <class F>
+int for_each_device(nbg_ctx* ctx, uint64_t n, F&& run_range) {
+  // Enqueue every device's chunks first, then wait: devices overlap.
+  const int ndev = (int)ctx->devs.size();
+  int rc = NBG_OK;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  for (int d = 0; d < ndev; ++d) locks.emplace_back(ctx->devs[d]->mu);
+  for (int d = 0; d < ndev && rc == NBG_OK; ++d) {
+    uint64_t lo, hi;
+    device_range(n, ndev, d, &lo, &hi);
+    if (hi <= lo) continue;
+    if (!cuda_ok(cudaSetDevice(ctx->devs[d]->id), "cudaSetDevice")) { rc = NBG_E_CUDA; break; }
+    rc = run_range(*ctx->devs[d], lo, hi);
+  }
+  for (int d = 0; d < ndev; ++d) {
+    cudaSetDevice(ctx->devs[d]->id);
+    if (!cuda_ok(cudaStreamSynchronize(ctx->devs[d]->s_run), "cudaStreamSynchronize") && rc == NBG_OK)
+      rc = NBG_E_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(ctx->devs[d]->s_in), "cudaStreamSynchronize") && rc == NBG_OK)
+      rc = NBG_E_CUDA;
+  }
+  return rc;
+}
+
+constexpr uint64_t kStsChunk = 8192;     // objects per pipeline chunk (~27 MB)
+constexpr uint64_t kSvcChunk = 65536;    // (~21 MB)
+constexpr uint64_t kVsChunk = 131072;    // (~20 MB)
+constexpr uint64_t kCullChunk = 262144;  // notebooks (~22 MB at 4 records each)
+
+int check_dev(const nbg_ctx* ctx, int device) {
+  if (!ctx) return NBG_E_INVAL;
+  if (device < 0 || device >= (int)ctx->devs.size()) return NBG_E_INVAL;
+  return NBG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nbg_abi_version(void) { return NBG_ABI_VERSION; }
+
+const char* nbg_last_cuda_error(void) { return g_cuda_err; }
+
+const char* nbg_strerror(int status) {
+  switch (status) {
+    case NBG_OK: return "ok";
+    case NBG_E_NODEVICE: return "no usable CUDA device (this library has no CPU path)";
+    case NBG_E_INVAL: return "invalid argument";
+    case NBG_E_NOMEM: return "device or pinned-host allocation failed";
+    case NBG_E_CUDA: return "CUDA call failed (see nbg_last_cuda_error)";
+    case NBG_E_NILREPLICAS: return "an object has a nil Spec.Replicas (the Go reference would panic)";
+    case NBG_E_RANGE: return "CSR offsets are not monotone";
+    case NBG_E_TOOBIG: return "batch exceeds a documented maximum";
+    default: return "unknown status";
+  }
+}
+
+uint64_t nbg_hash64(const void* data, size_t len) { return nbg_hash_bytes(data, len); }
+uint32_t nbg_shard_of(uint64_t ns_hash, uint32_t n_shards) { return nbg_shard_of_inline(ns_hash, n_shards); }
+
+int nbg_init(const int* devices, int n_devices, nbg_ctx** out) {
+  if (!out) return NBG_E_INVAL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+    cudaGetLastError();
+    return NBG_E_NODEVICE;
+  }
+  const int one = 0;
+  if (!devices) { devices = &one; n_devices = 1; }
+  if (n_devices <= 0) return NBG_E_INVAL;
+  nbg_ctx* ctx = new (std::nothrow) nbg_ctx();
+  if (!ctx) return NBG_E_NOMEM;
+  for (int k = 0; k < n_devices; ++k) {
+    if (devices[k] < 0 || devices[k] >= count) { nbg_destroy(ctx); return NBG_E_NODEVICE; }
+    Dev* d = new (std::nothrow) Dev();
+    if (!d) { nbg_destroy(ctx); return NBG_E_NOMEM; }
+    d->id = devices[k];
+    ctx->devs.push_back(d);
+    bool ok = cuda_ok(cudaSetDevice(d->id), "cudaSetDevice") &&
+              cuda_ok(cudaStreamCreateWithFlags(&d->s_in, cudaStreamNonBlocking), "cudaStreamCreate") &&
+              cuda_ok(cudaStreamCreateWithFlags(&d->s_run, cudaStreamNonBlocking), "cudaStreamCreate");
+    for (int s = 0; ok && s < 2; ++s)
+      ok = cuda_ok(cudaEventCreateWithFlags(&d->slot[s].in_done, cudaEventDisableTiming), "cudaEventCreate") &&
+           cuda_ok(cudaEventCreateWithFlags(&d->slot[s].free_ev, cudaEventDisableTiming), "cudaEventCreate");
+    if (!ok) { nbg_destroy(ctx); return NBG_E_CUDA; }
+  }
+  *out = ctx;
+  return NBG_OK;
+}
+
+void nbg_destroy(nbg_ctx* ctx) {
+  if (!ctx) return;
+  for (Dev* d : ctx->devs) {
+    cudaSetDevice(d->id);
+    if (d->s_run) cudaStreamSynchronize(d->s_run);
+    if (d->s_in) cudaStreamSynchronize(d->s_in);
+    for (auto& sl : d->slot) {
+      if (sl.dev) cudaFree(sl.dev);
+      if (sl.in_done) cudaEventDestroy(sl.in_done);
+      if (sl.free_ev) cudaEventDestroy(sl.free_ev);
+    }
+    if (d->s_in) cudaStreamDestroy(d->s_in);
+    if (d->s_run) cudaStreamDestroy(d->s_run);
+    delete d;
+  }
+  delete ctx;
+}
+
+int nbg_device_count(const nbg_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+uint64_t nbg_launch_count(const nbg_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+void* nbg_alloc_pinned(size_t bytes) {
+  void* p = nullptr;
+  if (!cuda_ok(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable), "cudaHostAlloc")) return nullptr;
+  return p;
+}
+void nbg_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+int nbg_sync(nbg_ctx* ctx, int device) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  CU(cudaStreamSynchronize(ctx->devs[device]->s_run));
+  return NBG_OK;
+}
+
+// ------------------------------------------------------------ device-pointer API
+int nbg_cull_device(nbg_ctx* ctx, int device, const nbg_cull_batch* in, uint64_t n,
+                    const nbg_cull_params* p, uint8_t* action, uint32_t* argmax,
+                    uint64_t* cull_bitmap, uint64_t* period_bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in || !p) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!action || !argmax || !cull_bitmap || !period_bitmap) return NBG_E_INVAL;
+  if (p->now_nsec < 0 || p->now_nsec > 999999999 || (p->mode != NBG_CULL_PREDICATES && p->mode != NBG_CULL_RECONCILE))
+    return NBG_E_INVAL;
+  if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
+      p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
+    return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  CU(nbg_launch_cull(in, n, p, 0, 0, action, argmax, cull_bitmap, period_bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
+                        uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  const unsigned bases[4] = {0, 0, 0, 0};
+  CU(nbg_launch_diff_sts(in, n, bases, reason, bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_svc_device(nbg_ctx* ctx, int device, const nbg_svc_batch* in, uint64_t n,
+                        uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  const unsigned bases[6] = {0, 0, 0, 0, 0, 0};
+  CU(nbg_launch_diff_svc(in, n, bases, reason, bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_vs_device(nbg_ctx* ctx, int device, const nbg_vs_batch* in, uint64_t n,
+                       uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  const unsigned bases[2] = {0, 0};
+  CU(nbg_launch_diff_vs(in, n, bases, reason, bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+// ------------------------------------------------------------ host-buffer API
+int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_params* p,
+             uint8_t* action, uint32_t* argmax, uint64_t* cull_bitmap, uint64_t* period_bitmap) {
+  if (!ctx || !in || !p) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!action || !argmax || !cull_bitmap || !period_bitmap) return NBG_E_INVAL;
+  if (!in->ann_sec || !in->ann_nsf || !in->chk_sec || !in->chk_nsf || !in->nb_flags) return NBG_E_INVAL;
+  if (p->now_nsec < 0 || p->now_nsec > 999999999 || (p->mode != NBG_CULL_PREDICATES && p->mode != NBG_CULL_RECONCILE))
+    return NBG_E_INVAL;
+  if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
+      p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
+    return NBG_E_INVAL;
+  if (!off_ok(in->k_off, n) || !off_ok(in->t_off, n)) return NBG_E_RANGE;
+  if ((in->k_off[n] > in->k_off[0] && (!in->k_sec || !in->k_nsf)) ||
+      (in->t_off[n] > in->t_off[0] && (!in->t_sec || !in->t_nsf)))
+    return NBG_E_INVAL;
+
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kCullChunk, ++c) {
+      const uint64_t i1 = i0 + kCullChunk < hi ? i0 + kCullChunk : hi, m = i1 - i0;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const unsigned kb = in->k_off[i0], tb = in->t_off[i0];
+      const size_t nk = in->k_off[i1] - kb, nt = in->t_off[i1] - tb;
+      const size_t a_koff = lay.in(in->k_off + i0, (m + 1) * 4);
+      const size_t a_ksec = lay.in(nk ? in->k_sec + kb : nullptr, nk * 8);
+      const size_t a_knsf = lay.in(nk ? in->k_nsf + kb : nullptr, nk * 4);
+      const size_t a_toff = lay.in(in->t_off + i0, (m + 1) * 4);
+      const size_t a_tsec = lay.in(nt ? in->t_sec + tb : nullptr, nt * 8);
+      const size_t a_tnsf = lay.in(nt ? in->t_nsf + tb : nullptr, nt * 4);
+      const size_t a_asec = lay.in(in->ann_sec + i0, m * 8);
+      const size_t a_ansf = lay.in(in->ann_nsf + i0, m * 4);
+      const size_t a_csec = lay.in(in->chk_sec + i0, m * 8);
+      const size_t a_cnsf = lay.in(in->chk_nsf + i0, m * 4);
+      const size_t a_flag = lay.in(in->nb_flags + i0, m);
+      const size_t words = (m + 63) / 64;
+      const size_t o_act = lay.out(action + i0, m);
+      const size_t o_arg = lay.out(argmax + i0, m * 4);
+      const size_t o_cull = lay.out(cull_bitmap + i0 / 64, words * 8);
+      const size_t o_per = lay.out(period_bitmap + i0 / 64, words * 8);
+      if (int rc = slot_upload(d, sl, lay)) return rc;
+      nbg_cull_batch b;
+      b.k_off = (const uint32_t*)(sl.dev + a_koff); b.k_sec = (const int64_t*)(sl.dev + a_ksec);
+      b.k_nsf = (const uint32_t*)(sl.dev + a_knsf); b.t_off = (const uint32_t*)(sl.dev + a_toff);
+      b.t_sec = (const int64_t*)(sl.dev + a_tsec); b.t_nsf = (const uint32_t*)(sl.dev + a_tnsf);
+      b.ann_sec = (const int64_t*)(sl.dev + a_asec); b.ann_nsf = (const uint32_t*)(sl.dev + a_ansf);
+      b.chk_sec = (const int64_t*)(sl.dev + a_csec); b.chk_nsf = (const uint32_t*)(sl.dev + a_cnsf);
+      b.nb_flags = (const uint8_t*)(sl.dev + a_flag);
+      CU(nbg_launch_cull(&b, m, p, kb, tb, (uint8_t*)(sl.dev + o_act), (uint32_t*)(sl.dev + o_arg),
+                         (uint64_t*)(sl.dev + o_cull), (uint64_t*)(sl.dev + o_per), d.s_run));
+      ctx->launches++;
+      if (int rc = slot_download(d, sl, lay)) return rc;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->replicas_from || !in->replicas_to || !in->tmpl_from || !in->tmpl_to ||
+      !in->pod_from || !in->pod_to)
+    return NBG_E_INVAL;
+  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
+      !csr_ok(in->ann_to, n))
+    return NBG_E_RANGE;
+
+  int rc = for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kStsChunk, ++c) {
+      const uint64_t i1 = i0 + kStsChunk < hi ? i0 + kStsChunk : hi, m = i1 - i0;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_rf = lay.in(in->replicas_from + i0, m * 4);
+      const size_t a_rt = lay.in(in->replicas_to + i0, m * 4);
+      const size_t a_tf = lay.in(in->tmpl_from + i0, m * 8);
+      const size_t a_tt = lay.in(in->tmpl_to + i0, m * 8);
+      const size_t a_pf = lay.in(in->pod_from + i0 * NBG_POD_SLOTS, m * NBG_POD_SLOTS * 8);
+      const size_t a_pt = lay.in(in->pod_to + i0 * NBG_POD_SLOTS, m * NBG_POD_SLOTS * 8);
+      const CsrDev lf = csr_in(lay, in->labels_from, i0, i1), lt = csr_in(lay, in->labels_to, i0, i1);
+      const CsrDev af = csr_in(lay, in->ann_from, i0, i1), at = csr_in(lay, in->ann_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_sts_batch b;
+      b.replicas_from = (const int32_t*)(sl.dev + a_rf); b.replicas_to = (const int32_t*)(sl.dev + a_rt);
+      b.tmpl_from = (const uint64_t*)(sl.dev + a_tf); b.tmpl_to = (const uint64_t*)(sl.dev + a_tt);
+      b.pod_from = (const uint64_t*)(sl.dev + a_pf); b.pod_to = (const uint64_t*)(sl.dev + a_pt);
+      b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt);
+      b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
+      const unsigned bases[4] = {lf.base, lt.base, af.base, at.base};
+      CU(nbg_launch_diff_sts(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+  if (rc != NBG_OK) return rc;
+  for (uint64_t i = 0; i < n; ++i)
+    if (reason[i] & NBG_STS_NILREPLICAS) return NBG_E_NILREPLICAS;
+  return NBG_OK;
+}
+
+int nbg_diff_svc(nbg_ctx* ctx, const nbg_svc_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->flags || !in->ports_from || !in->ports_to) return NBG_E_INVAL;
+  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
+      !csr_ok(in->ann_to, n) || !csr_ok(in->sel_from, n) || !csr_ok(in->sel_to, n))
+    return NBG_E_RANGE;
+
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kSvcChunk, ++c) {
+      const uint64_t i1 = i0 + kSvcChunk < hi ? i0 + kSvcChunk : hi, m = i1 - i0;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_fl = lay.in(in->flags + i0, m);
+      const size_t a_pf = lay.in(in->ports_from + i0 * NBG_SVC_SLOTS, m * NBG_SVC_SLOTS * 8);
+      const size_t a_pt = lay.in(in->ports_to + i0 * NBG_SVC_SLOTS, m * NBG_SVC_SLOTS * 8);
+      const CsrDev lf = csr_in(lay, in->labels_from, i0, i1), lt = csr_in(lay, in->labels_to, i0, i1);
+      const CsrDev af = csr_in(lay, in->ann_from, i0, i1), at = csr_in(lay, in->ann_to, i0, i1);
+      const CsrDev sf = csr_in(lay, in->sel_from, i0, i1), st = csr_in(lay, in->sel_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_svc_batch b;
+      b.flags = (const uint8_t*)(sl.dev + a_fl);
+      b.ports_from = (const uint64_t*)(sl.dev + a_pf); b.ports_to = (const uint64_t*)(sl.dev + a_pt);
+      b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt);
+      b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
+      b.sel_from = csr_ptr(sl, sf); b.sel_to = csr_ptr(sl, st);
+      const unsigned bases[6] = {lf.base, lt.base, af.base, at.base, sf.base, st.base};
+      CU(nbg_launch_diff_svc(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_diff_vs(nbg_ctx* ctx, const nbg_vs_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->flags || !in->spec_from || !in->spec_to) return NBG_E_INVAL;
+  if (!csr_ok(in->hdr_from, n) || !csr_ok(in->hdr_to, n)) return NBG_E_RANGE;
+
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kVsChunk, ++c) {
+      const uint64_t i1 = i0 + kVsChunk < hi ? i0 + kVsChunk : hi, m = i1 - i0;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_fl = lay.in(in->flags + i0, m);
+      const size_t a_sf = lay.in(in->spec_from + i0 * NBG_VS_SLOTS, m * NBG_VS_SLOTS * 8);
+      const size_t a_st = lay.in(in->spec_to + i0 * NBG_VS_SLOTS, m * NBG_VS_SLOTS * 8);
+      const CsrDev hf = csr_in(lay, in->hdr_from, i0, i1), ht = csr_in(lay, in->hdr_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_vs_batch b;
+      b.flags = (const uint8_t*)(sl.dev + a_fl);
+      b.spec_from = (const uint64_t*)(sl.dev + a_sf); b.spec_to = (const uint64_t*)(sl.dev + a_st);
+      b.hdr_from = csr_ptr(sl, hf); b.hdr_to = csr_ptr(sl, ht);
+      const unsigned bases[2] = {hf.base, ht.base};
+      CU(nbg_launch_diff_vs(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+}  // extern "C"

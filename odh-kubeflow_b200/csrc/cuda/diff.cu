@@ -1,0 +1,241 @@
+// diff.cu — desired-vs-live "needs update" predicates for whole fleets.
+//
+// Reference semantics (components/common/reconcilehelper/util.go = COMMON):
+//   CopyStatefulSetFields  COMMON:107-134   (+ caller pre-step NBCTL:188-194)
+//   CopyServiceFields      COMMON:166-195
+//   CopyVirtualService     COMMON:199-219
+//
+// Shape of every kernel: a warp owns 32 consecutive objects.
+//   * fixed-width tiles (PodSpec 1536 B, Service ports 128 B, VS spec 64 B per
+//     side) are streamed with 128-bit loads that bypass L1, the lanes of a
+//     warp covering contiguous bytes; the "any slot differs" reduction is a
+//     warp vote (__any_sync / __ballot_sync);
+//   * the small per-object string maps (CSR) are walked one object per lane;
+//   * lane j ends up holding object j's reason byte, so reason[] is written
+//     32 B at a time and the result bitmap one ballot half-word per warp.
+// Nothing is reused between objects, so there is no shared-memory staging:
+// HBM -> registers -> vote.  No tensor cores: there is no contraction here.
+#include "common.cuh"
+
+namespace nbg {
+
+__device__ __forceinline__ void store_results(unsigned long long base, unsigned long long n,
+                                              unsigned lane, unsigned reason, bool update,
+                                              uint8_t* __restrict__ reason_out,
+                                              uint32_t* __restrict__ bitmap_half) {
+  const unsigned long long i = base + lane;
+  if (i < n) reason_out[i] = (uint8_t)reason;
+  const unsigned bits = __ballot_sync(FULL, (i < n) && update);
+  if (lane == 0) {
+    bitmap_half[base >> 5] = bits;
+    if (((base >> 5) & 1) == 0 && base + 32 >= n) bitmap_half[(base >> 5) + 1] = 0u;
+  }
+}
+
+// ---------------------------------------------------------------- StatefulSet
+constexpr int kPodVec = NBG_POD_SLOTS * 8 / 16;       // 96 x 16 B per side
+constexpr int kPodVecPerLane = kPodVec / 32;          // 3
+
+__global__ void __launch_bounds__(128)
+diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
+                unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
+                uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const unsigned cnt = (unsigned)min(32ull, n - base);
+
+  // ---- per-lane scalar work for object `i`: R, D1', L, A
+  unsigned reason = 0;
+  if (i < n) {
+    const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
+    if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
+      reason |= NBG_STS_NILREPLICAS;                 // Go would panic at COMMON:123
+    } else if (rf != rt) {
+      reason |= NBG_STS_REPLICAS;                    // COMMON:123-126
+      // NBCTL:188-194: template labels are copied only on a replicas change
+      if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
+    }
+    if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
+                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
+                         __ldg(in.labels_to.off + i + 1) - lt_base))
+      reason |= NBG_STS_LABELS;                      // COMMON:109-113
+    if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
+                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
+                         __ldg(in.ann_to.off + i + 1) - at_base))
+      reason |= NBG_STS_ANNOTATIONS;                 // COMMON:116-120
+  }
+
+  // ---- warp-cooperative PodSpec compare (COMMON:128): object o's two tiles
+  // are 96 x 16 B each; lane l reads vectors l, l+32, l+64 of both.
+  const uint4* pf = reinterpret_cast<const uint4*>(in.pod_from) + base * kPodVec + lane;
+  const uint4* pt = reinterpret_cast<const uint4*>(in.pod_to) + base * kPodVec + lane;
+  unsigned pod_bits = 0;                             // bit o = object o differs
+  unsigned o = 0;
+  for (; o + 2 <= cnt; o += 2) {                     // two objects (6 KB) in flight per warp
+    uint4 a[2 * kPodVecPerLane], b[2 * kPodVecPerLane];
+#pragma unroll
+    for (int v = 0; v < 2 * kPodVecPerLane; ++v) {
+      a[v] = ld_stream(pf + (o * kPodVec) + v * 32);
+      b[v] = ld_stream(pt + (o * kPodVec) + v * 32);
+    }
+    unsigned d0 = 0, d1 = 0;
+#pragma unroll
+    for (int v = 0; v < kPodVecPerLane; ++v) {
+      d0 |= diff4(a[v], b[v]);
+      d1 |= diff4(a[v + kPodVecPerLane], b[v + kPodVecPerLane]);
+    }
+    if (__any_sync(FULL, d0 != 0)) pod_bits |= 1u << o;
+    if (__any_sync(FULL, d1 != 0)) pod_bits |= 2u << o;
+  }
+  if (o < cnt) {
+    unsigned d = 0;
+#pragma unroll
+    for (int v = 0; v < kPodVecPerLane; ++v)
+      d |= diff4(ld_stream(pf + (o * kPodVec) + v * 32), ld_stream(pt + (o * kPodVec) + v * 32));
+    if (__any_sync(FULL, d != 0)) pod_bits |= 1u << o;
+  }
+  if ((pod_bits >> lane) & 1u) reason |= NBG_STS_PODSPEC;
+
+  store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
+// ------------------------------------------------- small fixed tiles (Svc, VS)
+// VEC = 16-byte vectors per side per object (8 for Service ports, 4 for the VS
+// spec).  32/VEC objects are compared per load instruction; the warp covers its
+// 32 objects in VEC rounds.  Returns a mask: bit o = object o's tiles differ.
+template <int VEC>
+__device__ __forceinline__ unsigned tiles_differ(const uint64_t* __restrict__ from,
+                                                 const uint64_t* __restrict__ to,
+                                                 unsigned long long base, unsigned long long n,
+                                                 unsigned lane) {
+  constexpr int OBJ_PER_ROUND = 32 / VEC;
+  const uint4* pf = reinterpret_cast<const uint4*>(from) + base * VEC;
+  const uint4* pt = reinterpret_cast<const uint4*>(to) + base * VEC;
+  const unsigned long long limit = (n - base) * VEC;   // vectors that exist past `base`
+  unsigned mask = 0;
+#pragma unroll
+  for (int r = 0; r < VEC; ++r) {
+    const unsigned idx = r * 32 + lane;                // vector index within the warp's run
+    unsigned d = 0;
+    if (idx < limit) d = diff4(ld_stream(pf + idx), ld_stream(pt + idx));
+    const unsigned ballot = __ballot_sync(FULL, d != 0);
+#pragma unroll
+    for (int g = 0; g < OBJ_PER_ROUND; ++g) {
+      const unsigned group = (ballot >> (g * VEC)) & ((VEC == 32) ? FULL : ((1u << VEC) - 1u));
+      if (group) mask |= 1u << (r * OBJ_PER_ROUND + g);
+    }
+  }
+  return mask;
+}
+
+__global__ void __launch_bounds__(128)
+diff_svc_kernel(nbg_svc_batch in, unsigned long long n,
+                unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
+                unsigned sf_base, unsigned st_base,
+                uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+
+  const unsigned port_bits = tiles_differ<NBG_SVC_SLOTS / 2>(in.ports_from, in.ports_to, base, n, lane);
+
+  unsigned reason = 0;
+  if (i < n) {
+    const unsigned fl = __ldg(in.flags + i);
+    if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
+                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
+                         __ldg(in.labels_to.off + i + 1) - lt_base))
+      reason |= NBG_SVC_LABELS;                      // COMMON:168-172
+    if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
+                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
+                         __ldg(in.ann_to.off + i + 1) - at_base))
+      reason |= NBG_SVC_ANNOTATIONS;                 // COMMON:175-179
+    if (map_not_deep_equal(in.sel_from.ent, __ldg(in.sel_from.off + i) - sf_base,
+                           __ldg(in.sel_from.off + i + 1) - sf_base, (fl & NBG_F_FROM_SEL_NIL) != 0,
+                           in.sel_to.ent, __ldg(in.sel_to.off + i) - st_base,
+                           __ldg(in.sel_to.off + i + 1) - st_base, (fl & NBG_F_TO_SEL_NIL) != 0))
+      reason |= NBG_SVC_SELECTOR;                    // COMMON:184
+    if ((port_bits >> lane) & 1u) reason |= NBG_SVC_PORTS;  // COMMON:189
+  }
+  store_results(base, n, lane, reason, (reason & NBG_SVC_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
+__global__ void __launch_bounds__(128)
+diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned ht_base,
+               uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+
+  const unsigned spec_bits = tiles_differ<NBG_VS_SLOTS / 2>(in.spec_from, in.spec_to, base, n, lane);
+
+  unsigned reason = 0;
+  bool update = false;
+  if (i < n) {
+    const unsigned fl = __ldg(in.flags + i);
+    if (fl & NBG_F_FROM_SPEC_MISS) {                 // COMMON:200-206: return false
+      reason = NBG_VS_FROM_MISSING;
+    } else if (fl & NBG_F_TO_SPEC_MISS) {            // COMMON:208-212: copy, return true
+      reason = NBG_VS_TO_MISSING; update = true;
+    } else {                                         // COMMON:214
+      bool differs = (spec_bits >> lane) & 1u;
+      differs |= map_not_deep_equal(in.hdr_from.ent, __ldg(in.hdr_from.off + i) - hf_base,
+                                    __ldg(in.hdr_from.off + i + 1) - hf_base,
+                                    (fl & NBG_F_FROM_HDR_NIL) != 0,
+                                    in.hdr_to.ent, __ldg(in.hdr_to.off + i) - ht_base,
+                                    __ldg(in.hdr_to.off + i + 1) - ht_base,
+                                    (fl & NBG_F_TO_HDR_NIL) != 0);
+      if (differs) { reason = NBG_VS_SPEC_DIFFERS; update = true; }
+    }
+  }
+  store_results(base, n, lane, reason, update, reason_out, bitmap_half);
+}
+
+}  // namespace nbg
+
+// *_base: first CSR offset of the slice when the entry pointers already point
+// at the slice's first entry (host-buffer chunking); 0 for whole arrays.
+extern "C" cudaError_t nbg_launch_diff_sts(const nbg_sts_batch* in, unsigned long long n,
+                                           const unsigned* bases /*4*/, uint8_t* reason,
+                                           uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;                          // 4 warps = 128 objects per CTA
+  const unsigned long long grid = (n + block - 1) / block;
+  nbg::diff_sts_kernel<<<(unsigned)grid, block, 0, stream>>>(
+      *in, n, bases[0], bases[1], bases[2], bases[3], reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_diff_svc(const nbg_svc_batch* in, unsigned long long n,
+                                           const unsigned* bases /*6*/, uint8_t* reason,
+                                           uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  const unsigned long long grid = (n + block - 1) / block;
+  nbg::diff_svc_kernel<<<(unsigned)grid, block, 0, stream>>>(
+      *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
+      reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_diff_vs(const nbg_vs_batch* in, unsigned long long n,
+                                          const unsigned* bases /*2*/, uint8_t* reason,
+                                          uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  const unsigned long long grid = (n + block - 1) / block;
+  nbg::diff_vs_kernel<<<(unsigned)grid, block, 0, stream>>>(
+      *in, n, bases[0], bases[1], reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}

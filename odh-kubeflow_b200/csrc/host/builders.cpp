@@ -1,0 +1,440 @@
+// builders.cpp — the desired-object builders of the notebook controller,
+// restated on GVal.  They define the `from` side of every comparison:
+//   generateStatefulSet     NBCTL:433-523 (+ setPrefixEnvVar NBCTL:417-431)
+//   generateService         NBCTL:525-552
+//   generateVirtualService  NBCTL:558-658
+// and, for the ODH-shaped fleet (BASELINE config #4), the fields the ODH
+// mutating webhook injects into a Notebook before the controller sees it:
+//   InjectReconciliationLock ODHWH:105-114, InjectKubeRbacProxy ODHWH:177-326,
+//   InjectCertConfig ODHWH:666-781, MountPipelineRuntimeImages
+//   notebook_runtime.go:216-285, MountElyraRuntimeConfigSecret
+//   notebook_dspa_secret.go:375-450.
+#include "json.hpp"
+#include "k8s.hpp"
+#include "quantity.hpp"
+
+namespace nbh {
+namespace {
+
+const GVal kZero;
+
+const GVal& field(const GVal& s, const char* name) {
+  const GVal* p = s.find(name);
+  return p ? *p : kZero;
+}
+// s.a.b.c for nested structs
+const GVal& path(const GVal& s, std::initializer_list<const char*> names) {
+  const GVal* cur = &s;
+  for (const char* n : names) cur = &field(*cur, n);
+  return *cur;
+}
+// mutable nested struct field, created (as an empty struct) when absent
+GVal& ensure_struct(GVal& s, const char* name) {
+  if (!s.find(name)) {
+    // bypass set(): an empty struct is "zero" and would be dropped
+    auto it = std::lower_bound(s.kv.begin(), s.kv.end(), std::string(name),
+                               [](const std::pair<std::string, GVal>& e, const std::string& n) { return e.first < n; });
+    s.kv.insert(it, std::make_pair(std::string(name), GVal::strct()));
+  }
+  return *s.find(name);
+}
+
+bool contains(const std::string& hay, const char* needle) { return hay.find(needle) != std::string::npos; }
+
+GVal env_var(const std::string& name, const std::string& value) {
+  GVal e = GVal::strct();
+  e.set("name", GVal::str(name));
+  e.set("value", GVal::str(value));
+  return e;
+}
+GVal volume_mount(const std::string& name, const std::string& mount_path, bool read_only = false,
+                  const std::string& sub_path = std::string()) {
+  GVal m = GVal::strct();
+  m.set("name", GVal::str(name));
+  m.set("mountPath", GVal::str(mount_path));
+  m.set("readOnly", GVal::boolean(read_only));
+  m.set("subPath", GVal::str(sub_path));
+  return m;
+}
+GVal int_or_string_int(int64_t v) {
+  GVal g = GVal::strct();
+  g.set("IntVal", GVal::integer(v));
+  return g;
+}
+void append(GVal* list_or_null, GVal item) {  // Go append(): nil slice becomes non-nil
+  if (list_or_null->kind != GVal::List) *list_or_null = GVal::list();
+  list_or_null->items.push_back(std::move(item));
+}
+// the slice field `name` of struct `s`, inserted as Null when absent (caller appends)
+GVal& slice_field(GVal& s, const char* name) {
+  if (!s.find(name)) {
+    auto it = std::lower_bound(s.kv.begin(), s.kv.end(), std::string(name),
+                               [](const std::pair<std::string, GVal>& e, const std::string& n) { return e.first < n; });
+    s.kv.insert(it, std::make_pair(std::string(name), GVal()));
+  }
+  return *s.find(name);
+}
+
+}  // namespace
+
+// --------------------------------------------------------------------- G1
+bool generate_statefulset(const GVal& nb, const BuilderEnv& env, GVal* out, std::string* err) {
+  const GVal& meta = field(nb, "metadata");
+  const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
+  const GVal& nb_labels = field(meta, "labels");
+  const GVal& nb_ann = field(meta, "annotations");
+  const bool generate_name = name.size() > 52;            // NBCTL:145-149
+
+  // NBCTL:434-437: HasAnnotation is key presence, whatever the value
+  const int64_t replicas = (nb_ann.kind == GVal::Map && nb_ann.has("kubeflow-resource-stopped")) ? 0 : 1;
+
+  GVal ss_meta = GVal::strct();
+  if (!generate_name) {
+    ss_meta.set("name", GVal::str(name));
+    ss_meta.set("namespace", GVal::str(ns));
+    GVal labels = GVal::map();                            // Labels: map[string]string{}  (NBCTL:442)
+    if (nb_labels.kind == GVal::Map)
+      for (const auto& e : nb_labels.kv) labels.set(e.first, e.second);   // NBCTL:474-477
+    ss_meta.set("labels", std::move(labels));
+  } else {
+    ss_meta.set("generateName", GVal::str("nb-"));
+    ss_meta.set("namespace", GVal::str(ns));
+    if (nb_labels.kind == GVal::Map && !nb_labels.kv.empty()) {
+      if (err) *err = "assignment to entry in nil map (NBCTL:476 with isGenerateName)";
+      return false;
+    }
+  }
+
+  GVal tmpl_labels = GVal::map();                         // NBCTL:462-466
+  tmpl_labels.set("statefulset", GVal::str(name));
+  tmpl_labels.set("notebook-name", GVal::str(name));
+  tmpl_labels.set("opendatahub.io/workbenches", GVal::str("true"));
+  if (nb_labels.kind == GVal::Map)
+    for (const auto& e : nb_labels.kv) tmpl_labels.set(e.first, e.second);  // NBCTL:480-483
+  GVal tmpl_ann = GVal::map();                            // NBCTL:467, :486-491
+  if (nb_ann.kind == GVal::Map)
+    for (const auto& e : nb_ann.kv)
+      if (!contains(e.first, "kubectl") && !contains(e.first, "notebook")) tmpl_ann.set(e.first, e.second);
+
+  GVal pod = path(nb, {"spec", "template", "spec"});     // DeepCopy (NBCTL:469)
+  if (pod.kind != GVal::Struct) pod = GVal::strct();
+  GVal* containers = pod.find("containers");
+  if (!containers || containers->kind != GVal::List || containers->items.empty()) {
+    if (err) *err = "index out of range [0]: Notebook has no containers (NBCTL:494)";
+    return false;
+  }
+  GVal& c0 = containers->items[0];
+  if (c0.kind != GVal::Struct) c0 = GVal::strct();
+  if (c0.get_str("workingDir").empty()) c0.set("workingDir", GVal::str("/home/jovyan"));  // NBCTL:495-497
+  if (!c0.find("ports")) {                                // == nil, not len 0 (NBCTL:498)
+    GVal p = GVal::strct();
+    p.set("containerPort", GVal::integer(8888));
+    p.set("name", GVal::str("notebook-port"));
+    p.set("protocol", GVal::str("TCP"));
+    GVal ports = GVal::list();
+    ports.items.push_back(std::move(p));
+    c0.set("ports", std::move(ports));
+  }
+  {  // setPrefixEnvVar (NBCTL:417-431): an existing NB_PREFIX is left as it is
+    bool found = false;
+    const GVal* envs = c0.find("env");
+    if (envs && envs->kind == GVal::List)
+      for (const auto& e : envs->items)
+        if (e.get_str("name") == "NB_PREFIX") { found = true; break; }
+    if (!found) append(&slice_field(c0, "env"), env_var("NB_PREFIX", "/notebook/" + ns + "/" + name));
+  }
+  if (env.add_fsgroup && !pod.find("securityContext")) {  // NBCTL:514-521
+    GVal sc = GVal::strct();
+    sc.set("fsGroup", GVal::ptr(GVal::integer(100)));
+    pod.set("securityContext", GVal::ptr(std::move(sc)));
+  }
+
+  GVal tmpl_meta = GVal::strct();
+  tmpl_meta.set("labels", std::move(tmpl_labels));
+  tmpl_meta.set("annotations", std::move(tmpl_ann));
+  GVal tmpl = GVal::strct();
+  tmpl.set("metadata", std::move(tmpl_meta));
+  pod.canon();
+  tmpl.set("spec", std::move(pod));
+
+  GVal match = GVal::map();
+  match.set("statefulset", GVal::str(name));
+  GVal selector = GVal::strct();
+  selector.set("matchLabels", std::move(match));
+
+  GVal spec = GVal::strct();
+  spec.set("replicas", GVal::ptr(GVal::integer(replicas)));
+  spec.set("selector", GVal::ptr(std::move(selector)));
+  spec.set("template", std::move(tmpl));
+
+  GVal ss = GVal::strct();
+  ss.set("metadata", std::move(ss_meta));
+  ss.set("spec", std::move(spec));
+  *out = std::move(ss);
+  return true;
+}
+
+// --------------------------------------------------------------------- G2
+bool generate_service(const GVal& nb, GVal* out, std::string* err) {
+  const GVal& meta = field(nb, "metadata");
+  const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
+  const GVal& containers = path(nb, {"spec", "template", "spec", "containers"});
+  if (containers.kind != GVal::List || containers.items.empty()) {
+    if (err) *err = "index out of range [0]: Notebook has no containers (NBCTL:528)";
+    return false;
+  }
+  int64_t port = 8888;                                    // DefaultContainerPort
+  const GVal& ports = field(containers.items[0], "ports");
+  if (ports.kind == GVal::List) {                         // != nil (NBCTL:529)
+    if (ports.items.empty()) {
+      if (err) *err = "index out of range [0]: containers[0].ports is empty but not nil (NBCTL:530)";
+      return false;
+    }
+    port = field(ports.items[0], "containerPort").i;
+  }
+  GVal sp = GVal::strct();
+  sp.set("name", GVal::str("http-notebook"));
+  sp.set("port", GVal::integer(80));
+  sp.set("targetPort", int_or_string_int(port));
+  sp.set("protocol", GVal::str("TCP"));
+  GVal plist = GVal::list();
+  plist.items.push_back(std::move(sp));
+  GVal sel = GVal::map();
+  sel.set("statefulset", GVal::str(name));
+  GVal spec = GVal::strct();
+  spec.set("type", GVal::str("ClusterIP"));
+  spec.set("selector", std::move(sel));
+  spec.set("ports", std::move(plist));
+  GVal m = GVal::strct();
+  m.set("name", GVal::str(name));
+  m.set("namespace", GVal::str(ns));
+  GVal svc = GVal::strct();
+  svc.set("metadata", std::move(m));
+  svc.set("spec", std::move(spec));
+  *out = std::move(svc);
+  return true;
+}
+
+// --------------------------------------------------------------------- G3
+bool generate_virtualservice(const GVal& nb, const BuilderEnv& env, GVal* out, std::string* /*err*/) {
+  const GVal& meta = field(nb, "metadata");
+  const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
+  const GVal& ann = field(meta, "annotations");
+  const std::string prefix = "/notebook/" + ns + "/" + name + "/";
+  std::string rewrite = prefix;
+  const std::string rw = ann.kind == GVal::Map ? ann.get_str("notebooks.kubeflow.org/http-rewrite-uri") : "";
+  if (!rw.empty()) rewrite = rw;                           // NBCTL:571-574
+  const std::string service = name + "." + ns + ".svc." + env.cluster_domain;
+
+  GVal headers = GVal::map();                              // NBCTL:602-618
+  const std::string hj = ann.kind == GVal::Map ? ann.get_str("notebooks.kubeflow.org/http-headers-request-set") : "";
+  if (!hj.empty()) {
+    GVal parsed;
+    std::string perr;
+    bool ok = parse_json(hj, &parsed, &perr) && (parsed.kind == GVal::Map || parsed.is_null());
+    if (ok && parsed.kind == GVal::Map) {
+      // json.Unmarshal into map[string]string: any non-string, non-null value is an
+      // error => the reference falls back to an empty map (NBCTL:608-611)
+      for (const auto& e : parsed.kv) {
+        if (e.second.kind == GVal::Str) headers.set(e.first, e.second);
+        else if (e.second.is_null()) headers.set(e.first, GVal::str(""));
+        else { ok = false; break; }
+      }
+    }
+    if (!ok) headers = GVal::map();
+  }
+
+  auto obj = [](std::initializer_list<std::pair<const char*, GVal>> kvs) {
+    GVal m = GVal::map();
+    for (const auto& e : kvs) m.set(e.first, e.second);
+    return m;
+  };
+  auto lst = [](std::initializer_list<GVal> vs) {
+    GVal l = GVal::list();
+    for (const auto& v : vs) l.items.push_back(v);
+    return l;
+  };
+  GVal http = lst({obj({
+      {"headers", obj({{"request", obj({{"set", headers}})}})},
+      {"match", lst({obj({{"uri", obj({{"prefix", GVal::str(prefix)}})}})})},
+      {"rewrite", obj({{"uri", GVal::str(rewrite)}})},
+      {"route", lst({obj({{"destination", obj({{"host", GVal::str(service)},
+                                                {"port", obj({{"number", GVal::integer(80)}})}})}})})},
+  })});
+  GVal spec = obj({{"hosts", lst({GVal::str(env.istio_host)})},
+                   {"gateways", lst({GVal::str(env.istio_gateway)})},
+                   {"http", http}});
+  GVal vs = obj({{"apiVersion", GVal::str("networking.istio.io/v1alpha3")},
+                 {"kind", GVal::str("VirtualService")},
+                 {"metadata", obj({{"name", GVal::str("notebook-" + ns + "-" + name)},
+                                   {"namespace", GVal::str(ns)}})},
+                 {"spec", spec}});
+  *out = std::move(vs);
+  return true;
+}
+
+// --------------------------------------------------------------------- G4
+void odh_webhook_mutate(GVal* nb, const OdhInject& what) {
+  // create every container we are going to reference BEFORE taking references:
+  // inserting a field may move its siblings
+  ensure_struct(*nb, "metadata");
+  ensure_struct(*nb, "spec");
+  const std::string name = nb->find("metadata")->get_str("name");
+  if (what.lock) {                                         // ODHWH:105-114
+    GVal& meta = *nb->find("metadata");
+    GVal* ann = meta.find("annotations");
+    if (!ann || ann->kind != GVal::Map) { meta.set("annotations", GVal::map()); ann = meta.find("annotations"); }
+    ann->set("kubeflow-resource-stopped", GVal::str("odh-notebook-controller-lock"));
+  }
+  GVal& pod = ensure_struct(ensure_struct(*nb->find("spec"), "template"), "spec");
+  slice_field(pod, "volumes");
+  slice_field(pod, "serviceAccountName");
+  auto upsert_volume = [&](GVal vol, bool replace) {
+    GVal& vols = slice_field(pod, "volumes");
+    const std::string vname = vol.get_str("name");
+    if (vols.kind == GVal::List)
+      for (auto& v : vols.items)
+        if (v.get_str("name") == vname) { if (replace) v = std::move(vol); return; }
+    append(&vols, std::move(vol));
+  };
+  auto configmap_volume = [](const std::string& vname, const std::string& cm, bool optional, int64_t mode) {
+    GVal src = GVal::strct();
+    src.set("name", GVal::str(cm));
+    if (optional) src.set("optional", GVal::ptr(GVal::boolean(true)));
+    if (mode >= 0) src.set("defaultMode", GVal::ptr(GVal::integer(mode)));
+    GVal v = GVal::strct();
+    v.set("name", GVal::str(vname));
+    v.set("configMap", GVal::ptr(std::move(src)));
+    return v;
+  };
+  GVal& containers = slice_field(pod, "containers");
+
+  if (what.ca_bundle) {                                    // InjectCertConfig ODHWH:666-781
+    const std::string mp = "/etc/pki/tls/custom-certs/ca-bundle.crt";
+    GVal vol = configmap_volume("trusted-ca", "workbench-trusted-ca-bundle", true, -1);
+    GVal item = GVal::strct();
+    item.set("key", GVal::str("ca-bundle.crt"));
+    item.set("path", GVal::str("ca-bundle.crt"));
+    GVal items = GVal::list();
+    items.items.push_back(std::move(item));
+    vol.find("configMap")->items[0].set("items", std::move(items));
+    upsert_volume(std::move(vol), true);
+    if (containers.kind == GVal::List)
+      for (auto& c : containers.items) {
+        if (c.get_str("name") != name) continue;
+        // Go ranges over a map here (random order); this restatement uses sorted order.
+        static const char* keys[] = {"GIT_SSL_CAINFO", "KF_PIPELINES_SSL_SA_CERTS", "PIPELINES_SSL_SA_CERTS",
+                                     "PIP_CERT",       "REQUESTS_CA_BUNDLE",        "SSL_CERT_FILE"};
+        for (const char* k : keys) {
+          bool exists = false;
+          const GVal* envs = c.find("env");
+          if (envs && envs->kind == GVal::List)
+            for (const auto& e : envs->items) if (e.get_str("name") == k) exists = true;
+          if (!exists) append(&slice_field(c, "env"), env_var(k, mp));
+        }
+        GVal& mounts = slice_field(c, "volumeMounts");
+        bool replaced = false;
+        if (mounts.kind == GVal::List)
+          for (auto& m : mounts.items)
+            if (m.get_str("name") == "trusted-ca") { m = volume_mount("trusted-ca", mp, true, "ca-bundle.crt"); replaced = true; break; }
+        if (!replaced) append(&mounts, volume_mount("trusted-ca", mp, true, "ca-bundle.crt"));
+        break;
+      }
+  }
+  if (what.runtime_images) {                               // notebook_runtime.go:216-285
+    upsert_volume(configmap_volume("runtime-images", "pipeline-runtime-images", true, -1), false);
+    if (containers.kind == GVal::List)
+      for (auto& c : containers.items) {
+        bool exists = false;
+        const GVal* ms = c.find("volumeMounts");
+        if (ms && ms->kind == GVal::List)
+          for (const auto& m : ms->items) if (m.get_str("name") == "runtime-images") exists = true;
+        if (!exists) append(&slice_field(c, "volumeMounts"), volume_mount("runtime-images", "/opt/app-root/pipeline-runtimes/"));
+      }
+  }
+  if (what.elyra_secret) {                                 // notebook_dspa_secret.go:375-450
+    GVal src = GVal::strct();
+    src.set("secretName", GVal::str("ds-pipeline-config"));
+    src.set("optional", GVal::ptr(GVal::boolean(true)));
+    GVal v = GVal::strct();
+    v.set("name", GVal::str("elyra-dsp-details"));
+    v.set("secret", GVal::ptr(std::move(src)));
+    upsert_volume(std::move(v), false);
+    if (containers.kind == GVal::List)
+      for (auto& c : containers.items) {
+        bool exists = false;
+        const GVal* ms = c.find("volumeMounts");
+        if (ms && ms->kind == GVal::List)
+          for (const auto& m : ms->items)
+            if (m.get_str("name") == "elyra-dsp-details" || m.get_str("mountPath") == "/opt/app-root/runtimes") exists = true;
+        if (!exists) append(&slice_field(c, "volumeMounts"), volume_mount("elyra-dsp-details", "/opt/app-root/runtimes"));
+      }
+  }
+  if (what.rbac_proxy) {                                   // InjectKubeRbacProxy ODHWH:177-326
+    auto q = [](const char* text) { GVal g; parse_quantity(text, &g); return g; };
+    GVal req = GVal::map(), lim = GVal::map();
+    req.set("cpu", q("100m")); req.set("memory", q("64Mi"));
+    lim.set("cpu", q("100m")); lim.set("memory", q("64Mi"));
+    GVal res = GVal::strct();
+    res.set("requests", std::move(req));
+    res.set("limits", std::move(lim));
+    auto probe = [](int64_t initial_delay) {
+      GVal get = GVal::strct();
+      get.set("path", GVal::str("/healthz"));
+      get.set("port", int_or_string_int(8444));
+      get.set("scheme", GVal::str("HTTPS"));
+      GVal p = GVal::strct();
+      p.set("httpGet", GVal::ptr(std::move(get)));
+      p.set("initialDelaySeconds", GVal::integer(initial_delay));
+      p.set("timeoutSeconds", GVal::integer(1));
+      p.set("periodSeconds", GVal::integer(5));
+      p.set("successThreshold", GVal::integer(1));
+      p.set("failureThreshold", GVal::integer(3));
+      return GVal::ptr(std::move(p));
+    };
+    GVal args = GVal::list();
+    for (const char* a : {"--secure-listen-address=0.0.0.0:8443", "--upstream=http://127.0.0.1:8888/",
+                          "--logtostderr=true", "--v=10", "--proxy-endpoints-port=8444",
+                          "--config-file=/etc/kube-rbac-proxy/config-file.yaml",
+                          "--tls-cert-file=/etc/tls/private/tls.crt", "--tls-private-key-file=/etc/tls/private/tls.key",
+                          "--auth-header-fields-enabled=true", "--auth-header-user-field-name=X-Auth-Request-User",
+                          "--auth-header-groups-field-name=X-Auth-Request-Groups"})
+      args.items.push_back(GVal::str(a));
+    GVal port = GVal::strct();
+    port.set("name", GVal::str("kube-rbac-proxy"));
+    port.set("containerPort", GVal::integer(8443));
+    port.set("protocol", GVal::str("TCP"));
+    GVal ports = GVal::list();
+    ports.items.push_back(std::move(port));
+    GVal mounts = GVal::list();
+    mounts.items.push_back(volume_mount("kube-rbac-proxy-config", "/etc/kube-rbac-proxy"));
+    mounts.items.push_back(volume_mount("kube-rbac-proxy-tls-certificates", "/etc/tls/private"));
+    GVal pc = GVal::strct();
+    pc.set("name", GVal::str("kube-rbac-proxy"));
+    pc.set("image", GVal::str("registry.redhat.io/openshift4/ose-kube-rbac-proxy:latest"));
+    pc.set("imagePullPolicy", GVal::str("Always"));
+    pc.set("args", std::move(args));
+    pc.set("ports", std::move(ports));
+    pc.set("livenessProbe", probe(30));
+    pc.set("readinessProbe", probe(5));
+    pc.set("resources", std::move(res));
+    pc.set("volumeMounts", std::move(mounts));
+    bool replaced = false;
+    if (containers.kind == GVal::List)
+      for (auto& c : containers.items)
+        if (c.get_str("name") == "kube-rbac-proxy") { c = pc; replaced = true; break; }
+    if (!replaced) append(&containers, std::move(pc));
+    upsert_volume(configmap_volume("kube-rbac-proxy-config", name + "-kube-rbac-proxy-config", false, 420), true);
+    GVal ssrc = GVal::strct();
+    ssrc.set("secretName", GVal::str(name + "-kube-rbac-proxy-tls"));
+    ssrc.set("defaultMode", GVal::ptr(GVal::integer(420)));
+    GVal tls = GVal::strct();
+    tls.set("name", GVal::str("kube-rbac-proxy-tls-certificates"));
+    tls.set("secret", GVal::ptr(std::move(ssrc)));
+    upsert_volume(std::move(tls), true);
+    pod.set("serviceAccountName", GVal::str(name));
+  }
+  nb->canon();
+}
+
+}  // namespace nbh

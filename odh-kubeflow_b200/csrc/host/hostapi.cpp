@@ -1,0 +1,399 @@
+// hostapi.cpp — C ABI of libnbgraft_host.so (include/nbgraft_host.h).
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <sstream>
+#include <thread>
+
+#include "../../../include/nbgraft_host.h"
+#include "../hash.h"
+#include "fleet.hpp"
+#include "json.hpp"
+#include "k8s.hpp"
+#include "rfc3339.hpp"
+
+#define NBH_API extern "C" __attribute__((visibility("default")))
+
+using namespace nbh;
+
+struct nbh_obj { GVal v; };
+struct nbh_sts { StsBatch b; };
+struct nbh_svc { SvcBatch b; };
+struct nbh_vs { VsBatch b; };
+struct nbh_cull { CullBatch b; };
+struct nbh_fleet { Fleet f; };
+struct nbh_cullfleet { CullFleet f; };
+
+namespace {
+
+// dynamic parallel-for over blocks with plain std::thread (no OpenMP runtime needed)
+int host_threads() {
+  const unsigned hc = std::thread::hardware_concurrency();
+  const char* e = getenv("NBH_THREADS");
+  int n = e ? atoi(e) : (int)hc;
+  if (n < 1) n = 1;
+  if (n > 256) n = 256;
+  return n;
+}
+template <class F>
+void parallel_blocks(uint64_t nblocks, F&& body) {
+  const int nt = (int)std::min<uint64_t>((uint64_t)host_threads(), nblocks);
+  if (nt <= 1) { for (uint64_t b = 0; b < nblocks; ++b) body(b); return; }
+  std::atomic<uint64_t> next{0};
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nt; ++t)
+    pool.emplace_back([&] { for (uint64_t b; (b = next.fetch_add(1)) < nblocks;) body(b); });
+  for (auto& th : pool) th.join();
+}
+
+int fail(char* err, size_t errlen, const std::string& msg) {
+  if (err && errlen) { snprintf(err, errlen, "%s", msg.c_str()); }
+  return -1;
+}
+
+void dump_json(const GVal& v, std::string* o) {
+  auto esc = [&](const std::string& s) {
+    o->push_back('"');
+    for (char c : s) {
+      if (c == '"' || c == '\\') { o->push_back('\\'); o->push_back(c); }
+      else if ((unsigned char)c < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); *o += b; }
+      else o->push_back(c);
+    }
+    o->push_back('"');
+  };
+  switch (v.kind) {
+    case GVal::Null: *o += "null"; break;
+    case GVal::Bool: *o += v.i ? "true" : "false"; break;
+    case GVal::Int: *o += std::to_string(v.i); break;
+    case GVal::Float: { std::ostringstream os; os.precision(17); os << v.f; std::string t = os.str();
+                        if (t.find_first_of(".eEn") == std::string::npos) t += ".0"; *o += t; break; }
+    case GVal::Str: esc(v.s); break;
+    case GVal::List:
+      o->push_back('[');
+      for (size_t k = 0; k < v.items.size(); ++k) { if (k) o->push_back(','); dump_json(v.items[k], o); }
+      o->push_back(']');
+      break;
+    case GVal::Map: case GVal::Struct: {
+      o->push_back('{');
+      bool first = true;
+      for (const auto& e : v.kv) {
+        if (!first) o->push_back(',');
+        first = false;
+        esc(e.first); o->push_back(':'); dump_json(e.second, o);
+      }
+      o->push_back('}');
+      break;
+    }
+    case GVal::Ptr:
+      if (v.items.empty()) *o += "\"<extracted>\""; else dump_json(v.items[0], o);
+      break;
+  }
+}
+
+BuilderEnv to_env(const nbh_env* e) {
+  BuilderEnv b;
+  if (!e) return b;
+  b.add_fsgroup = e->add_fsgroup != 0;
+  if (e->cluster_domain) b.cluster_domain = e->cluster_domain;
+  if (e->istio_host && *e->istio_host) b.istio_host = e->istio_host;
+  if (e->istio_gateway && *e->istio_gateway) b.istio_gateway = e->istio_gateway;
+  return b;
+}
+
+bool cull_input_from_json(const std::string& text, CullInput* in, std::string* err) {
+  GVal j;
+  if (!parse_json(text, &j, err)) return false;
+  if (j.kind != GVal::Map) { *err = "culler input must be a JSON object"; return false; }
+  *in = CullInput();
+  const GVal* ann = j.find("annotations");
+  in->has_annotations = ann && ann->kind == GVal::Map;
+  if (in->has_annotations) {
+    if (ann->has("kubeflow-resource-stopped")) in->stop_set = true;
+    if (const GVal* la = ann->find("notebooks.kubeflow.org/last-activity")) { in->la_present = true; in->last_activity = la->s; }
+    if (const GVal* ck = ann->find("notebooks.kubeflow.org/last_activity_check_timestamp")) { in->chk_present = true; in->check_ts = ck->s; }
+  }
+  if (const GVal* pm = j.find("pod_missing")) in->pod_missing = pm->kind == GVal::Bool && pm->i;
+  auto recs = [&](const char* key, std::vector<CullInput::Rec>* out) {
+    const GVal* l = j.find(key);
+    if (!l || l->kind != GVal::List) return;
+    for (const auto& e : l->items) {
+      CullInput::Rec r;
+      if (e.kind == GVal::Map) { r.last_activity = e.get_str("last_activity"); r.state = e.get_str("execution_state"); }
+      out->push_back(std::move(r));
+    }
+  };
+  recs("kernels", &in->kernels);
+  recs("terminals", &in->terminals);
+  return true;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ objects
+NBH_API int nbh_obj_from_json(const char* type, const char* json, nbh_obj** out, char* err, size_t errlen) {
+  if (!type || !json || !out) return fail(err, errlen, "null argument");
+  nbh_obj* o = new nbh_obj();
+  std::string e;
+  if (!decode_typed_json(json, type, &o->v, &e)) { delete o; return fail(err, errlen, e); }
+  *out = o;
+  return 0;
+}
+NBH_API void nbh_obj_free(nbh_obj* o) { delete o; }
+NBH_API char* nbh_obj_to_json(const nbh_obj* o) {
+  std::string s;
+  if (o) dump_json(o->v, &s);
+  char* r = (char*)malloc(s.size() + 1);
+  if (r) memcpy(r, s.c_str(), s.size() + 1);
+  return r;
+}
+NBH_API void nbh_str_free(char* s) { free(s); }
+NBH_API int nbh_obj_get(const nbh_obj* o, const char* dotted_path, nbh_obj** out) {
+  if (!o || !dotted_path || !out) return -1;
+  const GVal* cur = &o->v;
+  std::string path(dotted_path);
+  size_t at = 0;
+  while (at <= path.size() && !path.empty()) {
+    const size_t dot = path.find('.', at);
+    const std::string key = path.substr(at, dot == std::string::npos ? std::string::npos : dot - at);
+    while (cur->kind == GVal::Ptr && !cur->items.empty()) cur = &cur->items[0];
+    if (cur->kind != GVal::Struct && cur->kind != GVal::Map) return -1;
+    cur = cur->find(key);
+    if (!cur) return -1;
+    if (dot == std::string::npos) break;
+    at = dot + 1;
+  }
+  nbh_obj* r = new nbh_obj();
+  r->v = *cur;
+  *out = r;
+  return 0;
+}
+NBH_API uint64_t nbh_obj_digest(const nbh_obj* o) { return o ? digest(o->v) : 0; }
+
+// ----------------------------------------------------------------- builders
+NBH_API int nbh_generate_statefulset(const nbh_obj* nb, const nbh_env* env, nbh_obj** out, char* err, size_t errlen) {
+  if (!nb || !out) return fail(err, errlen, "null argument");
+  nbh_obj* o = new nbh_obj();
+  std::string e;
+  if (!generate_statefulset(nb->v, to_env(env), &o->v, &e)) { delete o; return fail(err, errlen, e); }
+  *out = o;
+  return 0;
+}
+NBH_API int nbh_generate_service(const nbh_obj* nb, nbh_obj** out, char* err, size_t errlen) {
+  if (!nb || !out) return fail(err, errlen, "null argument");
+  nbh_obj* o = new nbh_obj();
+  std::string e;
+  if (!generate_service(nb->v, &o->v, &e)) { delete o; return fail(err, errlen, e); }
+  *out = o;
+  return 0;
+}
+NBH_API int nbh_generate_virtualservice(const nbh_obj* nb, const nbh_env* env, nbh_obj** out, char* err, size_t errlen) {
+  if (!nb || !out) return fail(err, errlen, "null argument");
+  nbh_obj* o = new nbh_obj();
+  std::string e;
+  if (!generate_virtualservice(nb->v, to_env(env), &o->v, &e)) { delete o; return fail(err, errlen, e); }
+  *out = o;
+  return 0;
+}
+NBH_API int nbh_odh_mutate(nbh_obj* nb, int flags) {
+  if (!nb) return -1;
+  OdhInject inj;
+  inj.lock = flags & 1; inj.ca_bundle = flags & 2; inj.runtime_images = flags & 4;
+  inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16;
+  odh_webhook_mutate(&nb->v, inj);
+  return 0;
+}
+
+// ------------------------------------------------------------------ batches
+NBH_API nbh_sts* nbh_sts_new(void) { return new nbh_sts(); }
+NBH_API void nbh_sts_free(nbh_sts* b) { delete b; }
+NBH_API int nbh_sts_add(nbh_sts* b, const nbh_obj* from, const nbh_obj* to) {
+  if (!b || !from || !to) return -1;
+  b->b.add(from->v, to->v);
+  return 0;
+}
+NBH_API uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+NBH_API nbh_svc* nbh_svc_new(void) { return new nbh_svc(); }
+NBH_API void nbh_svc_free(nbh_svc* b) { delete b; }
+NBH_API int nbh_svc_add(nbh_svc* b, const nbh_obj* from, const nbh_obj* to) {
+  if (!b || !from || !to) return -1;
+  b->b.add(from->v, to->v);
+  return 0;
+}
+NBH_API uint64_t nbh_svc_view(const nbh_svc* b, nbg_svc_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+NBH_API nbh_vs* nbh_vs_new(void) { return new nbh_vs(); }
+NBH_API void nbh_vs_free(nbh_vs* b) { delete b; }
+NBH_API int nbh_vs_add(nbh_vs* b, const nbh_obj* from, const nbh_obj* to) {
+  if (!b || !from || !to) return -1;
+  b->b.add(from->v, to->v);
+  return 0;
+}
+NBH_API uint64_t nbh_vs_view(const nbh_vs* b, nbg_vs_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+
+NBH_API nbh_cull* nbh_cull_new(void) { return new nbh_cull(); }
+NBH_API void nbh_cull_free(nbh_cull* b) { delete b; }
+NBH_API int nbh_cull_add_json(nbh_cull* b, const char* json, char* err, size_t errlen) {
+  if (!b || !json) return fail(err, errlen, "null argument");
+  CullInput in;
+  std::string e;
+  if (!cull_input_from_json(json, &in, &e)) return fail(err, errlen, e);
+  b->b.add(in);
+  return 0;
+}
+NBH_API uint64_t nbh_cull_view(const nbh_cull* b, nbg_cull_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+NBH_API uint64_t nbh_cull_records(const nbh_cull* b, uint64_t* kernels, uint64_t* terminals) {
+  if (!b) return 0;
+  if (kernels) *kernels = b->b.k_sec.size();
+  if (terminals) *terminals = b->b.t_sec.size();
+  return b->b.k_sec.size() + b->b.t_sec.size();
+}
+NBH_API int nbh_cull_new_last_activity(const nbh_cull* b, uint64_t i, uint8_t action, uint32_t argmax,
+                                       int64_t now_sec, int32_t now_offset_sec, char* buf, size_t buflen) {
+  if (!b || !buf || !buflen || i >= b->b.n) return -1;
+  std::string s;
+  switch (action & NBG_ACT_SRC_MASK) {
+    case 0: break;
+    case 1: s = format_rfc3339(now_sec, now_offset_sec); break;                  // createTimestamp(), CULL:512-515
+    case 2: {
+      const uint64_t r = (uint64_t)b->b.k_off[i] + argmax;
+      if (r >= b->b.k_off[i + 1]) return -1;
+      s = format_rfc3339(b->b.k_sec[r], b->b.k_zone[r]);                          // CULL:348
+      break;
+    }
+    case 3: {
+      const uint64_t r = (uint64_t)b->b.t_off[i] + argmax;
+      if (r >= b->b.t_off[i + 1]) return -1;
+      s = format_rfc3339(b->b.t_sec[r], b->b.t_zone[r]);
+      break;
+    }
+  }
+  if (s.size() + 1 > buflen) return -1;
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return (int)s.size();
+}
+
+NBH_API int nbh_parse_rfc3339(const char* s, int64_t* sec, int32_t* nsec, int32_t* offset_sec) {
+  Instant t;
+  if (!s || !parse_rfc3339(s, strlen(s), &t)) return 0;
+  if (sec) *sec = t.sec;
+  if (nsec) *nsec = t.nsec;
+  if (offset_sec) *offset_sec = t.offset;
+  return 1;
+}
+NBH_API int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_t buflen) {
+  const std::string s = format_rfc3339(sec, offset_sec);
+  if (!buf || s.size() + 1 > buflen) return -1;
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return (int)s.size();
+}
+
+// ------------------------------------------------------------------- fleets
+NBH_API nbh_fleet* nbh_fleet_new(int kind, uint64_t seed, uint64_t n, uint32_t n_namespaces) {
+  if (kind != FLEET_KUBEFLOW && kind != FLEET_ODH) return nullptr;
+  nbh_fleet* f = new nbh_fleet();
+  f->f.kind = kind; f->f.seed = seed; f->f.n = n; f->f.n_namespaces = n_namespaces;
+  f->f.init();
+  return f;
+}
+NBH_API void nbh_fleet_free(nbh_fleet* f) { delete f; }
+NBH_API int nbh_fleet_get(const nbh_fleet* f, uint64_t i, int which, nbh_obj** out) {
+  if (!f || !out || which < 0 || which > 6) return -1;
+  Pair p;
+  fleet_make(f->f, i, &p);
+  nbh_obj* o = new nbh_obj();
+  GVal* src[] = {&p.notebook, &p.sts_from, &p.sts_to, &p.svc_from, &p.svc_to, &p.vs_from, &p.vs_to};
+  o->v = std::move(*src[which]);
+  *out = o;
+  return 0;
+}
+NBH_API int nbh_fleet_drift_class(const nbh_fleet* f, uint64_t i) {
+  if (!f) return -1;
+  Pair p;
+  fleet_make(f->f, i, &p);
+  return p.drift_class;
+}
+NBH_API uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i) {
+  if (!f) return 0;
+  return hash_str(f->f.namespace_name(i));
+}
+
+NBH_API int nbh_threads(void) { return host_threads(); }
+
+NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                           nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
+  if (!f) return -1;
+  const uint64_t kBlock = 2048;
+  const uint64_t nblocks = (m + kBlock - 1) / kBlock;
+  std::vector<StsBatch> ps(sts ? nblocks : 0);
+  std::vector<SvcBatch> pv(svc ? nblocks : 0);
+  std::vector<VsBatch> pw(vs ? nblocks : 0);
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
+    Pair p;
+    for (uint64_t k = lo; k < hi; ++k) {
+      fleet_make(f->f, idx ? idx[k] : i0 + k, &p);
+      if (sts) ps[blk].add(p.sts_from, p.sts_to);
+      if (svc) pv[blk].add(p.svc_from, p.svc_to);
+      if (vs) pw[blk].add(p.vs_from, p.vs_to);
+    }
+  });
+  if (sts) {
+    nbh_sts* o = new nbh_sts();
+    o->b.pod_from.reserve(m * NBG_POD_SLOTS); o->b.pod_to.reserve(m * NBG_POD_SLOTS);
+    for (auto& b : ps) { o->b.append(b); b = StsBatch(); }
+    *sts = o;
+  }
+  if (svc) { nbh_svc* o = new nbh_svc(); for (auto& b : pv) { o->b.append(b); b = SvcBatch(); } *svc = o; }
+  if (vs) { nbh_vs* o = new nbh_vs(); for (auto& b : pw) { o->b.append(b); b = VsBatch(); } *vs = o; }
+  return 0;
+}
+
+NBH_API nbh_cullfleet* nbh_cullfleet_new(uint64_t seed, uint64_t n, int64_t now_sec, int32_t now_nsec, double mean_kernels) {
+  nbh_cullfleet* f = new nbh_cullfleet();
+  f->f.seed = seed; f->f.n = n; f->f.now_sec = now_sec; f->f.now_nsec = now_nsec;
+  if (mean_kernels > 0) f->f.mean_kernels = mean_kernels;
+  return f;
+}
+NBH_API void nbh_cullfleet_free(nbh_cullfleet* f) { delete f; }
+NBH_API char* nbh_cullfleet_json(const nbh_cullfleet* f, uint64_t i) {
+  if (!f) return nullptr;
+  CullInput in;
+  cullfleet_make(f->f, i, &in);
+  const std::string s = cull_input_json(in);
+  char* r = (char*)malloc(s.size() + 1);
+  if (r) memcpy(r, s.c_str(), s.size() + 1);
+  return r;
+}
+NBH_API int nbh_cullfleet_pack(const nbh_cullfleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_cull** out) {
+  if (!f || !out) return -1;
+  const uint64_t kBlock = 8192;
+  const uint64_t nblocks = (m + kBlock - 1) / kBlock;
+  std::vector<CullBatch> parts(nblocks);
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
+    CullInput in;
+    for (uint64_t k = lo; k < hi; ++k) {
+      cullfleet_make(f->f, idx ? idx[k] : i0 + k, &in);
+      parts[blk].add(in);
+    }
+  });
+  nbh_cull* o = new nbh_cull();
+  for (auto& b : parts) { o->b.append(b); b = CullBatch(); }
+  *out = o;
+  return 0;
+}

@@ -1,0 +1,54 @@
+// k8s.hpp — typed decoding of Kubernetes JSON into GVal, the desired-object
+// builders of the notebook controller, and the packer that flattens objects
+// into the structure-of-arrays schema of include/nbgraft.h.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../../include/nbgraft.h"
+#include "gval.hpp"
+
+namespace nbh {
+
+// ---- typed decoding (k8s.cpp) ---------------------------------------------
+// Convert the generic JSON tree `j` (json.hpp) into the GVal of Go type `type`:
+// "Notebook", "StatefulSet", "Service", "PodSpec", "ObjectMeta", ... as
+// encoding/json would fill k8s.io/api v0.33.7 structs.  Fields this table does
+// not know are kept as untyped JSON under "?<name>" so that they still take
+// part in comparisons (never silently dropped).
+bool decode_typed(const GVal& j, const std::string& type, GVal* out, std::string* err);
+bool decode_typed_json(const std::string& json, const std::string& type, GVal* out, std::string* err);
+
+// ---- builders (builders.cpp) ----------------------------------------------
+struct BuilderEnv {            // process environment read by the reference builders
+  bool add_fsgroup = true;     // ADD_FSGROUP unset or "true"  (NBCTL:514)
+  std::string cluster_domain = "cluster.local";  // CLUSTER_DOMAIN (NBCTL:576)
+  std::string istio_host = "*";                  // ISTIO_HOST (NBCTL:587-590)
+  std::string istio_gateway = "kubeflow/kubeflow-gateway";  // ISTIO_GATEWAY (NBCTL:596-599)
+};
+// generateStatefulSet (NBCTL:433-523).  false + err where the Go code panics.
+bool generate_statefulset(const GVal& notebook, const BuilderEnv& env, GVal* out, std::string* err);
+// generateService (NBCTL:525-552)
+bool generate_service(const GVal& notebook, GVal* out, std::string* err);
+// generateVirtualService (NBCTL:558-658): an unstructured (generic) object
+bool generate_virtualservice(const GVal& notebook, const BuilderEnv& env, GVal* out, std::string* err);
+// ODH mutating-webhook injections that shape config #4 (ODHWH:177-326,666-781 and
+// notebook_runtime.go:216-285, notebook_dspa_secret.go:375-450): applied to a Notebook.
+struct OdhInject {
+  bool lock = false, ca_bundle = true, runtime_images = true, elyra_secret = true, rbac_proxy = true;
+};
+void odh_webhook_mutate(GVal* notebook, const OdhInject& what);
+
+// ---- packing (pack.cpp) ---------------------------------------------------
+uint64_t hash_str(const std::string& s);
+uint64_t digest(const GVal& v);                 // canonical 64-bit digest of a value tree
+uint64_t digest_string_map(const GVal& m);      // nil != empty
+void pack_kvmap(const GVal& m, std::vector<nbg_kv>* out);   // sorted by key hash; Null/absent => none
+void pack_podspec(const GVal& podspec, uint64_t* slots /*NBG_POD_SLOTS*/);
+void pack_service_ports(const GVal& ports, uint64_t* slots /*NBG_SVC_SLOTS*/);
+// returns false when obj.spec is missing or not a map (NestedMap not found / error)
+bool pack_vs_spec(const GVal& vs_obj, uint64_t* slots /*NBG_VS_SLOTS*/, std::vector<nbg_kv>* headers,
+                  bool* headers_nil);
+
+}  // namespace nbh

@@ -1,0 +1,318 @@
+// pack.cpp — flatten Go-shaped objects (GVal) into the structure-of-arrays
+// schema of include/nbgraft.h.
+//
+// Soundness rule ("injective up to hash collision"): a tile must be a function
+// of the whole value, so that   tiles equal  <=>  reflect.DeepEqual(values).
+// Every tile therefore consists of
+//   * named slots holding a leaf (raw integer, or the 64-bit hash of a string,
+//     "" == 0) or the digest of a named sub-tree,
+//   * count tags that tell nil / empty / n for every list whose elements are
+//     slotted by position, and
+//   * a residual digest of everything that has no slot of its own (including
+//     list elements beyond the slotted capacity and fields outside the
+//     schema).  Nothing is ever dropped.
+// tests/test_pack.py checks the equivalence against the semantic oracle on
+// generated and hand-built pairs.
+#include <cstring>
+
+#include "../hash.h"
+#include "k8s.hpp"
+
+namespace nbh {
+
+uint64_t hash_str(const std::string& s) { return nbg_hash_bytes(s.data(), s.size()); }
+
+namespace {
+
+constexpr uint64_t K_NULL = 0x6E696C6E696C6E69ull, K_BOOL = 0xB001, K_INT = 0x1A7, K_FLOAT = 0xF10A7,
+                   K_STR = 0x57A, K_LIST = 0x1157, K_MAP = 0x3A9, K_STRUCT = 0x57AC7, K_PTR = 0x97A,
+                   K_MARK = 0x3A4B3A4B3A4B3A4Bull;
+
+const GVal kZero;
+const GVal& field(const GVal& s, const char* name) {
+  const GVal* p = (s.kind == GVal::Struct || s.kind == GVal::Map) ? s.find(name) : nullptr;
+  return p ? *p : kZero;
+}
+uint64_t str_of(const GVal& s, const char* name) {
+  const GVal& f = field(s, name);
+  return f.kind == GVal::Str ? hash_str(f.s) : 0;
+}
+// marker node: a Ptr without pointee cannot be produced by any decoder
+GVal marker() { GVal g; g.kind = GVal::Ptr; return g; }
+
+// count tag of a slice field: 0xFFFF nil, else min(len, 0xFFFE)
+uint64_t count_tag(const GVal& l) {
+  if (l.kind != GVal::List) return 0xFFFF;
+  return l.items.size() > 0xFFFE ? 0xFFFE : l.items.size();
+}
+// digest of elements [from, end) of a list (0 when there are none)
+uint64_t overflow_digest(const GVal& l, size_t from) {
+  if (l.kind != GVal::List || l.items.size() <= from) return 0;
+  uint64_t h = nbg_combine(K_LIST, l.items.size() - from);
+  for (size_t k = from; k < l.items.size(); ++k) h = nbg_combine(h, digest(l.items[k]));
+  return h;
+}
+// digest of a struct with some fields left out
+uint64_t digest_without(const GVal& s, std::initializer_list<const char*> skip) {
+  if (s.kind != GVal::Struct) return digest(s);
+  GVal c = s;
+  for (const char* n : skip) c.erase(n);
+  return c.kv.empty() ? 0 : digest(c);
+}
+
+void pack_quantity(const GVal& q, bool present, uint64_t* s3) {
+  s3[0] = s3[1] = s3[2] = 0;
+  if (!present) return;
+  const GVal& i = field(q, "i");
+  s3[0] = (uint64_t)field(i, "value").i;
+  const uint32_t scale = (uint32_t)(int32_t)field(i, "scale").i;
+  const std::string fmt = field(q, "Format").kind == GVal::Str ? field(q, "Format").s : std::string();
+  uint64_t code = fmt.empty() ? 0 : fmt == "DecimalSI" ? 1 : fmt == "BinarySI" ? 2 : fmt == "DecimalExponent" ? 3 : 255;
+  s3[1] = (uint64_t)scale | (code << 32) | (1ull << 40);
+  // everything else the struct holds: cached string, inf.Dec, odd formats, extra fields
+  GVal rest = q.kind == GVal::Struct ? q : GVal::strct();
+  rest.erase("i");
+  if (code != 255) rest.erase("Format");
+  s3[2] = rest.kv.empty() ? 0 : digest(rest);
+}
+
+constexpr int kPodLevel = 16, kVolSlots = 3, kMaxVol = 8, kContBase = kPodLevel + kVolSlots * kMaxVol,
+              kContSlots = 76, kMaxCont = 2;
+constexpr int kMaxPorts = 2, kMaxEnv = 14, kMaxMounts = 10;
+static_assert(kContBase + kContSlots * kMaxCont == (int)NBG_POD_SLOTS, "PodSpec tile layout");
+
+void pack_container(const GVal& c, uint64_t* s) {
+  s[0] = str_of(c, "name");
+  s[1] = str_of(c, "image");
+  s[2] = str_of(c, "workingDir");
+  s[3] = str_of(c, "imagePullPolicy");
+  const GVal &cmd = field(c, "command"), &args = field(c, "args"), &ports = field(c, "ports"),
+             &env = field(c, "env"), &mounts = field(c, "volumeMounts"), &env_from = field(c, "envFrom");
+  s[4] = cmd.is_null() ? 0 : digest(cmd);
+  s[5] = args.is_null() ? 0 : digest(args);
+  s[6] = count_tag(ports) | (count_tag(env) << 16) | (count_tag(mounts) << 32) | (count_tag(env_from) << 48);
+  const GVal& sc = field(c, "securityContext");
+  s[7] = sc.is_null() ? 0 : digest(sc);
+  const GVal &lp = field(c, "livenessProbe"), &rp = field(c, "readinessProbe");
+  s[8] = lp.is_null() ? 0 : digest(lp);
+  s[9] = rp.is_null() ? 0 : digest(rp);
+  s[10] = env_from.is_null() ? 0 : digest(env_from);
+
+  uint64_t* p = s + 12;
+  for (int k = 0; k < kMaxPorts; ++k, p += 2) {
+    p[0] = p[1] = 0;
+    if (ports.kind == GVal::List && (size_t)k < ports.items.size()) {
+      p[0] = str_of(ports.items[k], "name");
+      p[1] = digest_without(ports.items[k], {"name"});
+    }
+  }
+  for (int k = 0; k < kMaxEnv; ++k, p += 2) {
+    p[0] = p[1] = 0;
+    if (env.kind == GVal::List && (size_t)k < env.items.size()) {
+      const GVal& e = env.items[k];
+      p[0] = str_of(e, "name");
+      bool plain = e.kind == GVal::Struct;
+      if (plain) for (const auto& f : e.kv) if (f.first != "name" && f.first != "value") plain = false;
+      p[1] = plain ? str_of(e, "value") : nbg_combine(K_MARK, digest_without(e, {"name"}));
+    }
+  }
+  const GVal& res = field(c, "resources");
+  const GVal &lim = field(res, "limits"), &req = field(res, "requests");
+  static const char* rn[2] = {"cpu", "memory"};
+  for (int side = 0; side < 2; ++side) {
+    const GVal& m = side == 0 ? lim : req;
+    for (int r = 0; r < 2; ++r, p += 3) {
+      const GVal* q = m.kind == GVal::Map ? m.find(rn[r]) : nullptr;
+      pack_quantity(q ? *q : kZero, q != nullptr, p);
+    }
+  }
+  for (int k = 0; k < kMaxMounts; ++k, p += 2) {
+    p[0] = p[1] = 0;
+    if (mounts.kind == GVal::List && (size_t)k < mounts.items.size()) {
+      p[0] = str_of(mounts.items[k], "name");
+      p[1] = digest_without(mounts.items[k], {"name"});
+    }
+  }
+  // residual: the container minus everything slotted above; nil-ness and
+  // emptiness of the resource maps survive because only the entries are erased
+  GVal rest = c.kind == GVal::Struct ? c : GVal::strct();
+  for (const char* n : {"name", "image", "workingDir", "imagePullPolicy", "command", "args", "securityContext",
+                        "livenessProbe", "readinessProbe", "envFrom", "ports", "env", "volumeMounts"})
+    rest.erase(n);
+  if (GVal* r = rest.find("resources")) {
+    for (const char* side : {"limits", "requests"})
+      if (GVal* m = r->find(side))
+        if (m->kind == GVal::Map) for (const char* n : rn) m->erase(n);
+  }
+  uint64_t h = rest.kv.empty() ? 0 : digest(rest);
+  const uint64_t o1 = overflow_digest(ports, kMaxPorts), o2 = overflow_digest(env, kMaxEnv),
+                 o3 = overflow_digest(mounts, kMaxMounts);
+  if (o1 | o2 | o3) h = nbg_combine(nbg_combine(nbg_combine(h, o1), o2), o3);
+  s[11] = h;
+}
+
+}  // namespace
+
+uint64_t digest(const GVal& v) {
+  switch (v.kind) {
+    case GVal::Null: return K_NULL;
+    case GVal::Bool: return nbg_combine(K_BOOL, (uint64_t)v.i);
+    case GVal::Int: return nbg_combine(K_INT, (uint64_t)v.i);
+    case GVal::Float: {
+      double f = v.f == 0.0 ? 0.0 : v.f;
+      uint64_t b; memcpy(&b, &f, 8);
+      return nbg_combine(K_FLOAT, b);
+    }
+    case GVal::Str: return nbg_combine(K_STR, hash_str(v.s));
+    case GVal::List: {
+      uint64_t h = nbg_combine(K_LIST, v.items.size());
+      for (const auto& e : v.items) h = nbg_combine(h, digest(e));
+      return h;
+    }
+    case GVal::Map: case GVal::Struct: {
+      uint64_t h = v.kind == GVal::Map ? K_MAP : K_STRUCT;
+      size_t n = 0;
+      for (const auto& e : v.kv) {
+        if (v.kind == GVal::Struct && e.second.is_zero()) continue;
+        h = nbg_combine(nbg_combine(h, hash_str(e.first)), digest(e.second));
+        ++n;
+      }
+      return nbg_combine(h, n);
+    }
+    case GVal::Ptr: return nbg_combine(K_PTR, v.items.empty() ? K_MARK : digest(v.items[0]));
+  }
+  return 0;
+}
+
+uint64_t digest_string_map(const GVal& m) { return m.kind == GVal::Map ? digest(m) : K_NULL; }
+
+void pack_kvmap(const GVal& m, std::vector<nbg_kv>* out) {
+  if (m.kind != GVal::Map) return;
+  const size_t at = out->size();
+  for (const auto& e : m.kv) {
+    nbg_kv kv;
+    kv.key = hash_str(e.first);
+    kv.val = e.second.kind == GVal::Str ? hash_str(e.second.s) : nbg_combine(K_MARK, digest(e.second));
+    out->push_back(kv);
+  }
+  std::sort(out->begin() + at, out->end(), [](const nbg_kv& a, const nbg_kv& b) { return a.key < b.key; });
+}
+
+void pack_podspec(const GVal& pod, uint64_t* s) {
+  memset(s, 0, NBG_POD_SLOTS * sizeof(uint64_t));
+  s[0] = str_of(pod, "serviceAccountName");
+  s[1] = str_of(pod, "serviceAccount");
+  s[2] = str_of(pod, "restartPolicy");
+  s[3] = str_of(pod, "dnsPolicy");
+  const GVal& tg = field(pod, "terminationGracePeriodSeconds");
+  s[4] = tg.kind == GVal::Ptr && !tg.items.empty() ? (uint64_t)tg.items[0].i : 0;
+  s[5] = str_of(pod, "schedulerName");
+  s[6] = str_of(pod, "nodeName");
+  const GVal& scp = field(pod, "securityContext");
+  const GVal& sc = scp.kind == GVal::Ptr && !scp.items.empty() ? scp.items[0] : kZero;
+  const GVal &fsg = field(sc, "fsGroup"), &rau = field(sc, "runAsUser");
+  s[7] = fsg.kind == GVal::Ptr && !fsg.items.empty() ? (uint64_t)fsg.items[0].i : 0;
+  s[8] = rau.kind == GVal::Ptr && !rau.items.empty() ? (uint64_t)rau.items[0].i : 0;
+  s[9] = digest_without(sc, {"fsGroup", "runAsUser"});
+  const GVal &nsel = field(pod, "nodeSelector"), &tol = field(pod, "tolerations"), &aff = field(pod, "affinity"),
+             &ips = field(pod, "imagePullSecrets"), &vols = field(pod, "volumes"), &conts = field(pod, "containers");
+  s[10] = nsel.is_null() ? 0 : digest(nsel);
+  s[11] = tol.is_null() ? 0 : digest(tol);
+  s[12] = aff.is_null() ? 0 : digest(aff);
+  s[13] = ips.is_null() ? 0 : digest(ips);
+  s[14] = (uint64_t)(tg.kind == GVal::Ptr) | ((uint64_t)(scp.kind == GVal::Ptr) << 1) |
+          ((uint64_t)(fsg.kind == GVal::Ptr) << 2) | ((uint64_t)(rau.kind == GVal::Ptr) << 3) |
+          (count_tag(vols) << 16) | (count_tag(conts) << 32);
+
+  uint64_t* p = s + kPodLevel;
+  for (int k = 0; k < kMaxVol; ++k, p += kVolSlots) {
+    if (vols.kind != GVal::List || (size_t)k >= vols.items.size()) continue;
+    const GVal& v = vols.items[k];
+    p[0] = str_of(v, "name");
+    // the usual sources: kind + the one string that names the backing object
+    static const struct { const char* src; const char* ref; } known[] = {
+        {"persistentVolumeClaim", "claimName"}, {"configMap", "name"}, {"secret", "secretName"}, {"emptyDir", "medium"}};
+    GVal rest = v.kind == GVal::Struct ? v : GVal::strct();
+    rest.erase("name");
+    for (const auto& kn : known) {
+      GVal* src = rest.find(kn.src);
+      if (!src || src->kind != GVal::Ptr || src->items.empty() || src->items[0].kind != GVal::Struct) continue;
+      p[1] = nbg_combine(hash_str(kn.src), str_of(src->items[0], kn.ref));
+      src->items[0].erase(kn.ref);   // the pointer itself stays: &T{} != nil
+      break;
+    }
+    p[2] = rest.kv.empty() ? 0 : digest(rest);
+  }
+  for (int k = 0; k < kMaxCont; ++k)
+    if (conts.kind == GVal::List && (size_t)k < conts.items.size())
+      pack_container(conts.items[k], s + kContBase + k * kContSlots);
+
+  GVal rest = pod.kind == GVal::Struct ? pod : GVal::strct();
+  for (const char* n : {"serviceAccountName", "serviceAccount", "restartPolicy", "dnsPolicy",
+                        "terminationGracePeriodSeconds", "schedulerName", "nodeName", "securityContext",
+                        "nodeSelector", "tolerations", "affinity", "imagePullSecrets", "volumes", "containers"})
+    rest.erase(n);
+  uint64_t h = rest.kv.empty() ? 0 : digest(rest);
+  const uint64_t o1 = overflow_digest(vols, kMaxVol), o2 = overflow_digest(conts, kMaxCont);
+  if (o1 | o2) h = nbg_combine(nbg_combine(h, o1), o2);
+  s[15] = h;
+}
+
+void pack_service_ports(const GVal& ports, uint64_t* s) {
+  memset(s, 0, NBG_SVC_SLOTS * sizeof(uint64_t));
+  for (int k = 0; k < 2; ++k) {
+    if (ports.kind != GVal::List || (size_t)k >= ports.items.size()) continue;
+    const GVal& sp = ports.items[k];
+    uint64_t* p = s + k * 6;
+    p[0] = str_of(sp, "name");
+    p[1] = str_of(sp, "protocol");
+    const GVal& ap = field(sp, "appProtocol");
+    p[2] = ap.kind == GVal::Ptr ? nbg_combine(K_PTR, ap.items.empty() ? 0 : hash_str(ap.items[0].s)) : 0;
+    p[3] = (uint64_t)(uint32_t)field(sp, "port").i | ((uint64_t)(uint32_t)field(sp, "nodePort").i << 32);
+    const GVal& tp = field(sp, "targetPort");
+    p[4] = (uint64_t)(uint32_t)field(tp, "IntVal").i | ((uint64_t)field(tp, "Type").i << 32);
+    GVal rest = sp.kind == GVal::Struct ? sp : GVal::strct();
+    for (const char* n : {"name", "protocol", "appProtocol", "port", "nodePort"}) rest.erase(n);
+    if (GVal* t = rest.find("targetPort")) { t->erase("IntVal"); t->erase("Type"); }
+    rest.canon();
+    p[5] = rest.kv.empty() ? 0 : digest(rest);   // targetPort.StrVal and anything unexpected
+  }
+  s[12] = ports.kind == GVal::List ? ports.items.size() : 0xFFFFFFFFull;
+  s[13] = overflow_digest(ports, 2);
+}
+
+bool pack_vs_spec(const GVal& obj, uint64_t* s, std::vector<nbg_kv>* headers, bool* headers_nil) {
+  memset(s, 0, NBG_VS_SLOTS * sizeof(uint64_t));
+  *headers_nil = true;
+  // unstructured.NestedMap(obj, "spec"): found only if present, ok only if a map (COMMON:200,208)
+  const GVal* specp = obj.kind == GVal::Map ? obj.find("spec") : nullptr;
+  if (!specp || specp->kind != GVal::Map) return false;
+  GVal spec = *specp;  // leaves taken out below are replaced by a marker, so shape is kept
+
+  auto take_str = [](GVal* holder, uint64_t* slot) {
+    if (holder && holder->kind == GVal::Str) { *slot = hash_str(holder->s); *holder = marker(); }
+  };
+  auto first = [](GVal* l) -> GVal* { return (l && l->kind == GVal::List && !l->items.empty()) ? &l->items[0] : nullptr; };
+  auto child = [](GVal* m, const char* k) -> GVal* { return (m && m->kind == GVal::Map) ? m->find(k) : nullptr; };
+
+  take_str(first(child(&spec, "hosts")), &s[0]);
+  take_str(first(child(&spec, "gateways")), &s[1]);
+  GVal* http0 = first(child(&spec, "http"));
+  take_str(child(child(first(child(http0, "match")), "uri"), "prefix"), &s[2]);
+  take_str(child(child(http0, "rewrite"), "uri"), &s[3]);
+  GVal* dest = child(first(child(http0, "route")), "destination");
+  take_str(child(dest, "host"), &s[4]);
+  if (GVal* num = child(child(dest, "port"), "number")) {
+    if (num->kind == GVal::Int) { s[5] = (uint64_t)num->i; s[6] = 1; *num = marker(); }
+    else if (num->kind == GVal::Float) { memcpy(&s[5], &num->f, 8); if (num->f == 0.0) s[5] = 0; s[6] = 2; *num = marker(); }
+  }
+  if (GVal* set = child(child(child(http0, "headers"), "request"), "set")) {
+    bool all_str = set->kind == GVal::Map;
+    if (all_str) for (const auto& e : set->kv) if (e.second.kind != GVal::Str) all_str = false;
+    if (all_str) { pack_kvmap(*set, headers); *headers_nil = false; *set = marker(); }
+  }
+  s[7] = digest(spec);
+  return true;
+}
+
+}  // namespace nbh

@@ -1,0 +1,118 @@
+"""Batches resident in HBM.  torch is used here for what it is good at — device
+memory and streams; the compute is the nbg_*_device entry points of the C ABI,
+launched on torch's current stream so torch.cuda.Event brackets them."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native as N
+from . import host
+
+
+def _to_dev(a, device, tile=1, add=None):
+    t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).copy()).to(f"cuda:{device}")
+    if tile > 1:
+        t = t.repeat(tile)
+    return t
+
+
+class DeviceBatch:
+    """Uploads a host batch (optionally tiled `tile` times to build a larger fleet out of a
+    base fleet) and launches the matching kernel with device pointers."""
+
+    def __init__(self):
+        self.tensors = {}
+
+    @classmethod
+    def from_host(cls, batch, device=0, tile=1):
+        self = cls()
+        self.device, self.kind = device, type(batch).__name__
+        arrays = batch.arrays()
+        n0 = len(batch)
+        self.n = n0 * tile
+        self.in_bytes = 0
+        for name, a in arrays.items():
+            if name.endswith(".off") or name in ("k_off", "t_off"):
+                # CSR offsets of tile k are the base offsets shifted by k * (#entries)
+                base = a.astype(np.int64)
+                total = int(base[-1])
+                parts = [base[:-1] + k * total for k in range(tile)] + [np.array([tile * total])]
+                off = np.concatenate(parts)
+                assert off[-1] < 2 ** 32
+                t = torch.from_numpy(off.astype(np.uint32).view(np.uint8).copy()).to(f"cuda:{device}")
+            else:
+                t = _to_dev(a, device, tile)
+            self.tensors[name] = t
+            self.in_bytes += t.numel()
+        words = (self.n + 63) // 64
+        dev = f"cuda:{device}"
+        if self.kind == "CullBatch":
+            self.outs = [torch.empty(self.n, dtype=torch.uint8, device=dev), torch.empty(self.n * 4, dtype=torch.uint8, device=dev),
+                         torch.empty(words * 8, dtype=torch.uint8, device=dev), torch.empty(words * 8, dtype=torch.uint8, device=dev)]
+        else:
+            self.outs = [torch.empty(self.n, dtype=torch.uint8, device=dev), torch.empty(words * 8, dtype=torch.uint8, device=dev)]
+        self.out_bytes = sum(o.numel() for o in self.outs)
+        self._struct = self._build_struct()
+        return self
+
+    @property
+    def algorithmic_bytes(self):
+        return self.in_bytes + self.out_bytes
+
+    def _p(self, name, ctype):
+        return C.cast(self.tensors[name].data_ptr(), C.POINTER(ctype))
+
+    def _kv(self, prefix):
+        m = N.nbg_kvmap()
+        m.off = self._p(prefix + ".off", C.c_uint32)
+        m.ent = C.cast(self.tensors[prefix + ".ent"].data_ptr(), C.POINTER(N.nbg_kv))
+        return m
+
+    def _build_struct(self):
+        k = self.kind
+        if k == "StsBatch":
+            s = N.nbg_sts_batch()
+            s.replicas_from, s.replicas_to = self._p("replicas_from", C.c_int32), self._p("replicas_to", C.c_int32)
+            s.tmpl_from, s.tmpl_to = self._p("tmpl_from", C.c_uint64), self._p("tmpl_to", C.c_uint64)
+            s.pod_from, s.pod_to = self._p("pod_from", C.c_uint64), self._p("pod_to", C.c_uint64)
+            for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
+                setattr(s, f, self._kv(f))
+        elif k == "SvcBatch":
+            s = N.nbg_svc_batch()
+            s.flags = self._p("flags", C.c_uint8)
+            s.ports_from, s.ports_to = self._p("ports_from", C.c_uint64), self._p("ports_to", C.c_uint64)
+            for f in ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"):
+                setattr(s, f, self._kv(f))
+        elif k == "VsBatch":
+            s = N.nbg_vs_batch()
+            s.flags = self._p("flags", C.c_uint8)
+            s.spec_from, s.spec_to = self._p("spec_from", C.c_uint64), self._p("spec_to", C.c_uint64)
+            s.hdr_from, s.hdr_to = self._kv("hdr_from"), self._kv("hdr_to")
+        else:
+            s = N.nbg_cull_batch()
+            for f, ct in (("k_off", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32), ("t_off", C.c_uint32),
+                          ("t_sec", C.c_int64), ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32),
+                          ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)):
+                setattr(s, f, self._p(f, ct))
+        return s
+
+    def run(self, ctx, now=None, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE, stream=None):
+        """Enqueue the kernel (asynchronous).  Returns the device output tensors."""
+        lib = N.nbg()
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        o = [C.c_void_p(t.data_ptr()) for t in self.outs]
+        if self.kind == "CullBatch":
+            now = now or (host.NOW_SEC, host.NOW_NSEC)
+            p = N.nbg_cull_params(now[0], now[1], cull_idle_min, check_period_min, mode)
+            rc = lib.nbg_cull_device(ctx.handle, 0, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
+                                     C.c_void_p(stream))
+        else:
+            fn = {"StsBatch": lib.nbg_diff_sts_device, "SvcBatch": lib.nbg_diff_svc_device,
+                  "VsBatch": lib.nbg_diff_vs_device}[self.kind]
+            rc = fn(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
+        if rc != N.NBG_OK:
+            from .engine import NbgError
+            raise NbgError(rc, "nbg_*_device")
+        return self.outs

@@ -1,0 +1,113 @@
+"""Thin Python face of the C ABI (include/nbgraft.h).  Every method ends in a
+CUDA kernel of libnbgraft.so; nothing here computes a predicate itself."""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+
+class NbgError(RuntimeError):
+    def __init__(self, status, where):
+        lib = N.nbg()
+        msg = lib.nbg_strerror(status).decode()
+        cuda = lib.nbg_last_cuda_error().decode()
+        super().__init__(f"{where}: {msg} (status {status})" + (f" [{cuda}]" if cuda and status == N.NBG_E_CUDA else ""))
+        self.status = status
+
+
+def _check(status, where):
+    if status != N.NBG_OK:
+        raise NbgError(status, where)
+
+
+def hash64(s):
+    b = s.encode() if isinstance(s, str) else bytes(s)
+    return N.nbg().nbg_hash64(b, len(b))
+
+
+def shard_of(ns_hash, n_shards):
+    return N.nbg().nbg_shard_of(ns_hash, n_shards)
+
+
+class Context:
+    """nbg_ctx: one or more CUDA devices.  Raises NbgError(NBG_E_NODEVICE) when
+    there is no GPU — there is deliberately no CPU fallback."""
+
+    def __init__(self, devices=None):
+        self._lib = N.nbg()
+        self._h = C.c_void_p()
+        if devices is None:
+            rc = self._lib.nbg_init(None, 0, C.byref(self._h))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = self._lib.nbg_init(arr, len(devices), C.byref(self._h))
+        _check(rc, "nbg_init")
+
+    def close(self):
+        if self._h:
+            self._lib.nbg_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def launch_count(self):
+        return int(self._lib.nbg_launch_count(self._h))
+
+    # ---- host-buffer calls (H2D + kernel + D2H inside) -------------------
+    def _diff(self, fn, batch, allow_nil=False):
+        view = batch.view
+        n = batch.n
+        reason = np.zeros(n, dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        rc = fn(self._h, C.byref(view), n, reason.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+        if not (allow_nil and rc == N.NBG_E_NILREPLICAS):
+            _check(rc, fn.__name__)
+        return reason, bitmap
+
+    def diff_sts(self, batch, allow_nil=False):
+        """Batched CopyStatefulSetFields (COMMON:107-134) + NBCTL:188-194."""
+        return self._diff(self._lib.nbg_diff_sts, batch, allow_nil)
+
+    def diff_svc(self, batch):
+        """Batched CopyServiceFields (COMMON:166-195)."""
+        return self._diff(self._lib.nbg_diff_svc, batch)
+
+    def diff_vs(self, batch):
+        """Batched CopyVirtualService (COMMON:199-219)."""
+        return self._diff(self._lib.nbg_diff_vs, batch)
+
+    def cull(self, batch, now_sec, now_nsec, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE):
+        """Batched culler decision (CULL:86-241,315-428)."""
+        view = batch.view
+        n = batch.n
+        p = N.nbg_cull_params(now_sec, now_nsec, cull_idle_min, check_period_min, mode)
+        action = np.zeros(n, dtype=np.uint8)
+        argmax = np.zeros(n, dtype=np.uint32)
+        words = (n + 63) // 64
+        cull_bm = np.zeros(words, dtype=np.uint64)
+        period_bm = np.zeros(words, dtype=np.uint64)
+        _check(self._lib.nbg_cull(self._h, C.byref(view), n, C.byref(p), action.ctypes.data_as(C.c_void_p),
+                                  argmax.ctypes.data_as(C.c_void_p), cull_bm.ctypes.data_as(C.c_void_p),
+                                  period_bm.ctypes.data_as(C.c_void_p)), "nbg_cull")
+        return action, argmax, cull_bm, period_bm
+
+
+def bitmap_to_bools(bitmap, n):
+    """uint64 words -> bool[n] (bit i of word i//64)."""
+    bits = np.unpackbits(bitmap.view(np.uint8), bitorder="little")
+    return bits[:n].astype(bool)

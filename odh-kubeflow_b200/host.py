@@ -1,0 +1,385 @@
+"""Host side of the graft: objects, desired-object builders, packed batches and
+synthetic fleets, all implemented in libnbgraft_host.so (C++).
+
+Mirrors what the reference does in Go before its predicates run: decode objects,
+build the desired StatefulSet/Service/VirtualService (NBCTL:433-658) and — new in
+this build — flatten desired/live pairs into the structure-of-arrays batches of
+include/nbgraft.h.
+"""
+import ctypes as C
+import json
+
+import numpy as np
+
+from . import _native as N
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def _err():
+    return C.create_string_buffer(512)
+
+
+class Obj:
+    """One decoded object (a Go value tree held by the native library)."""
+
+    def __init__(self, handle):
+        self._h = C.c_void_p(handle)
+
+    @classmethod
+    def from_json(cls, type_name, obj):
+        text = obj if isinstance(obj, str) else json.dumps(obj)
+        out, err = C.c_void_p(), _err()
+        if N.nbh().nbh_obj_from_json(type_name.encode(), text.encode(), C.byref(out), err, len(err)) != 0:
+            raise HostError(err.value.decode())
+        return cls(out.value)
+
+    def to_python(self):
+        p = N.nbh().nbh_obj_to_json(self._h)
+        try:
+            return json.loads(C.string_at(p).decode())
+        finally:
+            N.nbh().nbh_str_free(p)
+
+    def digest(self):
+        return N.nbh().nbh_obj_digest(self._h)
+
+    def get(self, dotted_path):
+        """Copy of the sub-object at e.g. "spec.template.spec" (None if absent)."""
+        out = C.c_void_p()
+        if N.nbh().nbh_obj_get(self._h, dotted_path.encode(), C.byref(out)) != 0:
+            return None
+        return Obj(out.value)
+
+    def __del__(self):
+        try:
+            if self._h:
+                N.nbh().nbh_obj_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def Notebook(obj):
+    return Obj.from_json("Notebook", obj)
+
+
+def StatefulSet(obj):
+    return Obj.from_json("StatefulSet", obj)
+
+
+def Service(obj):
+    return Obj.from_json("Service", obj)
+
+
+def Unstructured(obj):
+    return Obj.from_json("Unstructured", obj)
+
+
+def _env(env):
+    if env is None:
+        return None
+    e = N.nbh_env()
+    e.add_fsgroup = 1 if env.get("ADD_FSGROUP", "true") == "true" else 0
+    e.cluster_domain = env["CLUSTER_DOMAIN"].encode() if "CLUSTER_DOMAIN" in env else None
+    e.istio_host = env.get("ISTIO_HOST", "").encode()
+    e.istio_gateway = env.get("ISTIO_GATEWAY", "").encode()
+    return C.byref(e)
+
+
+def generate_statefulset(notebook, env=None):
+    """generateStatefulSet (NBCTL:433-523). `env` = dict of the process env vars it reads."""
+    out, err = C.c_void_p(), _err()
+    if N.nbh().nbh_generate_statefulset(notebook._h, _env(env), C.byref(out), err, len(err)) != 0:
+        raise HostError("panic: " + err.value.decode())
+    return Obj(out.value)
+
+
+def generate_service(notebook):
+    """generateService (NBCTL:525-552)."""
+    out, err = C.c_void_p(), _err()
+    if N.nbh().nbh_generate_service(notebook._h, C.byref(out), err, len(err)) != 0:
+        raise HostError("panic: " + err.value.decode())
+    return Obj(out.value)
+
+
+def generate_virtualservice(notebook, env=None):
+    """generateVirtualService (NBCTL:558-658)."""
+    out, err = C.c_void_p(), _err()
+    if N.nbh().nbh_generate_virtualservice(notebook._h, _env(env), C.byref(out), err, len(err)) != 0:
+        raise HostError(err.value.decode())
+    return Obj(out.value)
+
+
+ODH_LOCK, ODH_CA_BUNDLE, ODH_RUNTIME_IMAGES, ODH_ELYRA_SECRET, ODH_RBAC_PROXY = 1, 2, 4, 8, 16
+
+
+def odh_mutate(notebook, flags=2 | 4 | 8 | 16):
+    """ODH mutating-webhook injections (ODHWH:105-114,177-326,666-781), in place."""
+    N.nbh().nbh_odh_mutate(notebook._h, flags)
+    return notebook
+
+
+def _arr(ptr, count, dtype):
+    if count == 0:
+        return np.empty(0, dtype=dtype)
+    ct = {np.uint8: C.c_uint8, np.uint32: C.c_uint32, np.uint64: C.c_uint64, np.int32: C.c_int32,
+          np.int64: C.c_int64}[dtype]
+    return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=(count,))
+
+
+def _kv_arrays(m, n, prefix, out):
+    off = _arr(m.off, n + 1, np.uint32)
+    out[prefix + ".off"] = off
+    cnt = int(off[n]) if n else 0
+    out[prefix + ".ent"] = _arr(m.ent, cnt * 2, np.uint64)
+
+
+class _Batch:
+    """A packed batch owned by the native library.  `.view` is the C struct of
+    include/nbgraft.h, `.arrays()` numpy views of every array it points to."""
+    _new = _free = _add = _view = None
+    _struct = None
+
+    def __init__(self, handle=None):
+        lib = N.nbh()
+        self._h = C.c_void_p(handle if handle is not None else getattr(lib, self._new)())
+        self._keep = []
+
+    def add(self, from_, to):
+        if getattr(N.nbh(), self._add)(self._h, from_._h, to._h) != 0:
+            raise HostError("add failed")
+        return self
+
+    @property
+    def view(self):
+        v = self._struct()
+        self.n = int(getattr(N.nbh(), self._view)(self._h, C.byref(v)))
+        return v
+
+    def __len__(self):
+        self.view
+        return self.n
+
+    def algorithmic_bytes(self):
+        """sum of sizeof(input arrays) + sizeof(output arrays): SURVEY.md 8(d)."""
+        n = len(self)
+        return sum(a.nbytes for a in self.arrays().values()) + self.output_bytes(n)
+
+    def __del__(self):
+        try:
+            if self._h:
+                getattr(N.nbh(), self._free)(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+class StsBatch(_Batch):
+    _new, _free, _add, _view, _struct = "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", N.nbg_sts_batch
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        out["replicas_from"] = _arr(v.replicas_from, n, np.int32)
+        out["replicas_to"] = _arr(v.replicas_to, n, np.int32)
+        out["tmpl_from"] = _arr(v.tmpl_from, n, np.uint64)
+        out["tmpl_to"] = _arr(v.tmpl_to, n, np.uint64)
+        out["pod_from"] = _arr(v.pod_from, n * N.NBG_POD_SLOTS, np.uint64)
+        out["pod_to"] = _arr(v.pod_to, n * N.NBG_POD_SLOTS, np.uint64)
+        for name in ("labels_from", "labels_to", "ann_from", "ann_to"):
+            _kv_arrays(getattr(v, name), n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+
+class SvcBatch(_Batch):
+    _new, _free, _add, _view, _struct = "nbh_svc_new", "nbh_svc_free", "nbh_svc_add", "nbh_svc_view", N.nbg_svc_batch
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        out["flags"] = _arr(v.flags, n, np.uint8)
+        out["ports_from"] = _arr(v.ports_from, n * N.NBG_SVC_SLOTS, np.uint64)
+        out["ports_to"] = _arr(v.ports_to, n * N.NBG_SVC_SLOTS, np.uint64)
+        for name in ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"):
+            _kv_arrays(getattr(v, name), n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+
+class VsBatch(_Batch):
+    _new, _free, _add, _view, _struct = "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", N.nbg_vs_batch
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        out["flags"] = _arr(v.flags, n, np.uint8)
+        out["spec_from"] = _arr(v.spec_from, n * N.NBG_VS_SLOTS, np.uint64)
+        out["spec_to"] = _arr(v.spec_to, n * N.NBG_VS_SLOTS, np.uint64)
+        for name in ("hdr_from", "hdr_to"):
+            _kv_arrays(getattr(v, name), n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+
+class CullBatch(_Batch):
+    _new, _free, _view, _struct = "nbh_cull_new", "nbh_cull_free", "nbh_cull_view", N.nbg_cull_batch
+
+    def add(self, notebook):
+        """notebook: {"annotations": {...}|None, "kernels": [...], "terminals": [...], "pod_missing": bool}"""
+        text = notebook if isinstance(notebook, str) else json.dumps(notebook)
+        err = _err()
+        if N.nbh().nbh_cull_add_json(self._h, text.encode(), err, len(err)) != 0:
+            raise HostError(err.value.decode())
+        return self
+
+    def records(self):
+        k, t = C.c_uint64(), C.c_uint64()
+        N.nbh().nbh_cull_records(self._h, C.byref(k), C.byref(t))
+        return int(k.value), int(t.value)
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        nk, nt = self.records()
+        out["k_off"] = _arr(v.k_off, n + 1, np.uint32)
+        out["k_sec"] = _arr(v.k_sec, nk, np.int64)
+        out["k_nsf"] = _arr(v.k_nsf, nk, np.uint32)
+        out["t_off"] = _arr(v.t_off, n + 1, np.uint32)
+        out["t_sec"] = _arr(v.t_sec, nt, np.int64)
+        out["t_nsf"] = _arr(v.t_nsf, nt, np.uint32)
+        out["ann_sec"] = _arr(v.ann_sec, n, np.int64)
+        out["ann_nsf"] = _arr(v.ann_nsf, n, np.uint32)
+        out["chk_sec"] = _arr(v.chk_sec, n, np.int64)
+        out["chk_nsf"] = _arr(v.chk_nsf, n, np.uint32)
+        out["nb_flags"] = _arr(v.nb_flags, n, np.uint8)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + 4 * n + 2 * ((n + 63) // 64 * 8)
+
+    def new_last_activity(self, i, action, argmax, now_sec, now_offset=0):
+        """The string CULL:386/399/425 would have written for notebook i ('' = unchanged)."""
+        buf = C.create_string_buffer(64)
+        r = N.nbh().nbh_cull_new_last_activity(self._h, i, int(action), int(argmax), now_sec, now_offset, buf, len(buf))
+        if r < 0:
+            raise HostError("bad argmax for notebook %d" % i)
+        return buf.value.decode()
+
+
+def parse_rfc3339(s):
+    """time.Parse(time.RFC3339, s) -> (sec, nsec, offset) or None."""
+    sec, nsec, off = C.c_int64(), C.c_int32(), C.c_int32()
+    if N.nbh().nbh_parse_rfc3339(s.encode(), C.byref(sec), C.byref(nsec), C.byref(off)):
+        return sec.value, nsec.value, off.value
+    return None
+
+
+def format_rfc3339(sec, offset=0):
+    buf = C.create_string_buffer(64)
+    N.nbh().nbh_format_rfc3339(sec, offset, buf, len(buf))
+    return buf.value.decode()
+
+
+FLEET_KUBEFLOW, FLEET_ODH = 2, 4
+SEED_BASE = 0x6E62677261667400  # seed = base + config number
+
+
+class Fleet:
+    """Seeded synthetic Notebook fleet (desired/live StatefulSet, Service, VirtualService pairs)."""
+    WHICH = {"notebook": 0, "sts_from": 1, "sts_to": 2, "svc_from": 3, "svc_to": 4, "vs_from": 5, "vs_to": 6}
+
+    def __init__(self, kind, seed, n, n_namespaces):
+        self.kind, self.seed, self.n, self.n_namespaces = kind, seed, n, n_namespaces
+        self._h = C.c_void_p(N.nbh().nbh_fleet_new(kind, seed, n, n_namespaces))
+        if not self._h:
+            raise HostError("bad fleet kind")
+
+    def get(self, i, which):
+        out = C.c_void_p()
+        if N.nbh().nbh_fleet_get(self._h, i, self.WHICH[which], C.byref(out)) != 0:
+            raise HostError("fleet_get")
+        return Obj(out.value)
+
+    def drift_class(self, i):
+        return N.nbh().nbh_fleet_drift_class(self._h, i)
+
+    def ns_hash(self, i):
+        return N.nbh().nbh_fleet_ns_hash(self._h, i)
+
+    def pack(self, i0=0, m=None, idx=None, sts=True, svc=True, vs=True):
+        """Pack objects [i0, i0+m) (or the explicit index list) on all host threads."""
+        if idx is not None:
+            idx = np.ascontiguousarray(idx, dtype=np.uint64)
+            m, ip = len(idx), idx.ctypes.data_as(N.u64p)
+        else:
+            m, ip = (self.n - i0 if m is None else m), None
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        if N.nbh().nbh_fleet_pack(self._h, ip, i0, m, C.byref(a) if sts else None, C.byref(b) if svc else None,
+                                  C.byref(c) if vs else None) != 0:
+            raise HostError("fleet_pack")
+        return (StsBatch(a.value) if sts else None, SvcBatch(b.value) if svc else None,
+                VsBatch(c.value) if vs else None)
+
+    def shard_indices(self, n_shards):
+        """Bucket object indices by nbg_shard_of(hash(namespace)) — SURVEY.md 8(e)."""
+        lib = N.nbg()
+        shard = np.fromiter((lib.nbg_shard_of(self.ns_hash(i), n_shards) for i in range(self.n)), dtype=np.uint32,
+                            count=self.n)
+        return [np.nonzero(shard == s)[0].astype(np.uint64) for s in range(n_shards)]
+
+    def __del__(self):
+        try:
+            if self._h:
+                N.nbh().nbh_fleet_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+NOW_SEC, NOW_NSEC = 1767225600, 123456789  # 2026-01-01T00:00:00.123456789Z
+
+
+class CullFleet:
+    def __init__(self, seed, n, now_sec=NOW_SEC, now_nsec=NOW_NSEC, mean_kernels=4.0):
+        self.seed, self.n, self.now_sec, self.now_nsec = seed, n, now_sec, now_nsec
+        self._h = C.c_void_p(N.nbh().nbh_cullfleet_new(seed, n, now_sec, now_nsec, mean_kernels))
+
+    def json(self, i):
+        p = N.nbh().nbh_cullfleet_json(self._h, i)
+        try:
+            return C.string_at(p).decode()
+        finally:
+            N.nbh().nbh_str_free(p)
+
+    def pack(self, i0=0, m=None, idx=None):
+        if idx is not None:
+            idx = np.ascontiguousarray(idx, dtype=np.uint64)
+            m, ip = len(idx), idx.ctypes.data_as(N.u64p)
+        else:
+            m, ip = (self.n - i0 if m is None else m), None
+        out = C.c_void_p()
+        if N.nbh().nbh_cullfleet_pack(self._h, ip, i0, m, C.byref(out)) != 0:
+            raise HostError("cullfleet_pack")
+        return CullBatch(out.value)
+
+    def __del__(self):
+        try:
+            if self._h:
+                N.nbh().nbh_cullfleet_free(self._h)
+                self._h = None
+        except Exception:
+            pass

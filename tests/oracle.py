@@ -1,0 +1,158 @@
+"""ctypes binding of oracle/_build/liboracle.so — the CPU checker (test
+infrastructure: only tests/, smoke() and bench.py's CPU legs import this)."""
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pkg = importlib.import_module("odh-kubeflow_b200")
+N = pkg._native
+host = pkg.host
+
+_lib = None
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle")], check=True)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        vp, cp = C.c_void_p, C.c_char_p
+        L.orc_deep_equal.argtypes = [vp, vp]
+        L.orc_strict_equal.argtypes = [vp, vp]
+        L.orc_copy_statefulset_fields.argtypes = [vp, vp, C.c_int]
+        L.orc_copy_service_fields.argtypes = [vp, vp]
+        L.orc_copy_virtualservice.argtypes = [vp, vp]
+        L.orc_bench_pairs.argtypes = [C.c_int, C.POINTER(vp), C.POINTER(vp), C.c_uint64, C.c_int, vp]
+        L.orc_bench_pairs.restype = C.c_double
+        L.orc_parse_rfc3339.argtypes = [cp, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.orc_format_rfc3339.argtypes = [C.c_int64, C.c_int32, cp, C.c_size_t]
+        L.orc_all_kernels_are_idle.argtypes = [cp]
+        L.orc_stop_annotation_is_set.argtypes = [cp]
+        L.orc_notebook_is_idle.argtypes = [cp, C.c_int64, C.c_int32, C.c_int]
+        L.orc_culling_check_period_has_passed.argtypes = [cp, C.c_int64, C.c_int32, C.c_int]
+        L.orc_cull.argtypes = [cp, C.c_int64, C.c_int32, C.c_int32, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint32),
+                               cp, C.c_size_t]
+        L.orc_bench_cull.argtypes = [C.POINTER(cp), C.c_uint64, C.c_int64, C.c_int32, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, vp, vp]
+        L.orc_bench_cull.restype = C.c_double
+        for name, bt in (("orc2_diff_sts", N.nbg_sts_batch), ("orc2_diff_svc", N.nbg_svc_batch),
+                         ("orc2_diff_vs", N.nbg_vs_batch)):
+            f = getattr(L, name)
+            f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
+            f.restype = C.c_double
+        L.orc2_cull.argtypes = [C.POINTER(N.nbg_cull_batch), C.c_uint64, C.POINTER(N.nbg_cull_params), C.c_int, vp, vp,
+                                vp, vp]
+        L.orc2_cull.restype = C.c_double
+        _lib = L
+    return _lib
+
+
+# ---- L1: semantic oracle on objects -----------------------------------------
+def deep_equal(a, b):
+    return bool(lib().orc_deep_equal(a._h, b._h))
+
+
+def copy_statefulset_fields(from_, to, prestep=1):
+    """returns reason bits (NBG_STS_*); mutates `to` (a host.Obj) like the Go code."""
+    return lib().orc_copy_statefulset_fields(from_._h, to._h, prestep)
+
+
+def copy_service_fields(from_, to):
+    return lib().orc_copy_service_fields(from_._h, to._h)
+
+
+def copy_virtualservice(from_, to):
+    return lib().orc_copy_virtualservice(from_._h, to._h)
+
+
+def parse_rfc3339(s):
+    sec, nsec, off = C.c_int64(), C.c_int32(), C.c_int32()
+    if lib().orc_parse_rfc3339(s.encode(), C.byref(sec), C.byref(nsec), C.byref(off)):
+        return sec.value, nsec.value, off.value
+    return None
+
+
+def format_rfc3339(sec, off=0):
+    buf = C.create_string_buffer(64)
+    lib().orc_format_rfc3339(sec, off, buf, len(buf))
+    return buf.value.decode()
+
+
+def _j(nb):
+    return (nb if isinstance(nb, str) else json.dumps(nb)).encode()
+
+
+def all_kernels_are_idle(kernels):
+    return bool(lib().orc_all_kernels_are_idle(_j({"kernels": kernels})))
+
+
+def stop_annotation_is_set(meta):
+    return bool(lib().orc_stop_annotation_is_set(_j({"annotations": (meta or {}).get("annotations")})))
+
+
+def notebook_is_idle(meta, now, cull_idle_min):
+    return bool(lib().orc_notebook_is_idle(_j({"annotations": (meta or {}).get("annotations")}), now[0], now[1],
+                                           cull_idle_min))
+
+
+def culling_check_period_has_passed(meta, now, period_min):
+    return bool(lib().orc_culling_check_period_has_passed(_j({"annotations": (meta or {}).get("annotations")}),
+                                                          now[0], now[1], period_min))
+
+
+def cull(nb_json, now, cull_idle_min, period_min, mode, now_offset=0):
+    """-> (action, argmax, new_last_activity_string)"""
+    am = C.c_uint32()
+    buf = C.create_string_buffer(64)
+    a = lib().orc_cull(_j(nb_json), now[0], now[1], now_offset, cull_idle_min, period_min, mode, C.byref(am), buf,
+                       len(buf))
+    if a < 0:
+        raise ValueError("bad culler input")
+    return a, am.value, buf.value.decode()
+
+
+# ---- L2: packed oracle on the SoA batches -------------------------------------
+def _diff2(fn, batch, threads):
+    view = batch.view
+    n = batch.n
+    reason = np.zeros(n, dtype=np.uint8)
+    bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+    secs = fn(C.byref(view), n, threads, reason.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+    return reason, bitmap, secs
+
+
+def packed_diff_sts(batch, threads=1):
+    return _diff2(lib().orc2_diff_sts, batch, threads)
+
+
+def packed_diff_svc(batch, threads=1):
+    return _diff2(lib().orc2_diff_svc, batch, threads)
+
+
+def packed_diff_vs(batch, threads=1):
+    return _diff2(lib().orc2_diff_vs, batch, threads)
+
+
+def packed_cull(batch, now, cull_idle_min=1440, period_min=1, mode=1, threads=1):
+    view = batch.view
+    n = batch.n
+    p = N.nbg_cull_params(now[0], now[1], cull_idle_min, period_min, mode)
+    action = np.zeros(n, dtype=np.uint8)
+    argmax = np.zeros(n, dtype=np.uint32)
+    words = (n + 63) // 64
+    cb, pb = np.zeros(words, dtype=np.uint64), np.zeros(words, dtype=np.uint64)
+    secs = lib().orc2_cull(C.byref(view), n, C.byref(p), threads, action.ctypes.data_as(C.c_void_p),
+                           argmax.ctypes.data_as(C.c_void_p), cb.ctypes.data_as(C.c_void_p),
+                           pb.ctypes.data_as(C.c_void_p))
+    return action, argmax, cb, pb, secs

@@ -1,0 +1,343 @@
+"""GPU parity tests: every result comes out of the CUDA kernels through the C ABI
+(libnbgraft.so) and is compared bit for bit with the CPU oracle."""
+import ctypes as C
+import importlib
+import json
+import os
+import time
+
+import numpy as np
+import pytest
+
+import cases
+import oracle as O
+from test_oracle_cases import GOLDEN, STS_PAIRS, SVC_PAIRS, VS_PAIRS, _resolve_now, check_cull_expectation
+
+pytestmark = pytest.mark.gpu
+
+pkg = O.pkg
+host = pkg.host
+N = pkg._native
+rh = importlib.import_module("odh-kubeflow_b200.reconcilehelper")
+culler = importlib.import_module("odh-kubeflow_b200.culler")
+bits = pkg.engine.bitmap_to_bools
+
+
+# ------------------------------------------- the reference's own table tests
+@pytest.mark.parametrize("case", GOLDEN["all_kernels_are_idle"]["cases"], ids=lambda c: c["name"])
+def test_ref_all_kernels_are_idle(ctx, case):
+    assert culler.allKernelsAreIdle(case["kernels"]) == case["result"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["notebook_is_idle"]["cases"], ids=lambda c: c["name"])
+def test_ref_notebook_is_idle(ctx, case, monkeypatch):
+    monkeypatch.setenv("CULL_IDLE_TIME", str(case["cull_idle_time"]))
+    culler.initGlobalVars()
+    t = time.time_ns()
+    now = (t // 10**9, t % 10**9)
+    assert culler.notebookIsIdle(_resolve_now(case["meta"], now[0]), now=now) == case["result"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["stop_annotation_is_set"]["cases"], ids=lambda c: c["name"])
+def test_ref_stop_annotation(ctx, case):
+    meta = _resolve_now(case["meta"], int(time.time()))
+    assert culler.StopAnnotationIsSet(meta) == case["result"]
+    # the same bit as the kernel reports it in Reconcile mode (NBG_ACT_STOPPED)
+    b = host.CullBatch().add({"annotations": meta.get("annotations")})
+    action = ctx.cull(b, int(time.time()), 0, 5, 1, N.CULL_RECONCILE)[0]
+    assert bool(action[0] & N.ACT_STOPPED) == case["result"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["set_stop_annotation"]["cases"], ids=lambda c: c["name"])
+def test_ref_set_stop_annotation(ctx, case):
+    meta = json.loads(json.dumps(case["meta"]))
+    culler.setStopAnnotation(meta)
+    assert culler.STOP_ANNOTATION in meta["annotations"]
+
+
+def test_ref_bdd_labels_need_no_update(ctx):
+    g = GOLDEN["bdd_statefulset_labels"]
+    nb = host.Notebook(g["notebook"])
+    desired = host.generate_statefulset(nb)
+    assert desired.to_python()["metadata"]["labels"] == g["expected_statefulset_labels"]
+    reason, bm = ctx.diff_sts(host.StsBatch().add(desired, desired))
+    assert reason[0] == 0 and bm[0] == 0
+
+
+# ---------------------------------------------------------- derived cases
+@pytest.mark.parametrize("name,frm,to,want", STS_PAIRS, ids=[p[0][:60] for p in STS_PAIRS])
+def test_derived_sts(ctx, name, frm, to, want):
+    to = json.loads(json.dumps(to))
+    got = rh.CopyStatefulSetFields(frm, to, ctx, caller_prestep=True)
+    assert got == ((want & 0x0F) != 0)
+    reason, bm = ctx.diff_sts(host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(to)))
+    assert reason[0] == 0, "after the copy a second pass must be clean"
+    # raw reason byte
+    r2, _ = ctx.diff_sts(host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(cases._edit(to, lambda d: None))))
+    assert r2[0] == 0
+
+
+@pytest.mark.parametrize("name,frm,to,want", STS_PAIRS, ids=[p[0][:60] for p in STS_PAIRS])
+def test_derived_sts_reason_bits(ctx, name, frm, to, want):
+    reason, bm = ctx.diff_sts(host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(to)))
+    assert int(reason[0]) == want
+    assert int(bm[0]) == int((want & 0x0F) != 0)
+
+
+def test_sts_nil_replicas(ctx):
+    frm = STS_PAIRS[0][1]
+    live = json.loads(json.dumps(frm))
+    del live["spec"]["replicas"]
+    with pytest.raises(RuntimeError, match="nil pointer"):
+        rh.CopyStatefulSetFields(frm, live, ctx)
+    with pytest.raises(pkg.NbgError) as ei:
+        ctx.diff_sts(host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(live)))
+    assert ei.value.status == N.NBG_E_NILREPLICAS
+
+
+@pytest.mark.parametrize("name,frm,to,want", SVC_PAIRS, ids=[p[0][:60] for p in SVC_PAIRS])
+def test_derived_svc(ctx, name, frm, to, want):
+    reason, bm = ctx.diff_svc(host.SvcBatch().add(host.Service(frm), host.Service(to)))
+    assert int(reason[0]) == want and int(bm[0]) == int(want != 0)
+    to = json.loads(json.dumps(to))
+    assert rh.CopyServiceFields(frm, to, ctx) == (want != 0)
+    assert rh.CopyServiceFields(frm, to, ctx) is False
+
+
+@pytest.mark.parametrize("name,frm,to,want", VS_PAIRS, ids=[p[0][:60] for p in VS_PAIRS])
+def test_derived_vs(ctx, name, frm, to, want):
+    reason, bm = ctx.diff_vs(host.VsBatch().add(host.Unstructured(frm), host.Unstructured(to)))
+    assert int(reason[0]) == want and int(bm[0]) == int(want in (1, 2))
+    to = json.loads(json.dumps(to))
+    assert rh.CopyVirtualService(frm, to, ctx) == (want in (1, 2))
+    if want in (1, 2):
+        assert to["spec"] == frm["spec"]
+
+
+@pytest.mark.parametrize("name,nb,idle,period,mode,want", cases.CULL_CASES, ids=[c[0][:60] for c in cases.CULL_CASES])
+def test_derived_cull(ctx, name, nb, idle, period, mode, want):
+    b = host.CullBatch().add(nb)
+    action, argmax, cb, pb = ctx.cull(b, cases.NOW[0], cases.NOW[1], idle, period, mode)
+    a1, am1, la1 = O.cull(nb, cases.NOW, idle, period, mode)
+    assert (int(action[0]), int(argmax[0])) == (a1, am1)
+    check_cull_expectation(int(action[0]), int(argmax[0]), b.new_last_activity(0, action[0], argmax[0], cases.NOW[0]), want)
+    assert int(cb[0]) == int(bool(a1 & 8)) and int(pb[0]) == int(bool(a1 & 4))
+
+
+def test_culler_mirror_updates_annotation(ctx):
+    culler.CULL_IDLE_TIME, culler.IDLENESS_CHECK_PERIOD = 1440, 1
+    meta = {"annotations": {culler.LAST_ACTIVITY_ANNOTATION: "2025-12-31T00:00:00Z"}}
+    ks = [{"last_activity": "2025-12-31T10:00:00.7Z", "execution_state": "idle"}]
+    assert culler.updateTimestampFromKernelsActivity(meta, ks, now=cases.NOW) is True
+    assert meta["annotations"][culler.LAST_ACTIVITY_ANNOTATION] == "2025-12-31T10:00:00Z"
+    ks[0]["execution_state"] = "busy"
+    assert culler.updateTimestampFromKernelsActivity(meta, ks, now=cases.NOW) is False
+    assert meta["annotations"][culler.LAST_ACTIVITY_ANNOTATION] == "2026-01-01T00:00:00Z"
+    assert culler.updateTimestampFromTerminalsActivity(meta, [{"last_activity": "2026-01-01T00:00:00.9Z"}], now=cases.NOW) is True
+    assert culler.updateTimestampFromKernelsActivity(meta, [], now=cases.NOW) is False
+    assert culler.cullingCheckPeriodHasPassed({"annotations": {culler.LAST_ACTIVITY_CHECK_TIMESTAMP_ANNOTATION: "x"}}, now=cases.NOW)
+
+
+# ------------------------------------------------- fleets at BASELINE sizes
+def _check_diff_fleet(ctx, fleet, sample_every):
+    sts, svc, vs = fleet.pack()
+    got = {"sts": ctx.diff_sts(sts), "svc": ctx.diff_svc(svc), "vs": ctx.diff_vs(vs)}
+    want = {"sts": O.packed_diff_sts(sts, threads=8), "svc": O.packed_diff_svc(svc, threads=8),
+            "vs": O.packed_diff_vs(vs, threads=8)}
+    for k in got:
+        assert np.array_equal(got[k][0], want[k][0]), k + " reason bytes"
+        assert np.array_equal(got[k][1], want[k][1]), k + " bitmap"
+    assert np.array_equal(bits(got["sts"][1], fleet.n), (got["sts"][0] & 0x0F) != 0)
+    for i in range(0, fleet.n, sample_every):   # and the object-level oracle on a sample
+        assert O.copy_statefulset_fields(fleet.get(i, "sts_from"), fleet.get(i, "sts_to"), 1) == got["sts"][0][i]
+        assert O.copy_service_fields(fleet.get(i, "svc_from"), fleet.get(i, "svc_to")) == got["svc"][0][i]
+        assert O.copy_virtualservice(fleet.get(i, "vs_from"), fleet.get(i, "vs_to")) == got["vs"][0][i]
+    return got
+
+
+def test_config2_10k_notebooks(ctx):
+    """BASELINE config #2: 10k synthetic Notebooks, StatefulSet/Service diff on one GPU."""
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 2, 10000, 200)
+    got = _check_diff_fleet(ctx, fleet, 37)
+    frac = ((got["sts"][0] & 0x0F) != 0).mean()
+    assert 0.3 < frac < 0.6          # 40% identical + the undetected classes
+
+
+def test_config4_odh_notebooks(ctx):
+    """BASELINE config #4 (ODH webhook-shaped, incl. VirtualService), 30k of the 100k here;
+    bench.py runs the full 100k."""
+    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 30000, 2000)
+    _check_diff_fleet(ctx, fleet, 211)
+
+
+def test_config3_1m_kernel_records(ctx):
+    """BASELINE config #3: ~1M kernel last_activity records over 250k notebooks."""
+    cf = host.CullFleet(host.SEED_BASE + 3, 250000)
+    b = cf.pack()
+    assert 900_000 < b.records()[0] < 1_100_000
+    now = (cf.now_sec, cf.now_nsec)
+    for mode in (N.CULL_PREDICATES, N.CULL_RECONCILE):
+        got = ctx.cull(b, now[0], now[1], 1440, 1, mode)
+        want = O.packed_cull(b, now, 1440, 1, mode, threads=8)
+        for k in range(4):
+            assert np.array_equal(got[k], want[k]), (mode, k)
+        for i in range(0, cf.n, 503):
+            a1, am1, la1 = O.cull(cf.json(i), now, 1440, 1, mode)
+            assert (a1, am1) == (int(got[0][i]), int(got[1][i]))
+            assert la1 == b.new_last_activity(i, got[0][i], got[1][i], now[0])
+
+
+# --------------------------------------------------------------- edge cases
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 63, 64, 65, 127, 129, 8191, 8193])
+def test_ragged_sizes(ctx, n):
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, 7, n, 3)
+    sts, svc, vs = fleet.pack()
+    for got, want in ((ctx.diff_sts(sts), O.packed_diff_sts(sts)), (ctx.diff_svc(svc), O.packed_diff_svc(svc)),
+                      (ctx.diff_vs(vs), O.packed_diff_vs(vs))):
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    cf = host.CullFleet(11, n)
+    b = cf.pack()
+    got, want = ctx.cull(b, cf.now_sec, cf.now_nsec, 1440, 1, 1), O.packed_cull(b, (cf.now_sec, cf.now_nsec), 1440, 1, 1)
+    for k in range(4):
+        assert np.array_equal(got[k], want[k])
+
+
+def test_empty_batches(ctx):
+    assert ctx.diff_sts(host.StsBatch())[0].size == 0
+    assert ctx.diff_svc(host.SvcBatch())[0].size == 0
+    assert ctx.diff_vs(host.VsBatch())[0].size == 0
+    assert ctx.cull(host.CullBatch(), 0, 0)[0].size == 0
+
+
+def test_objects_with_no_maps_and_no_records(ctx):
+    bare = {"metadata": {"name": "x"}, "spec": {"replicas": 1, "template": {"spec": {"containers": [{"name": "c"}]}}}}
+    r, bm = ctx.diff_sts(host.StsBatch().add(host.StatefulSet(bare), host.StatefulSet(bare)))
+    assert r[0] == 0 and bm[0] == 0
+    b = host.CullBatch()
+    for _ in range(70):
+        b.add({"annotations": None, "kernels": [], "terminals": []})
+    a, am, cb, pb = ctx.cull(b, 100, 5, 1, 1, 0)
+    assert not a.any() and (am == N.NBG_ARGMAX_NONE).all() and not cb.any() and not pb.any()
+
+
+def test_long_segments_and_big_maps(ctx):
+    """max-size rows: a notebook with 5000 kernels, an object with 3000 labels."""
+    ks = [{"last_activity": host.format_rfc3339(1767000000 + (i * 7919) % 100000), "execution_state": "idle"} for i in range(5000)]
+    nb = {"annotations": {culler.LAST_ACTIVITY_ANNOTATION: "2025-01-01T00:00:00Z"}, "kernels": ks, "terminals": ks[:777]}
+    b = host.CullBatch().add({"annotations": {}}).add(nb).add({"annotations": {}})
+    got, want = ctx.cull(b, cases.NOW[0], cases.NOW[1], 1440, 1, 0), O.packed_cull(b, cases.NOW, 1440, 1, 0)
+    for k in range(4):
+        assert np.array_equal(got[k], want[k])
+    assert got[0][1] & 3 and got[1][1] == O.cull(nb, cases.NOW, 1440, 1, 0)[1]
+    labels = {"k%04d" % i: "v%d" % (i % 13) for i in range(3000)}
+    frm = {"metadata": {"labels": labels}, "spec": {"replicas": 1}}
+    live = json.loads(json.dumps(frm))
+    live["metadata"]["labels"]["k2999"] = "changed"
+    batch = host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(frm)).add(host.StatefulSet(frm), host.StatefulSet(live))
+    r, _ = ctx.diff_sts(batch)
+    assert r.tolist() == [0, 1]
+
+
+def test_bad_arguments_are_rejected(ctx):
+    lib = N.nbg()
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, 1, 100, 2)
+    sts, _, _ = fleet.pack(svc=False, vs=False)
+    view = sts.view
+    reason = np.zeros(100, np.uint8)
+    bm = np.zeros(2, np.uint64)
+    rp, bp = reason.ctypes.data_as(C.c_void_p), bm.ctypes.data_as(C.c_void_p)
+    assert lib.nbg_diff_sts(None, C.byref(view), 100, rp, bp) == N.NBG_E_INVAL
+    assert lib.nbg_diff_sts(ctx.handle, None, 100, rp, bp) == N.NBG_E_INVAL
+    assert lib.nbg_diff_sts(ctx.handle, C.byref(view), 100, None, bp) == N.NBG_E_INVAL
+    off = sts.arrays()["labels_to.off"].copy()
+    off[50] = off[51] + 5                               # not monotone
+    view.labels_to.off = off.ctypes.data_as(N.u32p)
+    assert lib.nbg_diff_sts(ctx.handle, C.byref(view), 100, rp, bp) == N.NBG_E_RANGE
+    cb = host.CullFleet(3, 10).pack()
+    p = N.nbg_cull_params(0, 1_000_000_000, 1, 1, 0)    # nsec out of range
+    a, am = np.zeros(10, np.uint8), np.zeros(10, np.uint32)
+    v = cb.view
+    assert lib.nbg_cull(ctx.handle, C.byref(v), 10, C.byref(p), a.ctypes.data_as(C.c_void_p), am.ctypes.data_as(C.c_void_p), bp, bp) == N.NBG_E_INVAL
+    p = N.nbg_cull_params(0, 0, 2_000_000_000, 1, 0)
+    assert lib.nbg_cull(ctx.handle, C.byref(v), 10, C.byref(p), a.ctypes.data_as(C.c_void_p), am.ctypes.data_as(C.c_void_p), bp, bp) == N.NBG_E_INVAL
+    with pytest.raises(pkg.NbgError):
+        pkg.Context([99])
+
+
+# ---------------------------------------- device-pointer API, big inputs, shards
+def test_device_pointer_api_and_tiling_property(ctx):
+    """Inputs resident in HBM (torch tensors), launched on torch's stream.  A fleet tiled K
+    times must give the base result K times (size-independent property at ~0.6M objects)."""
+    dev = importlib.import_module("odh-kubeflow_b200.device")
+    import torch
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, 9984, 300)   # multiple of 64
+    sts, svc, vs = fleet.pack()
+    base = ctx.diff_sts(sts)
+    K = 64
+    d = dev.DeviceBatch.from_host(sts, device=0, tile=K)
+    reason, bitmap = d.run(ctx)
+    torch.cuda.synchronize()
+    assert d.n == 9984 * K
+    r = reason.cpu().numpy().reshape(K, -1)
+    assert (r == base[0][None, :]).all()
+    assert (bitmap.cpu().numpy().view(np.uint64).reshape(K, -1) == base[1][None, :]).all()
+    for batch, fn in ((svc, ctx.diff_svc), (vs, ctx.diff_vs)):
+        d = dev.DeviceBatch.from_host(batch, device=0, tile=3)
+        reason, bitmap = d.run(ctx)
+        torch.cuda.synchronize()
+        want = fn(batch)
+        assert (reason.cpu().numpy().reshape(3, -1) == want[0][None, :]).all()
+    cf = host.CullFleet(5, 64 * 500)
+    cb = cf.pack()
+    want = ctx.cull(cb, cf.now_sec, cf.now_nsec, 1440, 1, 1)
+    d = dev.DeviceBatch.from_host(cb, device=0, tile=5)
+    outs = d.run(ctx, now=(cf.now_sec, cf.now_nsec), cull_idle_min=1440, check_period_min=1, mode=1)
+    torch.cuda.synchronize()
+    assert (outs[0].cpu().numpy().reshape(5, -1) == want[0][None, :]).all()
+    assert (outs[1].cpu().numpy().view(np.uint32).reshape(5, -1) == want[1][None, :]).all()
+    assert (outs[2].cpu().numpy().view(np.uint64).reshape(5, -1) == want[2][None, :]).all()
+
+
+def test_sharding_by_namespace_is_a_partition(ctx):
+    """shard by nbg_shard_of(hash(namespace)); per-shard results gathered on the
+    host equal the unsharded result."""
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, 21, 6000, 97)
+    whole = ctx.diff_sts(fleet.pack(svc=False, vs=False)[0])[0]
+    for g in (2, 4, 8):
+        shards = fleet.shard_indices(g)
+        assert sum(len(s) for s in shards) == fleet.n
+        out = np.full(fleet.n, 255, np.uint8)
+        for idx in shards:
+            # one namespace never spans two shards
+            r, _ = ctx.diff_sts(fleet.pack(idx=idx, svc=False, vs=False)[0])
+            out[idx.astype(np.int64)] = r
+        assert np.array_equal(out, whole)
+    ns = np.array([fleet.ns_hash(i) for i in range(fleet.n)], dtype=np.uint64)
+    for idx in fleet.shard_indices(4):
+        others = np.setdiff1d(np.arange(fleet.n), idx.astype(np.int64))
+        assert not np.intersect1d(ns[idx.astype(np.int64)], ns[others]).size
+
+
+def test_concurrent_callers(ctx):
+    """The reference has two concurrent callers (notebook + Culler controllers)."""
+    import threading
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, 31, 20000, 50)
+    sts = fleet.pack(svc=False, vs=False)[0]
+    cb = host.CullFleet(32, 50000).pack()
+    want_s, want_c = O.packed_diff_sts(sts)[0], O.packed_cull(cb, cases.NOW, 1440, 1, 1)[0]
+    errs = []
+
+    def a():
+        for _ in range(5):
+            if not np.array_equal(ctx.diff_sts(sts)[0], want_s):
+                errs.append("sts")
+
+    def b():
+        for _ in range(5):
+            if not np.array_equal(ctx.cull(cb, cases.NOW[0], cases.NOW[1], 1440, 1, 1)[0], want_c):
+                errs.append("cull")
+
+    ts = [threading.Thread(target=a), threading.Thread(target=b)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs

@@ -1,0 +1,332 @@
+"""CPU tests: the oracle against the reference's own known-answer cases
+(tests/golden/reference_cases.json) and against the derived cases of cases.py;
+the host packer + packed oracle (L2) against the semantic oracle (L1)."""
+import json
+import os
+import time
+
+import numpy as np
+import pytest
+
+import cases
+import oracle as O
+
+host = O.host
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_cases.json")))
+
+
+def _resolve_now(meta, now_sec):
+    """'now-6m' -> RFC3339 string of now shifted by -6 minutes, as the Go tests build inputs."""
+    ann = meta.get("annotations")
+    if not ann:
+        return meta
+    out = {}
+    for k, v in ann.items():
+        if isinstance(v, str) and v.startswith("now"):
+            minutes = int(v[3:-1])
+            v = O.format_rfc3339(now_sec + minutes * 60)
+        out[k] = v
+    return {"annotations": out}
+
+
+# ------------------------------------------------ reference's own test vectors
+@pytest.mark.parametrize("case", GOLDEN["stop_annotation_is_set"]["cases"], ids=lambda c: c["name"])
+def test_ref_stop_annotation_is_set(case):
+    now = int(time.time())
+    assert O.stop_annotation_is_set(_resolve_now(case["meta"], now)) == case["result"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["all_kernels_are_idle"]["cases"], ids=lambda c: c["name"])
+def test_ref_all_kernels_are_idle(case):
+    assert O.all_kernels_are_idle(case["kernels"]) == case["result"]
+
+
+@pytest.mark.parametrize("case", GOLDEN["notebook_is_idle"]["cases"], ids=lambda c: c["name"])
+def test_ref_notebook_is_idle(case):
+    t = time.time_ns()
+    now = (t // 10**9, t % 10**9)
+    meta = _resolve_now(case["meta"], now[0])
+    assert O.notebook_is_idle(meta, now, case["cull_idle_time"]) == case["result"]
+    # and through the packed oracle (host parse + L2 loops)
+    b = host.CullBatch().add({"annotations": meta.get("annotations")})
+    action = O.packed_cull(b, now, case["cull_idle_time"], 1, 0)[0]
+    assert bool(action[0] & 8) == case["result"]
+
+
+def test_ref_bdd_statefulset_labels():
+    g = GOLDEN["bdd_statefulset_labels"]
+    sts = host.generate_statefulset(host.Notebook(g["notebook"])).to_python()
+    assert sts["metadata"]["labels"] == g["expected_statefulset_labels"]
+    assert sts["spec"]["replicas"] == 1
+    assert sts["spec"]["template"]["spec"]["containers"][0]["workingDir"] == "/home/jovyan"
+
+
+# ------------------------------------------------------------- derived cases
+def _desired_sts_dict(nb_dict):
+    """desired StatefulSet as a JSON dict that decodes back to the same object."""
+    return _typed_json(host.generate_statefulset(host.Notebook(nb_dict)))
+
+
+def _typed_json(obj):
+    """Obj -> JSON dict in Kubernetes wire form (quantities / IntOrString re-encoded)."""
+    def fix(v):
+        if isinstance(v, dict):
+            if set(v) <= {"i", "d", "s", "Format"} and ("i" in v or "s" in v or "Format" in v or "d" in v) and _is_quantity(v):
+                return _quantity_text(v)
+            if set(v) <= {"Type", "IntVal", "StrVal"} and v:
+                return v.get("StrVal", "") if v.get("Type") else v.get("IntVal", 0)
+            return {k: fix(x) for k, x in v.items()}
+        if isinstance(v, list):
+            return [fix(x) for x in v]
+        return v
+    return fix(obj.to_python())
+
+
+def _is_quantity(v):
+    return isinstance(v.get("i", {}), dict) and set(v.get("i", {})) <= {"value", "scale"}
+
+
+def _quantity_text(v):
+    if v.get("s"):
+        return v["s"]
+    val, scale = v.get("i", {}).get("value", 0), v.get("i", {}).get("scale", 0)
+    fmt = v.get("Format", "")
+    if fmt == "BinarySI":
+        for suf, sh in (("Gi", 30), ("Mi", 20), ("Ki", 10)):
+            if val % (1 << sh) == 0:
+                return "%d%s" % (val >> sh, suf)
+        return str(val)
+    if scale == -3:
+        return "%dm" % val
+    if scale == -1:
+        return "%d.%d" % (val // 10, val % 10)
+    if scale == 0:
+        return str(val)
+    return "%de%d" % (val, scale)
+
+
+def test_typed_json_round_trip():
+    d = _desired_sts_dict(cases.BASE_NOTEBOOK)
+    assert host.StatefulSet(d).digest() == host.generate_statefulset(host.Notebook(cases.BASE_NOTEBOOK)).digest()
+
+
+STS_PAIRS = list(cases.sts_case_pairs(_desired_sts_dict))
+
+
+@pytest.mark.parametrize("name,frm,to,want", STS_PAIRS, ids=[p[0][:60] for p in STS_PAIRS])
+def test_derived_sts(name, frm, to, want):
+    f, t = host.StatefulSet(frm), host.StatefulSet(to)
+    batch = host.StsBatch().add(f, t)
+    assert int(O.packed_diff_sts(batch)[0][0]) == want           # L2 on the packed pair
+    assert O.copy_statefulset_fields(f, t, 1) == want            # L1 on the objects
+    # Go side effect: afterwards `to` carries the desired owned fields => a second pass is clean
+    assert O.copy_statefulset_fields(f, t, 1) == 0
+
+
+def test_sts_nil_replicas_is_flagged():
+    d = _desired_sts_dict(cases.BASE_NOTEBOOK)
+    live = json.loads(json.dumps(d))
+    del live["spec"]["replicas"]
+    f, t = host.StatefulSet(d), host.StatefulSet(live)
+    assert O.copy_statefulset_fields(f, t, 1) & 0x80
+    assert int(O.packed_diff_sts(host.StsBatch().add(f, host.StatefulSet(live)))[0][0]) & 0x80
+
+
+def _svc_pairs():
+    desired = _typed_json(host.generate_service(host.Notebook(cases.BASE_NOTEBOOK)))
+    for name, edit, want in cases.SVC_CASES:
+        yield name, desired, cases._edit(desired, edit), want
+
+
+SVC_PAIRS = list(_svc_pairs())
+
+
+@pytest.mark.parametrize("name,frm,to,want", SVC_PAIRS, ids=[p[0][:60] for p in SVC_PAIRS])
+def test_derived_svc(name, frm, to, want):
+    f, t = host.Service(frm), host.Service(to)
+    assert int(O.packed_diff_svc(host.SvcBatch().add(f, t))[0][0]) == want
+    assert O.copy_service_fields(f, t) == want
+    assert O.copy_service_fields(f, t) == 0
+
+
+def _vs_pairs():
+    desired = host.generate_virtualservice(host.Notebook(cases.BASE_NOTEBOOK)).to_python()
+    for name, edit, want in cases.VS_CASES:
+        f, t = json.loads(json.dumps(desired)), json.loads(json.dumps(desired))
+        edit(f, t)
+        yield name, f, t, want
+
+
+VS_PAIRS = list(_vs_pairs())
+
+
+@pytest.mark.parametrize("name,frm,to,want", VS_PAIRS, ids=[p[0][:60] for p in VS_PAIRS])
+def test_derived_vs(name, frm, to, want):
+    f, t = host.Unstructured(frm), host.Unstructured(to)
+    assert int(O.packed_diff_vs(host.VsBatch().add(f, t))[0][0]) == want
+    assert O.copy_virtualservice(f, t) == want
+    if want in (1, 2):
+        assert O.copy_virtualservice(f, t) == 0  # spec was copied
+
+
+def check_cull_expectation(action, argmax, new_la, want):
+    if "action" in want:
+        assert action == want["action"]
+    if "src" in want:
+        assert action & 3 == want["src"]
+    if "argmax" in want:
+        assert argmax == want["argmax"]
+    if "period" in want:
+        assert bool(action & 4) == want["period"]
+    if "cull" in want:
+        assert bool(action & 8) == want["cull"]
+    if "new_la" in want:
+        assert new_la == want["new_la"]
+
+
+@pytest.mark.parametrize("name,nb,idle,period,mode,want", cases.CULL_CASES, ids=[c[0][:60] for c in cases.CULL_CASES])
+def test_derived_cull(name, nb, idle, period, mode, want):
+    a1, am1, la1 = O.cull(nb, cases.NOW, idle, period, mode)
+    check_cull_expectation(a1, am1, la1, want)
+    b = host.CullBatch().add(nb)
+    a2, am2, _, _, _ = O.packed_cull(b, cases.NOW, idle, period, mode)
+    assert (int(a2[0]), int(am2[0])) == (a1, am1)
+    assert b.new_last_activity(0, a2[0], am2[0], cases.NOW[0]) == la1
+
+
+@pytest.mark.parametrize("text,want", cases.RFC3339_CASES, ids=[c[0] or "empty" for c in cases.RFC3339_CASES])
+def test_rfc3339_parsers_agree(text, want):
+    assert O.parse_rfc3339(text) == want          # oracle's layout-driven parser
+    assert host.parse_rfc3339(text) == want       # product's packer
+    if want:
+        assert O.format_rfc3339(want[0], want[2]) == host.format_rfc3339(want[0], want[2])
+        again = O.parse_rfc3339(O.format_rfc3339(want[0], want[2]))
+        assert again == (want[0], 0, want[2])     # Format drops the fraction (CULL:348)
+
+
+@pytest.mark.parametrize("text,want", cases.QUANTITY_CASES, ids=[c[0] for c in cases.QUANTITY_CASES])
+def test_quantity_struct(text, want):
+    q = host.Obj.from_json("ResourceRequirements", {"limits": {"x": text}}).to_python()["limits"]["x"]
+    got = (q.get("i", {}).get("value", 0), q.get("i", {}).get("scale", 0), q.get("Format", ""), q.get("s", ""))
+    assert got == want
+
+
+# ------------------------------------------- packer + L2 against L1 on fleets
+@pytest.mark.parametrize("kind,seed,n", [(host.FLEET_KUBEFLOW, host.SEED_BASE + 2, 1500), (host.FLEET_ODH, host.SEED_BASE + 4, 700)])
+def test_fleet_packed_equals_semantic(kind, seed, n):
+    fleet = host.Fleet(kind, seed, n, 64)
+    sts, svc, vs = fleet.pack()
+    r_sts, bm_sts, _ = O.packed_diff_sts(sts, threads=2)
+    r_svc, _, _ = O.packed_diff_svc(svc)
+    r_vs, bm_vs, _ = O.packed_diff_vs(vs)
+    for i in range(n):
+        assert O.copy_statefulset_fields(fleet.get(i, "sts_from"), fleet.get(i, "sts_to"), 1) == r_sts[i], i
+        assert O.copy_service_fields(fleet.get(i, "svc_from"), fleet.get(i, "svc_to")) == r_svc[i], i
+        assert O.copy_virtualservice(fleet.get(i, "vs_from"), fleet.get(i, "vs_to")) == r_vs[i], i
+    bits = pkg_bits(bm_sts, n)
+    assert np.array_equal(bits, (r_sts & 0x0F) != 0)
+    assert np.array_equal(pkg_bits(bm_vs, n), (r_vs & 3) != 0)
+    # every drift class shows up with the reason it was built to trigger
+    want = {0: {0}, 1: {8}, 2: {1}, 3: {0}, 4: {0}, 5: {4, 20}, 6: {2}, 7: {8}, 8: {8}, 9: {8}}
+    for i in range(n):
+        assert int(r_sts[i]) in want[fleet.drift_class(i)], (i, fleet.drift_class(i), r_sts[i])
+
+
+def pkg_bits(bitmap, n):
+    return O.pkg.engine.bitmap_to_bools(bitmap, n)
+
+
+def test_pack_equal_iff_deep_equal():
+    """The packing rule: tiles equal <=> reflect.DeepEqual (L1) on every generated pair,
+    including pairs of DIFFERENT notebooks."""
+    fleet = host.Fleet(host.FLEET_ODH, 99, 400, 8)
+    sts, _, _ = fleet.pack(svc=False, vs=False)
+    pods = sts.arrays()["pod_to"].reshape(-1, 192)
+    frm = sts.arrays()["pod_from"].reshape(-1, 192)
+    objs_to = [fleet.get(i, "sts_to") for i in range(fleet.n)]
+    objs_from = [fleet.get(i, "sts_from") for i in range(fleet.n)]
+
+    def podspec(o):
+        return o.get("spec.template.spec")
+
+    for i in range(0, fleet.n, 7):
+        a, b = podspec(objs_from[i]), podspec(objs_to[i])
+        assert O.deep_equal(a, b) == bool(np.array_equal(frm[i], pods[i])), i
+        j = (i * 31 + 5) % fleet.n
+        c = podspec(objs_to[j])
+        assert O.deep_equal(b, c) == bool(np.array_equal(pods[i], pods[j])), (i, j)
+
+
+def test_cull_fleet_packed_equals_semantic():
+    cf = host.CullFleet(host.SEED_BASE + 3, 6000)
+    b = cf.pack()
+    now = (cf.now_sec, cf.now_nsec)
+    for mode in (0, 1):
+        a2, am2, cb, pb, _ = O.packed_cull(b, now, 1440, 1, mode, threads=3)
+        for i in range(cf.n):
+            a1, am1, la1 = O.cull(cf.json(i), now, 1440, 1, mode)
+            assert (a1, am1) == (int(a2[i]), int(am2[i])), (mode, i, cf.json(i))
+            assert la1 == b.new_last_activity(i, a2[i], am2[i], now[0]), (mode, i)
+        assert np.array_equal(pkg_bits(cb, cf.n), (a2 & 8) != 0)
+        assert np.array_equal(pkg_bits(pb, cf.n), (a2 & 4) != 0)
+    # the distribution exercises every branch
+    a2 = O.packed_cull(b, now, 1440, 1, 0)[0]
+    assert set((a2 & 3).tolist()) == {0, 1, 2, 3}
+
+
+def test_builders_follow_reference_rules():
+    nb = json.loads(json.dumps(cases.BASE_NOTEBOOK))
+    nb["metadata"]["annotations"].update({"kubectl.kubernetes.io/x": "1", "notebooks.kubeflow.org/last-activity": "t",
+                                          "kubeflow-resource-stopped": ""})
+    sts = host.generate_statefulset(host.Notebook(nb)).to_python()
+    assert sts["spec"]["replicas"] == 0                                   # key presence, empty value (NBCTL:435)
+    t = sts["spec"]["template"]
+    assert t["metadata"]["annotations"] == {"owner": "alice", "kubeflow-resource-stopped": ""}  # NBCTL:486-491
+    assert t["metadata"]["labels"] == {"app": "nb", "team": "x", "statefulset": "nb-a", "notebook-name": "nb-a",
+                                       "opendatahub.io/workbenches": "true"}
+    c0 = t["spec"]["containers"][0]
+    assert c0["ports"] == [{"containerPort": 8888, "name": "notebook-port", "protocol": "TCP"}]
+    assert c0["env"] == [{"name": "NB_PREFIX", "value": "/notebook/team-x/nb-a"}]
+    assert t["spec"]["securityContext"] == {"fsGroup": 100}
+    no_fs = host.generate_statefulset(host.Notebook(nb), {"ADD_FSGROUP": "false"}).to_python()
+    assert "securityContext" not in no_fs["spec"]["template"]["spec"]
+    nb2 = json.loads(json.dumps(nb))
+    nb2["spec"]["template"]["spec"]["containers"][0]["env"] = [{"name": "NB_PREFIX", "value": "/mine"}]
+    nb2["spec"]["template"]["spec"]["containers"][0]["ports"] = [{"containerPort": 9999}]
+    sts2 = host.generate_statefulset(host.Notebook(nb2)).to_python()
+    assert sts2["spec"]["template"]["spec"]["containers"][0]["env"] == [{"name": "NB_PREFIX", "value": "/mine"}]  # NBCTL:420-425
+    svc = host.generate_service(host.Notebook(nb2)).to_python()
+    assert svc["spec"]["ports"] == [{"name": "http-notebook", "port": 80, "protocol": "TCP", "targetPort": {"IntVal": 9999}}]
+    assert svc["spec"]["selector"] == {"statefulset": "nb-a"}
+    nb["metadata"]["annotations"]["notebooks.kubeflow.org/http-headers-request-set"] = '{"X-A": "1"}'
+    nb["metadata"]["annotations"]["notebooks.kubeflow.org/http-rewrite-uri"] = "/r/"
+    vs = host.generate_virtualservice(host.Notebook(nb), {"CLUSTER_DOMAIN": "c.local"}).to_python()
+    h = vs["spec"]["http"][0]
+    assert vs["metadata"]["name"] == "notebook-team-x-nb-a"
+    assert h["headers"]["request"]["set"] == {"X-A": "1"} and h["rewrite"]["uri"] == "/r/"
+    assert h["match"][0]["uri"]["prefix"] == "/notebook/team-x/nb-a/"
+    assert h["route"][0]["destination"] == {"host": "nb-a.team-x.svc.c.local", "port": {"number": 80}}
+    assert vs["spec"]["hosts"] == ["*"] and vs["spec"]["gateways"] == ["kubeflow/kubeflow-gateway"]
+    nb["metadata"]["annotations"]["notebooks.kubeflow.org/http-headers-request-set"] = "{not json"
+    vs = host.generate_virtualservice(host.Notebook(nb)).to_python()
+    assert vs["spec"]["http"][0]["headers"]["request"]["set"] == {}       # NBCTL:608-611
+    with pytest.raises(host.HostError):
+        host.generate_statefulset(host.Notebook({"metadata": {"name": "x"}, "spec": {"template": {"spec": {}}}}))
+
+
+def test_odh_webhook_shape():
+    nb = host.Notebook(cases.BASE_NOTEBOOK)
+    host.odh_mutate(nb, 1 | 2 | 4 | 8 | 16)
+    d = nb.to_python()
+    pod = d["spec"]["template"]["spec"]
+    assert d["metadata"]["annotations"]["kubeflow-resource-stopped"] == "odh-notebook-controller-lock"  # ODHWH:105-114
+    assert [c["name"] for c in pod["containers"]] == ["nb-a", "kube-rbac-proxy"]
+    assert {v["name"] for v in pod["volumes"]} == {"ws", "trusted-ca", "runtime-images", "elyra-dsp-details",
+                                                   "kube-rbac-proxy-config", "kube-rbac-proxy-tls-certificates"}
+    assert pod["serviceAccountName"] == "nb-a"                            # ODHWH:324
+    proxy = pod["containers"][1]
+    assert len(proxy["args"]) == 11 and proxy["resources"]["limits"]["cpu"]["s"] == "100m"
+    env_names = [e["name"] for e in pod["containers"][0]["env"]]
+    assert sorted(env_names) == sorted(["PIP_CERT", "REQUESTS_CA_BUNDLE", "SSL_CERT_FILE", "PIPELINES_SSL_SA_CERTS",
+                                        "KF_PIPELINES_SSL_SA_CERTS", "GIT_SSL_CAINFO"])
+    assert host.generate_statefulset(nb).to_python()["spec"]["replicas"] == 0
