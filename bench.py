@@ -1,0 +1,426 @@
+#!/usr/bin/env python
+"""bench.py — the graft's one headline measurement (contract: README of the task).
+
+A "step" is one pass of the hot path over one GPU's share of the fleet:
+diff_sts + diff_svc + diff_vs (Copy*Fields, COMMON:107-219) + cull (CULL:86-241,
+315-428) over the same notebooks.  Unit: objects/s where one object = one Notebook
+(its StatefulSet pair, Service pair, VirtualService pair and culler record set).
+
+  value      inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e        the same step through the host-buffer C ABI (nbg_diff_*, nbg_cull):
+             pinned host buffers -> H2D -> kernel -> D2H inside the timed region
+  roofline   dominant kernel (diff_sts): algorithmic bytes / its own CUDA-event time
+  cpu_baseline  the semantic oracle (CPU restatement of the Go predicates on whole
+             objects) on all host threads, bounded sample; N=1, rank 0 only
+
+--impl reference times that CPU restatement alone (the reference is Go and cannot
+be built here: no toolchain, un-vendored modules — see DESIGN.md).
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "objects/sec (batched reconcile-diff + cull predicate per Notebook)"
+UNIT = "objects/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--per-gpu", type=int, default=1_250_000, help="notebooks per GPU (10M / 8)")
+    ap.add_argument("--cpu-sample", type=int, default=40_000, help="notebooks in the CPU baseline sample")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary configs (#2, #3, #4)")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            pass
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        out = self.p.communicate()[0]
+        sm, mx, reasons = [], [], set()
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def pinned_copy(lib, arrays, keep):
+    """Copy numpy arrays into cudaHostAlloc'ed memory; returns name -> numpy view."""
+    out = {}
+    for name, a in arrays.items():
+        nbytes = max(a.nbytes, 1)
+        p = lib.nbg_alloc_pinned(nbytes)
+        if not p:
+            raise MemoryError("nbg_alloc_pinned(%d)" % nbytes)
+        keep.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        v = np.frombuffer(buf, dtype=np.uint8, count=a.nbytes).view(a.dtype)
+        v[...] = a
+        out[name] = v
+    return out
+
+
+def struct_over(N, kind, arr):
+    def p(name, ct):
+        return arr[name].ctypes.data_as(C.POINTER(ct))
+
+    def kv(prefix):
+        m = N.nbg_kvmap()
+        m.off = p(prefix + ".off", C.c_uint32)
+        m.ent = C.cast(arr[prefix + ".ent"].ctypes.data, C.POINTER(N.nbg_kv))
+        return m
+    if kind == "sts":
+        s = N.nbg_sts_batch()
+        s.replicas_from, s.replicas_to = p("replicas_from", C.c_int32), p("replicas_to", C.c_int32)
+        s.tmpl_from, s.tmpl_to = p("tmpl_from", C.c_uint64), p("tmpl_to", C.c_uint64)
+        s.pod_from, s.pod_to = p("pod_from", C.c_uint64), p("pod_to", C.c_uint64)
+        for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
+            setattr(s, f, kv(f))
+    elif kind == "svc":
+        s = N.nbg_svc_batch()
+        s.flags = p("flags", C.c_uint8)
+        s.ports_from, s.ports_to = p("ports_from", C.c_uint64), p("ports_to", C.c_uint64)
+        for f in ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"):
+            setattr(s, f, kv(f))
+    elif kind == "vs":
+        s = N.nbg_vs_batch()
+        s.flags = p("flags", C.c_uint8)
+        s.spec_from, s.spec_to = p("spec_from", C.c_uint64), p("spec_to", C.c_uint64)
+        s.hdr_from, s.hdr_to = kv("hdr_from"), kv("hdr_to")
+    else:
+        s = N.nbg_cull_batch()
+        for f, ct in (("k_off", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32), ("t_off", C.c_uint32),
+                      ("t_sec", C.c_int64), ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32),
+                      ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)):
+            setattr(s, f, p(f, ct))
+    return s
+
+
+class CpuReference:
+    """The CPU restatement of the Go path (semantic oracle: whole objects, reflect.DeepEqual
+    walk, RFC3339 strings) on `threads` threads over a bounded sample of notebooks."""
+
+    def __init__(self, pkg, O, sample, seed, threads):
+        host = pkg.host
+        self.sample, self.threads, self.L = sample, threads, O.lib()
+        fleet = host.Fleet(host.FLEET_KUBEFLOW, seed, sample, max(sample // 50, 1))
+        self.objs = fleet.objects(0, sample)
+        vp = C.c_void_p
+        self.arrs = []
+        for a, b in (("sts_from", "sts_to"), ("svc_from", "svc_to"), ("vs_from", "vs_to")):
+            self.arrs.append(((vp * sample)(*[o[a]._h for o in self.objs]), (vp * sample)(*[o[b]._h for o in self.objs])))
+        self.cf = host.CullFleet(seed + 1, sample)
+        self.texts = [self.cf.json(i).encode() for i in range(sample)]
+        self.jarr = (C.c_char_p * sample)(*self.texts)
+
+    def step(self):
+        """One pass of all four predicates over the sample; seconds inside the oracle loops."""
+        t = 0.0
+        for kind in range(3):
+            t += self.L.orc_bench_pairs(kind, self.arrs[kind][0], self.arrs[kind][1], self.sample, self.threads, None)
+        t += self.L.orc_bench_cull(self.jarr, self.sample, self.cf.now_sec, self.cf.now_nsec, 1440, 1, 1, self.threads, None, None)
+        return t
+
+    def rate(self, min_cpu_seconds=10.0, max_reps=64):
+        total, reps = 0.0, 0
+        while reps < max_reps and (total * self.threads < min_cpu_seconds or reps < 2):
+            total += self.step()
+            reps += 1
+        return self.sample * reps / total, {"sample_notebooks": self.sample, "repetitions": reps,
+                                            "cpu_seconds": round(total * self.threads, 2)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's algorithm on the host cores (the Go code itself
+    cannot be built in this image; the oracle port stands in, kind = "port")."""
+    if rank != 0:
+        return
+    pkg = importlib.import_module("odh-kubeflow_b200")
+    import oracle as O
+    threads = os.cpu_count() or 1
+    ref = CpuReference(pkg, O, args.cpu_sample, pkg.host.SEED_BASE + 5, threads)
+    secs = []
+    t0 = time.time()
+    for s in range(args.warmup + args.steps):
+        t = ref.step()
+        if s >= args.warmup:
+            secs.append(t)
+        if time.time() - t0 > 200 and len(secs) >= 1:
+            break
+    value = args.cpu_sample / statistics.median(secs)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": len(secs),
+            "warmup": args.warmup, "ms_per_step": 1000.0 * statistics.median(secs), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "config #5 share: %d-notebook sample of the 10M-notebook fleet per step, all 4 predicates per notebook"
+                                   % args.cpu_sample, "note": "CPU port of the Go predicates (semantic oracle); Go itself unavailable on this box"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": "%d notebooks per step, object-level DeepEqual + RFC3339 strings" % args.cpu_sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("odh-kubeflow_b200")
+    host, N = pkg.host, pkg._native
+    dev = importlib.import_module("odh-kubeflow_b200.device")
+    import oracle as O  # checker + cpu_baseline leg only
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # host threads are shared by the ranks of this node
+    if "NBH_THREADS" not in os.environ:
+        os.environ["NBH_THREADS"] = str(max(1, (os.cpu_count() or 1) // world))
+    ctx = pkg.Context([local])
+    lib = N.nbg()
+
+    # ---- this rank's shard of the fleet: namespaces are partitioned by nbg_shard_of, every
+    # shard takes the same number of notebooks (weak scaling)
+    per = args.per_gpu
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, per * world * 4, max(200, per * world // 50))
+    t0 = time.time()
+    idx = fleet.shard_indices(world, rank)[:per] if world > 1 else np.arange(per, dtype=np.uint64)
+    assert len(idx) == per, "shard too small"
+    sts, svc, vs = fleet.pack(idx=idx)
+    cfleet = host.CullFleet(host.SEED_BASE + 5 + 1000 * rank, per)
+    cull = cfleet.pack()
+    pack_s = time.time() - t0
+    now = (cfleet.now_sec, cfleet.now_nsec)
+
+    d_sts, d_svc, d_vs, d_cull = (dev.DeviceBatch.from_host(b, device=local) for b in (sts, svc, vs, cull))
+    batches = [("diff_sts", d_sts), ("diff_svc", d_svc), ("diff_vs", d_vs), ("cull", d_cull)]
+    alg_bytes = {name: b.algorithmic_bytes for name, b in batches}
+
+    def launch(name, b):
+        if name == "cull":
+            return b.run(ctx, now=now, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE)
+        return b.run(ctx)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: inputs resident in HBM
+    for _ in range(max(args.warmup, 3)):
+        for name, b in batches:
+            launch(name, b)
+    barrier()
+    sampler = ClockSampler(local)
+    ev = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in batches] for _ in range(args.steps)]
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = ctx.launch_count()
+    start.record()
+    for s in range(args.steps):
+        for k, (name, b) in enumerate(batches):
+            ev[s][k][0].record()
+            launch(name, b)
+            ev[s][k][1].record()
+    stop.record()
+    barrier()
+    gpu_launches = ctx.launch_count() - launches0
+    clocks = sampler.stop()
+    ms_total = start.elapsed_time(stop)
+    kernel_ms = {name: statistics.mean(ev[s][k][0].elapsed_time(ev[s][k][1]) for s in range(args.steps))
+                 for k, (name, _) in enumerate(batches)}
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    units = torch.tensor([float(per)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(units, op=dist.ReduceOp.SUM)
+    ms_step = t.item() / args.steps
+    value = units.item() / (ms_step / 1000.0)
+
+    # ---- parity of what was just computed (outside the timed region)
+    want = {"diff_sts": O.packed_diff_sts(sts, threads=8), "diff_svc": O.packed_diff_svc(svc, threads=8),
+            "diff_vs": O.packed_diff_vs(vs, threads=8), "cull": O.packed_cull(cull, now, 1440, 1, 1, threads=8)}
+    parity = True
+    for name, b in batches:
+        outs = [o.cpu().numpy() for o in b.outs]
+        parity &= bool(np.array_equal(outs[0], want[name][0]))
+        parity &= bool(np.array_equal(outs[-1].view(np.uint64), want[name][3 if name == "cull" else 1]))
+    if not parity:
+        raise SystemExit("bench: device results differ from the packed oracle")
+
+    # ---- e2e: the host-buffer C ABI with pinned host memory, copies inside the timed region
+    keep = []
+    views, outs_h = {}, {}
+    words = (per + 63) // 64
+    for kind, b in (("sts", sts), ("svc", svc), ("vs", vs), ("cull", cull)):
+        views[kind] = (struct_over(N, kind, pinned_copy(lib, b.arrays(), keep)), sum(a.nbytes for a in b.arrays().values()))
+    out_arr = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64), "a": np.zeros(per, np.uint32),
+                                "b2": np.zeros(words, np.uint64)}, keep)
+    rp, bp, ap_, b2p = (out_arr[k].ctypes.data_as(C.c_void_p) for k in ("r", "b", "a", "b2"))
+    params = N.nbg_cull_params(now[0], now[1], 1440, 1, N.CULL_RECONCILE)
+
+    def e2e_step():
+        rc = lib.nbg_diff_sts(ctx.handle, C.byref(views["sts"][0]), per, rp, bp)
+        rc |= lib.nbg_diff_svc(ctx.handle, C.byref(views["svc"][0]), per, rp, bp)
+        rc |= lib.nbg_diff_vs(ctx.handle, C.byref(views["vs"][0]), per, rp, bp)
+        rc |= lib.nbg_cull(ctx.handle, C.byref(views["cull"][0]), per, C.byref(params), rp, ap_, bp, b2p)
+        if rc:
+            raise SystemExit("bench: e2e call failed")
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = units.item() / te.item()
+    h2d = sum(v[1] for v in views.values())
+    d2h = 3 * (per + words * 8) + (per + 4 * per + 2 * words * 8)  # 3x (reason + bitmap); action + argmax + 2 bitmaps
+    assert np.array_equal(out_arr["r"], want["cull"][0]), "e2e cull action differs from the oracle"
+    for p in keep:
+        lib.nbg_free_pinned(p)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = peaks()
+    sts_gbs = alg_bytes["diff_sts"] / (kernel_ms["diff_sts"] * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+        "data": "synthetic",
+        "config": {"workload": "config #5 share: %d Notebooks per GPU (10M / 8), StatefulSet+Service+VirtualService diff + culler "
+                               "decision per Notebook" % per,
+                   "object": "one Notebook = 3 desired/live pairs + its kernel/terminal records",
+                   "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
+                   "l2": "inputs (%.1f GB per GPU) exceed L2; no flush needed" % (sum(alg_bytes.values()) / 1e9),
+                   "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI calls, max over ranks"},
+        "gpu_launches": int(gpu_launches),
+        "roofline": {"bound": "hbm", "kernel": "diff_sts_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
+                     "frac": sts_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(alg_bytes["diff_sts"]), "avg_launch_ms": kernel_ms["diff_sts"]},
+        "kernels": {name: {"avg_ms": kernel_ms[name], "GBps": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9,
+                           "frac_of_peak": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9 / peak} for name, _ in batches},
+        "parity": "bit-exact vs packed oracle on all %d objects x 4 kernels (device path) and cull (e2e path)" % per,
+        "host_pack": {"objects_per_s": per / pack_s, "threads": int(os.environ["NBH_THREADS"]), "seconds": pack_s},
+    }
+    if world == 1:
+        threads = os.cpu_count() or 1
+        rate, info = CpuReference(pkg, O, args.cpu_sample, host.SEED_BASE + 5, threads).rate()
+        # also the packed loops (the CPU version of OUR algorithm) for context
+        t_packed = sum(x[-1] for x in (O.packed_diff_sts(sts, threads=threads), O.packed_diff_svc(svc, threads=threads),
+                                       O.packed_diff_vs(vs, threads=threads), O.packed_cull(cull, now, 1440, 1, 1, threads=threads)))
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": "%(sample_notebooks)d notebooks x %(repetitions)d repetitions (%(cpu_seconds)s CPU-s): "
+                                          "object-level CopyStatefulSetFields/ServiceFields/VirtualService + culler on RFC3339 strings" % info,
+                                "packed_loops_value": per / t_packed,
+                                "packed_loops_note": "plain C loops over the same SoA batches, all %d objects, %d threads" % (per, threads)}
+        if not args.no_extra:
+            line["other_configs"] = other_configs(pkg, dev, ctx, torch, peak)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def other_configs(pkg, dev, ctx, torch, peak):
+    """Device-timed numbers for BASELINE configs #2, #3, #4 (parity for these is in tests/)."""
+    host, N = pkg.host, pkg._native
+    out = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def timed(b, reps=20, **kw):
+        ms = []
+        for _ in range(3):
+            b.run(ctx, **kw)
+        for _ in range(reps):
+            flush.fill_(1)
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); b.run(ctx, **kw); e.record()
+            torch.cuda.synchronize()
+            ms.append(s.elapsed_time(e))
+        return statistics.median(ms)
+
+    f2 = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 2, 10_000, 200)
+    sts, svc, _ = f2.pack(vs=False)
+    ms = timed(dev.DeviceBatch.from_host(sts)) + timed(dev.DeviceBatch.from_host(svc))
+    out["config2_10k_sts_svc"] = {"objects_per_s": 10_000 / (ms * 1e-3), "ms": ms, "roofline": "n/a (36 MB, launch-bound; L2 flushed between launches)"}
+    cf = host.CullFleet(host.SEED_BASE + 3, 250_000)
+    cb = cf.pack()
+    d = dev.DeviceBatch.from_host(cb)
+    ms = timed(d, now=(cf.now_sec, cf.now_nsec))
+    out["config3_1M_kernel_records"] = {"records_per_s": sum(cb.records()) / (ms * 1e-3), "notebooks_per_s": 250_000 / (ms * 1e-3), "ms": ms,
+                                        "GBps": d.algorithmic_bytes / (ms * 1e-3) / 1e9, "roofline": "n/a (22 MB, launch-bound; L2 flushed)"}
+    f4 = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 100_000, 2000)
+    sts, _, vs = f4.pack(svc=False)
+    d1, d2 = dev.DeviceBatch.from_host(sts), dev.DeviceBatch.from_host(vs)
+    m1, m2 = timed(d1), timed(d2)
+    out["config4_100k_odh_sts_vs"] = {"objects_per_s": 100_000 / ((m1 + m2) * 1e-3), "ms": m1 + m2,
+                                      "sts_GBps": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9, "sts_frac_of_peak": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9 / peak}
+    return out
+
+
+if __name__ == "__main__":
+    main()

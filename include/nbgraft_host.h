@@ -116,6 +116,12 @@ uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i);   /* nbg_hash64(name
 int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                    nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
 
+/* Indices i in [0,n) whose namespace maps to `shard` of `n_shards` (nbg_shard_of), ascending.
+ * Returns the count; writes at most cap of them (call with out=NULL to size). */
+uint64_t nbh_fleet_shard_indices(const nbh_fleet* f, uint32_t n_shards, uint32_t shard, uint64_t* out, uint64_t cap);
+/* Materialise objects of m notebooks at once: out[k*7 + which] (see nbh_fleet_get). */
+int nbh_fleet_objects(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_obj** out);
+
 nbh_cullfleet* nbh_cullfleet_new(uint64_t seed, uint64_t n, int64_t now_sec, int32_t now_nsec, double mean_kernels);
 void nbh_cullfleet_free(nbh_cullfleet* f);
 char* nbh_cullfleet_json(const nbh_cullfleet* f, uint64_t i);  /* free with nbh_str_free */

@@ -170,6 +170,8 @@ def _bind_nbh(lib):
         "nbh_cullfleet_json": ([_vp, C.c_uint64], _vp),
         "nbh_cullfleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp)], C.c_int),
         "nbh_threads": ([], C.c_int),
+        "nbh_fleet_shard_indices": ([_vp, C.c_uint32, C.c_uint32, u64p, C.c_uint64], C.c_uint64),
+        "nbh_fleet_objects": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp)], C.c_int),
     }
     for name, (args, res) in sig.items():
         f = getattr(lib, name)
@@ -186,7 +188,7 @@ NBH_SYMBOLS = [
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
     "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
-    "nbh_cullfleet_pack", "nbh_threads",
+    "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
 ]
 
 _nbg = None

@@ -334,6 +334,44 @@ NBH_API uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i) {
 
 NBH_API int nbh_threads(void) { return host_threads(); }
 
+NBH_API uint64_t nbh_fleet_shard_indices(const nbh_fleet* f, uint32_t n_shards, uint32_t shard, uint64_t* out,
+                                         uint64_t cap) {
+  if (!f || n_shards == 0) return 0;
+  const uint64_t n = f->f.n, kBlock = 65536, nblocks = (n + kBlock - 1) / kBlock;
+  // the namespace -> shard map is tiny: compute it once per namespace
+  std::vector<uint8_t> mine(f->f.n_namespaces);
+  for (uint32_t k = 0; k < f->f.n_namespaces; ++k) {
+    char buf[32];
+    snprintf(buf, sizeof buf, "ns-%06u", k);
+    mine[k] = nbg_shard_of_inline(nbg_hash_bytes(buf, strlen(buf)), n_shards) == shard;
+  }
+  std::vector<std::vector<uint64_t>> parts(nblocks);
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < n ? lo + kBlock : n;
+    for (uint64_t i = lo; i < hi; ++i)
+      if (mine[f->f.namespace_of(i)]) parts[blk].push_back(i);
+  });
+  uint64_t count = 0;
+  for (const auto& v : parts)
+    for (uint64_t i : v) { if (out && count < cap) out[count] = i; ++count; }
+  return count;
+}
+
+NBH_API int nbh_fleet_objects(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_obj** out) {
+  if (!f || !out) return -1;
+  const uint64_t kBlock = 256, nblocks = (m + kBlock - 1) / kBlock;
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
+    Pair p;
+    for (uint64_t k = lo; k < hi; ++k) {
+      fleet_make(f->f, idx ? idx[k] : i0 + k, &p);
+      GVal* src[] = {&p.notebook, &p.sts_from, &p.sts_to, &p.svc_from, &p.svc_to, &p.vs_from, &p.vs_to};
+      for (int w = 0; w < 7; ++w) { nbh_obj* o = new nbh_obj(); o->v = std::move(*src[w]); out[k * 7 + w] = o; }
+    }
+  });
+  return 0;
+}
+
 NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                            nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
   if (!f) return -1;

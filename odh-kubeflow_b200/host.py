@@ -334,12 +334,28 @@ class Fleet:
         return (StsBatch(a.value) if sts else None, SvcBatch(b.value) if svc else None,
                 VsBatch(c.value) if vs else None)
 
-    def shard_indices(self, n_shards):
-        """Bucket object indices by nbg_shard_of(hash(namespace)) — SURVEY.md 8(e)."""
-        lib = N.nbg()
-        shard = np.fromiter((lib.nbg_shard_of(self.ns_hash(i), n_shards) for i in range(self.n)), dtype=np.uint32,
-                            count=self.n)
-        return [np.nonzero(shard == s)[0].astype(np.uint64) for s in range(n_shards)]
+    def shard_indices(self, n_shards, shard=None):
+        """Bucket object indices by nbg_shard_of(hash(namespace)) — SURVEY.md 8(e).
+        Returns the list of all shards' index arrays, or one shard's array."""
+        def one(s):
+            cnt = N.nbh().nbh_fleet_shard_indices(self._h, n_shards, s, None, 0)
+            out = np.empty(cnt, dtype=np.uint64)
+            N.nbh().nbh_fleet_shard_indices(self._h, n_shards, s, out.ctypes.data_as(N.u64p), cnt)
+            return out
+        return one(shard) if shard is not None else [one(s) for s in range(n_shards)]
+
+    def objects(self, i0=0, m=None, idx=None):
+        """All seven objects of m notebooks at once -> list of dicts name -> Obj."""
+        if idx is not None:
+            idx = np.ascontiguousarray(idx, dtype=np.uint64)
+            m, ip = len(idx), idx.ctypes.data_as(N.u64p)
+        else:
+            m, ip = (self.n - i0 if m is None else m), None
+        out = (C.c_void_p * (m * 7))()
+        if N.nbh().nbh_fleet_objects(self._h, ip, i0, m, out) != 0:
+            raise HostError("fleet_objects")
+        names = sorted(self.WHICH, key=self.WHICH.get)
+        return [{nm: Obj(out[k * 7 + w]) for w, nm in enumerate(names)} for k in range(m)]
 
     def __del__(self):
         try:
