@@ -278,7 +278,6 @@ def main():
     stop.record()
     barrier()
     gpu_launches = ctx.launch_count() - launches0
-    clocks = sampler.stop()
     ms_total = start.elapsed_time(stop)
     kernel_ms = {name: statistics.mean(ev[s][k][0].elapsed_time(ev[s][k][1]) for s in range(args.steps))
                  for k, (name, _) in enumerate(batches)}
@@ -328,6 +327,7 @@ def main():
         e2e_step()
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
+    clocks = sampler.stop()  # sampled from the start of the device-timed steps to the end of the e2e steps
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)

@@ -221,8 +221,9 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n,
 /* ---- device-pointer entry points (asynchronous, no copies) ------------- */
 /* Same kernels on buffers already resident in HBM.  Every pointer inside the
  * batch and every output is a DEVICE pointer on `device` (an index into the
- * list given to nbg_init); `stream` is a cudaStream_t (NULL = the context's
- * own stream).  The call only enqueues work.  CSR offsets are NOT validated
+ * list given to nbg_init); `stream` is a cudaStream_t, passed through as is
+ * (NULL = the CUDA default stream; nbg_ctx_stream() gives the context's own
+ * non-blocking stream).  The call only enqueues work.  CSR offsets are NOT validated
  * here (the host-buffer calls validate them before upload). */
 int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
                         uint8_t* reason, uint64_t* bitmap, void* stream);
@@ -234,6 +235,8 @@ int nbg_cull_device(nbg_ctx* ctx, int device, const nbg_cull_batch* in, uint64_t
                     const nbg_cull_params* params,
                     uint8_t* action, uint32_t* argmax,
                     uint64_t* cull_bitmap, uint64_t* period_bitmap, void* stream);
+/* The context's own (non-blocking) run stream on `device`, as a cudaStream_t. */
+void* nbg_ctx_stream(nbg_ctx* ctx, int device);
 /* Block until everything enqueued on the context's own stream of `device` is done. */
 int nbg_sync(nbg_ctx* ctx, int device);
 /* Number of kernels this library has launched since nbg_init (all devices). */

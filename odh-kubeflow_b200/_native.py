@@ -91,7 +91,7 @@ NBG_SYMBOLS = [
     "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of",
     "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull",
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
-    "nbg_sync", "nbg_launch_count",
+    "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
 ]
 
 _vp = C.c_void_p
@@ -127,6 +127,8 @@ def _bind_nbg(lib):
     lib.nbg_cull_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_cull_batch), C.c_uint64, C.POINTER(nbg_cull_params),
                                     _vp, _vp, _vp, _vp, _vp]
     lib.nbg_cull_device.restype = C.c_int
+    lib.nbg_ctx_stream.argtypes = [_vp, C.c_int]
+    lib.nbg_ctx_stream.restype = _vp
     lib.nbg_sync.argtypes = [_vp, C.c_int]
     lib.nbg_sync.restype = C.c_int
     lib.nbg_launch_count.argtypes = [_vp]

@@ -279,6 +279,11 @@ void* nbg_alloc_pinned(size_t bytes) {
 }
 void nbg_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
+void* nbg_ctx_stream(nbg_ctx* ctx, int device) {
+  if (check_dev(ctx, device) != NBG_OK) return nullptr;
+  return (void*)ctx->devs[device]->s_run;
+}
+
 int nbg_sync(nbg_ctx* ctx, int device) {
   if (int rc = check_dev(ctx, device)) return rc;
   CU(cudaSetDevice(ctx->devs[device]->id));
@@ -300,7 +305,7 @@ int nbg_cull_device(nbg_ctx* ctx, int device, const nbg_cull_batch* in, uint64_t
       p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
     return NBG_E_INVAL;
   CU(cudaSetDevice(ctx->devs[device]->id));
-  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  cudaStream_t s = (cudaStream_t)stream;
   CU(nbg_launch_cull(in, n, p, 0, 0, action, argmax, cull_bitmap, period_bitmap, s));
   ctx->launches++;
   return NBG_OK;
@@ -313,7 +318,7 @@ int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint6
   if (n == 0) return NBG_OK;
   if (!reason || !bitmap) return NBG_E_INVAL;
   CU(cudaSetDevice(ctx->devs[device]->id));
-  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[4] = {0, 0, 0, 0};
   CU(nbg_launch_diff_sts(in, n, bases, reason, bitmap, s));
   ctx->launches++;
@@ -327,7 +332,7 @@ int nbg_diff_svc_device(nbg_ctx* ctx, int device, const nbg_svc_batch* in, uint6
   if (n == 0) return NBG_OK;
   if (!reason || !bitmap) return NBG_E_INVAL;
   CU(cudaSetDevice(ctx->devs[device]->id));
-  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[6] = {0, 0, 0, 0, 0, 0};
   CU(nbg_launch_diff_svc(in, n, bases, reason, bitmap, s));
   ctx->launches++;
@@ -341,7 +346,7 @@ int nbg_diff_vs_device(nbg_ctx* ctx, int device, const nbg_vs_batch* in, uint64_
   if (n == 0) return NBG_OK;
   if (!reason || !bitmap) return NBG_E_INVAL;
   CU(cudaSetDevice(ctx->devs[device]->id));
-  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->devs[device]->s_run;
+  cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[2] = {0, 0};
   CU(nbg_launch_diff_vs(in, n, bases, reason, bitmap, s));
   ctx->launches++;
