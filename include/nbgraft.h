@@ -218,6 +218,19 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n,
              uint8_t* action, uint32_t* argmax,
              uint64_t* cull_bitmap, uint64_t* period_bitmap);
 
+/* Batched "find the StatefulSet this Notebook controls": the loop over the
+ * namespace's StatefulSets with metav1.IsControlledBy at NBCTL:157-170, as a hash
+ * join.  nb_key[i] = nbg_join_key(hash64(namespace), hash64(metadata.uid)) of
+ * Notebook i; sts_key[j] = the same for StatefulSet j's namespace and the UID of
+ * its controller owner reference, or 0 when it has none.  match[i] = the lowest j
+ * with sts_key[j] == nb_key[i] (the first list entry, as the reference's `break`
+ * picks), or NBG_ARGMAX_NONE => the Notebook has no StatefulSet yet (NBCTL:172-183
+ * creates it).  m < 2^31. */
+int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n,
+                   const uint64_t* sts_key, uint64_t m, uint32_t* match);
+/* never 0 */
+uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
+
 /* ---- device-pointer entry points (asynchronous, no copies) ------------- */
 /* Same kernels on buffers already resident in HBM.  Every pointer inside the
  * batch and every output is a DEVICE pointer on `device` (an index into the
@@ -235,6 +248,13 @@ int nbg_cull_device(nbg_ctx* ctx, int device, const nbg_cull_batch* in, uint64_t
                     const nbg_cull_params* params,
                     uint8_t* action, uint32_t* argmax,
                     uint64_t* cull_bitmap, uint64_t* period_bitmap, void* stream);
+/* Device form of nbg_owner_join.  `scratch` is device memory for the join's hash
+ * table: nbg_owner_join_scratch_bytes(m) bytes, 8-byte aligned, contents
+ * irrelevant on entry (the call clears it), clobbered on return. */
+size_t nbg_owner_join_scratch_bytes(uint64_t m);
+int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint64_t n,
+                          const uint64_t* sts_key, uint64_t m, uint32_t* match,
+                          void* scratch, size_t scratch_bytes, void* stream);
 /* The context's own (non-blocking) run stream on `device`, as a cudaStream_t. */
 void* nbg_ctx_stream(nbg_ctx* ctx, int device);
 /* Block until everything enqueued on the context's own stream of `device` is done. */

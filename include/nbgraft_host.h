@@ -45,6 +45,10 @@ char* nbh_obj_to_json(const nbh_obj* o);
 void nbh_str_free(char* s);
 /* Copy of the sub-object at a dotted field path ("spec.template.spec"); -1 if absent. */
 int nbh_obj_get(const nbh_obj* o, const char* dotted_path, nbh_obj** out);
+/* Edit in place: remove the field / set a string field at a dotted path; list elements are
+ * addressed by number ("metadata.ownerReferences.0.uid"). */
+int nbh_obj_erase(nbh_obj* o, const char* dotted_path);
+int nbh_obj_set_str(nbh_obj* o, const char* dotted_path, const char* value);
 /* canonical digest of the whole value: equal digests <=> reflect.DeepEqual (mod 2^-64) */
 uint64_t nbh_obj_digest(const nbh_obj* o);
 
@@ -104,6 +108,13 @@ int nbh_parse_rfc3339(const char* s, int64_t* sec, int32_t* nsec, int32_t* offse
 /* t.Format(time.RFC3339) */
 int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_t buflen);
 
+/* ---- owner join keys (NBCTL:157-170) -------------------------------------- */
+/* key of an owner (Notebook): nbg_join_key(hash(namespace), hash(metadata.uid)) */
+uint64_t nbh_join_key_owner(const nbh_obj* owner);
+/* key of a dependent (StatefulSet): its namespace + the UID of its controller owner reference
+ * (metav1.GetControllerOf: first reference with controller == true), 0 if there is none */
+uint64_t nbh_join_key_controlled(const nbh_obj* obj);
+
 /* ---- synthetic fleets ------------------------------------- */
 /* kind: 2 = Kubeflow loadtest-shaped notebooks (configs #2/#5), 4 = ODH-webhook-shaped (#4) */
 nbh_fleet* nbh_fleet_new(int kind, uint64_t seed, uint64_t n, uint32_t n_namespaces);
@@ -121,6 +132,11 @@ int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_
 uint64_t nbh_fleet_shard_indices(const nbh_fleet* f, uint32_t n_shards, uint32_t shard, uint64_t* out, uint64_t cap);
 /* Materialise objects of m notebooks at once: out[k*7 + which] (see nbh_fleet_get). */
 int nbh_fleet_objects(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_obj** out);
+
+/* Synthetic StatefulSet list for notebooks [0,n) in seeded random order (see hostapi.cpp);
+ * returns its length m (call with NULL outputs to size; at most cap entries are written). */
+uint64_t nbh_fleet_join_lists(const nbh_fleet* f, uint64_t n, uint64_t* nb_keys, uint64_t* sts_keys,
+                              int64_t* sts_owner, uint64_t cap);
 
 nbh_cullfleet* nbh_cullfleet_new(uint64_t seed, uint64_t n, int64_t now_sec, int32_t now_nsec, double mean_kernels);
 void nbh_cullfleet_free(nbh_cullfleet* f);

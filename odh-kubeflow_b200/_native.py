@@ -18,7 +18,8 @@ class NativeLibraryMissing(ImportError):
 
 
 def _load(name):
-    path = os.path.join(_HERE, name)
+    # NBGRAFT_LIB points at an alternative build of libnbgraft.so (kernel variants under tools/)
+    path = os.environ.get("NBGRAFT_LIB") if name == "libnbgraft.so" and os.environ.get("NBGRAFT_LIB") else os.path.join(_HERE, name)
     if not os.path.exists(path):
         raise NativeLibraryMissing(
             f"{path} is not built. Run `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -92,6 +93,7 @@ NBG_SYMBOLS = [
     "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull",
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
+    "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
 ]
 
 _vp = C.c_void_p
@@ -127,6 +129,14 @@ def _bind_nbg(lib):
     lib.nbg_cull_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_cull_batch), C.c_uint64, C.POINTER(nbg_cull_params),
                                     _vp, _vp, _vp, _vp, _vp]
     lib.nbg_cull_device.restype = C.c_int
+    lib.nbg_owner_join.argtypes = [_vp, _vp, C.c_uint64, _vp, C.c_uint64, _vp]
+    lib.nbg_owner_join.restype = C.c_int
+    lib.nbg_join_key.argtypes = [C.c_uint64, C.c_uint64]
+    lib.nbg_join_key.restype = C.c_uint64
+    lib.nbg_owner_join_scratch_bytes.argtypes = [C.c_uint64]
+    lib.nbg_owner_join_scratch_bytes.restype = C.c_size_t
+    lib.nbg_owner_join_device.argtypes = [_vp, C.c_int, _vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp, C.c_size_t, _vp]
+    lib.nbg_owner_join_device.restype = C.c_int
     lib.nbg_ctx_stream.argtypes = [_vp, C.c_int]
     lib.nbg_ctx_stream.restype = _vp
     lib.nbg_sync.argtypes = [_vp, C.c_int]
@@ -145,6 +155,8 @@ def _bind_nbh(lib):
         "nbh_obj_to_json": ([_vp], _vp),
         "nbh_str_free": ([_vp], None),
         "nbh_obj_get": ([_vp, cp, P(_vp)], C.c_int),
+        "nbh_obj_erase": ([_vp, cp], C.c_int),
+        "nbh_obj_set_str": ([_vp, cp, cp], C.c_int),
         "nbh_obj_digest": ([_vp], C.c_uint64),
         "nbh_generate_statefulset": ([_vp, P(nbh_env), P(_vp), cp, sz], C.c_int),
         "nbh_generate_service": ([_vp, P(_vp), cp, sz], C.c_int),
@@ -172,6 +184,9 @@ def _bind_nbh(lib):
         "nbh_cullfleet_json": ([_vp, C.c_uint64], _vp),
         "nbh_cullfleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp)], C.c_int),
         "nbh_threads": ([], C.c_int),
+        "nbh_join_key_owner": ([_vp], C.c_uint64),
+        "nbh_join_key_controlled": ([_vp], C.c_uint64),
+        "nbh_fleet_join_lists": ([_vp, C.c_uint64, u64p, u64p, i64p, C.c_uint64], C.c_uint64),
         "nbh_fleet_shard_indices": ([_vp, C.c_uint32, C.c_uint32, u64p, C.c_uint64], C.c_uint64),
         "nbh_fleet_objects": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp)], C.c_int),
     }
@@ -183,7 +198,7 @@ def _bind_nbh(lib):
 
 
 NBH_SYMBOLS = [
-    "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_digest",
+    "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_erase", "nbh_obj_set_str", "nbh_obj_digest",
     "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate",
     "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
     "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_cull_new", "nbh_cull_free",
@@ -191,6 +206,7 @@ NBH_SYMBOLS = [
     "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
     "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
+    "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",
 ]
 
 _nbg = None

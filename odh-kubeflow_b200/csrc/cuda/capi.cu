@@ -28,6 +28,9 @@ cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const 
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
                                uint64_t*, cudaStream_t);
+unsigned long long nbg_join_table_slots(unsigned long long m);
+cudaError_t nbg_launch_owner_join(const unsigned long long*, unsigned long long, const unsigned long long*,
+                                  unsigned long long, uint32_t*, void*, cudaStream_t);
 }
 
 namespace {
@@ -52,6 +55,8 @@ struct Dev {
   int id = 0;
   cudaStream_t s_in = nullptr, s_run = nullptr;
   Slot slot[2];
+  char* scratch = nullptr;   // grow-only kernel scratch (the owner join's hash table)
+  size_t scratch_cap = 0;
   std::mutex mu;
 };
 
@@ -257,6 +262,7 @@ void nbg_destroy(nbg_ctx* ctx) {
     cudaSetDevice(d->id);
     if (d->s_run) cudaStreamSynchronize(d->s_run);
     if (d->s_in) cudaStreamSynchronize(d->s_in);
+    if (d->scratch) cudaFree(d->scratch);
     for (auto& sl : d->slot) {
       if (sl.dev) cudaFree(sl.dev);
       if (sl.in_done) cudaEventDestroy(sl.in_done);
@@ -353,7 +359,59 @@ int nbg_diff_vs_device(nbg_ctx* ctx, int device, const nbg_vs_batch* in, uint64_
   return NBG_OK;
 }
 
+size_t nbg_owner_join_scratch_bytes(uint64_t m) { return (size_t)nbg_join_table_slots(m) * 12u; }
+
+uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash) {
+  const uint64_t k = nbg_combine(nbg_combine(0x6A6F696E6B657921ull, ns_hash), uid_hash);
+  return k ? k : 1;
+}
+
+int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint64_t n,
+                          const uint64_t* sts_key, uint64_t m, uint32_t* match,
+                          void* scratch, size_t scratch_bytes, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (n == 0) return NBG_OK;
+  if (!nb_key || !match || (m && !sts_key) || !scratch) return NBG_E_INVAL;
+  if (m >= (1ull << 31)) return NBG_E_TOOBIG;
+  if (scratch_bytes < nbg_owner_join_scratch_bytes(m) || ((uintptr_t)scratch & 7u)) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  CU(nbg_launch_owner_join((const unsigned long long*)nb_key, n, (const unsigned long long*)sts_key, m, match,
+                           scratch, (cudaStream_t)stream));
+  ctx->launches += m ? 2 : 1;
+  return NBG_OK;
+}
+
 // ------------------------------------------------------------ host-buffer API
+int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n, const uint64_t* sts_key, uint64_t m,
+                   uint32_t* match) {
+  if (!ctx) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!nb_key || !match || (m && !sts_key)) return NBG_E_INVAL;
+  if (m >= (1ull << 31)) return NBG_E_TOOBIG;
+  // One device: the join is a single table; a multi-device context uses its first device.
+  Dev& d = *ctx->devs[0];
+  std::unique_lock<std::mutex> lock(d.mu);
+  CU(cudaSetDevice(d.id));
+  const size_t need = nbg_owner_join_scratch_bytes(m);
+  if (d.scratch_cap < need) {
+    CU(cudaStreamSynchronize(d.s_run));
+    if (d.scratch) { CU(cudaFree(d.scratch)); d.scratch = nullptr; d.scratch_cap = 0; }
+    if (!cuda_ok(cudaMalloc(&d.scratch, need), "cudaMalloc(join table)")) { d.scratch = nullptr; return NBG_E_NOMEM; }
+    d.scratch_cap = need;
+  }
+  Slot& sl = d.slot[0];
+  Layout lay;
+  const size_t a_nb = lay.in(nb_key, n * 8), a_sts = lay.in(sts_key, m * 8);
+  const size_t o_match = lay.out(match, n * 4);
+  if (int rc = slot_upload(d, sl, lay)) return rc;
+  CU(nbg_launch_owner_join((const unsigned long long*)(sl.dev + a_nb), n, (const unsigned long long*)(sl.dev + a_sts), m,
+                           (uint32_t*)(sl.dev + o_match), d.scratch, d.s_run));
+  ctx->launches += m ? 2 : 1;
+  if (int rc = slot_download(d, sl, lay)) return rc;
+  CU(cudaStreamSynchronize(d.s_run));
+  return NBG_OK;
+}
+
 int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_params* p,
              uint8_t* action, uint32_t* argmax, uint64_t* cull_bitmap, uint64_t* period_bitmap) {
   if (!ctx || !in || !p) return NBG_E_INVAL;

@@ -224,6 +224,11 @@ GVal make_notebook(const Fleet& f, uint64_t i, Rng& r) {
   GVal meta = GVal::strct();
   meta.set("name", GVal::str(name));
   meta.set("namespace", GVal::str(ns));
+  {
+    char uid[40];
+    snprintf(uid, sizeof uid, "%016llx-nb", (unsigned long long)nbg_mix64(f.seed ^ (i * 0x9E3779B97F4A7C15ull)));
+    meta.set("uid", GVal::str(uid));
+  }
   GVal labels = GVal::map();
   const int nl = 3 + (int)r.below(4);
   for (int k = 0; k < nl; ++k) {
@@ -374,6 +379,20 @@ void fleet_make(const Fleet& f, uint64_t i, Pair* out) {
   generate_statefulset(out->notebook, f.env, &out->sts_from, &err);
   generate_service(out->notebook, &out->svc_from, &err);
   generate_virtualservice(out->notebook, f.env, &out->vs_from, &err);
+  {  // ctrl.SetControllerReference(instance, ss, r.Scheme) — NBCTL:153,208
+    const GVal* nbm = out->notebook.find("metadata");
+    GVal ref = GVal::strct();
+    ref.set("apiVersion", GVal::str("kubeflow.org/v1beta1"));
+    ref.set("kind", GVal::str("Notebook"));
+    ref.set("name", GVal::str(nbm->get_str("name")));
+    ref.set("uid", GVal::str(nbm->get_str("uid")));
+    ref.set("controller", GVal::ptr(GVal::boolean(true)));
+    ref.set("blockOwnerDeletion", GVal::ptr(GVal::boolean(true)));
+    GVal refs = GVal::list();
+    refs.items.push_back(std::move(ref));
+    out->sts_from.find("metadata")->set("ownerReferences", refs);
+    out->svc_from.find("metadata")->set("ownerReferences", refs);
+  }
   out->sts_to = out->sts_from;
   out->svc_to = out->svc_from;
   out->vs_to = out->vs_from;

@@ -152,7 +152,7 @@ NBH_API int nbh_obj_get(const nbh_obj* o, const char* dotted_path, nbh_obj** out
   const GVal* cur = &o->v;
   std::string path(dotted_path);
   size_t at = 0;
-  while (at <= path.size() && !path.empty()) {
+  while (!path.empty()) {
     const size_t dot = path.find('.', at);
     const std::string key = path.substr(at, dot == std::string::npos ? std::string::npos : dot - at);
     while (cur->kind == GVal::Ptr && !cur->items.empty()) cur = &cur->items[0];
@@ -168,6 +168,47 @@ NBH_API int nbh_obj_get(const nbh_obj* o, const char* dotted_path, nbh_obj** out
   return 0;
 }
 NBH_API uint64_t nbh_obj_digest(const nbh_obj* o) { return o ? digest(o->v) : 0; }
+
+namespace {
+// walk "a.b.0.c" (numbers index lists, pointers are looked through); returns the parent of the last element
+GVal* walk_parent(GVal* cur, const std::string& path, std::string* last) {
+  size_t at = 0;
+  while (true) {
+    const size_t dot = path.find('.', at);
+    const std::string key = path.substr(at, dot == std::string::npos ? std::string::npos : dot - at);
+    while (cur->kind == GVal::Ptr && !cur->items.empty()) cur = &cur->items[0];
+    if (dot == std::string::npos) { *last = key; return cur; }
+    if (cur->kind == GVal::List) {
+      const size_t k = (size_t)atoll(key.c_str());
+      if (k >= cur->items.size()) return nullptr;
+      cur = &cur->items[k];
+    } else if (cur->kind == GVal::Struct || cur->kind == GVal::Map) {
+      cur = cur->find(key);
+      if (!cur) return nullptr;
+    } else {
+      return nullptr;
+    }
+    at = dot + 1;
+  }
+}
+}  // namespace
+
+NBH_API int nbh_obj_erase(nbh_obj* o, const char* dotted_path) {
+  if (!o || !dotted_path) return -1;
+  std::string last;
+  GVal* parent = walk_parent(&o->v, dotted_path, &last);
+  if (!parent || (parent->kind != GVal::Struct && parent->kind != GVal::Map)) return -1;
+  parent->erase(last);
+  return 0;
+}
+NBH_API int nbh_obj_set_str(nbh_obj* o, const char* dotted_path, const char* value) {
+  if (!o || !dotted_path || !value) return -1;
+  std::string last;
+  GVal* parent = walk_parent(&o->v, dotted_path, &last);
+  if (!parent || (parent->kind != GVal::Struct && parent->kind != GVal::Map)) return -1;
+  parent->set(last, GVal::str(value));
+  return 0;
+}
 
 // ----------------------------------------------------------------- builders
 NBH_API int nbh_generate_statefulset(const nbh_obj* nb, const nbh_env* env, nbh_obj** out, char* err, size_t errlen) {
@@ -302,6 +343,34 @@ NBH_API int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_
   return (int)s.size();
 }
 
+// --------------------------------------------------------------- owner join
+namespace {
+uint64_t join_key(uint64_t ns_hash, uint64_t uid_hash) {   // == nbg_join_key (capi.cu)
+  const uint64_t k = nbg_combine(nbg_combine(0x6A6F696E6B657921ull, ns_hash), uid_hash);
+  return k ? k : 1;
+}
+const GVal* meta_of(const GVal& o) { return (o.kind == GVal::Struct || o.kind == GVal::Map) ? o.find("metadata") : nullptr; }
+}  // namespace
+
+NBH_API uint64_t nbh_join_key_owner(const nbh_obj* owner) {
+  const GVal* m = owner ? meta_of(owner->v) : nullptr;
+  if (!m) return 0;
+  return join_key(hash_str(m->get_str("namespace")), hash_str(m->get_str("uid")));
+}
+// metav1.GetControllerOf: the first owner reference with controller != nil && *controller
+NBH_API uint64_t nbh_join_key_controlled(const nbh_obj* obj) {
+  const GVal* m = obj ? meta_of(obj->v) : nullptr;
+  if (!m) return 0;
+  const GVal* refs = m->find("ownerReferences");
+  if (!refs || refs->kind != GVal::List) return 0;
+  for (const auto& r : refs->items) {
+    const GVal* c = (r.kind == GVal::Struct || r.kind == GVal::Map) ? r.find("controller") : nullptr;
+    const bool is_ctrl = c && ((c->kind == GVal::Ptr && !c->items.empty() && c->items[0].i) || (c->kind == GVal::Bool && c->i));
+    if (is_ctrl) return join_key(hash_str(m->get_str("namespace")), hash_str(r.get_str("uid")));
+  }
+  return 0;
+}
+
 // ------------------------------------------------------------------- fleets
 NBH_API nbh_fleet* nbh_fleet_new(int kind, uint64_t seed, uint64_t n, uint32_t n_namespaces) {
   if (kind != FLEET_KUBEFLOW && kind != FLEET_ODH) return nullptr;
@@ -399,6 +468,37 @@ NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0,
   if (svc) { nbh_svc* o = new nbh_svc(); for (auto& b : pv) { o->b.append(b); b = SvcBatch(); } *svc = o; }
   if (vs) { nbh_vs* o = new nbh_vs(); for (auto& b : pw) { o->b.append(b); b = VsBatch(); } *vs = o; }
   return 0;
+}
+
+// A synthetic "List(StatefulSets)" for notebooks [0,n): most notebooks have one StatefulSet,
+// 3 % none yet, 2 % two (the first in list order must win), plus 2 % StatefulSets without a
+// controller reference and 1 % controlled by a Notebook that no longer exists.  The list is in
+// a seeded random order.  sts_owner[j] = owning notebook index, -1 (no controller), -2 (gone).
+NBH_API uint64_t nbh_fleet_join_lists(const nbh_fleet* f, uint64_t n, uint64_t* nb_keys, uint64_t* sts_keys,
+                                      int64_t* sts_owner, uint64_t cap) {
+  if (!f) return 0;
+  struct Ent { uint64_t order, key; int64_t owner; };
+  std::vector<Ent> ents;
+  ents.reserve(n + n / 8);
+  for (uint64_t i = 0; i < n; ++i) {
+    Rng r(f->f.seed ^ nbg_mix64(i * 2 + 0x6A6F696Eull));
+    char uid[40];
+    snprintf(uid, sizeof uid, "%016llx-nb", (unsigned long long)nbg_mix64(f->f.seed ^ (i * 0x9E3779B97F4A7C15ull)));
+    const uint64_t nsh = hash_str(f->f.namespace_name(i));
+    const uint64_t key = join_key(nsh, hash_str(uid));
+    if (nb_keys) nb_keys[i] = key;
+    const double u = r.unit();
+    const int copies = u < 0.03 ? 0 : u < 0.05 ? 2 : 1;
+    for (int c = 0; c < copies; ++c) ents.push_back({r.next(), key, (int64_t)i});
+    if (r.chance(0.02)) ents.push_back({r.next(), 0, -1});
+    if (r.chance(0.01)) ents.push_back({r.next(), join_key(nsh, hash_str(std::string(uid) + "-deleted")), -2});
+  }
+  std::sort(ents.begin(), ents.end(), [](const Ent& a, const Ent& b) { return a.order < b.order; });
+  for (uint64_t j = 0; j < ents.size() && j < cap; ++j) {
+    if (sts_keys) sts_keys[j] = ents[j].key;
+    if (sts_owner) sts_owner[j] = ents[j].owner;
+  }
+  return ents.size();
 }
 
 NBH_API nbh_cullfleet* nbh_cullfleet_new(uint64_t seed, uint64_t n, int64_t now_sec, int32_t now_nsec, double mean_kernels) {

@@ -107,6 +107,20 @@ class Context:
         return action, argmax, cull_bm, period_bm
 
 
+def _owner_join(self, nb_keys, sts_keys):
+    """Batched NBCTL:157-170: match[i] = index of the first StatefulSet controlled by Notebook i
+    (0xFFFFFFFF = none yet).  Keys from host.join_key_owner / join_key_controlled."""
+    nb = np.ascontiguousarray(nb_keys, dtype=np.uint64)
+    st = np.ascontiguousarray(sts_keys, dtype=np.uint64)
+    match = np.empty(len(nb), dtype=np.uint32)
+    _check(self._lib.nbg_owner_join(self._h, nb.ctypes.data_as(C.c_void_p), len(nb), st.ctypes.data_as(C.c_void_p),
+                                    len(st), match.ctypes.data_as(C.c_void_p)), "nbg_owner_join")
+    return match
+
+
+Context.owner_join = _owner_join
+
+
 def bitmap_to_bools(bitmap, n):
     """uint64 words -> bool[n] (bit i of word i//64)."""
     bits = np.unpackbits(bitmap.view(np.uint8), bitorder="little")

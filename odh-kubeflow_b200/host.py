@@ -53,6 +53,16 @@ class Obj:
             return None
         return Obj(out.value)
 
+    def erase(self, dotted_path):
+        if N.nbh().nbh_obj_erase(self._h, dotted_path.encode()) != 0:
+            raise HostError("no such path: " + dotted_path)
+        return self
+
+    def set_str(self, dotted_path, value):
+        if N.nbh().nbh_obj_set_str(self._h, dotted_path.encode(), value.encode()) != 0:
+            raise HostError("no such path: " + dotted_path)
+        return self
+
     def __del__(self):
         try:
             if self._h:
@@ -294,6 +304,16 @@ def format_rfc3339(sec, offset=0):
     return buf.value.decode()
 
 
+def join_key_owner(obj):
+    """Join key of an owner (Notebook): namespace + metadata.uid."""
+    return N.nbh().nbh_join_key_owner(obj._h)
+
+
+def join_key_controlled(obj):
+    """Join key of a dependent (StatefulSet): namespace + UID of its controller owner reference; 0 = none."""
+    return N.nbh().nbh_join_key_controlled(obj._h)
+
+
 FLEET_KUBEFLOW, FLEET_ODH = 2, 4
 SEED_BASE = 0x6E62677261667400  # SURVEY.md 8(d): seed = base + config number
 
@@ -343,6 +363,14 @@ class Fleet:
             N.nbh().nbh_fleet_shard_indices(self._h, n_shards, s, out.ctypes.data_as(N.u64p), cnt)
             return out
         return one(shard) if shard is not None else [one(s) for s in range(n_shards)]
+
+    def join_lists(self, n):
+        """Synthetic StatefulSet list for notebooks [0,n): (nb_keys[n], sts_keys[m], sts_owner[m])."""
+        m = N.nbh().nbh_fleet_join_lists(self._h, n, None, None, None, 0)
+        nb, st, ow = np.empty(n, np.uint64), np.empty(m, np.uint64), np.empty(m, np.int64)
+        N.nbh().nbh_fleet_join_lists(self._h, n, nb.ctypes.data_as(N.u64p), st.ctypes.data_as(N.u64p),
+                                     ow.ctypes.data_as(N.i64p), m)
+        return nb, st, ow
 
     def objects(self, i0=0, m=None, idx=None):
         """All seven objects of m notebooks at once -> list of dicts name -> Obj."""

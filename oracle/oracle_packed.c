@@ -229,3 +229,34 @@ ORC_API double orc2_cull(const nbg_cull_batch* in, uint64_t n, const nbg_cull_pa
                          uint32_t* argmax, uint64_t* cull_bitmap, uint64_t* period_bitmap) {
   return run(3, in, p, n, threads, action, argmax, cull_bitmap, period_bitmap);
 }
+
+/* Owner join on keys (notebook_controller.go:157-170): first list entry with the
+ * notebook's key.  Sort-free and obviously right: a chained table of list
+ * positions, filled back to front so each chain head is the lowest index. */
+ORC_API double orc2_owner_join(const uint64_t* nb_key, uint64_t n, const uint64_t* sts_key, uint64_t m, uint32_t* match) {
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  uint64_t buckets = 1024;
+  while (buckets < 2 * m) buckets <<= 1;
+  int64_t* head = (int64_t*)malloc(buckets * sizeof(int64_t));
+  int64_t* next = (int64_t*)malloc((m ? m : 1) * sizeof(int64_t));
+  for (uint64_t b = 0; b < buckets; ++b) head[b] = -1;
+  for (int64_t j = (int64_t)m - 1; j >= 0; --j) {
+    if (sts_key[j] == 0) continue;
+    const uint64_t b = (sts_key[j] * 0x9E3779B97F4A7C15ull >> 20) & (buckets - 1);
+    next[j] = head[b];
+    head[b] = j;
+  }
+  for (uint64_t i = 0; i < n; ++i) {
+    uint32_t found = NBG_ARGMAX_NONE;
+    if (nb_key[i] != 0) {
+      const uint64_t b = (nb_key[i] * 0x9E3779B97F4A7C15ull >> 20) & (buckets - 1);
+      for (int64_t j = head[b]; j >= 0; j = next[j])
+        if (sts_key[j] == nb_key[i]) { found = (uint32_t)j; break; }
+    }
+    match[i] = found;
+  }
+  free(head); free(next);
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  return (double)(t1.tv_sec - t0.tv_sec) + (double)(t1.tv_nsec - t0.tv_nsec) * 1e-9;
+}

@@ -550,7 +550,40 @@ int cull_decide(Meta& m, const std::vector<Kernel>& ks, const std::vector<Kernel
 
 }  // namespace
 
+// ----------------------------------------------------------- owner lookup
+// metav1.GetControllerOfNoCopy + IsControlledBy (k8s.io/apimachinery v0.33.7,
+// pkg/apis/meta/v1/controller_ref.go — not under /root/reference, restated):
+// the controller reference is the first owner reference whose Controller pointer is
+// non-nil and true; obj is controlled by owner iff that reference's UID == owner's UID.
+const GVal* controller_ref(const GVal& obj) {
+  const GVal& refs = field(field(obj, "metadata"), "ownerReferences");
+  if (refs.kind != GVal::List) return nullptr;
+  for (const auto& r : refs.items) {
+    const GVal& c = field(r, "controller");
+    if (c.kind == GVal::Ptr && !c.items.empty() && c.items[0].i) return &r;
+  }
+  return nullptr;
+}
+bool is_controlled_by(const GVal& obj, const GVal& owner) {
+  const GVal* ref = controller_ref(obj);
+  if (!ref) return false;
+  return field(*ref, "uid").s == field(field(owner, "metadata"), "uid").s;
+}
+// notebook_controller.go:157-170: List(InNamespace(ns)) then the first controlled item
+long find_controlled(const GVal& owner, const nbh_obj* const* list, uint64_t count) {
+  const std::string ns = field(field(owner, "metadata"), "namespace").s;
+  for (uint64_t j = 0; j < count; ++j) {
+    if (field(field(list[j]->v, "metadata"), "namespace").s != ns) continue;   // client.InNamespace
+    if (is_controlled_by(list[j]->v, owner)) return (long)j;
+  }
+  return -1;
+}
+
 // ============================================================ exported API
+ORC_API long orc_find_controlled(const nbh_obj* owner, const nbh_obj* const* list, uint64_t count) {
+  return find_controlled(owner->v, list, count);
+}
+
 ORC_API int orc_deep_equal(const nbh_obj* a, const nbh_obj* b) { return deep_equal(a->v, b->v) ? 1 : 0; }
 ORC_API int orc_strict_equal(const nbh_obj* a, const nbh_obj* b) { return strict_equal(a->v, b->v) ? 1 : 0; }
 

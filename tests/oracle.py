@@ -51,6 +51,10 @@ def lib():
             f = getattr(L, name)
             f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
             f.restype = C.c_double
+        L.orc_find_controlled.argtypes = [vp, C.POINTER(vp), C.c_uint64]
+        L.orc_find_controlled.restype = C.c_long
+        L.orc2_owner_join.argtypes = [vp, C.c_uint64, vp, C.c_uint64, vp]
+        L.orc2_owner_join.restype = C.c_double
         L.orc2_cull.argtypes = [C.POINTER(N.nbg_cull_batch), C.c_uint64, C.POINTER(N.nbg_cull_params), C.c_int, vp, vp,
                                 vp, vp]
         L.orc2_cull.restype = C.c_double
@@ -156,3 +160,19 @@ def packed_cull(batch, now, cull_idle_min=1440, period_min=1, mode=1, threads=1)
                            argmax.ctypes.data_as(C.c_void_p), cb.ctypes.data_as(C.c_void_p),
                            pb.ctypes.data_as(C.c_void_p))
     return action, argmax, cb, pb, secs
+
+
+def find_controlled(owner, sts_list):
+    """notebook_controller.go:157-170 on objects: index of the first StatefulSet in the owner's
+    namespace whose controller reference carries the owner's UID, or -1."""
+    arr = (C.c_void_p * len(sts_list))(*[o._h for o in sts_list])
+    return lib().orc_find_controlled(owner._h, arr, len(sts_list))
+
+
+def packed_owner_join(nb_keys, sts_keys):
+    nb = np.ascontiguousarray(nb_keys, dtype=np.uint64)
+    st = np.ascontiguousarray(sts_keys, dtype=np.uint64)
+    match = np.empty(len(nb), dtype=np.uint32)
+    secs = lib().orc2_owner_join(nb.ctypes.data_as(C.c_void_p), len(nb), st.ctypes.data_as(C.c_void_p), len(st),
+                                 match.ctypes.data_as(C.c_void_p))
+    return match, secs
