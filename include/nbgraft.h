@@ -255,6 +255,26 @@ size_t nbg_owner_join_scratch_bytes(uint64_t m);
 int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint64_t n,
                           const uint64_t* sts_key, uint64_t m, uint32_t* match,
                           void* scratch, size_t scratch_bytes, void* stream);
+/* Owner join that allocates nothing — it has no counterpart in the reference.
+ * For callers that may not call the CUDA allocator while they run: code on a
+ * reconcile path with a latency bound (cudaMalloc/cudaFree synchronise the whole
+ * device), or a controller sharing its GPU with the notebooks it manages, where
+ * an allocation made on demand can fail because the workloads got the memory
+ * first.  Same inputs, outputs and result as nbg_owner_join_device (all pointers
+ * are DEVICE pointers on the CURRENT CUDA device; no context is needed), but the
+ * hash table is a fixed array inside the library, so:
+ *   - at most NBG_JOIN_STATIC_MAX_STS StatefulSets per call; more is rejected
+ *     with NBG_E_TOOBIG and nothing is launched;
+ *   - every GPU that loads the library holds the table (3 MiB) until exit;
+ *   - the first call on each device looks the table's address up
+ *     (cudaGetSymbolAddress); make that first call before any stream capture;
+ *   - all calls on a device share the one table (each call clears it before
+ *     use): two calls whose GPU work overlaps — different streams, or several
+ *     threads — race.  Order them on one stream or with events.
+ * The call itself performs no cudaMalloc/cudaFree and only enqueues work. */
+#define NBG_JOIN_STATIC_MAX_STS 131072u
+int nbg_owner_join_static(const uint64_t* nb_key, uint64_t n, const uint64_t* sts_key, uint64_t m,
+                          uint32_t* match, void* stream);
 /* The context's own (non-blocking) run stream on `device`, as a cudaStream_t. */
 void* nbg_ctx_stream(nbg_ctx* ctx, int device);
 /* Block until everything enqueued on the context's own stream of `device` is done. */

@@ -80,6 +80,7 @@ NBG_OK, NBG_E_NODEVICE, NBG_E_INVAL, NBG_E_NOMEM, NBG_E_CUDA = 0, -1, -2, -3, -4
 NBG_E_NILREPLICAS, NBG_E_RANGE, NBG_E_TOOBIG = -5, -6, -7
 NBG_POD_SLOTS, NBG_SVC_SLOTS, NBG_VS_SLOTS = 192, 16, 8
 NBG_REPLICAS_NIL = -(2 ** 31)
+NBG_JOIN_STATIC_MAX_STS = 131072
 NBG_ARGMAX_NONE = 0xFFFFFFFF
 STS_LABELS, STS_ANNOTATIONS, STS_REPLICAS, STS_PODSPEC, STS_TMPL_LABELS, STS_NILREPLICAS = 1, 2, 4, 8, 16, 0x80
 SVC_LABELS, SVC_ANNOTATIONS, SVC_SELECTOR, SVC_PORTS = 1, 2, 4, 8
@@ -94,6 +95,7 @@ NBG_SYMBOLS = [
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
+    "nbg_owner_join_static",
 ]
 
 _vp = C.c_void_p
@@ -137,6 +139,8 @@ def _bind_nbg(lib):
     lib.nbg_owner_join_scratch_bytes.restype = C.c_size_t
     lib.nbg_owner_join_device.argtypes = [_vp, C.c_int, _vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp, C.c_size_t, _vp]
     lib.nbg_owner_join_device.restype = C.c_int
+    lib.nbg_owner_join_static.argtypes = [_vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp]
+    lib.nbg_owner_join_static.restype = C.c_int
     lib.nbg_ctx_stream.argtypes = [_vp, C.c_int]
     lib.nbg_ctx_stream.restype = _vp
     lib.nbg_sync.argtypes = [_vp, C.c_int]
