@@ -116,10 +116,13 @@ def struct_over(N, kind, arr):
         m.ent = C.cast(arr[prefix + ".ent"].ctypes.data, C.POINTER(N.nbg_kv))
         return m
     if kind == "sts":
-        s = N.nbg_sts_batch()
+        s = N.nbg_sts_sparse_batch()
         s.replicas_from, s.replicas_to = p("replicas_from", C.c_int32), p("replicas_to", C.c_int32)
         s.tmpl_from, s.tmpl_to = p("tmpl_from", C.c_uint64), p("tmpl_to", C.c_uint64)
-        s.pod_from, s.pod_to = p("pod_from", C.c_uint64), p("pod_to", C.c_uint64)
+        for side in ("pod_from", "pod_to"):
+            ps = N.nbg_podsparse()
+            ps.mask, ps.off, ps.val = p(side + ".mask", C.c_uint64), p(side + ".voff", C.c_uint32), p(side + ".val", C.c_uint64)
+            setattr(s, side, ps)
         for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
             setattr(s, f, kv(f))
     elif kind == "svc":
@@ -245,7 +248,9 @@ def main():
     pack_s = time.time() - t0
     now = (cfleet.now_sec, cfleet.now_nsec)
 
-    d_sts, d_svc, d_vs, d_cull = (dev.DeviceBatch.from_host(b, device=local) for b in (sts, svc, vs, cull))
+    # the step compares StatefulSets on SPARSE PodSpec tiles (same answer as the dense tiles, ~4x fewer bytes)
+    sts_sp = sts.sparse()
+    d_sts, d_svc, d_vs, d_cull = (dev.DeviceBatch.from_host(b, device=local) for b in (sts_sp, svc, vs, cull))
     batches = [("diff_sts", d_sts), ("diff_svc", d_svc), ("diff_vs", d_vs), ("cull", d_cull)]
     alg_bytes = {name: b.algorithmic_bytes for name, b in batches}
 
@@ -290,21 +295,38 @@ def main():
     value = units.item() / (ms_step / 1000.0)
 
     # ---- parity of what was just computed (outside the timed region)
-    want = {"diff_sts": O.packed_diff_sts(sts, threads=8), "diff_svc": O.packed_diff_svc(svc, threads=8),
+    want = {"diff_sts": O.packed_diff_sts_sparse(sts_sp, threads=8), "diff_svc": O.packed_diff_svc(svc, threads=8),
             "diff_vs": O.packed_diff_vs(vs, threads=8), "cull": O.packed_cull(cull, now, 1440, 1, 1, threads=8)}
     parity = True
     for name, b in batches:
         outs = [o.cpu().numpy() for o in b.outs]
         parity &= bool(np.array_equal(outs[0], want[name][0]))
         parity &= bool(np.array_equal(outs[-1].view(np.uint64), want[name][3 if name == "cull" else 1]))
+    dense_want = O.packed_diff_sts(sts, threads=8)
+    parity &= bool(np.array_equal(dense_want[0], want["diff_sts"][0]))          # sparse tiles == dense tiles
     if not parity:
         raise SystemExit("bench: device results differ from the packed oracle")
+    # the dense-tile kernel on the same pairs, timed alone for comparison
+    d_dense = dev.DeviceBatch.from_host(sts, device=local)
+    for _ in range(3):
+        d_dense.run(ctx)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        d_dense.run(ctx)
+    e1.record()
+    torch.cuda.synchronize()
+    dense_ms = e0.elapsed_time(e1) / 5
+    parity_dense = bool(np.array_equal(d_dense.outs[0].cpu().numpy(), dense_want[0]))
+    dense_bytes = d_dense.algorithmic_bytes
+    del d_dense
+    torch.cuda.empty_cache()
 
     # ---- e2e: the host-buffer C ABI with pinned host memory, copies inside the timed region
     keep = []
     views, outs_h = {}, {}
     words = (per + 63) // 64
-    for kind, b in (("sts", sts), ("svc", svc), ("vs", vs), ("cull", cull)):
+    for kind, b in (("sts", sts_sp), ("svc", svc), ("vs", vs), ("cull", cull)):
         views[kind] = (struct_over(N, kind, pinned_copy(lib, b.arrays(), keep)), sum(a.nbytes for a in b.arrays().values()))
     out_arr = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64), "a": np.zeros(per, np.uint32),
                                 "b2": np.zeros(words, np.uint64)}, keep)
@@ -312,7 +334,7 @@ def main():
     params = N.nbg_cull_params(now[0], now[1], 1440, 1, N.CULL_RECONCILE)
 
     def e2e_step():
-        rc = lib.nbg_diff_sts(ctx.handle, C.byref(views["sts"][0]), per, rp, bp)
+        rc = lib.nbg_diff_sts_sparse(ctx.handle, C.byref(views["sts"][0]), per, rp, bp)
         rc |= lib.nbg_diff_svc(ctx.handle, C.byref(views["svc"][0]), per, rp, bp)
         rc |= lib.nbg_diff_vs(ctx.handle, C.byref(views["vs"][0]), per, rp, bp)
         rc |= lib.nbg_cull(ctx.handle, C.byref(views["cull"][0]), per, C.byref(params), rp, ap_, bp, b2p)
@@ -352,6 +374,7 @@ def main():
         "config": {"workload": "config #5 share: %d Notebooks per GPU (10M / 8), StatefulSet+Service+VirtualService diff + culler "
                                "decision per Notebook" % per,
                    "object": "one Notebook = 3 desired/live pairs + its kernel/terminal records",
+                   "tiles": "PodSpec tiles stored sparsely (192-bit mask + non-zero slots); dense tiles reported under dense_tiles",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
                    "l2": "inputs (%.1f GB per GPU) exceed L2; no flush needed" % (sum(alg_bytes.values()) / 1e9),
                    "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},
@@ -359,19 +382,23 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI calls, max over ranks"},
         "gpu_launches": int(gpu_launches),
-        "roofline": {"bound": "hbm", "kernel": "diff_sts_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "diff_sts_sparse_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
                      "frac": sts_gbs / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes["diff_sts"]), "avg_launch_ms": kernel_ms["diff_sts"]},
         "kernels": {name: {"avg_ms": kernel_ms[name], "GBps": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9,
                            "frac_of_peak": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9 / peak} for name, _ in batches},
-        "parity": "bit-exact vs packed oracle on all %d objects x 4 kernels (device path) and cull (e2e path)" % per,
+        "parity": "bit-exact vs packed oracle on all %d objects x 4 kernels (device path) and cull (e2e path); "
+                  "sparse-tile results == dense-tile results" % per,
+        "dense_tiles": {"kernel": "diff_sts_kernel", "avg_ms": dense_ms, "GBps": dense_bytes / (dense_ms * 1e-3) / 1e9,
+                        "frac_of_peak": dense_bytes / (dense_ms * 1e-3) / 1e9 / peak, "bytes_per_object": round(dense_bytes / per, 1),
+                        "parity": parity_dense, "note": "same pairs, dense 192-slot tiles (timed alone, back to back)"},
         "host_pack": {"objects_per_s": per / pack_s, "threads": int(os.environ["NBH_THREADS"]), "seconds": pack_s},
     }
     if world == 1:
         threads = os.cpu_count() or 1
         rate, info = CpuReference(pkg, O, args.cpu_sample, host.SEED_BASE + 5, threads).rate()
         # also the packed loops (the CPU version of OUR algorithm) for context
-        t_packed = sum(x[-1] for x in (O.packed_diff_sts(sts, threads=threads), O.packed_diff_svc(svc, threads=threads),
+        t_packed = sum(x[-1] for x in (O.packed_diff_sts_sparse(sts_sp, threads=threads), O.packed_diff_svc(svc, threads=threads),
                                        O.packed_diff_vs(vs, threads=threads), O.packed_cull(cull, now, 1440, 1, 1, threads=threads)))
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": "%(sample_notebooks)d notebooks x %(repetitions)d repetitions (%(cpu_seconds)s CPU-s): "

@@ -76,6 +76,9 @@ void nbh_sts_free(nbh_sts* b);
 int nbh_sts_add(nbh_sts* b, const nbh_obj* from, const nbh_obj* to);
 uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out);   /* returns n; pointers live as long as b is unchanged */
 
+/* the same pairs with sparsely stored PodSpec tiles (nbg_diff_sts_sparse) */
+uint64_t nbh_sts_view_sparse(const nbh_sts* b, nbg_sts_sparse_batch* out);
+
 nbh_svc* nbh_svc_new(void);
 void nbh_svc_free(nbh_svc* b);
 int nbh_svc_add(nbh_svc* b, const nbh_obj* from, const nbh_obj* to);

@@ -46,6 +46,17 @@ class nbg_sts_batch(C.Structure):
                 ("ann_from", nbg_kvmap), ("ann_to", nbg_kvmap)]
 
 
+class nbg_podsparse(C.Structure):
+    _fields_ = [("mask", u64p), ("off", u32p), ("val", u64p)]
+
+
+class nbg_sts_sparse_batch(C.Structure):
+    _fields_ = [("replicas_from", i32p), ("replicas_to", i32p), ("tmpl_from", u64p), ("tmpl_to", u64p),
+                ("pod_from", nbg_podsparse), ("pod_to", nbg_podsparse),
+                ("labels_from", nbg_kvmap), ("labels_to", nbg_kvmap),
+                ("ann_from", nbg_kvmap), ("ann_to", nbg_kvmap)]
+
+
 class nbg_svc_batch(C.Structure):
     _fields_ = [("flags", u8p), ("ports_from", u64p), ("ports_to", u64p),
                 ("labels_from", nbg_kvmap), ("labels_to", nbg_kvmap),
@@ -95,7 +106,7 @@ NBG_SYMBOLS = [
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
-    "nbg_owner_join_static",
+    "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
 ]
 
 _vp = C.c_void_p
@@ -119,7 +130,8 @@ def _bind_nbg(lib):
     lib.nbg_hash64.restype = C.c_uint64
     lib.nbg_shard_of.argtypes = [C.c_uint64, C.c_uint32]
     lib.nbg_shard_of.restype = C.c_uint32
-    for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch)):
+    for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch),
+                     ("nbg_diff_sts_sparse", nbg_sts_sparse_batch)):
         f = getattr(lib, name)
         f.argtypes = [_vp, C.POINTER(bt), C.c_uint64, _vp, _vp]
         f.restype = C.c_int
@@ -168,6 +180,7 @@ def _bind_nbh(lib):
         "nbh_odh_mutate": ([_vp, C.c_int], C.c_int),
         "nbh_sts_new": ([], _vp), "nbh_sts_free": ([_vp], None),
         "nbh_sts_add": ([_vp, _vp, _vp], C.c_int), "nbh_sts_view": ([_vp, P(nbg_sts_batch)], C.c_uint64),
+        "nbh_sts_view_sparse": ([_vp, P(nbg_sts_sparse_batch)], C.c_uint64),
         "nbh_svc_new": ([], _vp), "nbh_svc_free": ([_vp], None),
         "nbh_svc_add": ([_vp, _vp, _vp], C.c_int), "nbh_svc_view": ([_vp, P(nbg_svc_batch)], C.c_uint64),
         "nbh_vs_new": ([], _vp), "nbh_vs_free": ([_vp], None),
@@ -204,7 +217,7 @@ def _bind_nbh(lib):
 NBH_SYMBOLS = [
     "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_erase", "nbh_obj_set_str", "nbh_obj_digest",
     "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate",
-    "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
+    "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_sts_view_sparse", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
     "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",

@@ -24,6 +24,8 @@ cudaError_t nbg_launch_cull(const nbg_cull_batch*, unsigned long long, const nbg
                             cudaStream_t);
 cudaError_t nbg_launch_diff_sts(const nbg_sts_batch*, unsigned long long, const unsigned*, uint8_t*,
                                 uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch*, unsigned long long, const unsigned*, uint8_t*,
+                                       uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const unsigned*, uint8_t*,
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
@@ -190,6 +192,7 @@ int for_each_device(nbg_ctx* ctx, uint64_t n, F&& run_range) {
 }
 
 constexpr uint64_t kStsChunk = 8192;     // objects per pipeline chunk (~27 MB)
+constexpr uint64_t kStsSparseChunk = 32768;  // (~25 MB at ~35 non-zero slots per side)
 constexpr uint64_t kSvcChunk = 65536;    // (~21 MB)
 constexpr uint64_t kVsChunk = 131072;    // (~20 MB)
 constexpr uint64_t kCullChunk = 262144;  // notebooks (~22 MB at 4 records each)
@@ -327,6 +330,19 @@ int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint6
   cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[4] = {0, 0, 0, 0};
   CU(nbg_launch_diff_sts(in, n, bases, reason, bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_sts_sparse_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* in, uint64_t n,
+                               uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[6] = {0, 0, 0, 0, 0, 0};
+  CU(nbg_launch_diff_sts_sparse(in, n, bases, reason, bitmap, (cudaStream_t)stream));
   ctx->launches++;
   return NBG_OK;
 }
@@ -504,6 +520,65 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
       b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
       const unsigned bases[4] = {lf.base, lt.base, af.base, at.base};
       CU(nbg_launch_diff_sts(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+  if (rc != NBG_OK) return rc;
+  for (uint64_t i = 0; i < n; ++i)
+    if (reason[i] & NBG_STS_NILREPLICAS) return NBG_E_NILREPLICAS;
+  return NBG_OK;
+}
+
+int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->replicas_from || !in->replicas_to || !in->tmpl_from || !in->tmpl_to ||
+      !in->pod_from.mask || !in->pod_to.mask)
+    return NBG_E_INVAL;
+  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
+      !csr_ok(in->ann_to, n) || !off_ok(in->pod_from.off, n) || !off_ok(in->pod_to.off, n))
+    return NBG_E_RANGE;
+  if ((in->pod_from.off[n] > in->pod_from.off[0] && !in->pod_from.val) ||
+      (in->pod_to.off[n] > in->pod_to.off[0] && !in->pod_to.val))
+    return NBG_E_INVAL;
+  if (((uintptr_t)in->pod_from.val | (uintptr_t)in->pod_to.val) & 15u) return NBG_E_INVAL;   // 128-bit loads
+  for (uint64_t i = 0; i <= n; ++i)  // runs are even-padded ...
+    if ((in->pod_from.off[i] | in->pod_to.off[i]) & 1u) return NBG_E_RANGE;
+  for (uint64_t i = 0; i < n; ++i)   // ... and never longer than the tile
+    if (in->pod_from.off[i + 1] - in->pod_from.off[i] > NBG_POD_SLOTS || in->pod_to.off[i + 1] - in->pod_to.off[i] > NBG_POD_SLOTS)
+      return NBG_E_RANGE;
+
+  int rc = for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kStsSparseChunk, ++c) {
+      const uint64_t i1 = i0 + kStsSparseChunk < hi ? i0 + kStsSparseChunk : hi, m = i1 - i0;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_rf = lay.in(in->replicas_from + i0, m * 4), a_rt = lay.in(in->replicas_to + i0, m * 4);
+      const size_t a_tf = lay.in(in->tmpl_from + i0, m * 8), a_tt = lay.in(in->tmpl_to + i0, m * 8);
+      const size_t a_mf = lay.in(in->pod_from.mask + i0 * 3, m * 24), a_mt = lay.in(in->pod_to.mask + i0 * 3, m * 24);
+      const size_t a_of = lay.in(in->pod_from.off + i0, (m + 1) * 4), a_ot = lay.in(in->pod_to.off + i0, (m + 1) * 4);
+      const unsigned vfb = in->pod_from.off[i0], vtb = in->pod_to.off[i0];
+      const size_t nvf = in->pod_from.off[i1] - vfb, nvt = in->pod_to.off[i1] - vtb;
+      const size_t a_vf = lay.in(nvf ? in->pod_from.val + vfb : nullptr, nvf * 8);
+      const size_t a_vt = lay.in(nvt ? in->pod_to.val + vtb : nullptr, nvt * 8);
+      const CsrDev lf = csr_in(lay, in->labels_from, i0, i1), lt = csr_in(lay, in->labels_to, i0, i1);
+      const CsrDev af = csr_in(lay, in->ann_from, i0, i1), at = csr_in(lay, in->ann_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_sts_sparse_batch b;
+      b.replicas_from = (const int32_t*)(sl.dev + a_rf); b.replicas_to = (const int32_t*)(sl.dev + a_rt);
+      b.tmpl_from = (const uint64_t*)(sl.dev + a_tf); b.tmpl_to = (const uint64_t*)(sl.dev + a_tt);
+      b.pod_from.mask = (const uint64_t*)(sl.dev + a_mf); b.pod_to.mask = (const uint64_t*)(sl.dev + a_mt);
+      b.pod_from.off = (const uint32_t*)(sl.dev + a_of); b.pod_to.off = (const uint32_t*)(sl.dev + a_ot);
+      b.pod_from.val = (const uint64_t*)(sl.dev + a_vf); b.pod_to.val = (const uint64_t*)(sl.dev + a_vt);
+      b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt);
+      b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
+      const unsigned bases[6] = {lf.base, lt.base, af.base, at.base, vfb, vtb};
+      CU(nbg_launch_diff_sts_sparse(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
       ctx->launches++;
       if (int r = slot_download(d, sl, lay)) return r;
     }

@@ -104,6 +104,93 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
   store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
 }
 
+// ------------------------------------------------ StatefulSet, sparse tiles
+// Same predicate, PodSpec tiles stored as (192-bit mask, packed non-zero slots).
+// Lane j compares object j's masks itself (2 x 24 B); objects whose masks agree
+// have equally long value runs, which the warp then compares run by run: runs
+// are padded to an even number of values and start 16-byte aligned, so a run of
+// up to 64 values is ONE 128-bit streaming load per lane and side.  Four
+// objects are in flight per warp.  Objects whose masks differ are decided
+// without their values ever being read.
+constexpr unsigned kSparseGroup = 4;
+
+__global__ void __launch_bounds__(128)
+diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
+                       unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
+                       unsigned vf_base, unsigned vt_base,
+                       uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const unsigned cnt = (unsigned)min(32ull, n - base);
+
+  unsigned reason = 0;
+  unsigned vf0 = 0, vt0 = 0, my_vecs = 0;               // run starts and length, in 16-byte vectors
+  bool mask_ne = false;
+  if (i < n) {
+    const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
+    if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
+      reason |= NBG_STS_NILREPLICAS;
+    } else if (rf != rt) {
+      reason |= NBG_STS_REPLICAS;
+      if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
+    }
+    const unsigned long long* mf = reinterpret_cast<const unsigned long long*>(in.pod_from.mask) + i * 3;
+    const unsigned long long* mt = reinterpret_cast<const unsigned long long*>(in.pod_to.mask) + i * 3;
+    mask_ne = (__ldg(mf) != __ldg(mt)) | (__ldg(mf + 1) != __ldg(mt + 1)) | (__ldg(mf + 2) != __ldg(mt + 2));
+    const unsigned f0 = __ldg(in.pod_from.off + i) - vf_base, f1 = __ldg(in.pod_from.off + i + 1) - vf_base;
+    vf0 = f0 >> 1;
+    vt0 = (__ldg(in.pod_to.off + i) - vt_base) >> 1;
+    my_vecs = mask_ne ? 0u : (f1 - f0) >> 1;
+    if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
+                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
+                         __ldg(in.labels_to.off + i + 1) - lt_base))
+      reason |= NBG_STS_LABELS;
+    if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
+                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
+                         __ldg(in.ann_to.off + i + 1) - at_base))
+      reason |= NBG_STS_ANNOTATIONS;
+  }
+
+  unsigned pod_bits = __ballot_sync(FULL, mask_ne);
+  const uint4* fv = reinterpret_cast<const uint4*>(in.pod_from.val);
+  const uint4* tv = reinterpret_cast<const uint4*>(in.pod_to.val);
+  for (unsigned o = 0; o < cnt; o += kSparseGroup) {
+    unsigned d[kSparseGroup];
+    uint4 x[kSparseGroup], y[kSparseGroup];
+    unsigned more = 0;                                   // some run of this group is longer than 32 vectors
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g) {
+      const unsigned src = min(o + g, 31u);
+      const unsigned vecs = __shfl_sync(FULL, my_vecs, src);   // 0 past the end (my_vecs == 0 there)
+      const unsigned fo = __shfl_sync(FULL, vf0, src), to = __shfl_sync(FULL, vt0, src);
+      x[g] = make_uint4(0, 0, 0, 0); y[g] = x[g];
+      if (lane < vecs) { x[g] = ld_stream(fv + fo + lane); y[g] = ld_stream(tv + to + lane); }
+      more |= vecs > 32u;
+    }
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g) d[g] = diff4(x[g], y[g]);
+    if (more) {                                          // warp-uniform; runs of 65..192 values
+#pragma unroll
+      for (unsigned g = 0; g < kSparseGroup; ++g) {
+        const unsigned src = min(o + g, 31u);
+        const unsigned vecs = __shfl_sync(FULL, my_vecs, src);
+        const unsigned fo = __shfl_sync(FULL, vf0, src), to = __shfl_sync(FULL, vt0, src);
+        for (unsigned k = lane + 32u; k < vecs; k += 32u) d[g] |= diff4(ld_stream(fv + fo + k), ld_stream(tv + to + k));
+      }
+    }
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g)
+      if (__any_sync(FULL, d[g] != 0)) pod_bits |= 1u << min(o + g, 31u);
+  }
+  if ((pod_bits >> lane) & 1u) reason |= NBG_STS_PODSPEC;
+  store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
 // ------------------------------------------------- small fixed tiles (Svc, VS)
 // VEC = 16-byte vectors per side per object (8 for Service ports, 4 for the VS
 // spec).  32/VEC objects are compared per load instruction; the warp covers its
@@ -214,6 +301,18 @@ extern "C" cudaError_t nbg_launch_diff_sts(const nbg_sts_batch* in, unsigned lon
   const unsigned long long grid = (n + block - 1) / block;
   nbg::diff_sts_kernel<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch* in, unsigned long long n,
+                                                  const unsigned* bases /*6*/, uint8_t* reason,
+                                                  uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  const unsigned long long grid = (n + block - 1) / block;
+  nbg::diff_sts_sparse_kernel<<<(unsigned)grid, block, 0, stream>>>(
+      *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
+      reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
 

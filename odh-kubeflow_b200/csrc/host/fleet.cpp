@@ -56,9 +56,26 @@ void StsBatch::add(const GVal& from, const GVal& to) {
   labels_to.add(path(to, {"metadata", "labels"}));
   ann_from.add(path(from, {"metadata", "annotations"}));
   ann_to.add(path(to, {"metadata", "annotations"}));
+  auto sparsify = [](const uint64_t* tile, std::vector<uint64_t>& mask, std::vector<uint64_t>& val, std::vector<uint32_t>& off) {
+    uint64_t m[3] = {0, 0, 0};
+    for (unsigned s = 0; s < NBG_POD_SLOTS; ++s)
+      if (tile[s]) { m[s >> 6] |= 1ull << (s & 63); val.push_back(tile[s]); }
+    if (val.size() & 1) val.push_back(0);   // runs are padded to an even count: 16-byte aligned starts
+    mask.insert(mask.end(), m, m + 3);
+    off.push_back((uint32_t)val.size());
+  };
+  sparsify(&pod_from[n * NBG_POD_SLOTS], mask_from, val_from, voff_from);
+  sparsify(&pod_to[n * NBG_POD_SLOTS], mask_to, val_to, voff_to);
   ++n;
 }
 void StsBatch::append(const StsBatch& o) {
+  {
+    const uint32_t bf = (uint32_t)val_from.size(), bt = (uint32_t)val_to.size();
+    for (size_t k = 1; k < o.voff_from.size(); ++k) voff_from.push_back(bf + o.voff_from[k]);
+    for (size_t k = 1; k < o.voff_to.size(); ++k) voff_to.push_back(bt + o.voff_to[k]);
+    extend(mask_from, o.mask_from); extend(mask_to, o.mask_to);
+    extend(val_from, o.val_from); extend(val_to, o.val_to);
+  }
   extend(replicas_from, o.replicas_from); extend(replicas_to, o.replicas_to);
   extend(tmpl_from, o.tmpl_from); extend(tmpl_to, o.tmpl_to);
   extend(pod_from, o.pod_from); extend(pod_to, o.pod_to);
@@ -71,6 +88,17 @@ nbg_sts_batch StsBatch::view() const {
   b.replicas_from = replicas_from.data(); b.replicas_to = replicas_to.data();
   b.tmpl_from = tmpl_from.data(); b.tmpl_to = tmpl_to.data();
   b.pod_from = pod_from.data(); b.pod_to = pod_to.data();
+  b.labels_from = labels_from.view(); b.labels_to = labels_to.view();
+  b.ann_from = ann_from.view(); b.ann_to = ann_to.view();
+  return b;
+}
+
+nbg_sts_sparse_batch StsBatch::view_sparse() const {
+  nbg_sts_sparse_batch b;
+  b.replicas_from = replicas_from.data(); b.replicas_to = replicas_to.data();
+  b.tmpl_from = tmpl_from.data(); b.tmpl_to = tmpl_to.data();
+  b.pod_from.mask = mask_from.data(); b.pod_from.off = voff_from.data(); b.pod_from.val = val_from.data();
+  b.pod_to.mask = mask_to.data(); b.pod_to.off = voff_to.data(); b.pod_to.val = val_to.data();
   b.labels_from = labels_from.view(); b.labels_to = labels_to.view();
   b.ann_from = ann_from.view(); b.ann_to = ann_to.view();
   return b;

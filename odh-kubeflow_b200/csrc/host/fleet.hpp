@@ -44,10 +44,14 @@ struct StsBatch {
   std::vector<int32_t> replicas_from, replicas_to;
   std::vector<uint64_t> tmpl_from, tmpl_to, pod_from, pod_to;
   KvCsr labels_from, labels_to, ann_from, ann_to;
+  // the same tiles stored sparsely (nbg_podsparse): presence mask + non-zero slots
+  std::vector<uint64_t> mask_from, mask_to, val_from, val_to;
+  std::vector<uint32_t> voff_from{0}, voff_to{0};
   uint64_t n = 0;
   void add(const GVal& from, const GVal& to);
   void append(const StsBatch& o);
   nbg_sts_batch view() const;
+  nbg_sts_sparse_batch view_sparse() const;
 };
 struct SvcBatch {
   std::vector<uint8_t> flags;

@@ -257,6 +257,11 @@ NBH_API uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out) {
   *out = b->b.view();
   return b->b.n;
 }
+NBH_API uint64_t nbh_sts_view_sparse(const nbh_sts* b, nbg_sts_sparse_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view_sparse();
+  return b->b.n;
+}
 NBH_API nbh_svc* nbh_svc_new(void) { return new nbh_svc(); }
 NBH_API void nbh_svc_free(nbh_svc* b) { delete b; }
 NBH_API int nbh_svc_add(nbh_svc* b, const nbh_obj* from, const nbh_obj* to) {

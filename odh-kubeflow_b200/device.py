@@ -33,7 +33,7 @@ class DeviceBatch:
         self.n = n0 * tile
         self.in_bytes = 0
         for name, a in arrays.items():
-            if name.endswith(".off") or name in ("k_off", "t_off"):
+            if name.endswith(".off") or name.endswith(".voff") or name in ("k_off", "t_off"):
                 # CSR offsets of tile k are the base offsets shifted by k * (#entries)
                 base = a.astype(np.int64)
                 total = int(base[-1])
@@ -78,6 +78,17 @@ class DeviceBatch:
             s.pod_from, s.pod_to = self._p("pod_from", C.c_uint64), self._p("pod_to", C.c_uint64)
             for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
                 setattr(s, f, self._kv(f))
+        elif k == "StsSparseBatch":
+            s = N.nbg_sts_sparse_batch()
+            s.replicas_from, s.replicas_to = self._p("replicas_from", C.c_int32), self._p("replicas_to", C.c_int32)
+            s.tmpl_from, s.tmpl_to = self._p("tmpl_from", C.c_uint64), self._p("tmpl_to", C.c_uint64)
+            for side in ("pod_from", "pod_to"):
+                ps = N.nbg_podsparse()
+                ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
+                                           self._p(side + ".val", C.c_uint64))
+                setattr(s, side, ps)
+            for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
+                setattr(s, f, self._kv(f))
         elif k == "SvcBatch":
             s = N.nbg_svc_batch()
             s.flags = self._p("flags", C.c_uint8)
@@ -109,7 +120,8 @@ class DeviceBatch:
             rc = lib.nbg_cull_device(ctx.handle, 0, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
                                      C.c_void_p(stream))
         else:
-            fn = {"StsBatch": lib.nbg_diff_sts_device, "SvcBatch": lib.nbg_diff_svc_device,
+            fn = {"StsBatch": lib.nbg_diff_sts_device, "StsSparseBatch": lib.nbg_diff_sts_sparse_device,
+                  "SvcBatch": lib.nbg_diff_svc_device,
                   "VsBatch": lib.nbg_diff_vs_device}[self.kind]
             rc = fn(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
         if rc != N.NBG_OK:

@@ -83,6 +83,10 @@ class Context:
         """Batched CopyStatefulSetFields (COMMON:107-134) + NBCTL:188-194."""
         return self._diff(self._lib.nbg_diff_sts, batch, allow_nil)
 
+    def diff_sts_sparse(self, batch, allow_nil=False):
+        """Same predicate on sparsely stored PodSpec tiles (batch = StsBatch.sparse())."""
+        return self._diff(self._lib.nbg_diff_sts_sparse, batch, allow_nil)
+
     def diff_svc(self, batch):
         """Batched CopyServiceFields (COMMON:166-195)."""
         return self._diff(self._lib.nbg_diff_svc, batch)

@@ -208,6 +208,53 @@ class StsBatch(_Batch):
         return n + (n + 63) // 64 * 8
 
 
+    def sparse(self):
+        """The same pairs with sparsely stored PodSpec tiles (include/nbgraft.h: nbg_sts_sparse_batch)."""
+        return StsSparseBatch(self)
+
+
+class StsSparseBatch:
+    """Non-owning sparse view of a StsBatch (keeps the parent alive)."""
+
+    def __init__(self, parent):
+        self.parent = parent
+
+    @property
+    def view(self):
+        v = N.nbg_sts_sparse_batch()
+        self.n = int(N.nbh().nbh_sts_view_sparse(self.parent._h, C.byref(v)))
+        return v
+
+    def __len__(self):
+        self.view
+        return self.n
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        out["replicas_from"] = _arr(v.replicas_from, n, np.int32)
+        out["replicas_to"] = _arr(v.replicas_to, n, np.int32)
+        out["tmpl_from"] = _arr(v.tmpl_from, n, np.uint64)
+        out["tmpl_to"] = _arr(v.tmpl_to, n, np.uint64)
+        for side in ("pod_from", "pod_to"):
+            ps = getattr(v, side)
+            off = _arr(ps.off, n + 1, np.uint32)
+            out[side + ".mask"] = _arr(ps.mask, n * 3, np.uint64)
+            out[side + ".voff"] = off
+            out[side + ".val"] = _arr(ps.val, int(off[n]) if n else 0, np.uint64)
+        for name in ("labels_from", "labels_to", "ann_from", "ann_to"):
+            _kv_arrays(getattr(v, name), n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+    def algorithmic_bytes(self):
+        n = len(self)
+        return sum(a.nbytes for a in self.arrays().values()) + self.output_bytes(n)
+
+
 class SvcBatch(_Batch):
     _new, _free, _add, _view, _struct = "nbh_svc_new", "nbh_svc_free", "nbh_svc_add", "nbh_svc_view", N.nbg_svc_batch
 

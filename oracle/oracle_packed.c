@@ -80,6 +80,34 @@ static void sts_range(const nbg_sts_batch* in, uint64_t lo, uint64_t hi, uint8_t
   }
 }
 
+static void sts_sparse_range(const nbg_sts_sparse_batch* in, uint64_t lo, uint64_t hi, uint8_t* reason, uint64_t* bitmap) {
+  for (uint64_t i = lo; i < hi; ++i) {
+    unsigned r = 0;
+    const int32_t rf = in->replicas_from[i], rt = in->replicas_to[i];
+    if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) r |= NBG_STS_NILREPLICAS;
+    else if (rf != rt) {
+      r |= NBG_STS_REPLICAS;
+      if (in->tmpl_from[i] != in->tmpl_to[i]) r |= NBG_STS_TMPL_LABELS;
+    }
+    if (live_differs(&in->labels_from, &in->labels_to, i)) r |= NBG_STS_LABELS;
+    if (live_differs(&in->ann_from, &in->ann_to, i)) r |= NBG_STS_ANNOTATIONS;
+    /* rebuild both dense tiles and compare them: the sparse form must mean exactly the dense one */
+    uint64_t a[NBG_POD_SLOTS], b[NBG_POD_SLOTS];
+    for (int side = 0; side < 2; ++side) {
+      const nbg_podsparse* p = side ? &in->pod_to : &in->pod_from;
+      uint64_t* t = side ? b : a;
+      uint32_t at = p->off[i];
+      for (unsigned s = 0; s < NBG_POD_SLOTS; ++s)
+        t[s] = (p->mask[i * 3 + (s >> 6)] >> (s & 63) & 1) ? p->val[at++] : 0;
+      if (at & 1) { if (p->val[at] != 0) r |= 0x40; ++at; }   /* runs are zero-padded to an even count */
+      if (at != p->off[i + 1]) r |= 0x40;                      /* malformed input: popcount(mask) != run length */
+    }
+    if (memcmp(a, b, sizeof a) != 0) r |= NBG_STS_PODSPEC;
+    reason[i] = (uint8_t)r;
+    set_bit(bitmap, i, (r & NBG_STS_UPDATE_MASK) != 0);
+  }
+}
+
 static void svc_range(const nbg_svc_batch* in, uint64_t lo, uint64_t hi, uint8_t* reason, uint64_t* bitmap) {
   for (uint64_t i = lo; i < hi; ++i) {
     unsigned r = 0;
@@ -184,6 +212,7 @@ static void* run_job(void* arg) {
   switch (j->kind) {
     case 0: sts_range((const nbg_sts_batch*)j->in, j->lo, j->hi, j->out8, j->bm1); break;
     case 1: svc_range((const nbg_svc_batch*)j->in, j->lo, j->hi, j->out8, j->bm1); break;
+    case 4: sts_sparse_range((const nbg_sts_sparse_batch*)j->in, j->lo, j->hi, j->out8, j->bm1); break;
     case 2: vs_range((const nbg_vs_batch*)j->in, j->lo, j->hi, j->out8, j->bm1); break;
     default: cull_range((const nbg_cull_batch*)j->in, j->p, j->lo, j->hi, j->out8, j->out32, j->bm1, j->bm2); break;
   }
@@ -218,6 +247,9 @@ static double run(int kind, const void* in, const nbg_cull_params* p, uint64_t n
 /* Each returns the seconds spent in the compare loops (for bench.py). */
 ORC_API double orc2_diff_sts(const nbg_sts_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
   return run(0, in, NULL, n, threads, reason, NULL, bitmap, NULL);
+}
+ORC_API double orc2_diff_sts_sparse(const nbg_sts_sparse_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
+  return run(4, in, NULL, n, threads, reason, NULL, bitmap, NULL);
 }
 ORC_API double orc2_diff_svc(const nbg_svc_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
   return run(1, in, NULL, n, threads, reason, NULL, bitmap, NULL);

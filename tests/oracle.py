@@ -47,7 +47,7 @@ def lib():
                                      C.c_int, vp, vp]
         L.orc_bench_cull.restype = C.c_double
         for name, bt in (("orc2_diff_sts", N.nbg_sts_batch), ("orc2_diff_svc", N.nbg_svc_batch),
-                         ("orc2_diff_vs", N.nbg_vs_batch)):
+                         ("orc2_diff_vs", N.nbg_vs_batch), ("orc2_diff_sts_sparse", N.nbg_sts_sparse_batch)):
             f = getattr(L, name)
             f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
             f.restype = C.c_double
@@ -138,6 +138,10 @@ def _diff2(fn, batch, threads):
 
 def packed_diff_sts(batch, threads=1):
     return _diff2(lib().orc2_diff_sts, batch, threads)
+
+
+def packed_diff_sts_sparse(batch, threads=1):
+    return _diff2(lib().orc2_diff_sts_sparse, batch, threads)
 
 
 def packed_diff_svc(batch, threads=1):

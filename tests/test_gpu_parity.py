@@ -341,3 +341,50 @@ def test_concurrent_callers(ctx):
     [t.start() for t in ts]
     [t.join() for t in ts]
     assert not errs
+
+
+# ------------------------------------------------------------ sparse tiles
+@pytest.mark.parametrize("kind,n", [(host.FLEET_KUBEFLOW, 20011), (host.FLEET_ODH, 9000), (host.FLEET_KUBEFLOW, 1),
+                                    (host.FLEET_KUBEFLOW, 65), (host.FLEET_ODH, 32769)])
+def test_sparse_tiles_give_the_dense_answer(ctx, kind, n):
+    fleet = host.Fleet(kind, host.SEED_BASE + 9, n, max(n // 30, 1))
+    sts = fleet.pack(svc=False, vs=False)[0]
+    dense = ctx.diff_sts(sts)
+    sparse = ctx.diff_sts_sparse(sts.sparse())
+    want = O.packed_diff_sts_sparse(sts.sparse(), threads=4)
+    assert np.array_equal(sparse[0], dense[0]) and np.array_equal(sparse[1], dense[1])
+    assert np.array_equal(sparse[0], want[0]) and np.array_equal(sparse[1], want[1])
+    assert sts.sparse().algorithmic_bytes() < 0.6 * sts.algorithmic_bytes()
+
+
+@pytest.mark.parametrize("name,frm,to,want", STS_PAIRS, ids=[p[0][:60] for p in STS_PAIRS])
+def test_derived_sts_sparse(ctx, name, frm, to, want):
+    b = host.StsBatch().add(host.StatefulSet(frm), host.StatefulSet(to))
+    reason, bm = ctx.diff_sts_sparse(b.sparse())
+    assert int(reason[0]) == want and int(bm[0]) == int((want & 0x0F) != 0)
+
+
+def test_sparse_device_api_tiled(ctx):
+    dev = importlib.import_module("odh-kubeflow_b200.device")
+    import torch
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, 9984, 300)
+    sts = fleet.pack(svc=False, vs=False)[0]
+    base = ctx.diff_sts(sts)
+    d = dev.DeviceBatch.from_host(sts.sparse(), device=0, tile=40)
+    reason, bitmap = d.run(ctx)
+    torch.cuda.synchronize()
+    assert (reason.cpu().numpy().reshape(40, -1) == base[0][None, :]).all()
+    assert (bitmap.cpu().numpy().view(np.uint64).reshape(40, -1) == base[1][None, :]).all()
+
+
+def test_sparse_bad_runs_are_rejected(ctx):
+    lib = N.nbg()
+    sts = host.Fleet(host.FLEET_KUBEFLOW, 1, 100, 2).pack(svc=False, vs=False)[0]
+    sp = sts.sparse()
+    view = sp.view
+    off = sp.arrays()["pod_to.voff"].copy()
+    off[10:] += 500                                     # one run longer than a tile
+    view.pod_to.off = off.ctypes.data_as(N.u32p)
+    reason, bm = np.zeros(100, np.uint8), np.zeros(2, np.uint64)
+    assert lib.nbg_diff_sts_sparse(ctx.handle, C.byref(view), 100, reason.ctypes.data_as(C.c_void_p),
+                                   bm.ctypes.data_as(C.c_void_p)) == N.NBG_E_RANGE

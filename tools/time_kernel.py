@@ -14,7 +14,8 @@ if kind == "cull":
     cf = host.CullFleet(host.SEED_BASE + 3, n); b = cf.pack(); kw = dict(now=(cf.now_sec, cf.now_nsec))
 else:
     f = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, n, max(200, n // 50))
-    b = f.pack(sts=kind == "sts", svc=kind == "svc", vs=kind == "vs")[{"sts": 0, "svc": 1, "vs": 2}[kind]]; kw = {}
+    b = f.pack(sts=kind in ("sts", "sts_sparse"), svc=kind == "svc", vs=kind == "vs")[{"sts": 0, "sts_sparse": 0, "svc": 1, "vs": 2}[kind]]; kw = {}
+    if kind == "sts_sparse": b = b.sparse()
 d = dev.DeviceBatch.from_host(b)
 flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 for mode in ((1, 0) if kind == "cull" else (None,)):
