@@ -10,6 +10,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -128,19 +129,15 @@ int slot_download(Dev& d, Slot& sl, const Layout& lay) {
   return NBG_OK;
 }
 
-bool csr_ok(const nbg_kvmap& m, uint64_t n) {
-  if (!m.off) return false;
-  for (uint64_t i = 0; i < n; ++i)
-    if (m.off[i] > m.off[i + 1]) return false;
-  if (m.off[n] > m.off[0] && !m.ent) return false;
-  return true;
+// Offsets of rows [i0,i1] must be monotone.  Branch-free so it vectorises: the check runs
+// per pipeline chunk, right before that chunk is queued, and must not hold the copies up.
+bool off_ok(const uint32_t* off, uint64_t i0, uint64_t i1) {
+  unsigned bad = 0;
+  for (uint64_t i = i0; i < i1; ++i) bad |= (unsigned)(off[i] > off[i + 1]);
+  return bad == 0;
 }
-bool off_ok(const uint32_t* off, uint64_t n) {
-  if (!off) return false;
-  for (uint64_t i = 0; i < n; ++i)
-    if (off[i] > off[i + 1]) return false;
-  return true;
-}
+bool csr_ok(const nbg_kvmap& m, uint64_t i0, uint64_t i1) { return off_ok(m.off, i0, i1); }
+bool csr_ptrs_ok(const nbg_kvmap& m, uint64_t n) { return m.off && (m.ent || m.off[n] == m.off[0]); }
 
 // Upload rows [i0,i1) of a CSR map; returns device pointers and the base offset.
 struct CsrDev { size_t off_at, ent_at; unsigned base; };
@@ -191,11 +188,21 @@ int for_each_device(nbg_ctx* ctx, uint64_t n, F&& run_range) {
   return rc;
 }
 
-constexpr uint64_t kStsChunk = 8192;     // objects per pipeline chunk (~27 MB)
-constexpr uint64_t kStsSparseChunk = 32768;  // (~25 MB at ~35 non-zero slots per side)
-constexpr uint64_t kSvcChunk = 65536;    // (~21 MB)
-constexpr uint64_t kVsChunk = 131072;    // (~20 MB)
-constexpr uint64_t kCullChunk = 262144;  // notebooks (~22 MB at 4 records each)
+// Objects per pipeline chunk (multiples of 64 so bitmap words never straddle chunks).
+// NBG_CHUNK_SCALE (environment, power of two, default 2) scales all of them — a tuning knob.
+uint64_t chunk_scale() {
+  static const uint64_t s = [] {
+    const char* e = getenv("NBG_CHUNK_SCALE");
+    long v = e ? atol(e) : 2;
+    return (uint64_t)(v >= 1 && v <= 64 ? v : 1);
+  }();
+  return s;
+}
+#define kStsChunk (8192 * chunk_scale())          // ~27 MB
+#define kStsSparseChunk (32768 * chunk_scale())   // ~25 MB at ~35 non-zero slots per side
+#define kSvcChunk (65536 * chunk_scale())         // ~21 MB
+#define kVsChunk (131072 * chunk_scale())         // ~20 MB
+#define kCullChunk (262144 * chunk_scale())       // notebooks, ~22 MB at 4 records each
 
 int check_dev(const nbg_ctx* ctx, int device) {
   if (!ctx) return NBG_E_INVAL;
@@ -439,7 +446,7 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_
   if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
       p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
     return NBG_E_INVAL;
-  if (!off_ok(in->k_off, n) || !off_ok(in->t_off, n)) return NBG_E_RANGE;
+  if (!in->k_off || !in->t_off) return NBG_E_INVAL;
   if ((in->k_off[n] > in->k_off[0] && (!in->k_sec || !in->k_nsf)) ||
       (in->t_off[n] > in->t_off[0] && (!in->t_sec || !in->t_nsf)))
     return NBG_E_INVAL;
@@ -448,6 +455,7 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_
     uint64_t c = 0;
     for (uint64_t i0 = lo; i0 < hi; i0 += kCullChunk, ++c) {
       const uint64_t i1 = i0 + kCullChunk < hi ? i0 + kCullChunk : hi, m = i1 - i0;
+      if (!off_ok(in->k_off, i0, i1) || !off_ok(in->t_off, i0, i1)) return NBG_E_RANGE;
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const unsigned kb = in->k_off[i0], tb = in->t_off[i0];
@@ -491,14 +499,17 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
   if (!reason || !bitmap || !in->replicas_from || !in->replicas_to || !in->tmpl_from || !in->tmpl_to ||
       !in->pod_from || !in->pod_to)
     return NBG_E_INVAL;
-  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
-      !csr_ok(in->ann_to, n))
-    return NBG_E_RANGE;
+  if (!csr_ptrs_ok(in->labels_from, n) || !csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_from, n) ||
+      !csr_ptrs_ok(in->ann_to, n))
+    return NBG_E_INVAL;
 
   int rc = for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
     uint64_t c = 0;
     for (uint64_t i0 = lo; i0 < hi; i0 += kStsChunk, ++c) {
       const uint64_t i1 = i0 + kStsChunk < hi ? i0 + kStsChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_from, i0, i1) || !csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_from, i0, i1) ||
+          !csr_ok(in->ann_to, i0, i1))
+        return NBG_E_RANGE;
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const size_t a_rf = lay.in(in->replicas_from + i0, m * 4);
@@ -526,9 +537,9 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
     return NBG_OK;
   });
   if (rc != NBG_OK) return rc;
-  for (uint64_t i = 0; i < n; ++i)
-    if (reason[i] & NBG_STS_NILREPLICAS) return NBG_E_NILREPLICAS;
-  return NBG_OK;
+  unsigned any = 0;
+  for (uint64_t i = 0; i < n; ++i) any |= reason[i];
+  return (any & NBG_STS_NILREPLICAS) ? NBG_E_NILREPLICAS : NBG_OK;
 }
 
 int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
@@ -537,23 +548,29 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
   if (!reason || !bitmap || !in->replicas_from || !in->replicas_to || !in->tmpl_from || !in->tmpl_to ||
       !in->pod_from.mask || !in->pod_to.mask)
     return NBG_E_INVAL;
-  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
-      !csr_ok(in->ann_to, n) || !off_ok(in->pod_from.off, n) || !off_ok(in->pod_to.off, n))
-    return NBG_E_RANGE;
+  if (!csr_ptrs_ok(in->labels_from, n) || !csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_from, n) ||
+      !csr_ptrs_ok(in->ann_to, n) || !in->pod_from.off || !in->pod_to.off)
+    return NBG_E_INVAL;
   if ((in->pod_from.off[n] > in->pod_from.off[0] && !in->pod_from.val) ||
       (in->pod_to.off[n] > in->pod_to.off[0] && !in->pod_to.val))
     return NBG_E_INVAL;
   if (((uintptr_t)in->pod_from.val | (uintptr_t)in->pod_to.val) & 15u) return NBG_E_INVAL;   // 128-bit loads
-  for (uint64_t i = 0; i <= n; ++i)  // runs are even-padded ...
-    if ((in->pod_from.off[i] | in->pod_to.off[i]) & 1u) return NBG_E_RANGE;
-  for (uint64_t i = 0; i < n; ++i)   // ... and never longer than the tile
-    if (in->pod_from.off[i + 1] - in->pod_from.off[i] > NBG_POD_SLOTS || in->pod_to.off[i + 1] - in->pod_to.off[i] > NBG_POD_SLOTS)
-      return NBG_E_RANGE;
 
   int rc = for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
     uint64_t c = 0;
     for (uint64_t i0 = lo; i0 < hi; i0 += kStsSparseChunk, ++c) {
       const uint64_t i1 = i0 + kStsSparseChunk < hi ? i0 + kStsSparseChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_from, i0, i1) || !csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_from, i0, i1) ||
+          !csr_ok(in->ann_to, i0, i1) || !off_ok(in->pod_from.off, i0, i1) || !off_ok(in->pod_to.off, i0, i1))
+        return NBG_E_RANGE;
+      {  // runs are even-padded and never longer than a tile
+        const uint32_t *of = in->pod_from.off, *ot = in->pod_to.off;
+        unsigned bad = (of[i0] | ot[i0]) & 1u;
+        for (uint64_t i = i0; i < i1; ++i)
+          bad |= ((of[i + 1] | ot[i + 1]) & 1u) | (unsigned)(of[i + 1] - of[i] > NBG_POD_SLOTS) |
+                 (unsigned)(ot[i + 1] - ot[i] > NBG_POD_SLOTS);
+        if (bad) return NBG_E_RANGE;
+      }
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const size_t a_rf = lay.in(in->replicas_from + i0, m * 4), a_rt = lay.in(in->replicas_to + i0, m * 4);
@@ -585,23 +602,26 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
     return NBG_OK;
   });
   if (rc != NBG_OK) return rc;
-  for (uint64_t i = 0; i < n; ++i)
-    if (reason[i] & NBG_STS_NILREPLICAS) return NBG_E_NILREPLICAS;
-  return NBG_OK;
+  unsigned any = 0;
+  for (uint64_t i = 0; i < n; ++i) any |= reason[i];
+  return (any & NBG_STS_NILREPLICAS) ? NBG_E_NILREPLICAS : NBG_OK;
 }
 
 int nbg_diff_svc(nbg_ctx* ctx, const nbg_svc_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
   if (!ctx || !in) return NBG_E_INVAL;
   if (n == 0) return NBG_OK;
   if (!reason || !bitmap || !in->flags || !in->ports_from || !in->ports_to) return NBG_E_INVAL;
-  if (!csr_ok(in->labels_from, n) || !csr_ok(in->labels_to, n) || !csr_ok(in->ann_from, n) ||
-      !csr_ok(in->ann_to, n) || !csr_ok(in->sel_from, n) || !csr_ok(in->sel_to, n))
-    return NBG_E_RANGE;
+  if (!csr_ptrs_ok(in->labels_from, n) || !csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_from, n) ||
+      !csr_ptrs_ok(in->ann_to, n) || !csr_ptrs_ok(in->sel_from, n) || !csr_ptrs_ok(in->sel_to, n))
+    return NBG_E_INVAL;
 
   return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
     uint64_t c = 0;
     for (uint64_t i0 = lo; i0 < hi; i0 += kSvcChunk, ++c) {
       const uint64_t i1 = i0 + kSvcChunk < hi ? i0 + kSvcChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_from, i0, i1) || !csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_from, i0, i1) ||
+          !csr_ok(in->ann_to, i0, i1) || !csr_ok(in->sel_from, i0, i1) || !csr_ok(in->sel_to, i0, i1))
+        return NBG_E_RANGE;
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const size_t a_fl = lay.in(in->flags + i0, m);
@@ -632,12 +652,13 @@ int nbg_diff_vs(nbg_ctx* ctx, const nbg_vs_batch* in, uint64_t n, uint8_t* reaso
   if (!ctx || !in) return NBG_E_INVAL;
   if (n == 0) return NBG_OK;
   if (!reason || !bitmap || !in->flags || !in->spec_from || !in->spec_to) return NBG_E_INVAL;
-  if (!csr_ok(in->hdr_from, n) || !csr_ok(in->hdr_to, n)) return NBG_E_RANGE;
+  if (!csr_ptrs_ok(in->hdr_from, n) || !csr_ptrs_ok(in->hdr_to, n)) return NBG_E_INVAL;
 
   return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
     uint64_t c = 0;
     for (uint64_t i0 = lo; i0 < hi; i0 += kVsChunk, ++c) {
       const uint64_t i1 = i0 + kVsChunk < hi ? i0 + kVsChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->hdr_from, i0, i1) || !csr_ok(in->hdr_to, i0, i1)) return NBG_E_RANGE;
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const size_t a_fl = lay.in(in->flags + i0, m);
