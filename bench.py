@@ -478,6 +478,49 @@ def other_configs(pkg, dev, ctx, torch, peak):
                                "algorithmic_GBps": stream_bytes / (med * 1e-3) / 1e9,
                                "table_bytes": int(need), "note": "hash table (scratch) is L2-resident; random access, not a streaming roofline",
                                "cpu_packed_1thread_notebooks_per_s": n / cpu_s, "parity": "bit-exact vs packed oracle"}
+    # RFC3339 parse + "idle" compare of kernel records on the device
+    import json as _json
+    cf2 = host.CullFleet(host.SEED_BASE + 3, 250_000)
+    la, st = [], []
+    for i in range(0, 250_000):
+        nb = _json.loads(cf2.json(i))
+        for k in nb["kernels"]:
+            la.append(k["last_activity"]); st.append(k["execution_state"])
+    ta, ts = pkg.engine.StringTable(la), pkg.engine.StringTable(st)
+    R = ta.n
+    dv = {}
+    for name, t in (("a", ta), ("s", ts)):
+        dv[name] = (torch.from_numpy(t.off.view(np.int32)).cuda(), torch.from_numpy(t.bytes.copy()).cuda())
+    va = N.nbg_strings(C.cast(dv["a"][0].data_ptr(), N.u32p), C.cast(dv["a"][1].data_ptr(), N.u8p))
+    vs_ = N.nbg_strings(C.cast(dv["s"][0].data_ptr(), N.u32p), C.cast(dv["s"][1].data_ptr(), N.u8p))
+    d_sec = torch.zeros(R, dtype=torch.int64, device="cuda")
+    d_nsf = torch.zeros(R, dtype=torch.int32, device="cuda")
+    d_zone = torch.zeros(R, dtype=torch.int32, device="cuda")
+
+    def parse():
+        assert lib.nbg_parse_records_device(ctx.handle, 0, C.byref(va), C.byref(vs_), R, d_sec.data_ptr(), d_nsf.data_ptr(),
+                                            d_zone.data_ptr(), stream) == 0
+    ms = []
+    for it in range(13):
+        flush.fill_(it)
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record(); parse(); e.record()
+        torch.cuda.synchronize()
+        if it >= 3:
+            ms.append(s.elapsed_time(e))
+    med = statistics.median(ms)
+    t0 = time.perf_counter()
+    cpu = [host.parse_rfc3339(x) for x in la[:200_000]]
+    cpu_s = time.perf_counter() - t0
+    ok = all((c is None and not (w & 0x40000000)) or (c is not None and c[0] == s_ and c[1] == (w & 0x3FFFFFFF))
+             for c, s_, w in zip(cpu, d_sec[:200_000].cpu().tolist(), d_nsf[:200_000].cpu().numpy().view(np.uint32).tolist()))
+    assert ok, "device RFC3339 parse differs from the host parser"
+    text_bytes = int(ta.off[-1]) + int(ts.off[-1]) + 8 * (R + 1) + 16 * R
+    out["rfc3339_parse_1M_records"] = {"records_per_s": R / (med * 1e-3), "ms": med, "records": R,
+                                       "algorithmic_GBps": text_bytes / (med * 1e-3) / 1e9, "frac_of_peak": text_bytes / (med * 1e-3) / 1e9 / peak,
+                                       "bytes_per_record": round(text_bytes / R, 1),
+                                       "cpu_host_parser_via_ctypes_records_per_s": 200_000 / cpu_s,
+                                       "parity": "bit-exact vs host parser on 200k records (tests: vs both CPU parsers + fuzz)"}
     return out
 
 

@@ -260,6 +260,20 @@ int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n,
 /* never 0 */
 uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
 
+/* ---- strings on the device (the host work right in front of the predicates) ---- */
+/* A table of R strings as CSR: string r is bytes[off[r] .. off[r+1]).  `bytes` must be
+ * 16-byte aligned and its allocation padded to a multiple of 16 bytes (the kernels copy
+ * whole 16-byte vectors). */
+typedef struct nbg_strings { const uint32_t* off; const uint8_t* bytes; } nbg_strings;
+/* time.Parse(time.RFC3339, last_activity) for R kernel/terminal records (CULL:332,339) and,
+ * when `state` is given, execution_state == "idle" (CULL:320): fills exactly the
+ * (sec, nsf) words nbg_cull_batch wants (NBG_REC_PARSE_OK, NBG_REC_IDLE, nsec), plus the
+ * zone offset in seconds of every record (nullable) for formatting results. */
+int nbg_parse_records(nbg_ctx* ctx, const nbg_strings* last_activity, const nbg_strings* state /*nullable*/,
+                      uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone /*nullable*/);
+/* nbg_hash64 of every string of the table (label keys/values, env values, ...). */
+int nbg_hash_strings(nbg_ctx* ctx, const nbg_strings* strings, uint64_t R, uint64_t* out);
+
 /* ---- device-pointer entry points (asynchronous, no copies) ------------- */
 /* Same kernels on buffers already resident in HBM.  Every pointer inside the
  * batch and every output is a DEVICE pointer on `device` (an index into the
@@ -286,6 +300,10 @@ size_t nbg_owner_join_scratch_bytes(uint64_t m);
 int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint64_t n,
                           const uint64_t* sts_key, uint64_t m, uint32_t* match,
                           void* scratch, size_t scratch_bytes, void* stream);
+int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* last_activity, const nbg_strings* state,
+                             uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone, void* stream);
+int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings, uint64_t R, uint64_t* out,
+                            void* stream);
 /* Owner join that allocates nothing — it has no counterpart in the reference.
  * For callers that may not call the CUDA allocator while they run: code on a
  * reconcile path with a latency bound (cudaMalloc/cudaFree synchronise the whole

@@ -69,6 +69,10 @@ class nbg_vs_batch(C.Structure):
                 ("hdr_from", nbg_kvmap), ("hdr_to", nbg_kvmap)]
 
 
+class nbg_strings(C.Structure):
+    _fields_ = [("off", u32p), ("bytes", u8p)]
+
+
 class nbg_cull_batch(C.Structure):
     _fields_ = [("k_off", u32p), ("k_sec", i64p), ("k_nsf", u32p),
                 ("t_off", u32p), ("t_sec", i64p), ("t_nsf", u32p),
@@ -107,6 +111,7 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
+    "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
 
 _vp = C.c_void_p
@@ -153,6 +158,15 @@ def _bind_nbg(lib):
     lib.nbg_owner_join_device.restype = C.c_int
     lib.nbg_owner_join_static.argtypes = [_vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp]
     lib.nbg_owner_join_static.restype = C.c_int
+    PS = C.POINTER(nbg_strings)
+    lib.nbg_parse_records.argtypes = [_vp, PS, PS, C.c_uint64, _vp, _vp, _vp]
+    lib.nbg_parse_records.restype = C.c_int
+    lib.nbg_parse_records_device.argtypes = [_vp, C.c_int, PS, PS, C.c_uint64, _vp, _vp, _vp, _vp]
+    lib.nbg_parse_records_device.restype = C.c_int
+    lib.nbg_hash_strings.argtypes = [_vp, PS, C.c_uint64, _vp]
+    lib.nbg_hash_strings.restype = C.c_int
+    lib.nbg_hash_strings_device.argtypes = [_vp, C.c_int, PS, C.c_uint64, _vp, _vp]
+    lib.nbg_hash_strings_device.restype = C.c_int
     lib.nbg_ctx_stream.argtypes = [_vp, C.c_int]
     lib.nbg_ctx_stream.restype = _vp
     lib.nbg_sync.argtypes = [_vp, C.c_int]

@@ -31,6 +31,10 @@ cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const 
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
                                uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_parse_records(const uint32_t*, const unsigned char*, const uint32_t*, const unsigned char*,
+                                     unsigned long long, unsigned, unsigned, int64_t*, uint32_t*, int32_t*, cudaStream_t);
+cudaError_t nbg_launch_hash_strings(const uint32_t*, const unsigned char*, unsigned long long, unsigned, uint64_t*,
+                                    cudaStream_t);
 unsigned long long nbg_join_table_slots(unsigned long long m);
 cudaError_t nbg_launch_owner_join(const unsigned long long*, unsigned long long, const unsigned long long*,
                                   unsigned long long, uint32_t*, void*, cudaStream_t);
@@ -203,6 +207,7 @@ uint64_t chunk_scale() {
 #define kSvcChunk (65536 * chunk_scale())         // ~21 MB
 #define kVsChunk (131072 * chunk_scale())         // ~20 MB
 #define kCullChunk (262144 * chunk_scale())       // notebooks, ~22 MB at 4 records each
+#define kTextChunk (1048576 * chunk_scale())      // strings, ~30 MB of timestamps
 
 int check_dev(const nbg_ctx* ctx, int device) {
   if (!ctx) return NBG_E_INVAL;
@@ -404,7 +409,88 @@ int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint
   return NBG_OK;
 }
 
+int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* la, const nbg_strings* state, uint64_t R,
+                             int64_t* sec, uint32_t* nsf, int32_t* zone, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (R == 0) return NBG_OK;
+  if (!la || !la->off || !la->bytes || !sec || !nsf || (state && (!state->off || !state->bytes))) return NBG_E_INVAL;
+  if (((uintptr_t)la->bytes & 15u) || (state && ((uintptr_t)state->bytes & 15u))) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  CU(nbg_launch_parse_records(la->off, la->bytes, state ? state->off : nullptr, state ? state->bytes : nullptr, R, 0, 0,
+                              sec, nsf, zone, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings, uint64_t R, uint64_t* out, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (R == 0) return NBG_OK;
+  if (!strings || !strings->off || !strings->bytes || !out) return NBG_E_INVAL;
+  if ((uintptr_t)strings->bytes & 15u) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  CU(nbg_launch_hash_strings(strings->off, strings->bytes, R, 0, out, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
 // ------------------------------------------------------------ host-buffer API
+int nbg_parse_records(nbg_ctx* ctx, const nbg_strings* la, const nbg_strings* state, uint64_t R, int64_t* sec,
+                      uint32_t* nsf, int32_t* zone) {
+  if (!ctx || !la) return NBG_E_INVAL;
+  if (R == 0) return NBG_OK;
+  if (!la->off || !sec || !nsf || (state && !state->off)) return NBG_E_INVAL;
+  if ((la->off[R] > la->off[0] && !la->bytes) || (state && state->off[R] > state->off[0] && !state->bytes)) return NBG_E_INVAL;
+  return for_each_device(ctx, R, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kTextChunk, ++c) {
+      const uint64_t i1 = i0 + kTextChunk < hi ? i0 + kTextChunk : hi, m = i1 - i0;
+      if (!off_ok(la->off, i0, i1) || (state && !off_ok(state->off, i0, i1))) return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const unsigned tb = la->off[i0], sb = state ? state->off[i0] : 0;
+      const size_t nt = la->off[i1] - tb, ns = state ? state->off[i1] - sb : 0;
+      const size_t a_to = lay.in(la->off + i0, (m + 1) * 4), a_tx = lay.in(nt ? la->bytes + tb : nullptr, nt);
+      const size_t a_so = state ? lay.in(state->off + i0, (m + 1) * 4) : 0, a_sx = state ? lay.in(ns ? state->bytes + sb : nullptr, ns) : 0;
+      const size_t o_sec = lay.out(sec + i0, m * 8), o_nsf = lay.out(nsf + i0, m * 4);
+      const size_t o_zone = zone ? lay.out(zone + i0, m * 4) : 0;
+      if (int r = slot_upload(d, sl, lay)) return r;
+      CU(nbg_launch_parse_records((const uint32_t*)(sl.dev + a_to), (const unsigned char*)(sl.dev + a_tx),
+                                  state ? (const uint32_t*)(sl.dev + a_so) : nullptr,
+                                  state ? (const unsigned char*)(sl.dev + a_sx) : nullptr, m, tb, sb,
+                                  (int64_t*)(sl.dev + o_sec), (uint32_t*)(sl.dev + o_nsf),
+                                  zone ? (int32_t*)(sl.dev + o_zone) : nullptr, d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_hash_strings(nbg_ctx* ctx, const nbg_strings* strings, uint64_t R, uint64_t* out) {
+  if (!ctx || !strings) return NBG_E_INVAL;
+  if (R == 0) return NBG_OK;
+  if (!strings->off || !out || (strings->off[R] > strings->off[0] && !strings->bytes)) return NBG_E_INVAL;
+  return for_each_device(ctx, R, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kTextChunk, ++c) {
+      const uint64_t i1 = i0 + kTextChunk < hi ? i0 + kTextChunk : hi, m = i1 - i0;
+      if (!off_ok(strings->off, i0, i1)) return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const unsigned b0 = strings->off[i0];
+      const size_t nb = strings->off[i1] - b0;
+      const size_t a_o = lay.in(strings->off + i0, (m + 1) * 4), a_x = lay.in(nb ? strings->bytes + b0 : nullptr, nb);
+      const size_t o_h = lay.out(out + i0, m * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      CU(nbg_launch_hash_strings((const uint32_t*)(sl.dev + a_o), (const unsigned char*)(sl.dev + a_x), m, b0,
+                                 (uint64_t*)(sl.dev + o_h), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
 int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n, const uint64_t* sts_key, uint64_t m,
                    uint32_t* match) {
   if (!ctx) return NBG_E_INVAL;

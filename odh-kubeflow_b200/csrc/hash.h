@@ -17,7 +17,13 @@
 extern "C" {
 #endif
 
-static inline uint64_t nbg_mix64(uint64_t x) { /* splitmix64 finaliser */
+#ifdef __CUDACC__
+#define NBG_HD __host__ __device__
+#else
+#define NBG_HD
+#endif
+
+NBG_HD static inline uint64_t nbg_mix64(uint64_t x) { /* splitmix64 finaliser */
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
   x ^= x >> 27; x *= 0x94D049BB133111EBull;
   x ^= x >> 31;

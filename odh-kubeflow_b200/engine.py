@@ -125,6 +125,50 @@ def _owner_join(self, nb_keys, sts_keys):
 Context.owner_join = _owner_join
 
 
+class StringTable:
+    """R strings as CSR (off u32[R+1], bytes padded to 16) — the layout of nbg_strings."""
+
+    def __init__(self, strings):
+        enc = [s if isinstance(s, (bytes, bytearray)) else s.encode() for s in strings]
+        self.n = len(enc)
+        lens = np.fromiter((len(b) for b in enc), dtype=np.int64, count=self.n)
+        self.off = np.zeros(self.n + 1, dtype=np.uint32)
+        np.cumsum(lens, out=self.off[1:])
+        total = int(self.off[-1])
+        raw = np.zeros((total + 15) // 16 * 16 + 16, dtype=np.uint8)
+        # 16-byte aligned start inside the numpy buffer
+        shift = (-raw.ctypes.data) % 16
+        self._raw = raw
+        self.bytes = raw[shift:shift + (total + 15) // 16 * 16]
+        self.bytes[:total] = np.frombuffer(b"".join(enc), dtype=np.uint8)
+        self.view = N.nbg_strings(self.off.ctypes.data_as(N.u32p), self.bytes.ctypes.data_as(N.u8p))
+
+
+def _parse_records(self, last_activity, states=None):
+    """time.Parse(RFC3339) + execution_state == "idle" for every record, on the GPU.
+    Returns (sec int64[R], nsf uint32[R], zone int32[R])."""
+    la = last_activity if isinstance(last_activity, StringTable) else StringTable(last_activity)
+    st = None if states is None else (states if isinstance(states, StringTable) else StringTable(states))
+    R = la.n
+    sec, nsf, zone = np.zeros(R, np.int64), np.zeros(R, np.uint32), np.zeros(R, np.int32)
+    _check(self._lib.nbg_parse_records(self._h, C.byref(la.view), C.byref(st.view) if st else None, R,
+                                       sec.ctypes.data_as(C.c_void_p), nsf.ctypes.data_as(C.c_void_p),
+                                       zone.ctypes.data_as(C.c_void_p)), "nbg_parse_records")
+    return sec, nsf, zone
+
+
+def _hash_strings(self, strings):
+    """nbg_hash64 of every string, on the GPU."""
+    tab = strings if isinstance(strings, StringTable) else StringTable(strings)
+    out = np.zeros(tab.n, np.uint64)
+    _check(self._lib.nbg_hash_strings(self._h, C.byref(tab.view), tab.n, out.ctypes.data_as(C.c_void_p)), "nbg_hash_strings")
+    return out
+
+
+Context.parse_records = _parse_records
+Context.hash_strings = _hash_strings
+
+
 def bitmap_to_bools(bitmap, n):
     """uint64 words -> bool[n] (bit i of word i//64)."""
     bits = np.unpackbits(bitmap.view(np.uint8), bitorder="little")

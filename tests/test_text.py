@@ -1,0 +1,131 @@
+"""Device-side string work: time.Parse(time.RFC3339) + "idle" compare for
+kernel/terminal records, and nbg_hash64 of string tables.  Bit-exact against the CPU parsers
+(the oracle's layout-driven one and the packer's) and the host hash."""
+import random
+
+import numpy as np
+import pytest
+
+import cases
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+pkg, host, N = O.pkg, O.host, O.N
+PARSE_OK, IDLE, NSEC = 0x40000000, 0x80000000, 0x3FFFFFFF
+
+
+def _expect(strings):
+    sec, nsf, zone = [], [], []
+    for s in strings:
+        r = O.parse_rfc3339(s.decode("latin-1") if isinstance(s, bytes) else s)
+        if r:
+            sec.append(r[0]); nsf.append(r[1] | PARSE_OK); zone.append(r[2])
+        else:
+            sec.append(0); nsf.append(0); zone.append(0)
+    return np.array(sec, np.int64), np.array(nsf, np.uint32), np.array(zone, np.int32)
+
+
+def test_reference_and_derived_timestamp_cases(ctx):
+    texts = [c[0] for c in cases.RFC3339_CASES]
+    sec, nsf, zone = ctx.parse_records(texts)
+    for (text, want), s, w, z in zip(cases.RFC3339_CASES, sec, nsf, zone):
+        got = (int(s), int(w & NSEC), int(z)) if w & PARSE_OK else None
+        assert got == want, text
+
+
+def _mutations(rng, n):
+    base = ["2025-12-31T23:10:00Z", "2025-12-31T23:10:00.123456Z", "2021-08-30T15:37:36.990063Z", "2024-02-29T00:00:00+05:30",
+            "1999-01-01T01:02:03.000000001-11:00", "2026-01-01T00:00:00,5Z", "0001-01-01T00:00:00Z", "9999-12-31T23:59:59.999999999+24:00",
+            "2025-06-15T7:08:09Z", "2025-12-31T23:10:00.12345678901234567890Z"]
+    alphabet = "0123456789-:TZ.,+ tz/"
+    out = []
+    for _ in range(n):
+        s = list(rng.choice(base))
+        for _ in range(rng.choice([0, 1, 1, 2, 3])):
+            op = rng.randrange(3)
+            if op == 0 and s:
+                s[rng.randrange(len(s))] = rng.choice(alphabet)
+            elif op == 1 and s:
+                del s[rng.randrange(len(s))]
+            else:
+                s.insert(rng.randrange(len(s) + 1), rng.choice(alphabet))
+        out.append("".join(s))
+    return out
+
+
+def test_fuzz_against_both_cpu_parsers(ctx):
+    rng = random.Random(1234)
+    texts = _mutations(rng, 60000) + ["", "x", "2025"]
+    sec, nsf, zone = ctx.parse_records(texts)
+    want = _expect(texts)
+    assert np.array_equal(sec, want[0]) and np.array_equal(nsf, want[1]) and np.array_equal(zone, want[2])
+    assert 0.05 < (nsf & PARSE_OK).astype(bool).mean() < 0.95          # both outcomes well represented
+    for t in texts[:3000]:                                             # and the packer's parser agrees too
+        assert host.parse_rfc3339(t) == O.parse_rfc3339(t), t
+
+
+def test_fleet_records_match_the_host_packer(ctx):
+    """Device parse + idle flag == the words the host packer produces for the cull kernel."""
+    import json
+    cf = host.CullFleet(host.SEED_BASE + 3, 30000)
+    b = cf.pack()
+    arr = b.arrays()
+    la, st = [], []
+    for i in range(cf.n):
+        nb = json.loads(cf.json(i))
+        for k in nb["kernels"]:
+            la.append(k["last_activity"]); st.append(k["execution_state"])
+    sec, nsf, zone = ctx.parse_records(la, st)
+    assert np.array_equal(sec, arr["k_sec"]) and np.array_equal(nsf, arr["k_nsf"])
+    # feeding the device-parsed words to the cull kernel gives the same decisions
+    assert (nsf & IDLE).astype(bool).mean() > 0.7
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 4097])
+def test_ragged_and_long_strings(ctx, n):
+    rng = random.Random(n)
+    texts = _mutations(rng, n)
+    texts[0] = "2025-12-31T23:10:00." + "1" * 3000 + "Z"               # longer than the staging buffer: global path
+    sec, nsf, zone = ctx.parse_records(texts)
+    want = _expect(texts)
+    assert np.array_equal(sec, want[0]) and np.array_equal(nsf, want[1]) and np.array_equal(zone, want[2])
+    assert nsf[0] & PARSE_OK and (nsf[0] & NSEC) == 111111111
+
+
+def test_hash_strings_equals_host_hash(ctx):
+    rng = random.Random(7)
+    strings = ["", "a", "app", "opendatahub.io/dashboard", "x" * 7, "y" * 8, "z" * 9, "w" * 4000]
+    strings += ["".join(rng.choice("abcdefghijklmnopqrstuvwxyz0123456789-./") for _ in range(rng.randrange(0, 70))) for _ in range(50000)]
+    strings += [bytes([rng.randrange(256) for _ in range(rng.randrange(1, 40))]) for _ in range(2000)]
+    got = ctx.hash_strings(strings)
+    want = np.array([pkg.engine.hash64(s) for s in strings], np.uint64)
+    assert np.array_equal(got, want)
+    empty = np.array([len(s) == 0 for s in strings])
+    assert (got[empty] == 0).all() and (got[~empty] != 0).all()
+
+
+def test_text_device_api_and_errors(ctx):
+    import ctypes as C
+    import torch
+    lib = N.nbg()
+    texts = _mutations(random.Random(5), 20000)
+    tab = pkg.engine.StringTable(texts)
+    d_off = torch.from_numpy(tab.off.view(np.int32)).cuda()
+    d_bytes = torch.from_numpy(tab.bytes.copy()).cuda()
+    d_sec = torch.zeros(tab.n, dtype=torch.int64, device="cuda")
+    d_nsf = torch.zeros(tab.n, dtype=torch.int32, device="cuda")
+    view = N.nbg_strings(C.cast(d_off.data_ptr(), N.u32p), C.cast(d_bytes.data_ptr(), N.u8p))
+    stream = torch.cuda.current_stream().cuda_stream
+    assert lib.nbg_parse_records_device(ctx.handle, 0, C.byref(view), None, tab.n, d_sec.data_ptr(), d_nsf.data_ptr(), None, stream) == 0
+    d_h = torch.zeros(tab.n, dtype=torch.int64, device="cuda")
+    assert lib.nbg_hash_strings_device(ctx.handle, 0, C.byref(view), tab.n, d_h.data_ptr(), stream) == 0
+    torch.cuda.synchronize()
+    want = _expect(texts)
+    assert np.array_equal(d_sec.cpu().numpy(), want[0]) and np.array_equal(d_nsf.cpu().numpy().view(np.uint32), want[1])
+    assert np.array_equal(d_h.cpu().numpy().view(np.uint64), np.array([pkg.engine.hash64(s) for s in texts], np.uint64))
+    bad = N.nbg_strings(C.cast(d_off.data_ptr(), N.u32p), C.cast(d_bytes.data_ptr() + 1, N.u8p))   # misaligned bytes
+    assert lib.nbg_hash_strings_device(ctx.handle, 0, C.byref(bad), tab.n, d_h.data_ptr(), stream) == N.NBG_E_INVAL
+    off = tab.off.copy(); off[5] = off[6] + 3
+    v2 = N.nbg_strings(off.ctypes.data_as(N.u32p), tab.bytes.ctypes.data_as(N.u8p))
+    out = np.zeros(tab.n, np.uint64)
+    assert lib.nbg_hash_strings(ctx.handle, C.byref(v2), tab.n, out.ctypes.data_as(C.c_void_p)) == N.NBG_E_RANGE
