@@ -478,6 +478,25 @@ def other_configs(pkg, dev, ctx, torch, peak):
                                "algorithmic_GBps": stream_bytes / (med * 1e-3) / 1e9,
                                "table_bytes": int(need), "note": "hash table (scratch) is L2-resident; random access, not a streaming roofline",
                                "cpu_packed_1thread_notebooks_per_s": n / cpu_s, "parity": "bit-exact vs packed oracle"}
+    # ODH comparator family and the webhook restart-block predicate, ~1 M pairs (tiled 64x on device)
+    fo = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 11, 16384, 400)
+    objs = fo.objects(0, 16384)
+    gb = host.GenBatch(N.GEN_DEEPEQUAL, "metadata.labels", "spec.template.spec")
+    rb = host.RestartBatch()
+    for o in objs:
+        gb.add(o["sts_from"], o["sts_to"])
+        mutated = o["notebook"].clone()
+        host.odh_mutate(mutated, 2 | 4 | 8 | 16)
+        rb.add(o["notebook"], o["notebook"], mutated)
+    for name, hb, want in (("odh_comparators_1M", gb, O.packed_diff_generic(gb)[0]), ("restart_block_1M", rb, O.packed_restart_block(rb)[0])):
+        db = dev.DeviceBatch.from_host(hb, tile=64)
+        ms = timed(db)
+        got = db.outs[0].cpu().numpy().reshape(64, -1)
+        assert (got == want[None, :]).all(), name + " differs from the oracle"
+        out[name] = {"pairs_per_s": db.n / (ms * 1e-3), "ms": ms, "pairs": db.n, "GBps": db.algorithmic_bytes / (ms * 1e-3) / 1e9,
+                     "frac_of_peak": db.algorithmic_bytes / (ms * 1e-3) / 1e9 / peak, "bytes_per_pair": round(db.algorithmic_bytes / db.n, 1),
+                     "parity": "bit-exact vs packed oracle (16384 distinct pairs tiled 64x)"}
+        del db
     # RFC3339 parse + "idle" compare of kernel records on the device
     import json as _json
     cf2 = host.CullFleet(host.SEED_BASE + 3, 250_000)

@@ -260,6 +260,47 @@ int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n,
 /* never 0 */
 uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
 
+/* ---- the ODH comparator family ------------------------------ */
+/* Pairs (a = desired, b = found) of arbitrary objects reduced to two key/value
+ * vectors each: "labels" and "spec".
+ *  NBG_GEN_DEEPEQUAL  each vector is a FLATTENED value tree (nbh_flatten: one entry per
+ *      leaf / container marker, key = hash of the path, sorted by key), so vectors are equal
+ *      <=> reflect.DeepEqual of the trees.  This is CompareNotebookHTTPRoutes
+ *      (odh notebook_route.go:134-138), CompareNotebookNetworkPolicies (notebook_network.go:
+ *      125-129), CompareNotebookReferenceGrants (notebook_referencegrant.go:72-76) — labels
+ *      and spec — and the RoleBinding subjects test (notebook_rbac.go:131).
+ *  NBG_GEN_CONFIGMAP  the vectors are plain string maps (hash(key), hash(value)); the test is
+ *      the loop of notebook_kube_rbac_auth.go:240-266: lengths differ, or some desired
+ *      (k, v) has found[k] != v with a missing key reading as "" — on `spec` (= Data) and on
+ *      `labels`.
+ * reason bit0 = labels differ, bit1 = spec/data differ; bitmap bit = reason != 0 (the
+ * reference's Compare* functions return the negation: true when equal). */
+typedef struct nbg_generic_batch { nbg_kvmap labels_a, labels_b, spec_a, spec_b; } nbg_generic_batch;
+#define NBG_GEN_DEEPEQUAL 0
+#define NBG_GEN_CONFIGMAP 1
+#define NBG_GEN_LABELS 0x01u
+#define NBG_GEN_SPEC   0x02u
+int nbg_diff_generic(nbg_ctx* ctx, const nbg_generic_batch* in, uint64_t n, int mode,
+                     uint8_t* reason, uint64_t* bitmap);
+
+/* The webhook's restart-block predicate, maybeRestartRunningNotebook (odh notebook_webhook.go:
+ * 505-564), for a fleet.  Per Notebook three PodSpecs as sparse SEMANTIC tiles (the packer's
+ * semantic flavour: nil == empty slices/maps, Quantity by value — equal tiles <=>
+ * equality.Semantic.DeepEqual): the stored one, the one the user sent, and that one after
+ * the webhook's injections. */
+typedef struct nbg_restart_batch {
+  const uint8_t* flags;                      /* n; NBG_RB_CREATE / _STOPPED / _RESTARTING */
+  nbg_podsparse old_spec, updated_spec, mutated_spec;
+} nbg_restart_batch;
+#define NBG_RB_CREATE      0x01u /* req.Operation == Create (:515)                              */
+#define NBG_RB_STOPPED     0x02u /* mutated notebook carries kubeflow-resource-stopped (:521)   */
+#define NBG_RB_RESTARTING  0x04u /* ... carries notebooks.opendatahub.io/notebook-restart (:527) */
+/* decision byte */
+#define NBG_RB_BLOCKED         0x01u /* keep the updated PodSpec, report UpdatesPending (:559-563) */
+#define NBG_RB_EXTERNAL_CHANGE 0x02u /* the user's update already changes the pod template (:548)  */
+#define NBG_RB_NO_CHANGE       0x04u /* old == updated == mutated (:554)                           */
+int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uint8_t* decision, uint64_t* blocked_bitmap);
+
 /* ---- strings on the device (the host work right in front of the predicates) ---- */
 /* A table of R strings as CSR: string r is bytes[off[r] .. off[r+1]).  `bytes` must be
  * 16-byte aligned and its allocation padded to a multiple of 16 bytes (the kernels copy
@@ -300,6 +341,10 @@ size_t nbg_owner_join_scratch_bytes(uint64_t m);
 int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint64_t n,
                           const uint64_t* sts_key, uint64_t m, uint32_t* match,
                           void* scratch, size_t scratch_bytes, void* stream);
+int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* in, uint64_t n, int mode,
+                            uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_restart_block_device(nbg_ctx* ctx, int device, const nbg_restart_batch* in, uint64_t n, uint8_t* decision,
+                             uint64_t* blocked_bitmap, void* stream);
 int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* last_activity, const nbg_strings* state,
                              uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone, void* stream);
 int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings, uint64_t R, uint64_t* out,

@@ -31,6 +31,8 @@ typedef struct nbh_sts nbh_sts;     /* packed StatefulSet pairs  -> nbg_sts_batc
 typedef struct nbh_svc nbh_svc;     /* packed Service pairs      -> nbg_svc_batch    */
 typedef struct nbh_vs nbh_vs;       /* packed VirtualService pairs -> nbg_vs_batch   */
 typedef struct nbh_cull nbh_cull;   /* packed culler inputs      -> nbg_cull_batch   */
+typedef struct nbh_gen nbh_gen;     /* ODH comparator pairs      -> nbg_generic_batch */
+typedef struct nbh_rb nbh_rb;       /* webhook restart-block     -> nbg_restart_batch */
 typedef struct nbh_fleet nbh_fleet; /* seeded synthetic Notebook fleet (diff side)   */
 typedef struct nbh_cullfleet nbh_cullfleet; /* seeded synthetic culler fleet         */
 
@@ -88,6 +90,21 @@ nbh_vs* nbh_vs_new(void);
 void nbh_vs_free(nbh_vs* b);
 int nbh_vs_add(nbh_vs* b, const nbh_obj* from, const nbh_obj* to);
 uint64_t nbh_vs_view(const nbh_vs* b, nbg_vs_batch* out);
+
+/* ODH comparator pairs (desired a, found b): the sub-objects at labels_path / spec_path of both,
+ * flattened (mode NBG_GEN_DEEPEQUAL) or as plain string maps (mode NBG_GEN_CONFIGMAP). */
+nbh_gen* nbh_gen_new(void);
+void nbh_gen_free(nbh_gen* b);
+int nbh_gen_add(nbh_gen* b, const nbh_obj* a, const nbh_obj* found, const char* labels_path, const char* spec_path, int mode);
+uint64_t nbh_gen_view(const nbh_gen* b, nbg_generic_batch* out);
+
+/* Webhook restart-block inputs (ODHWH:505-564): the stored Notebook, the one the user sent and the
+ * one after the webhook's mutations (spec.template.spec of each, as semantic sparse tiles). */
+nbh_rb* nbh_rb_new(void);
+void nbh_rb_free(nbh_rb* b);
+int nbh_rb_add(nbh_rb* b, const nbh_obj* old_nb, const nbh_obj* updated_nb, const nbh_obj* mutated_nb, int create);
+uint64_t nbh_rb_view(const nbh_rb* b, nbg_restart_batch* out);
+nbh_obj* nbh_obj_clone(const nbh_obj* o);
 
 /* One notebook as the culler sees it, as JSON:
  *   {"annotations": {..}|null, "pod_missing": bool,

@@ -69,6 +69,21 @@ class nbg_vs_batch(C.Structure):
                 ("hdr_from", nbg_kvmap), ("hdr_to", nbg_kvmap)]
 
 
+class nbg_restart_batch(C.Structure):
+    _fields_ = [("flags", u8p), ("old_spec", nbg_podsparse), ("updated_spec", nbg_podsparse), ("mutated_spec", nbg_podsparse)]
+
+
+RB_CREATE, RB_STOPPED, RB_RESTARTING = 1, 2, 4
+RB_BLOCKED, RB_EXTERNAL_CHANGE, RB_NO_CHANGE = 1, 2, 4
+
+
+class nbg_generic_batch(C.Structure):
+    _fields_ = [("labels_a", nbg_kvmap), ("labels_b", nbg_kvmap), ("spec_a", nbg_kvmap), ("spec_b", nbg_kvmap)]
+
+
+GEN_DEEPEQUAL, GEN_CONFIGMAP = 0, 1
+
+
 class nbg_strings(C.Structure):
     _fields_ = [("off", u32p), ("bytes", u8p)]
 
@@ -111,6 +126,7 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
+    "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
     "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
 
@@ -158,6 +174,14 @@ def _bind_nbg(lib):
     lib.nbg_owner_join_device.restype = C.c_int
     lib.nbg_owner_join_static.argtypes = [_vp, C.c_uint64, _vp, C.c_uint64, _vp, _vp]
     lib.nbg_owner_join_static.restype = C.c_int
+    lib.nbg_diff_generic.argtypes = [_vp, C.POINTER(nbg_generic_batch), C.c_uint64, C.c_int, _vp, _vp]
+    lib.nbg_diff_generic.restype = C.c_int
+    lib.nbg_diff_generic_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_generic_batch), C.c_uint64, C.c_int, _vp, _vp, _vp]
+    lib.nbg_diff_generic_device.restype = C.c_int
+    lib.nbg_restart_block.argtypes = [_vp, C.POINTER(nbg_restart_batch), C.c_uint64, _vp, _vp]
+    lib.nbg_restart_block.restype = C.c_int
+    lib.nbg_restart_block_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_restart_batch), C.c_uint64, _vp, _vp, _vp]
+    lib.nbg_restart_block_device.restype = C.c_int
     PS = C.POINTER(nbg_strings)
     lib.nbg_parse_records.argtypes = [_vp, PS, PS, C.c_uint64, _vp, _vp, _vp]
     lib.nbg_parse_records.restype = C.c_int
@@ -199,6 +223,11 @@ def _bind_nbh(lib):
         "nbh_svc_add": ([_vp, _vp, _vp], C.c_int), "nbh_svc_view": ([_vp, P(nbg_svc_batch)], C.c_uint64),
         "nbh_vs_new": ([], _vp), "nbh_vs_free": ([_vp], None),
         "nbh_vs_add": ([_vp, _vp, _vp], C.c_int), "nbh_vs_view": ([_vp, P(nbg_vs_batch)], C.c_uint64),
+        "nbh_gen_new": ([], _vp), "nbh_gen_free": ([_vp], None),
+        "nbh_gen_add": ([_vp, _vp, _vp, cp, cp, C.c_int], C.c_int), "nbh_gen_view": ([_vp, P(nbg_generic_batch)], C.c_uint64),
+        "nbh_rb_new": ([], _vp), "nbh_rb_free": ([_vp], None),
+        "nbh_rb_add": ([_vp, _vp, _vp, _vp, C.c_int], C.c_int), "nbh_rb_view": ([_vp, P(nbg_restart_batch)], C.c_uint64),
+        "nbh_obj_clone": ([_vp], _vp),
         "nbh_cull_new": ([], _vp), "nbh_cull_free": ([_vp], None),
         "nbh_cull_add_json": ([_vp, cp, cp, sz], C.c_int), "nbh_cull_view": ([_vp, P(nbg_cull_batch)], C.c_uint64),
         "nbh_cull_records": ([_vp, P(C.c_uint64), P(C.c_uint64)], C.c_uint64),
@@ -232,7 +261,7 @@ NBH_SYMBOLS = [
     "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_erase", "nbh_obj_set_str", "nbh_obj_digest",
     "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate",
     "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_sts_view_sparse", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
-    "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_cull_new", "nbh_cull_free",
+    "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
     "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",

@@ -31,6 +31,10 @@ cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const 
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
                                uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_generic(const nbg_generic_batch*, unsigned long long, int, const unsigned*, uint8_t*,
+                                    uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_restart_block(const nbg_restart_batch*, unsigned long long, const unsigned*, uint8_t*, uint64_t*,
+                                     cudaStream_t);
 cudaError_t nbg_launch_parse_records(const uint32_t*, const unsigned char*, const uint32_t*, const unsigned char*,
                                      unsigned long long, unsigned, unsigned, int64_t*, uint32_t*, int32_t*, cudaStream_t);
 cudaError_t nbg_launch_hash_strings(const uint32_t*, const unsigned char*, unsigned long long, unsigned, uint64_t*,
@@ -409,6 +413,32 @@ int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint
   return NBG_OK;
 }
 
+int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* in, uint64_t n, int mode,
+                            uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in || (mode != NBG_GEN_DEEPEQUAL && mode != NBG_GEN_CONFIGMAP)) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[4] = {0, 0, 0, 0};
+  CU(nbg_launch_diff_generic(in, n, mode, bases, reason, bitmap, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_restart_block_device(nbg_ctx* ctx, int device, const nbg_restart_batch* in, uint64_t n, uint8_t* decision,
+                             uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!decision || !bitmap || !in->flags) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[3] = {0, 0, 0};
+  CU(nbg_launch_restart_block(in, n, bases, decision, bitmap, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
 int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* la, const nbg_strings* state, uint64_t R,
                              int64_t* sec, uint32_t* nsf, int32_t* zone, void* stream) {
   if (int rc = check_dev(ctx, device)) return rc;
@@ -434,6 +464,88 @@ int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings
 }
 
 // ------------------------------------------------------------ host-buffer API
+int nbg_diff_generic(nbg_ctx* ctx, const nbg_generic_batch* in, uint64_t n, int mode, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in || (mode != NBG_GEN_DEEPEQUAL && mode != NBG_GEN_CONFIGMAP)) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  if (!csr_ptrs_ok(in->labels_a, n) || !csr_ptrs_ok(in->labels_b, n) || !csr_ptrs_ok(in->spec_a, n) ||
+      !csr_ptrs_ok(in->spec_b, n))
+    return NBG_E_INVAL;
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kSvcChunk, ++c) {
+      const uint64_t i1 = i0 + kSvcChunk < hi ? i0 + kSvcChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_a, i0, i1) || !csr_ok(in->labels_b, i0, i1) || !csr_ok(in->spec_a, i0, i1) ||
+          !csr_ok(in->spec_b, i0, i1))
+        return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const CsrDev la = csr_in(lay, in->labels_a, i0, i1), lb = csr_in(lay, in->labels_b, i0, i1);
+      const CsrDev sa = csr_in(lay, in->spec_a, i0, i1), sb = csr_in(lay, in->spec_b, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_generic_batch b;
+      b.labels_a = csr_ptr(sl, la); b.labels_b = csr_ptr(sl, lb);
+      b.spec_a = csr_ptr(sl, sa); b.spec_b = csr_ptr(sl, sb);
+      const unsigned bases[4] = {la.base, lb.base, sa.base, sb.base};
+      CU(nbg_launch_diff_generic(&b, m, mode, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uint8_t* decision, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!decision || !bitmap || !in->flags) return NBG_E_INVAL;
+  const nbg_podsparse* sp[3] = {&in->old_spec, &in->updated_spec, &in->mutated_spec};
+  for (const nbg_podsparse* p : sp) {
+    if (!p->mask || !p->off || (p->off[n] > p->off[0] && !p->val) || ((uintptr_t)p->val & 15u)) return NBG_E_INVAL;
+  }
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kStsSparseChunk, ++c) {
+      const uint64_t i1 = i0 + kStsSparseChunk < hi ? i0 + kStsSparseChunk : hi, m = i1 - i0;
+      for (const nbg_podsparse* p : sp) {
+        if (!off_ok(p->off, i0, i1)) return NBG_E_RANGE;
+        unsigned bad = p->off[i0] & 1u;
+        for (uint64_t i = i0; i < i1; ++i) bad |= (p->off[i + 1] & 1u) | (unsigned)(p->off[i + 1] - p->off[i] > NBG_POD_SLOTS);
+        if (bad) return NBG_E_RANGE;
+      }
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_fl = lay.in(in->flags + i0, m);
+      size_t a_m[3], a_o[3], a_v[3];
+      unsigned bases[3];
+      for (int k = 0; k < 3; ++k) {
+        bases[k] = sp[k]->off[i0];
+        const size_t nv = sp[k]->off[i1] - bases[k];
+        a_m[k] = lay.in(sp[k]->mask + i0 * 3, m * 24);
+        a_o[k] = lay.in(sp[k]->off + i0, (m + 1) * 4);
+        a_v[k] = lay.in(nv ? sp[k]->val + bases[k] : nullptr, nv * 8);
+      }
+      const size_t o_dec = lay.out(decision + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_restart_batch b;
+      b.flags = (const uint8_t*)(sl.dev + a_fl);
+      nbg_podsparse* dst[3] = {&b.old_spec, &b.updated_spec, &b.mutated_spec};
+      for (int k = 0; k < 3; ++k) {
+        dst[k]->mask = (const uint64_t*)(sl.dev + a_m[k]);
+        dst[k]->off = (const uint32_t*)(sl.dev + a_o[k]);
+        dst[k]->val = (const uint64_t*)(sl.dev + a_v[k]);
+      }
+      CU(nbg_launch_restart_block(&b, m, bases, (uint8_t*)(sl.dev + o_dec), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
 int nbg_parse_records(nbg_ctx* ctx, const nbg_strings* la, const nbg_strings* state, uint64_t R, int64_t* sec,
                       uint32_t* nsf, int32_t* zone) {
   if (!ctx || !la) return NBG_E_INVAL;

@@ -114,6 +114,55 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
 // without their values ever being read.
 constexpr unsigned kSparseGroup = 4;
 
+// bit o of the result = the sparse tiles of object base+o differ (warp-cooperative)
+__device__ __forceinline__ unsigned sparse_tiles_differ(const nbg_podsparse& a, const nbg_podsparse& b,
+                                                        unsigned long long i, bool live, unsigned cnt, unsigned lane,
+                                                        unsigned a_base, unsigned b_base) {
+  unsigned va0 = 0, vb0 = 0, my_vecs = 0;               // run starts and length, in 16-byte vectors
+  bool mask_ne = false;
+  if (live) {
+    const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
+    const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
+    mask_ne = (__ldg(ma) != __ldg(mb)) | (__ldg(ma + 1) != __ldg(mb + 1)) | (__ldg(ma + 2) != __ldg(mb + 2));
+    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = __ldg(a.off + i + 1) - a_base;
+    va0 = f0 >> 1;
+    vb0 = (__ldg(b.off + i) - b_base) >> 1;
+    my_vecs = mask_ne ? 0u : (f1 - f0) >> 1;
+  }
+  unsigned bits = __ballot_sync(FULL, mask_ne);
+  const uint4* av = reinterpret_cast<const uint4*>(a.val);
+  const uint4* bv = reinterpret_cast<const uint4*>(b.val);
+  for (unsigned o = 0; o < cnt; o += kSparseGroup) {
+    unsigned d[kSparseGroup];
+    uint4 x[kSparseGroup], y[kSparseGroup];
+    unsigned more = 0;                                   // some run of this group is longer than 32 vectors
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g) {
+      const unsigned src = min(o + g, 31u);
+      const unsigned vecs = __shfl_sync(FULL, my_vecs, src);   // 0 past the end (my_vecs == 0 there)
+      const unsigned ao = __shfl_sync(FULL, va0, src), bo = __shfl_sync(FULL, vb0, src);
+      x[g] = make_uint4(0, 0, 0, 0); y[g] = x[g];
+      if (lane < vecs) { x[g] = ld_stream(av + ao + lane); y[g] = ld_stream(bv + bo + lane); }
+      more |= vecs > 32u;
+    }
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g) d[g] = diff4(x[g], y[g]);
+    if (more) {                                          // warp-uniform; runs of 65..192 values
+#pragma unroll
+      for (unsigned g = 0; g < kSparseGroup; ++g) {
+        const unsigned src = min(o + g, 31u);
+        const unsigned vecs = __shfl_sync(FULL, my_vecs, src);
+        const unsigned ao = __shfl_sync(FULL, va0, src), bo = __shfl_sync(FULL, vb0, src);
+        for (unsigned k = lane + 32u; k < vecs; k += 32u) d[g] |= diff4(ld_stream(av + ao + k), ld_stream(bv + bo + k));
+      }
+    }
+#pragma unroll
+    for (unsigned g = 0; g < kSparseGroup; ++g)
+      if (__any_sync(FULL, d[g] != 0)) bits |= 1u << min(o + g, 31u);
+  }
+  return bits;
+}
+
 __global__ void __launch_bounds__(128)
 diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
                        unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
@@ -126,9 +175,9 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
   const unsigned long long i = base + lane;
   const unsigned cnt = (unsigned)min(32ull, n - base);
 
-  unsigned reason = 0;
-  unsigned vf0 = 0, vt0 = 0, my_vecs = 0;               // run starts and length, in 16-byte vectors
-  bool mask_ne = false;
+  // tiles first (the streaming part), then the per-lane scalar work: keeps the two register sets apart
+  const unsigned pod_bits = sparse_tiles_differ(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
+  unsigned reason = ((pod_bits >> lane) & 1u) ? NBG_STS_PODSPEC : 0u;
   if (i < n) {
     const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
     if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
@@ -137,13 +186,6 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
       reason |= NBG_STS_REPLICAS;
       if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
     }
-    const unsigned long long* mf = reinterpret_cast<const unsigned long long*>(in.pod_from.mask) + i * 3;
-    const unsigned long long* mt = reinterpret_cast<const unsigned long long*>(in.pod_to.mask) + i * 3;
-    mask_ne = (__ldg(mf) != __ldg(mt)) | (__ldg(mf + 1) != __ldg(mt + 1)) | (__ldg(mf + 2) != __ldg(mt + 2));
-    const unsigned f0 = __ldg(in.pod_from.off + i) - vf_base, f1 = __ldg(in.pod_from.off + i + 1) - vf_base;
-    vf0 = f0 >> 1;
-    vt0 = (__ldg(in.pod_to.off + i) - vt_base) >> 1;
-    my_vecs = mask_ne ? 0u : (f1 - f0) >> 1;
     if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
                          __ldg(in.labels_from.off + i + 1) - lf_base,
                          in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
@@ -155,40 +197,37 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
                          __ldg(in.ann_to.off + i + 1) - at_base))
       reason |= NBG_STS_ANNOTATIONS;
   }
-
-  unsigned pod_bits = __ballot_sync(FULL, mask_ne);
-  const uint4* fv = reinterpret_cast<const uint4*>(in.pod_from.val);
-  const uint4* tv = reinterpret_cast<const uint4*>(in.pod_to.val);
-  for (unsigned o = 0; o < cnt; o += kSparseGroup) {
-    unsigned d[kSparseGroup];
-    uint4 x[kSparseGroup], y[kSparseGroup];
-    unsigned more = 0;                                   // some run of this group is longer than 32 vectors
-#pragma unroll
-    for (unsigned g = 0; g < kSparseGroup; ++g) {
-      const unsigned src = min(o + g, 31u);
-      const unsigned vecs = __shfl_sync(FULL, my_vecs, src);   // 0 past the end (my_vecs == 0 there)
-      const unsigned fo = __shfl_sync(FULL, vf0, src), to = __shfl_sync(FULL, vt0, src);
-      x[g] = make_uint4(0, 0, 0, 0); y[g] = x[g];
-      if (lane < vecs) { x[g] = ld_stream(fv + fo + lane); y[g] = ld_stream(tv + to + lane); }
-      more |= vecs > 32u;
-    }
-#pragma unroll
-    for (unsigned g = 0; g < kSparseGroup; ++g) d[g] = diff4(x[g], y[g]);
-    if (more) {                                          // warp-uniform; runs of 65..192 values
-#pragma unroll
-      for (unsigned g = 0; g < kSparseGroup; ++g) {
-        const unsigned src = min(o + g, 31u);
-        const unsigned vecs = __shfl_sync(FULL, my_vecs, src);
-        const unsigned fo = __shfl_sync(FULL, vf0, src), to = __shfl_sync(FULL, vt0, src);
-        for (unsigned k = lane + 32u; k < vecs; k += 32u) d[g] |= diff4(ld_stream(fv + fo + k), ld_stream(tv + to + k));
-      }
-    }
-#pragma unroll
-    for (unsigned g = 0; g < kSparseGroup; ++g)
-      if (__any_sync(FULL, d[g] != 0)) pod_bits |= 1u << min(o + g, 31u);
-  }
-  if ((pod_bits >> lane) & 1u) reason |= NBG_STS_PODSPEC;
   store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
+// ------------------------------------------------ webhook restart-block predicate
+// maybeRestartRunningNotebook (odh notebook_webhook.go:505-564) for a fleet: three PodSpecs per
+// Notebook — old, updated (what the user sent) and mutated (after the webhook's injections) —
+// as SEMANTIC tiles (pack_podspec(semantic_canon(x)): equal tiles <=> equality.Semantic.DeepEqual).
+//   create / stopped / restarting           -> let the update through           (:515-531)
+//   old != updated                          -> the user already restarts the pod (:548-551)
+//   old == updated == mutated               -> nothing changes                   (:554-557)
+//   old == updated != mutated               -> BLOCK: keep the updated spec      (:559-563)
+__global__ void __launch_bounds__(128)
+restart_block_kernel(nbg_restart_batch in, unsigned long long n, unsigned o_base, unsigned u_base, unsigned m_base,
+                     uint8_t* __restrict__ decision_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const unsigned cnt = (unsigned)min(32ull, n - base);
+  const bool live = i < n;
+  const unsigned fl = live ? __ldg(in.flags + i) : 0u;
+  const unsigned upd_bits = sparse_tiles_differ(in.old_spec, in.updated_spec, i, live, cnt, lane, o_base, u_base);
+  const unsigned mut_bits = sparse_tiles_differ(in.old_spec, in.mutated_spec, i, live, cnt, lane, o_base, m_base);
+  unsigned decision = 0;
+  if (live && !(fl & (NBG_RB_CREATE | NBG_RB_STOPPED | NBG_RB_RESTARTING))) {
+    if ((upd_bits >> lane) & 1u) decision = NBG_RB_EXTERNAL_CHANGE;
+    else if (!((mut_bits >> lane) & 1u)) decision = NBG_RB_NO_CHANGE;
+    else decision = NBG_RB_BLOCKED;
+  }
+  store_results(base, n, lane, decision, (decision & NBG_RB_BLOCKED) != 0, decision_out, bitmap_half);
 }
 
 // ------------------------------------------------- small fixed tiles (Svc, VS)
@@ -289,7 +328,47 @@ diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned
   store_results(base, n, lane, reason, update, reason_out, bitmap_half);
 }
 
+// ------------------------------------------------ ODH comparator family
+// One object pair per lane; both tests are short loops over small CSR vectors.
+__global__ void __launch_bounds__(128)
+diff_generic_kernel(nbg_generic_batch in, unsigned long long n, int mode,
+                    unsigned la_base, unsigned lb_base, unsigned sa_base, unsigned sb_base,
+                    uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  unsigned reason = 0;
+  if (i < n) {
+    const unsigned la0 = __ldg(in.labels_a.off + i) - la_base, la1 = __ldg(in.labels_a.off + i + 1) - la_base;
+    const unsigned lb0 = __ldg(in.labels_b.off + i) - lb_base, lb1 = __ldg(in.labels_b.off + i + 1) - lb_base;
+    const unsigned sa0 = __ldg(in.spec_a.off + i) - sa_base, sa1 = __ldg(in.spec_a.off + i + 1) - sa_base;
+    const unsigned sb0 = __ldg(in.spec_b.off + i) - sb_base, sb1 = __ldg(in.spec_b.off + i + 1) - sb_base;
+    if (mode == NBG_GEN_DEEPEQUAL) {
+      // flattened trees: nil-ness, lengths and kinds are entries of the vectors themselves
+      if (map_not_deep_equal(in.labels_a.ent, la0, la1, false, in.labels_b.ent, lb0, lb1, false)) reason |= NBG_GEN_LABELS;
+      if (map_not_deep_equal(in.spec_a.ent, sa0, sa1, false, in.spec_b.ent, sb0, sb1, false)) reason |= NBG_GEN_SPEC;
+    } else {
+      // len(found) != len(desired), or a desired entry whose found value differs ("" when missing)
+      if ((la1 - la0) != (lb1 - lb0) || live_map_differs(in.labels_b.ent, lb0, lb1, in.labels_a.ent, la0, la1)) reason |= NBG_GEN_LABELS;
+      if ((sa1 - sa0) != (sb1 - sb0) || live_map_differs(in.spec_b.ent, sb0, sb1, in.spec_a.ent, sa0, sa1)) reason |= NBG_GEN_SPEC;
+    }
+  }
+  store_results(base, n, lane, reason, reason != 0, reason_out, bitmap_half);
+}
+
 }  // namespace nbg
+
+extern "C" cudaError_t nbg_launch_diff_generic(const nbg_generic_batch* in, unsigned long long n, int mode,
+                                               const unsigned* bases /*4*/, uint8_t* reason, uint64_t* bitmap,
+                                               cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  nbg::diff_generic_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+      *in, n, mode, bases[0], bases[1], bases[2], bases[3], reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
 
 // *_base: first CSR offset of the slice when the entry pointers already point
 // at the slice's first entry (host-buffer chunking); 0 for whole arrays.
@@ -313,6 +392,15 @@ extern "C" cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch* in
   nbg::diff_sts_sparse_kernel<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
       reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_restart_block(const nbg_restart_batch* in, unsigned long long n, const unsigned* bases /*3*/,
+                                                uint8_t* decision, uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  nbg::restart_block_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+      *in, n, bases[0], bases[1], bases[2], decision, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
 

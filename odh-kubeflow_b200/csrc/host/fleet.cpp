@@ -39,6 +39,37 @@ void extend(std::vector<T>& a, const std::vector<T>& b) { a.insert(a.end(), b.be
 }  // namespace
 
 // ------------------------------------------------------------------ batches
+void sparsify_tile(const uint64_t* tile, std::vector<uint64_t>& mask, std::vector<uint64_t>& val, std::vector<uint32_t>& off) {
+  uint64_t m[3] = {0, 0, 0};
+  for (unsigned s = 0; s < NBG_POD_SLOTS; ++s)
+    if (tile[s]) { m[s >> 6] |= 1ull << (s & 63); val.push_back(tile[s]); }
+  if (val.size() & 1) val.push_back(0);   // runs are padded to an even count: 16-byte aligned starts
+  mask.insert(mask.end(), m, m + 3);
+  off.push_back((uint32_t)val.size());
+}
+
+void RestartBatch::add(const GVal& old_nb, const GVal& updated_nb, const GVal& mutated_nb, bool create) {
+  const GVal* nbs[3] = {&old_nb, &updated_nb, &mutated_nb};
+  for (int k = 0; k < 3; ++k) {
+    uint64_t tile[NBG_POD_SLOTS];
+    pack_podspec(semantic_canon(path(*nbs[k], {"spec", "template", "spec"})), tile);
+    sparsify_tile(tile, mask[k], val[k], off[k]);
+  }
+  const GVal& ann = path(mutated_nb, {"metadata", "annotations"});   // metav1.HasAnnotation(mutatedNotebook...), ODHWH:521,527
+  uint8_t f = create ? NBG_RB_CREATE : 0;
+  if (ann.kind == GVal::Map && ann.has("kubeflow-resource-stopped")) f |= NBG_RB_STOPPED;
+  if (ann.kind == GVal::Map && ann.has("notebooks.opendatahub.io/notebook-restart")) f |= NBG_RB_RESTARTING;
+  flags.push_back(f);
+  ++n;
+}
+nbg_restart_batch RestartBatch::view() const {
+  nbg_restart_batch b;
+  b.flags = flags.data();
+  nbg_podsparse* dst[3] = {&b.old_spec, &b.updated_spec, &b.mutated_spec};
+  for (int k = 0; k < 3; ++k) { dst[k]->mask = mask[k].data(); dst[k]->off = off[k].data(); dst[k]->val = val[k].data(); }
+  return b;
+}
+
 void StsBatch::add(const GVal& from, const GVal& to) {
   auto replicas = [](const GVal& o) -> int32_t {
     const GVal& r = path(o, {"spec", "replicas"});
@@ -56,16 +87,8 @@ void StsBatch::add(const GVal& from, const GVal& to) {
   labels_to.add(path(to, {"metadata", "labels"}));
   ann_from.add(path(from, {"metadata", "annotations"}));
   ann_to.add(path(to, {"metadata", "annotations"}));
-  auto sparsify = [](const uint64_t* tile, std::vector<uint64_t>& mask, std::vector<uint64_t>& val, std::vector<uint32_t>& off) {
-    uint64_t m[3] = {0, 0, 0};
-    for (unsigned s = 0; s < NBG_POD_SLOTS; ++s)
-      if (tile[s]) { m[s >> 6] |= 1ull << (s & 63); val.push_back(tile[s]); }
-    if (val.size() & 1) val.push_back(0);   // runs are padded to an even count: 16-byte aligned starts
-    mask.insert(mask.end(), m, m + 3);
-    off.push_back((uint32_t)val.size());
-  };
-  sparsify(&pod_from[n * NBG_POD_SLOTS], mask_from, val_from, voff_from);
-  sparsify(&pod_to[n * NBG_POD_SLOTS], mask_to, val_to, voff_to);
+  sparsify_tile(&pod_from[n * NBG_POD_SLOTS], mask_from, val_from, voff_from);
+  sparsify_tile(&pod_to[n * NBG_POD_SLOTS], mask_to, val_to, voff_to);
   ++n;
 }
 void StsBatch::append(const StsBatch& o) {
@@ -154,6 +177,21 @@ nbg_vs_batch VsBatch::view() const {
   nbg_vs_batch b;
   b.flags = flags.data(); b.spec_from = spec_from.data(); b.spec_to = spec_to.data();
   b.hdr_from = hdr_from.view(); b.hdr_to = hdr_to.view();
+  return b;
+}
+
+void GenBatch::add(const GVal& la, const GVal& lb, const GVal& sa, const GVal& sb, bool flatten) {
+  auto put = [&](KvCsr& c, const GVal& v) {
+    if (flatten) flatten_tree(v, &c.ent); else pack_kvmap(v, &c.ent);
+    c.off.push_back((uint32_t)c.ent.size());
+  };
+  put(labels_a, la); put(labels_b, lb); put(spec_a, sa); put(spec_b, sb);
+  ++n;
+}
+nbg_generic_batch GenBatch::view() const {
+  nbg_generic_batch b;
+  b.labels_a = labels_a.view(); b.labels_b = labels_b.view();
+  b.spec_a = spec_a.view(); b.spec_b = spec_b.view();
   return b;
 }
 

@@ -72,6 +72,29 @@ struct VsBatch {
   nbg_vs_batch view() const;
 };
 
+// Pairs for the ODH comparator family (nbg_generic_batch).
+struct GenBatch {
+  KvCsr labels_a, labels_b, spec_a, spec_b;
+  uint64_t n = 0;
+  // flattened trees (NBG_GEN_DEEPEQUAL) or plain string maps (NBG_GEN_CONFIGMAP)
+  void add(const GVal& la, const GVal& lb, const GVal& sa, const GVal& sb, bool flatten);
+  nbg_generic_batch view() const;
+};
+
+// Append one dense 192-slot tile in sparse form (mask + even-padded run of non-zero slots).
+void sparsify_tile(const uint64_t* tile, std::vector<uint64_t>& mask, std::vector<uint64_t>& val, std::vector<uint32_t>& off);
+
+// Webhook restart-block inputs (nbg_restart_batch): old / updated / mutated Notebook PodSpecs as
+// semantic sparse tiles.
+struct RestartBatch {
+  std::vector<uint8_t> flags;
+  std::vector<uint64_t> mask[3], val[3];
+  std::vector<uint32_t> off[3] = {{0}, {0}, {0}};
+  uint64_t n = 0;
+  void add(const GVal& old_nb, const GVal& updated_nb, const GVal& mutated_nb, bool create);
+  nbg_restart_batch view() const;
+};
+
 // One notebook as the culler sees it: annotations + what the two Jupyter
 // endpoints returned (CULL:243-313), all still strings.
 struct CullInput {

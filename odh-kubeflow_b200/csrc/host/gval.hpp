@@ -26,9 +26,12 @@
 
 namespace nbh {
 
+constexpr uint8_t kTagQuantity = 1;
+
 struct GVal {
   enum Kind : uint8_t { Null, Bool, Int, Float, Str, List, Map, Struct, Ptr };
   Kind kind = Null;
+  uint8_t tag = 0; // kTagQuantity marks a resource.Quantity struct (semantic equality compares it by value)
   int64_t i = 0;   // Bool, Int
   double f = 0.0;  // Float
   std::string s;   // Str

@@ -21,6 +21,8 @@ struct nbh_sts { StsBatch b; };
 struct nbh_svc { SvcBatch b; };
 struct nbh_vs { VsBatch b; };
 struct nbh_cull { CullBatch b; };
+struct nbh_gen { GenBatch b; };
+struct nbh_rb { RestartBatch b; };
 struct nbh_fleet { Fleet f; };
 struct nbh_cullfleet { CullFleet f; };
 
@@ -285,6 +287,56 @@ NBH_API uint64_t nbh_vs_view(const nbh_vs* b, nbg_vs_batch* out) {
   if (!b || !out) return 0;
   *out = b->b.view();
   return b->b.n;
+}
+
+// ODH comparator pairs: `labels_path` / `spec_path` are dotted paths inside the two objects
+// ("metadata.labels", "spec", "data", "subjects"); a missing path is the nil / zero value.
+NBH_API nbh_gen* nbh_gen_new(void) { return new nbh_gen(); }
+NBH_API void nbh_gen_free(nbh_gen* b) { delete b; }
+NBH_API int nbh_gen_add(nbh_gen* b, const nbh_obj* a, const nbh_obj* o, const char* labels_path, const char* spec_path,
+                        int mode) {
+  if (!b || !a || !o || !labels_path || !spec_path) return -1;
+  auto at = [](const GVal& root, const std::string& path) -> GVal {
+    const GVal* cur = &root;
+    size_t pos = 0;
+    while (!path.empty()) {
+      const size_t dot = path.find('.', pos);
+      const std::string key = path.substr(pos, dot == std::string::npos ? std::string::npos : dot - pos);
+      while (cur->kind == GVal::Ptr && !cur->items.empty()) cur = &cur->items[0];
+      if (cur->kind != GVal::Struct && cur->kind != GVal::Map) return GVal();
+      cur = cur->find(key);
+      if (!cur) return GVal();
+      if (dot == std::string::npos) break;
+      pos = dot + 1;
+    }
+    return *cur;
+  };
+  b->b.add(at(a->v, labels_path), at(o->v, labels_path), at(a->v, spec_path), at(o->v, spec_path), mode == NBG_GEN_DEEPEQUAL);
+  return 0;
+}
+NBH_API uint64_t nbh_gen_view(const nbh_gen* b, nbg_generic_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+
+NBH_API nbh_rb* nbh_rb_new(void) { return new nbh_rb(); }
+NBH_API void nbh_rb_free(nbh_rb* b) { delete b; }
+NBH_API int nbh_rb_add(nbh_rb* b, const nbh_obj* old_nb, const nbh_obj* updated_nb, const nbh_obj* mutated_nb, int create) {
+  if (!b || !old_nb || !updated_nb || !mutated_nb) return -1;
+  b->b.add(old_nb->v, updated_nb->v, mutated_nb->v, create != 0);
+  return 0;
+}
+NBH_API uint64_t nbh_rb_view(const nbh_rb* b, nbg_restart_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view();
+  return b->b.n;
+}
+NBH_API nbh_obj* nbh_obj_clone(const nbh_obj* o) {
+  if (!o) return nullptr;
+  nbh_obj* r = new nbh_obj();
+  r->v = o->v;
+  return r;
 }
 
 NBH_API nbh_cull* nbh_cull_new(void) { return new nbh_cull(); }

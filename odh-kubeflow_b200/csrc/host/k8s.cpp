@@ -4,7 +4,10 @@
 // and the Notebook CRD (reference: components/notebook-controller/api/v1beta1/
 // notebook_types.go:26-33, NotebookSpec.Template.Spec = corev1.PodSpec).  The
 // k8s.io/api module is a go.mod dependency (NBC/go.mod:13) and is not under the
-// reference tree; names and kinds are the published API.
+// reference tree; names and kinds are the published API.  HTTPRoute / ReferenceGrant
+// are sigs.k8s.io/gateway-api v1.2.1 (ODH/go.mod:24; inlined CommonRouteSpec, BackendRef
+// and BackendObjectReference are flattened), NetworkPolicy is networking/v1, RoleBinding
+// rbac/v1 — the objects the ODH comparators look at.
 //
 // Type syntax of the table: s string, i integer, b bool, f float, q Quantity,
 // ios IntOrString, any untyped JSON, [T slice, *T pointer, {s map[string]string,
@@ -90,6 +93,30 @@ StatefulSet: apiVersion:s kind:s metadata:ObjectMeta spec:StatefulSetSpec status
 ServicePort: name:s protocol:s appProtocol:*s port:i targetPort:ios nodePort:i
 ServiceSpec: ports:[ServicePort selector:{s clusterIP:s clusterIPs:[s type:s externalIPs:[s sessionAffinity:s loadBalancerIP:s loadBalancerSourceRanges:[s externalName:s externalTrafficPolicy:s healthCheckNodePort:i publishNotReadyAddresses:b sessionAffinityConfig:any ipFamilies:[s ipFamilyPolicy:*s allocateLoadBalancerNodePorts:*b loadBalancerClass:*s internalTrafficPolicy:*s trafficDistribution:*s
 Service: apiVersion:s kind:s metadata:ObjectMeta spec:ServiceSpec status:any
+ParentReference: group:*s kind:*s namespace:*s name:s sectionName:*s port:*i
+HTTPPathMatch: type:*s value:*s
+HTTPHeaderMatch: type:*s name:s value:s
+HTTPQueryParamMatch: type:*s name:s value:s
+HTTPRouteMatch: path:*HTTPPathMatch headers:[HTTPHeaderMatch queryParams:[HTTPQueryParamMatch method:*s
+HTTPBackendRef: group:*s kind:*s name:s namespace:*s port:*i weight:*i filters:any
+HTTPRouteRule: name:*s matches:[HTTPRouteMatch filters:any backendRefs:[HTTPBackendRef timeouts:any retry:any sessionPersistence:any
+HTTPRouteSpec: parentRefs:[ParentReference hostnames:[s rules:[HTTPRouteRule
+HTTPRoute: apiVersion:s kind:s metadata:ObjectMeta spec:HTTPRouteSpec status:any
+NetworkPolicyPort: protocol:*s port:*ios endPort:*i
+IPBlock: cidr:s except:[s
+NetworkPolicyPeer: podSelector:*LabelSelector namespaceSelector:*LabelSelector ipBlock:*IPBlock
+NetworkPolicyIngressRule: ports:[NetworkPolicyPort from:[NetworkPolicyPeer
+NetworkPolicyEgressRule: ports:[NetworkPolicyPort to:[NetworkPolicyPeer
+NetworkPolicySpec: podSelector:LabelSelector ingress:[NetworkPolicyIngressRule egress:[NetworkPolicyEgressRule policyTypes:[s
+NetworkPolicy: apiVersion:s kind:s metadata:ObjectMeta spec:NetworkPolicySpec
+ReferenceGrantFrom: group:s kind:s namespace:s
+ReferenceGrantTo: group:s kind:s name:*s
+ReferenceGrantSpec: from:[ReferenceGrantFrom to:[ReferenceGrantTo
+ReferenceGrant: apiVersion:s kind:s metadata:ObjectMeta spec:ReferenceGrantSpec
+ConfigMap: apiVersion:s kind:s metadata:ObjectMeta immutable:*b data:{s binaryData:any
+Subject: kind:s apiGroup:s name:s namespace:s
+RoleRef: apiGroup:s kind:s name:s
+RoleBinding: apiVersion:s kind:s metadata:ObjectMeta subjects:[Subject roleRef:RoleRef
 NotebookTemplateSpec: spec:PodSpec
 NotebookSpec: template:NotebookTemplateSpec
 Notebook: apiVersion:s kind:s metadata:ObjectMeta spec:NotebookSpec status:any

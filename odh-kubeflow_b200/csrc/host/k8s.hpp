@@ -45,7 +45,14 @@ uint64_t hash_str(const std::string& s);
 uint64_t digest(const GVal& v);                 // canonical 64-bit digest of a value tree
 uint64_t digest_string_map(const GVal& m);      // nil != empty
 void pack_kvmap(const GVal& m, std::vector<nbg_kv>* out);   // sorted by key hash; Null/absent => none
+// Flatten a whole value tree into (hash(path), leaf-or-marker) entries sorted by key, such that
+// two flattened vectors are equal  <=>  reflect.DeepEqual of the trees (NBG_GEN_DEEPEQUAL).
+void flatten_tree(const GVal& v, std::vector<nbg_kv>* out);
 void pack_podspec(const GVal& podspec, uint64_t* slots /*NBG_POD_SLOTS*/);
+// The tree as apimachinery's equality.Semantic.DeepEqual sees it: nil and empty slices/maps are
+// the same, a Quantity is its number.  pack_podspec(semantic_canon(x)) tiles are equal
+// <=> equality.Semantic.DeepEqual(x, y)  (ODHWH:547-563).
+GVal semantic_canon(const GVal& v);
 void pack_service_ports(const GVal& ports, uint64_t* slots /*NBG_SVC_SLOTS*/);
 // returns false when obj.spec is missing or not a map (NestedMap not found / error)
 bool pack_vs_spec(const GVal& vs_obj, uint64_t* slots /*NBG_VS_SLOTS*/, std::vector<nbg_kv>* headers,

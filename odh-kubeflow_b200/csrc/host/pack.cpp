@@ -17,6 +17,7 @@
 
 #include "../hash.h"
 #include "k8s.hpp"
+#include "quantity.hpp"
 
 namespace nbh {
 
@@ -196,6 +197,64 @@ void pack_kvmap(const GVal& m, std::vector<nbg_kv>* out) {
     out->push_back(kv);
   }
   std::sort(out->begin() + at, out->end(), [](const nbg_kv& a, const nbg_kv& b) { return a.key < b.key; });
+}
+
+namespace {
+constexpr uint64_t K_KEY = 0x6B65796B65796B65ull, K_FIELD = 0x6669656C64ull, K_INDEX = 0x696E646578ull;
+void flatten_into(const GVal& v, uint64_t path, std::vector<nbg_kv>* out) {
+  switch (v.kind) {
+    case GVal::Struct:                              // a zero struct emits nothing: it IS the absent field
+      for (const auto& e : v.kv)
+        if (!e.second.is_zero()) flatten_into(e.second, nbg_combine(nbg_combine(path, K_FIELD), hash_str(e.first)), out);
+      return;
+    case GVal::Map:
+      out->push_back({path, nbg_combine(K_MAP, v.kv.size())});          // non-nil, this many entries
+      for (const auto& e : v.kv) flatten_into(e.second, nbg_combine(nbg_combine(path, K_KEY), hash_str(e.first)), out);
+      return;
+    case GVal::List:
+      out->push_back({path, nbg_combine(K_LIST, v.items.size())});
+      for (size_t k = 0; k < v.items.size(); ++k) {
+        const uint64_t p = nbg_combine(nbg_combine(path, K_INDEX), k);
+        // a zero struct element still occupies its position; the length marker covers it
+        flatten_into(v.items[k], p, out);
+      }
+      return;
+    case GVal::Ptr:
+      out->push_back({path, K_PTR});                                     // non-nil pointer, whatever it points to
+      if (!v.items.empty()) flatten_into(v.items[0], nbg_combine(path, K_PTR), out);
+      return;
+    default:
+      out->push_back({path, digest(v)});                                 // typed leaf (Null included)
+      return;
+  }
+}
+}  // namespace
+
+void flatten_tree(const GVal& v, std::vector<nbg_kv>* out) {
+  const size_t at = out->size();
+  // an absent root and a zero struct / zero leaf are the same Go value: neither emits anything
+  if (v.is_zero()) return;
+  flatten_into(v, 0x726F6F74726F6F74ull, out);
+  std::sort(out->begin() + at, out->end(), [](const nbg_kv& a, const nbg_kv& b) { return a.key < b.key; });
+}
+
+GVal semantic_canon(const GVal& v) {
+  if (v.tag == kTagQuantity) {
+    std::string digits;
+    int64_t exp;
+    quantity_number(v, &digits, &exp);
+    GVal q = GVal::strct();
+    q.set("num", GVal::str(digits));
+    q.kv.emplace_back("exp", GVal::integer(exp));      // kept even when 0: "num" alone identifies zero anyway
+    std::sort(q.kv.begin(), q.kv.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    return q;
+  }
+  GVal o = v;
+  for (auto& c : o.items) c = semantic_canon(c);
+  for (auto& e : o.kv) e.second = semantic_canon(e.second);
+  if ((o.kind == GVal::List && o.items.empty()) || (o.kind == GVal::Map && o.kv.empty())) return GVal();   // == nil
+  if (o.kind == GVal::Struct) o.canon();
+  return o;
 }
 
 void pack_podspec(const GVal& pod, uint64_t* s) {

@@ -27,6 +27,7 @@ inline GVal make_quantity(int64_t value, int32_t scale, const std::string& forma
                           const std::string& s, const std::string& dec_unscaled = std::string(),
                           int32_t dec_scale = 0) {
   GVal q = GVal::strct();
+  q.tag = kTagQuantity;
   GVal i = GVal::strct();
   i.set("value", GVal::integer(value));
   i.set("scale", GVal::integer(scale));
@@ -124,6 +125,34 @@ inline std::string u128_str(u128 v) {
 }
 
 }  // namespace qdetail
+
+// The number a Quantity holds, normalised so that numerically equal quantities give the same
+// (digits, exponent): value = digits x 10^exponent, digits without trailing zeros, "0" for zero.
+// This is what equality.Semantic compares (Quantity.Cmp == 0).
+inline void quantity_number(const GVal& q, std::string* digits, int64_t* exponent) {
+  std::string d;
+  int64_t e = 0;
+  const GVal* dd = q.find("d");
+  const GVal* dec = dd ? dd->find("Dec") : nullptr;
+  if (dec && dec->kind == GVal::Ptr && !dec->items.empty()) {
+    d = dec->items[0].get_str("unscaled");
+    const GVal* sc = dec->items[0].find("scale");
+    e = -(sc ? sc->i : 0);
+  } else {
+    const GVal* i = q.find("i");
+    const GVal* v = i ? i->find("value") : nullptr;
+    const GVal* sc = i ? i->find("scale") : nullptr;
+    d = std::to_string(v ? v->i : 0);
+    e = sc ? sc->i : 0;
+  }
+  bool neg = !d.empty() && d[0] == '-';
+  if (neg) d.erase(0, 1);
+  while (d.size() > 1 && d[0] == '0') d.erase(0, 1);
+  while (d.size() > 1 && d.back() == '0') { d.pop_back(); ++e; }
+  if (d.empty() || d == "0") { d = "0"; e = 0; neg = false; }
+  *digits = (neg ? "-" : "") + d;
+  *exponent = e;
+}
 
 // ParseQuantity(str) -> GVal.  Returns false where the Go function returns an error.
 inline bool parse_quantity(const std::string& str, GVal* out) {

@@ -28,6 +28,7 @@ class DeviceBatch:
     def from_host(cls, batch, device=0, tile=1):
         self = cls()
         self.device, self.kind = device, type(batch).__name__
+        self.mode = getattr(batch, "mode", 0)
         arrays = batch.arrays()
         n0 = len(batch)
         self.n = n0 * tile
@@ -89,6 +90,18 @@ class DeviceBatch:
                 setattr(s, side, ps)
             for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
                 setattr(s, f, self._kv(f))
+        elif k == "GenBatch":
+            s = N.nbg_generic_batch()
+            for f in ("labels_a", "labels_b", "spec_a", "spec_b"):
+                setattr(s, f, self._kv(f))
+        elif k == "RestartBatch":
+            s = N.nbg_restart_batch()
+            s.flags = self._p("flags", C.c_uint8)
+            for side in ("old_spec", "updated_spec", "mutated_spec"):
+                ps = N.nbg_podsparse()
+                ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
+                                           self._p(side + ".val", C.c_uint64))
+                setattr(s, side, ps)
         elif k == "SvcBatch":
             s = N.nbg_svc_batch()
             s.flags = self._p("flags", C.c_uint8)
@@ -119,6 +132,10 @@ class DeviceBatch:
             p = N.nbg_cull_params(now[0], now[1], cull_idle_min, check_period_min, mode)
             rc = lib.nbg_cull_device(ctx.handle, 0, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
                                      C.c_void_p(stream))
+        elif self.kind == "GenBatch":
+            rc = lib.nbg_diff_generic_device(ctx.handle, 0, C.byref(self._struct), self.n, self.mode, o[0], o[1], C.c_void_p(stream))
+        elif self.kind == "RestartBatch":
+            rc = lib.nbg_restart_block_device(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
         else:
             fn = {"StsBatch": lib.nbg_diff_sts_device, "StsSparseBatch": lib.nbg_diff_sts_sparse_device,
                   "SvcBatch": lib.nbg_diff_svc_device,

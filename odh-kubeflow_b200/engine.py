@@ -87,6 +87,26 @@ class Context:
         """Same predicate on sparsely stored PodSpec tiles (batch = StsBatch.sparse())."""
         return self._diff(self._lib.nbg_diff_sts_sparse, batch, allow_nil)
 
+    def diff_generic(self, batch):
+        """The ODH comparator family on a host.GenBatch (reason bit0 labels, bit1 spec/data differ)."""
+        view = batch.view
+        n = batch.n
+        reason = np.zeros(n, dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        _check(self._lib.nbg_diff_generic(self._h, C.byref(view), n, batch.mode, reason.ctypes.data_as(C.c_void_p),
+                                          bitmap.ctypes.data_as(C.c_void_p)), "nbg_diff_generic")
+        return reason, bitmap
+
+    def restart_block(self, batch):
+        """Batched maybeRestartRunningNotebook (ODHWH:505-564) on a host.RestartBatch."""
+        view = batch.view
+        n = batch.n
+        decision = np.zeros(n, dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        _check(self._lib.nbg_restart_block(self._h, C.byref(view), n, decision.ctypes.data_as(C.c_void_p),
+                                           bitmap.ctypes.data_as(C.c_void_p)), "nbg_restart_block")
+        return decision, bitmap
+
     def diff_svc(self, batch):
         """Batched CopyServiceFields (COMMON:166-195)."""
         return self._diff(self._lib.nbg_diff_svc, batch)

@@ -53,6 +53,9 @@ class Obj:
             return None
         return Obj(out.value)
 
+    def clone(self):
+        return Obj(N.nbh().nbh_obj_clone(self._h))
+
     def erase(self, dotted_path):
         if N.nbh().nbh_obj_erase(self._h, dotted_path.encode()) != 0:
             raise HostError("no such path: " + dotted_path)
@@ -284,6 +287,56 @@ class VsBatch(_Batch):
         out["spec_to"] = _arr(v.spec_to, n * N.NBG_VS_SLOTS, np.uint64)
         for name in ("hdr_from", "hdr_to"):
             _kv_arrays(getattr(v, name), n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+
+class GenBatch(_Batch):
+    """Pairs for the ODH comparator family (nbg_generic_batch)."""
+    _new, _free, _view, _struct = "nbh_gen_new", "nbh_gen_free", "nbh_gen_view", N.nbg_generic_batch
+
+    def __init__(self, mode=N.GEN_DEEPEQUAL, labels_path="metadata.labels", spec_path="spec"):
+        super().__init__()
+        self.mode, self.labels_path, self.spec_path = mode, labels_path, spec_path
+
+    def add(self, desired, found):
+        if N.nbh().nbh_gen_add(self._h, desired._h, found._h, self.labels_path.encode(), self.spec_path.encode(), self.mode) != 0:
+            raise HostError("gen add failed")
+        return self
+
+    def arrays(self):
+        v, out = self.view, {}
+        for name in ("labels_a", "labels_b", "spec_a", "spec_b"):
+            _kv_arrays(getattr(v, name), self.n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+
+class RestartBatch(_Batch):
+    """Webhook restart-block inputs (nbg_restart_batch)."""
+    _new, _free, _view, _struct = "nbh_rb_new", "nbh_rb_free", "nbh_rb_view", N.nbg_restart_batch
+
+    def add(self, old_nb, updated_nb, mutated_nb, create=False):
+        if N.nbh().nbh_rb_add(self._h, old_nb._h, updated_nb._h, mutated_nb._h, 1 if create else 0) != 0:
+            raise HostError("rb add failed")
+        return self
+
+    def arrays(self):
+        v, out = self.view, {}
+        n = self.n
+        out["flags"] = _arr(v.flags, n, np.uint8)
+        for side in ("old_spec", "updated_spec", "mutated_spec"):
+            ps = getattr(v, side)
+            off = _arr(ps.off, n + 1, np.uint32)
+            out[side + ".mask"] = _arr(ps.mask, n * 3, np.uint64)
+            out[side + ".voff"] = off
+            out[side + ".val"] = _arr(ps.val, int(off[n]) if n else 0, np.uint64)
         return out
 
     @staticmethod

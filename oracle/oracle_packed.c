@@ -292,3 +292,43 @@ ORC_API double orc2_owner_join(const uint64_t* nb_key, uint64_t n, const uint64_
   clock_gettime(CLOCK_MONOTONIC, &t1);
   return (double)(t1.tv_sec - t0.tv_sec) + (double)(t1.tv_nsec - t0.tv_nsec) * 1e-9;
 }
+
+/* ODH comparator family on packed vectors (include/nbgraft.h: nbg_generic_batch). */
+ORC_API void orc2_diff_generic(const nbg_generic_batch* in, uint64_t n, int mode, uint8_t* reason, uint64_t* bitmap) {
+  memset(bitmap, 0, (n + 63) / 64 * 8);
+  for (uint64_t i = 0; i < n; ++i) {
+    unsigned r = 0;
+    if (mode == NBG_GEN_DEEPEQUAL) {
+      if (map_not_equal(&in->labels_a, 0, &in->labels_b, 0, i)) r |= NBG_GEN_LABELS;
+      if (map_not_equal(&in->spec_a, 0, &in->spec_b, 0, i)) r |= NBG_GEN_SPEC;
+    } else {
+      if (in->labels_a.off[i + 1] - in->labels_a.off[i] != in->labels_b.off[i + 1] - in->labels_b.off[i] ||
+          live_differs(&in->labels_b, &in->labels_a, i)) r |= NBG_GEN_LABELS;
+      if (in->spec_a.off[i + 1] - in->spec_a.off[i] != in->spec_b.off[i + 1] - in->spec_b.off[i] ||
+          live_differs(&in->spec_b, &in->spec_a, i)) r |= NBG_GEN_SPEC;
+    }
+    reason[i] = (uint8_t)r;
+    set_bit(bitmap, i, r != 0);
+  }
+}
+
+/* Webhook restart-block predicate on packed sparse tiles (nbg_restart_batch). */
+static int sparse_differs(const nbg_podsparse* a, const nbg_podsparse* b, uint64_t i) {
+  if (memcmp(a->mask + i * 3, b->mask + i * 3, 24) != 0) return 1;
+  const uint32_t na = a->off[i + 1] - a->off[i];
+  if (na != b->off[i + 1] - b->off[i]) return 1;
+  return memcmp(a->val + a->off[i], b->val + b->off[i], (size_t)na * 8) != 0;
+}
+ORC_API void orc2_restart_block(const nbg_restart_batch* in, uint64_t n, uint8_t* decision, uint64_t* bitmap) {
+  memset(bitmap, 0, (n + 63) / 64 * 8);
+  for (uint64_t i = 0; i < n; ++i) {
+    unsigned d = 0;
+    if (!(in->flags[i] & (NBG_RB_CREATE | NBG_RB_STOPPED | NBG_RB_RESTARTING))) {
+      if (sparse_differs(&in->old_spec, &in->updated_spec, i)) d = NBG_RB_EXTERNAL_CHANGE;
+      else if (!sparse_differs(&in->old_spec, &in->mutated_spec, i)) d = NBG_RB_NO_CHANGE;
+      else d = NBG_RB_BLOCKED;
+    }
+    decision[i] = (uint8_t)d;
+    set_bit(bitmap, i, (d & NBG_RB_BLOCKED) != 0);
+  }
+}

@@ -579,7 +579,136 @@ long find_controlled(const GVal& owner, const nbh_obj* const* list, uint64_t cou
   return -1;
 }
 
+// ------------------------------------------------- ODH comparator family
+// odh-notebook-controller/controllers: CompareNotebookHTTPRoutes notebook_route.go:134-138,
+// CompareNotebookNetworkPolicies notebook_network.go:125-129, CompareNotebookReferenceGrants
+// notebook_referencegrant.go:72-76 — all `reflect.DeepEqual(a.Labels, b.Labels) &&
+// reflect.DeepEqual(a.Spec, b.Spec)`; RoleBinding subjects notebook_rbac.go:131.
+const GVal& at_path(const GVal& root, const std::string& path) {
+  const GVal* cur = &root;
+  size_t pos = 0;
+  while (!path.empty()) {
+    const size_t dot = path.find('.', pos);
+    const std::string key = path.substr(pos, dot == std::string::npos ? std::string::npos : dot - pos);
+    while (cur->kind == GVal::Ptr && !cur->items.empty()) cur = &cur->items[0];
+    cur = &field(*cur, key.c_str());
+    if (dot == std::string::npos) break;
+    pos = dot + 1;
+  }
+  return *cur;
+}
+bool go_deep_equal(const GVal& a, const GVal& b) {      // an absent field is its zero value; nil != empty
+  if (a.kind == GVal::Null && b.kind == GVal::Null) return true;
+  if (a.kind == GVal::Null) return b.is_zero();
+  if (b.kind == GVal::Null) return a.is_zero();
+  return deep_equal(a, b);
+}
+// notebook_kube_rbac_auth.go:240-266 on one map[string]string pair
+bool configmap_map_differs(const GVal& found, const GVal& desired) {
+  const size_t nf = found.kind == GVal::Map ? found.kv.size() : 0, nd = desired.kind == GVal::Map ? desired.kv.size() : 0;
+  if (nf != nd) return true;
+  if (desired.kind == GVal::Map)
+    for (const auto& e : desired.kv) {
+      const GVal* f = found.kind == GVal::Map ? found.find(e.first) : nullptr;
+      const std::string fv = (f && f->kind == GVal::Str) ? f->s : std::string();
+      if (fv != e.second.s) return true;
+    }
+  return false;
+}
+
+// ------------------------------------------ equality.Semantic.DeepEqual
+// k8s.io/apimachinery v0.33.7 (pkg/api/equality/semantic.go + third_party/forked/golang/reflect/
+// deep_equal.go; a go.mod dependency, not under /root/reference — restated from its published
+// behaviour): like reflect.DeepEqual except that a nil and an empty slice/map are equal, and
+// resource.Quantity values are equal when a.Cmp(b) == 0.  Pointers keep nil != &T{}.
+void quantity_value(const GVal& q, std::string* digits, long long* exp) {
+  // value x 10^scale (int64Amount) or unscaled x 10^-scale (inf.Dec), normalised: no trailing zeros
+  std::string d; long long e = 0;
+  const GVal& dec = field(field(q, "d"), "Dec");
+  if (dec.kind == GVal::Ptr && !dec.items.empty()) { d = field(dec.items[0], "unscaled").s; e = -field(dec.items[0], "scale").i; }
+  else { d = std::to_string((long long)field(field(q, "i"), "value").i); e = field(field(q, "i"), "scale").i; }
+  bool neg = false;
+  if (!d.empty() && d[0] == '-') { neg = true; d.erase(0, 1); }
+  size_t nz = d.find_first_not_of('0');
+  d = nz == std::string::npos ? "0" : d.substr(nz);
+  while (d.size() > 1 && d.back() == '0') { d.pop_back(); ++e; }
+  if (d == "0") { e = 0; neg = false; }
+  *digits = (neg ? "-" : "") + d; *exp = e;
+}
+bool semantic_equal(const GVal& a, const GVal& b) {
+  if (a.tag == nbh::kTagQuantity || b.tag == nbh::kTagQuantity) {
+    if (a.tag != b.tag) return a.is_zero() && b.is_zero();     // Quantity{} against an absent one
+    std::string da, db; long long ea, eb;
+    quantity_value(a, &da, &ea); quantity_value(b, &db, &eb);
+    return da == db && ea == eb;
+  }
+  auto empty_seq = [](const GVal& v) { return v.kind == GVal::Null || (v.kind == GVal::List && v.items.empty()) ||
+                                              (v.kind == GVal::Map && v.kv.empty()); };
+  if ((a.kind == GVal::List || a.kind == GVal::Map || b.kind == GVal::List || b.kind == GVal::Map) &&
+      (empty_seq(a) || empty_seq(b)))
+    return empty_seq(a) && empty_seq(b);
+  if (a.kind == GVal::Struct && b.kind == GVal::Null) return semantic_equal(a, GVal::strct());
+  if (a.kind == GVal::Null && b.kind == GVal::Struct) return semantic_equal(GVal::strct(), b);
+  if (a.kind != b.kind) {
+    if (a.kind == GVal::Null) return b.is_zero();
+    if (b.kind == GVal::Null) return a.is_zero();
+    return false;
+  }
+  switch (a.kind) {
+    case GVal::List:
+      if (a.items.size() != b.items.size()) return false;
+      for (size_t k = 0; k < a.items.size(); ++k) if (!semantic_equal(a.items[k], b.items[k])) return false;
+      return true;
+    case GVal::Map:
+      if (a.kv.size() != b.kv.size()) return false;
+      for (const auto& e : a.kv) { const GVal* o = b.find(e.first); if (!o || !semantic_equal(e.second, *o)) return false; }
+      return true;
+    case GVal::Struct: {
+      // union of field names; an absent field is the zero value (which may itself equal an empty slice)
+      for (const auto& e : a.kv) { const GVal* o = b.find(e.first); if (!semantic_equal(e.second, o ? *o : kZero)) return false; }
+      for (const auto& e : b.kv) if (!a.find(e.first) && !semantic_equal(kZero, e.second)) return false;
+      return true;
+    }
+    case GVal::Ptr:
+      if (a.items.empty() || b.items.empty()) return a.items.empty() == b.items.empty();
+      return semantic_equal(a.items[0], b.items[0]);
+    default: return deep_equal(a, b);
+  }
+}
+// notebook_webhook.go:505-564; returns the decision byte of include/nbgraft.h
+int restart_block(const GVal& old_nb, const GVal& updated_nb, const GVal& mutated_nb, bool create) {
+  if (create) return 0;                                                                    // :515-518
+  const GVal& ann = field(field(mutated_nb, "metadata"), "annotations");
+  if (ann.kind == GVal::Map && ann.has("kubeflow-resource-stopped")) return 0;            // :521-524
+  if (ann.kind == GVal::Map && ann.has("notebooks.opendatahub.io/notebook-restart")) return 0;   // :527-530
+  auto pod = [](const GVal& nb) -> const GVal& { return field(field(field(nb, "spec"), "template"), "spec"); };
+  if (!semantic_equal(pod(old_nb), pod(updated_nb))) return 2;                             // :548-551
+  if (semantic_equal(pod(old_nb), pod(mutated_nb))) return 4;                              // :554-557
+  return 1;                                                                                // :559-563
+}
+
 // ============================================================ exported API
+ORC_API int orc_semantic_equal(const nbh_obj* a, const nbh_obj* b) { return semantic_equal(a->v, b->v) ? 1 : 0; }
+ORC_API int orc_restart_block(const nbh_obj* old_nb, const nbh_obj* updated_nb, const nbh_obj* mutated_nb, int create) {
+  return restart_block(old_nb->v, updated_nb->v, mutated_nb->v, create != 0);
+}
+// reason bits as nbg_diff_generic: 1 labels differ, 2 spec/data differ
+ORC_API int orc_compare_generic(const nbh_obj* desired, const nbh_obj* found, const char* labels_path, const char* spec_path, int mode) {
+  const std::string lp(labels_path), sp(spec_path);
+  const GVal& la = at_path(desired->v, lp);
+  const GVal& lb = at_path(found->v, lp);
+  const GVal& sa = at_path(desired->v, sp);
+  const GVal& sb = at_path(found->v, sp);
+  int r = 0;
+  if (mode == 0) {
+    if (!go_deep_equal(la, lb)) r |= 1;
+    if (!go_deep_equal(sa, sb)) r |= 2;
+  } else {
+    if (configmap_map_differs(lb, la)) r |= 1;
+    if (configmap_map_differs(sb, sa)) r |= 2;
+  }
+  return r;
+}
 ORC_API long orc_find_controlled(const nbh_obj* owner, const nbh_obj* const* list, uint64_t count) {
   return find_controlled(owner->v, list, count);
 }

@@ -51,6 +51,13 @@ def lib():
             f = getattr(L, name)
             f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
             f.restype = C.c_double
+        L.orc_semantic_equal.argtypes = [vp, vp]
+        L.orc_restart_block.argtypes = [vp, vp, vp, C.c_int]
+        L.orc2_restart_block.argtypes = [C.POINTER(N.nbg_restart_batch), C.c_uint64, vp, vp]
+        L.orc2_restart_block.restype = None
+        L.orc_compare_generic.argtypes = [vp, vp, cp, cp, C.c_int]
+        L.orc2_diff_generic.argtypes = [C.POINTER(N.nbg_generic_batch), C.c_uint64, C.c_int, vp, vp]
+        L.orc2_diff_generic.restype = None
         L.orc_find_controlled.argtypes = [vp, C.POINTER(vp), C.c_uint64]
         L.orc_find_controlled.restype = C.c_long
         L.orc2_owner_join.argtypes = [vp, C.c_uint64, vp, C.c_uint64, vp]
@@ -180,3 +187,36 @@ def packed_owner_join(nb_keys, sts_keys):
     secs = lib().orc2_owner_join(nb.ctypes.data_as(C.c_void_p), len(nb), st.ctypes.data_as(C.c_void_p), len(st),
                                  match.ctypes.data_as(C.c_void_p))
     return match, secs
+
+
+def compare_generic(desired, found, labels_path="metadata.labels", spec_path="spec", mode=0):
+    """L1: the ODH comparators on objects -> reason bits (1 labels differ, 2 spec/data differ)."""
+    return lib().orc_compare_generic(desired._h, found._h, labels_path.encode(), spec_path.encode(), mode)
+
+
+def packed_diff_generic(batch):
+    view = batch.view
+    n = batch.n
+    reason = np.zeros(n, dtype=np.uint8)
+    bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+    lib().orc2_diff_generic(C.byref(view), n, batch.mode, reason.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+    return reason, bitmap
+
+
+def semantic_equal(a, b):
+    """equality.Semantic.DeepEqual on objects (L1)."""
+    return bool(lib().orc_semantic_equal(a._h, b._h))
+
+
+def restart_block(old_nb, updated_nb, mutated_nb, create=False):
+    """maybeRestartRunningNotebook on objects (L1) -> decision byte."""
+    return lib().orc_restart_block(old_nb._h, updated_nb._h, mutated_nb._h, 1 if create else 0)
+
+
+def packed_restart_block(batch):
+    view = batch.view
+    n = batch.n
+    decision = np.zeros(n, dtype=np.uint8)
+    bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+    lib().orc2_restart_block(C.byref(view), n, decision.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+    return decision, bitmap
