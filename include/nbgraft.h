@@ -260,6 +260,15 @@ int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n,
 /* never 0 */
 uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
 
+/* Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98) as a segmented
+ * count: counts[ns] = number of StatefulSets j with ns_id[j] == ns whose pod-template label
+ * "notebook-name" is present (flags[j] & 1) and equals the StatefulSet's name
+ * (label_hash[j] == name_hash[j]).  ns_id are dense namespace ids < n_namespaces assigned by the
+ * host (ids >= n_namespaces are ignored).  A namespace whose count stays 0 gets no gauge update
+ * in the reference (stsCache has no entry for it). */
+int nbg_count_running(nbg_ctx* ctx, const uint32_t* ns_id, const uint64_t* name_hash, const uint64_t* label_hash,
+                      const uint8_t* flags, uint64_t m, uint32_t n_namespaces, uint32_t* counts);
+
 /* ---- the ODH comparator family ------------------------------ */
 /* Pairs (a = desired, b = found) of arbitrary objects reduced to two key/value
  * vectors each: "labels" and "spec".
@@ -343,6 +352,9 @@ int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint
                           void* scratch, size_t scratch_bytes, void* stream);
 int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* in, uint64_t n, int mode,
                             uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_count_running_device(nbg_ctx* ctx, int device, const uint32_t* ns_id, const uint64_t* name_hash,
+                             const uint64_t* label_hash, const uint8_t* flags, uint64_t m, uint32_t n_namespaces,
+                             uint32_t* counts, void* stream);
 int nbg_restart_block_device(nbg_ctx* ctx, int device, const nbg_restart_batch* in, uint64_t n, uint8_t* decision,
                              uint64_t* blocked_bitmap, void* stream);
 int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* last_activity, const nbg_strings* state,

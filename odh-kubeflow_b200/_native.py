@@ -126,7 +126,7 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
-    "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
+    "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
     "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
 
@@ -182,6 +182,10 @@ def _bind_nbg(lib):
     lib.nbg_restart_block.restype = C.c_int
     lib.nbg_restart_block_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_restart_batch), C.c_uint64, _vp, _vp, _vp]
     lib.nbg_restart_block_device.restype = C.c_int
+    lib.nbg_count_running.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp]
+    lib.nbg_count_running.restype = C.c_int
+    lib.nbg_count_running_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]
+    lib.nbg_count_running_device.restype = C.c_int
     PS = C.POINTER(nbg_strings)
     lib.nbg_parse_records.argtypes = [_vp, PS, PS, C.c_uint64, _vp, _vp, _vp]
     lib.nbg_parse_records.restype = C.c_int

@@ -33,6 +33,8 @@ cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const un
                                uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_generic(const nbg_generic_batch*, unsigned long long, int, const unsigned*, uint8_t*,
                                     uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_count_running(const uint32_t*, const uint64_t*, const uint64_t*, const uint8_t*, unsigned long long,
+                                     unsigned, uint32_t*, cudaStream_t);
 cudaError_t nbg_launch_restart_block(const nbg_restart_batch*, unsigned long long, const unsigned*, uint8_t*, uint64_t*,
                                      cudaStream_t);
 cudaError_t nbg_launch_parse_records(const uint32_t*, const unsigned char*, const uint32_t*, const unsigned char*,
@@ -426,6 +428,18 @@ int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* i
   return NBG_OK;
 }
 
+int nbg_count_running_device(nbg_ctx* ctx, int device, const uint32_t* ns_id, const uint64_t* name_hash,
+                             const uint64_t* label_hash, const uint8_t* flags, uint64_t m, uint32_t n_namespaces,
+                             uint32_t* counts, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (n_namespaces == 0) return NBG_OK;
+  if (!counts || (m && (!ns_id || !name_hash || !label_hash || !flags))) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  CU(nbg_launch_count_running(ns_id, name_hash, label_hash, flags, m, n_namespaces, counts, (cudaStream_t)stream));
+  ctx->launches += m ? 1 : 0;
+  return NBG_OK;
+}
+
 int nbg_restart_block_device(nbg_ctx* ctx, int device, const nbg_restart_batch* in, uint64_t n, uint8_t* decision,
                              uint64_t* bitmap, void* stream) {
   if (int rc = check_dev(ctx, device)) return rc;
@@ -495,6 +509,28 @@ int nbg_diff_generic(nbg_ctx* ctx, const nbg_generic_batch* in, uint64_t n, int 
     }
     return NBG_OK;
   });
+}
+
+int nbg_count_running(nbg_ctx* ctx, const uint32_t* ns_id, const uint64_t* name_hash, const uint64_t* label_hash,
+                      const uint8_t* flags, uint64_t m, uint32_t n_namespaces, uint32_t* counts) {
+  if (!ctx) return NBG_E_INVAL;
+  if (n_namespaces == 0) return NBG_OK;
+  if (!counts || (m && (!ns_id || !name_hash || !label_hash || !flags))) return NBG_E_INVAL;
+  Dev& d = *ctx->devs[0];                              // one table of counts: a single device
+  std::unique_lock<std::mutex> lock(d.mu);
+  CU(cudaSetDevice(d.id));
+  Slot& sl = d.slot[0];
+  Layout lay;
+  const size_t a_ns = lay.in(ns_id, m * 4), a_nm = lay.in(name_hash, m * 8), a_lb = lay.in(label_hash, m * 8);
+  const size_t a_fl = lay.in(flags, m);
+  const size_t o_c = lay.out(counts, (size_t)n_namespaces * 4);
+  if (int rc = slot_upload(d, sl, lay)) return rc;
+  CU(nbg_launch_count_running((const uint32_t*)(sl.dev + a_ns), (const uint64_t*)(sl.dev + a_nm), (const uint64_t*)(sl.dev + a_lb),
+                              (const uint8_t*)(sl.dev + a_fl), m, n_namespaces, (uint32_t*)(sl.dev + o_c), d.s_run));
+  ctx->launches += m ? 1 : 0;
+  if (int rc = slot_download(d, sl, lay)) return rc;
+  CU(cudaStreamSynchronize(d.s_run));
+  return NBG_OK;
 }
 
 int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uint8_t* decision, uint64_t* bitmap) {

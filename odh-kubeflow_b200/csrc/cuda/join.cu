@@ -62,7 +62,44 @@ join_probe_kernel(const unsigned long long* __restrict__ nb_key, unsigned long l
   match[i] = found;
 }
 
+// ---------------------------------------------------------------- metrics scrape
+// Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98): over ALL
+// StatefulSets, count per namespace those whose pod-template label "notebook-name" is present
+// and equals the StatefulSet's own name — the notebook_running gauge.  A segmented count:
+// one StatefulSet per lane, lanes of a warp that share a namespace elect a leader
+// (__match_any_sync) which adds the whole group with one atomic.
+__global__ void __launch_bounds__(256)
+count_running_kernel(const uint32_t* __restrict__ ns_id, const unsigned long long* __restrict__ name_hash,
+                     const unsigned long long* __restrict__ label_hash, const uint8_t* __restrict__ flags,
+                     unsigned long long m, unsigned n_namespaces, unsigned* __restrict__ counts) {
+  const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool hit = false;
+  unsigned ns = 0xFFFFFFFFu;
+  if (j < m) {
+    ns = __ldg(ns_id + j);
+    // `name, ok := labels["notebook-name"]; ok && name == v.Name`
+    hit = (__ldg(flags + j) & 1u) && __ldg(label_hash + j) == __ldg(name_hash + j) && ns < n_namespaces;
+  }
+  const unsigned active = __ballot_sync(FULL, hit);
+  if (hit) {
+    const unsigned peers = __match_any_sync(active, ns);
+    if ((threadIdx.x & 31u) == (unsigned)(__ffs(peers) - 1)) atomicAdd(counts + ns, (unsigned)__popc(peers));
+  }
+}
+
 }  // namespace nbg
+
+extern "C" cudaError_t nbg_launch_count_running(const uint32_t* ns_id, const uint64_t* name_hash, const uint64_t* label_hash,
+                                                const uint8_t* flags, unsigned long long m, unsigned n_namespaces,
+                                                uint32_t* counts, cudaStream_t stream) {
+  cudaError_t e = cudaMemsetAsync(counts, 0, (size_t)n_namespaces * sizeof(uint32_t), stream);
+  if (e != cudaSuccess || m == 0) return e;
+  const unsigned block = 256;
+  nbg::count_running_kernel<<<(unsigned)((m + block - 1) / block), block, 0, stream>>>(
+      ns_id, reinterpret_cast<const unsigned long long*>(name_hash), reinterpret_cast<const unsigned long long*>(label_hash),
+      flags, m, n_namespaces, counts);
+  return cudaGetLastError();
+}
 
 // Table geometry shared by every caller: cap slots, keys then values.
 extern "C" unsigned long long nbg_join_table_slots(unsigned long long m) {

@@ -145,6 +145,22 @@ def _owner_join(self, nb_keys, sts_keys):
 Context.owner_join = _owner_join
 
 
+def _count_running(self, ns_id, name_hash, label_hash, flags, n_namespaces):
+    """Metrics.scrape (metrics.go:82-98) as a segmented count -> uint32[n_namespaces]."""
+    ns = np.ascontiguousarray(ns_id, np.uint32)
+    nm = np.ascontiguousarray(name_hash, np.uint64)
+    lb = np.ascontiguousarray(label_hash, np.uint64)
+    fl = np.ascontiguousarray(flags, np.uint8)
+    counts = np.zeros(n_namespaces, np.uint32)
+    _check(self._lib.nbg_count_running(self._h, ns.ctypes.data_as(C.c_void_p), nm.ctypes.data_as(C.c_void_p),
+                                       lb.ctypes.data_as(C.c_void_p), fl.ctypes.data_as(C.c_void_p), len(ns), n_namespaces,
+                                       counts.ctypes.data_as(C.c_void_p)), "nbg_count_running")
+    return counts
+
+
+Context.count_running = _count_running
+
+
 class StringTable:
     """R strings as CSR (off u32[R+1], bytes padded to 16) — the layout of nbg_strings."""
 

@@ -688,6 +688,12 @@ int restart_block(const GVal& old_nb, const GVal& updated_nb, const GVal& mutate
 }
 
 // ============================================================ exported API
+// metrics.go:82-98 on objects: returns 1 when the StatefulSet counts towards its namespace
+ORC_API int orc_counts_as_running(const nbh_obj* sts) {
+  const GVal& labels = field(field(field(field(sts->v, "spec"), "template"), "metadata"), "labels");
+  const GVal* name = labels.kind == GVal::Map ? labels.find("notebook-name") : nullptr;
+  return (name && name->s == field(field(sts->v, "metadata"), "name").s) ? 1 : 0;
+}
 ORC_API int orc_semantic_equal(const nbh_obj* a, const nbh_obj* b) { return semantic_equal(a->v, b->v) ? 1 : 0; }
 ORC_API int orc_restart_block(const nbh_obj* old_nb, const nbh_obj* updated_nb, const nbh_obj* mutated_nb, int create) {
   return restart_block(old_nb->v, updated_nb->v, mutated_nb->v, create != 0);

@@ -51,6 +51,7 @@ def lib():
             f = getattr(L, name)
             f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
             f.restype = C.c_double
+        L.orc_counts_as_running.argtypes = [vp]
         L.orc_semantic_equal.argtypes = [vp, vp]
         L.orc_restart_block.argtypes = [vp, vp, vp, C.c_int]
         L.orc2_restart_block.argtypes = [C.POINTER(N.nbg_restart_batch), C.c_uint64, vp, vp]
@@ -220,3 +221,8 @@ def packed_restart_block(batch):
     bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
     lib().orc2_restart_block(C.byref(view), n, decision.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
     return decision, bitmap
+
+
+def counts_as_running(sts):
+    """metrics.go:90-93 on one StatefulSet object."""
+    return bool(lib().orc_counts_as_running(sts._h))
