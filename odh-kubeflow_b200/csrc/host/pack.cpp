@@ -53,12 +53,21 @@ uint64_t overflow_digest(const GVal& l, size_t from) {
   for (size_t k = from; k < l.items.size(); ++k) h = nbg_combine(h, digest(l.items[k]));
   return h;
 }
-// digest of a struct with some fields left out
+// digest of a struct with some fields left out — same value as digest(copy with the fields
+// erased), computed without copying the tree (0 when nothing is left)
 uint64_t digest_without(const GVal& s, std::initializer_list<const char*> skip) {
   if (s.kind != GVal::Struct) return digest(s);
-  GVal c = s;
-  for (const char* n : skip) c.erase(n);
-  return c.kv.empty() ? 0 : digest(c);
+  uint64_t h = K_STRUCT;
+  size_t n = 0;
+  for (const auto& e : s.kv) {
+    if (e.second.is_zero()) continue;
+    bool skipped = false;
+    for (const char* k : skip) if (e.first == k) { skipped = true; break; }
+    if (skipped) continue;
+    h = nbg_combine(nbg_combine(h, hash_str(e.first)), digest(e.second));
+    ++n;
+  }
+  return n ? nbg_combine(h, n) : 0;
 }
 
 void pack_quantity(const GVal& q, bool present, uint64_t* s3) {
@@ -71,10 +80,7 @@ void pack_quantity(const GVal& q, bool present, uint64_t* s3) {
   uint64_t code = fmt.empty() ? 0 : fmt == "DecimalSI" ? 1 : fmt == "BinarySI" ? 2 : fmt == "DecimalExponent" ? 3 : 255;
   s3[1] = (uint64_t)scale | (code << 32) | (1ull << 40);
   // everything else the struct holds: cached string, inf.Dec, odd formats, extra fields
-  GVal rest = q.kind == GVal::Struct ? q : GVal::strct();
-  rest.erase("i");
-  if (code != 255) rest.erase("Format");
-  s3[2] = rest.kv.empty() ? 0 : digest(rest);
+  s3[2] = code != 255 ? digest_without(q, {"i", "Format"}) : digest_without(q, {"i"});
 }
 
 constexpr int kPodLevel = 16, kVolSlots = 3, kMaxVol = 8, kContBase = kPodLevel + kVolSlots * kMaxVol,
@@ -134,18 +140,48 @@ void pack_container(const GVal& c, uint64_t* s) {
       p[1] = digest_without(mounts.items[k], {"name"});
     }
   }
-  // residual: the container minus everything slotted above; nil-ness and
-  // emptiness of the resource maps survive because only the entries are erased
-  GVal rest = c.kind == GVal::Struct ? c : GVal::strct();
-  for (const char* n : {"name", "image", "workingDir", "imagePullPolicy", "command", "args", "securityContext",
-                        "livenessProbe", "readinessProbe", "envFrom", "ports", "env", "volumeMounts"})
-    rest.erase(n);
-  if (GVal* r = rest.find("resources")) {
-    for (const char* side : {"limits", "requests"})
-      if (GVal* m = r->find(side))
-        if (m->kind == GVal::Map) for (const char* n : rn) m->erase(n);
+  // residual: the container minus everything slotted above; nil-ness and emptiness of the
+  // resource maps survive because only the four slotted entries are left out
+  uint64_t h = K_STRUCT;
+  size_t nrest = 0;
+  for (const auto& e : c.kind == GVal::Struct ? c.kv : kZero.kv) {
+    if (e.second.is_zero()) continue;
+    static const char* slotted[] = {"name", "image", "workingDir", "imagePullPolicy", "command", "args", "securityContext",
+                                    "livenessProbe", "readinessProbe", "envFrom", "ports", "env", "volumeMounts"};
+    bool skip = false;
+    for (const char* k : slotted) if (e.first == k) { skip = true; break; }
+    if (skip) continue;
+    uint64_t dv;
+    if (e.first == "resources" && e.second.kind == GVal::Struct) {
+      // digest(resources) with cpu/memory left out of limits and requests
+      uint64_t hr = K_STRUCT;
+      size_t nr = 0;
+      for (const auto& f : e.second.kv) {
+        if (f.second.is_zero()) continue;
+        uint64_t df;
+        if ((f.first == "limits" || f.first == "requests") && f.second.kind == GVal::Map) {
+          uint64_t hm = K_MAP;
+          size_t nm = 0;
+          for (const auto& q : f.second.kv) {
+            if (q.first == "cpu" || q.first == "memory") continue;
+            hm = nbg_combine(nbg_combine(hm, hash_str(q.first)), digest(q.second));
+            ++nm;
+          }
+          df = nbg_combine(hm, nm);
+        } else {
+          df = digest(f.second);
+        }
+        hr = nbg_combine(nbg_combine(hr, hash_str(f.first)), df);
+        ++nr;
+      }
+      dv = nbg_combine(hr, nr);
+    } else {
+      dv = digest(e.second);
+    }
+    h = nbg_combine(nbg_combine(h, hash_str(e.first)), dv);
+    ++nrest;
   }
-  uint64_t h = rest.kv.empty() ? 0 : digest(rest);
+  h = nrest ? nbg_combine(h, nrest) : 0;
   const uint64_t o1 = overflow_digest(ports, kMaxPorts), o2 = overflow_digest(env, kMaxEnv),
                  o3 = overflow_digest(mounts, kMaxMounts);
   if (o1 | o2 | o3) h = nbg_combine(nbg_combine(nbg_combine(h, o1), o2), o3);
@@ -306,12 +342,11 @@ void pack_podspec(const GVal& pod, uint64_t* s) {
     if (conts.kind == GVal::List && (size_t)k < conts.items.size())
       pack_container(conts.items[k], s + kContBase + k * kContSlots);
 
-  GVal rest = pod.kind == GVal::Struct ? pod : GVal::strct();
-  for (const char* n : {"serviceAccountName", "serviceAccount", "restartPolicy", "dnsPolicy",
-                        "terminationGracePeriodSeconds", "schedulerName", "nodeName", "securityContext",
-                        "nodeSelector", "tolerations", "affinity", "imagePullSecrets", "volumes", "containers"})
-    rest.erase(n);
-  uint64_t h = rest.kv.empty() ? 0 : digest(rest);
+  uint64_t h = digest_without(pod.kind == GVal::Struct ? pod : kZero,
+                              {"serviceAccountName", "serviceAccount", "restartPolicy", "dnsPolicy",
+                               "terminationGracePeriodSeconds", "schedulerName", "nodeName", "securityContext",
+                               "nodeSelector", "tolerations", "affinity", "imagePullSecrets", "volumes", "containers"});
+  if (pod.kind != GVal::Struct) h = 0;
   const uint64_t o1 = overflow_digest(vols, kMaxVol), o2 = overflow_digest(conts, kMaxCont);
   if (o1 | o2) h = nbg_combine(nbg_combine(h, o1), o2);
   s[15] = h;
