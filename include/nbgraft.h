@@ -321,6 +321,27 @@ typedef struct nbg_strings { const uint32_t* off; const uint8_t* bytes; } nbg_st
  * zone offset in seconds of every record (nullable) for formatting results. */
 int nbg_parse_records(nbg_ctx* ctx, const nbg_strings* last_activity, const nbg_strings* state /*nullable*/,
                       uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone /*nullable*/);
+/* The culler decision straight from the strings the reference handles (CULL:86-241,315-428):
+ * kernel/terminal last_activity + execution_state texts and the two annotation values per
+ * notebook; the device parses them (as nbg_parse_records) and decides (as nbg_cull) in one call,
+ * so the host never parses a timestamp.  ann_text / chk_text hold one string per notebook ("" when
+ * the key is absent — absence itself is in nb_flags / NBG_NBT_* below).  Outputs as nbg_cull, plus
+ * the zone offset (seconds) of the record that supplies the new last-activity (0 otherwise), which
+ * is all the host needs to format it as Format(time.RFC3339) does. */
+typedef struct nbg_cull_text_batch {
+  const uint32_t* k_off;        /* n+1: kernels of notebook i are records k_off[i]..k_off[i+1)      */
+  nbg_strings k_last_activity;  /* K strings                                                        */
+  nbg_strings k_state;          /* K strings                                                        */
+  const uint32_t* t_off;        /* n+1: terminals                                                   */
+  nbg_strings t_last_activity;  /* T strings                                                        */
+  nbg_strings ann_text;         /* n strings: notebooks.kubeflow.org/last-activity                  */
+  nbg_strings chk_text;         /* n strings: notebooks.kubeflow.org/last_activity_check_timestamp  */
+  const uint8_t* nb_flags;      /* n: NBG_NB_* | NBG_NBT_*                                           */
+} nbg_cull_text_batch;
+#define NBG_NBT_STOP_SET    0x10u /* kubeflow-resource-stopped present                               */
+#define NBG_NBT_CHK_PRESENT 0x20u /* check-timestamp key present                                      */
+int nbg_cull_text(nbg_ctx* ctx, const nbg_cull_text_batch* in, uint64_t n, const nbg_cull_params* params,
+                  uint8_t* action, uint32_t* argmax, int32_t* argmax_zone, uint64_t* cull_bitmap, uint64_t* period_bitmap);
 /* nbg_hash64 of every string of the table (label keys/values, env values, ...). */
 int nbg_hash_strings(nbg_ctx* ctx, const nbg_strings* strings, uint64_t R, uint64_t* out);
 

@@ -125,6 +125,9 @@ int nbh_cull_new_last_activity(const nbh_cull* b, uint64_t i, uint8_t action, ui
 
 /* time.Parse(time.RFC3339, s): 1 if it parses, else 0 */
 int nbh_parse_rfc3339(const char* s, int64_t* sec, int32_t* nsec, int32_t* offset_sec);
+/* Host-side counterpart of nbg_parse_records on all host threads (same CSR inputs and outputs). */
+int nbh_parse_records(const uint32_t* off, const uint8_t* bytes, const uint32_t* s_off, const uint8_t* s_bytes,
+                      uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone);
 /* t.Format(time.RFC3339) */
 int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_t buflen);
 

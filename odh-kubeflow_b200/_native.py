@@ -88,6 +88,14 @@ class nbg_strings(C.Structure):
     _fields_ = [("off", u32p), ("bytes", u8p)]
 
 
+class nbg_cull_text_batch(C.Structure):
+    _fields_ = [("k_off", u32p), ("k_last_activity", nbg_strings), ("k_state", nbg_strings), ("t_off", u32p),
+                ("t_last_activity", nbg_strings), ("ann_text", nbg_strings), ("chk_text", nbg_strings), ("nb_flags", u8p)]
+
+
+NB_LA_PRESENT, NB_POD_MISSING, NBT_STOP_SET, NBT_CHK_PRESENT = 1, 2, 0x10, 0x20
+
+
 class nbg_cull_batch(C.Structure):
     _fields_ = [("k_off", u32p), ("k_sec", i64p), ("k_nsf", u32p),
                 ("t_off", u32p), ("t_sec", i64p), ("t_nsf", u32p),
@@ -127,7 +135,7 @@ NBG_SYMBOLS = [
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
-    "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
+    "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
 
 _vp = C.c_void_p
@@ -191,6 +199,8 @@ def _bind_nbg(lib):
     lib.nbg_parse_records.restype = C.c_int
     lib.nbg_parse_records_device.argtypes = [_vp, C.c_int, PS, PS, C.c_uint64, _vp, _vp, _vp, _vp]
     lib.nbg_parse_records_device.restype = C.c_int
+    lib.nbg_cull_text.argtypes = [_vp, C.POINTER(nbg_cull_text_batch), C.c_uint64, C.POINTER(nbg_cull_params), _vp, _vp, _vp, _vp, _vp]
+    lib.nbg_cull_text.restype = C.c_int
     lib.nbg_hash_strings.argtypes = [_vp, PS, C.c_uint64, _vp]
     lib.nbg_hash_strings.restype = C.c_int
     lib.nbg_hash_strings_device.argtypes = [_vp, C.c_int, PS, C.c_uint64, _vp, _vp]
@@ -238,6 +248,7 @@ def _bind_nbh(lib):
         "nbh_cull_new_last_activity": ([_vp, C.c_uint64, C.c_uint8, C.c_uint32, C.c_int64, C.c_int32, cp, sz], C.c_int),
         "nbh_parse_rfc3339": ([cp, P(C.c_int64), P(C.c_int32), P(C.c_int32)], C.c_int),
         "nbh_format_rfc3339": ([C.c_int64, C.c_int32, cp, sz], C.c_int),
+        "nbh_parse_records": ([u32p, u8p, u32p, u8p, C.c_uint64, _vp, _vp, _vp], C.c_int),
         "nbh_fleet_new": ([C.c_int, C.c_uint64, C.c_uint64, C.c_uint32], _vp), "nbh_fleet_free": ([_vp], None),
         "nbh_fleet_get": ([_vp, C.c_uint64, C.c_int, P(_vp)], C.c_int),
         "nbh_fleet_drift_class": ([_vp, C.c_uint64], C.c_int),
@@ -267,7 +278,7 @@ NBH_SYMBOLS = [
     "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_sts_view_sparse", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
     "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
-    "nbh_format_rfc3339", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
+    "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
     "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
     "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",

@@ -33,6 +33,9 @@ cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const un
                                uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_generic(const nbg_generic_batch*, unsigned long long, int, const unsigned*, uint8_t*,
                                     uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_cull_text_fixup(const uint8_t*, unsigned long long, uint32_t*, uint32_t*, uint8_t*, cudaStream_t);
+cudaError_t nbg_launch_cull_text_zone(const uint8_t*, const uint32_t*, const uint32_t*, const int32_t*, unsigned,
+                                      const uint32_t*, const int32_t*, unsigned, unsigned long long, int32_t*, cudaStream_t);
 cudaError_t nbg_launch_count_running(const uint32_t*, const uint64_t*, const uint64_t*, const uint8_t*, unsigned long long,
                                      unsigned, uint32_t*, cudaStream_t);
 cudaError_t nbg_launch_restart_block(const nbg_restart_batch*, unsigned long long, const unsigned*, uint8_t*, uint64_t*,
@@ -95,6 +98,11 @@ struct Layout {
   size_t in(const void* host, size_t bytes) {
     const size_t off = total;
     ins.push_back({host, bytes, off});
+    total += align_up(bytes ? bytes : 1);
+    return off;
+  }
+  size_t scratch(size_t bytes) {            // device-only region of the arena (neither uploaded nor downloaded)
+    const size_t off = total;
     total += align_up(bytes ? bytes : 1);
     return off;
   }
@@ -609,6 +617,91 @@ int nbg_parse_records(nbg_ctx* ctx, const nbg_strings* la, const nbg_strings* st
                                   zone ? (int32_t*)(sl.dev + o_zone) : nullptr, d.s_run));
       ctx->launches++;
       if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_cull_text(nbg_ctx* ctx, const nbg_cull_text_batch* in, uint64_t n, const nbg_cull_params* p, uint8_t* action,
+                  uint32_t* argmax, int32_t* argmax_zone, uint64_t* cull_bitmap, uint64_t* period_bitmap) {
+  if (!ctx || !in || !p) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!action || !argmax || !cull_bitmap || !period_bitmap || !in->k_off || !in->t_off || !in->nb_flags ||
+      !in->ann_text.off || !in->chk_text.off)
+    return NBG_E_INVAL;
+  if (p->now_nsec < 0 || p->now_nsec > 999999999 || (p->mode != NBG_CULL_PREDICATES && p->mode != NBG_CULL_RECONCILE))
+    return NBG_E_INVAL;
+  if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
+      p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
+    return NBG_E_INVAL;
+  if ((in->k_off[n] > in->k_off[0] && (!in->k_last_activity.off || !in->k_state.off)) ||
+      (in->t_off[n] > in->t_off[0] && !in->t_last_activity.off))
+    return NBG_E_INVAL;
+
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kCullChunk, ++c) {
+      const uint64_t i1 = i0 + kCullChunk < hi ? i0 + kCullChunk : hi, m = i1 - i0;
+      if (!off_ok(in->k_off, i0, i1) || !off_ok(in->t_off, i0, i1) || !off_ok(in->ann_text.off, i0, i1) ||
+          !off_ok(in->chk_text.off, i0, i1))
+        return NBG_E_RANGE;
+      const uint64_t kb = in->k_off[i0], ke = in->k_off[i1], tb = in->t_off[i0], te = in->t_off[i1];
+      const uint64_t nk = ke - kb, nt = te - tb;
+      if ((nk && (!off_ok(in->k_last_activity.off, kb, ke) || !off_ok(in->k_state.off, kb, ke))) ||
+          (nt && !off_ok(in->t_last_activity.off, tb, te)))
+        return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      // a string-table slice: offsets [r0..r1] and the bytes they span
+      struct Str { size_t off_at = 0, bytes_at = 0; unsigned base = 0; };
+      auto str_in = [&](const nbg_strings& t, uint64_t r0, uint64_t r1) {
+        Str s;
+        if (r1 == r0) { s.off_at = lay.scratch(8); s.bytes_at = lay.scratch(16); return s; }
+        s.base = t.off[r0];
+        s.off_at = lay.in(t.off + r0, (r1 - r0 + 1) * 4);
+        const size_t nb = t.off[r1] - s.base;
+        s.bytes_at = lay.in(nb ? t.bytes + s.base : nullptr, nb);
+        return s;
+      };
+      const size_t a_koff = lay.in(in->k_off + i0, (m + 1) * 4), a_toff = lay.in(in->t_off + i0, (m + 1) * 4);
+      const Str kla = str_in(in->k_last_activity, kb, ke), kst = str_in(in->k_state, kb, ke);
+      const Str tla = str_in(in->t_last_activity, tb, te);
+      const Str ann = str_in(in->ann_text, i0, i1), chk = str_in(in->chk_text, i0, i1);
+      const size_t a_flags = lay.in(in->nb_flags + i0, m);
+      // device-only intermediates: what the host packer would have produced
+      const size_t s_ksec = lay.scratch(nk * 8), s_knsf = lay.scratch(nk * 4), s_kzone = lay.scratch(nk * 4);
+      const size_t s_tsec = lay.scratch(nt * 8), s_tnsf = lay.scratch(nt * 4), s_tzone = lay.scratch(nt * 4);
+      const size_t s_asec = lay.scratch(m * 8), s_ansf = lay.scratch(m * 4), s_csec = lay.scratch(m * 8), s_cnsf = lay.scratch(m * 4);
+      const size_t s_nbf = lay.scratch(m);
+      const size_t words = (m + 63) / 64;
+      const size_t o_act = lay.out(action + i0, m), o_arg = lay.out(argmax + i0, m * 4);
+      const size_t o_zone = argmax_zone ? lay.out(argmax_zone + i0, m * 4) : lay.scratch(m * 4);
+      const size_t o_cull = lay.out(cull_bitmap + i0 / 64, words * 8), o_per = lay.out(period_bitmap + i0 / 64, words * 8);
+      if (int rc = slot_upload(d, sl, lay)) return rc;
+      char* D = sl.dev;
+      auto u32 = [&](size_t at) { return (uint32_t*)(D + at); };
+      if (nk) CU(nbg_launch_parse_records(u32(kla.off_at), (const unsigned char*)(D + kla.bytes_at), u32(kst.off_at),
+                                          (const unsigned char*)(D + kst.bytes_at), nk, kla.base, kst.base,
+                                          (int64_t*)(D + s_ksec), u32(s_knsf), (int32_t*)(D + s_kzone), d.s_run));
+      if (nt) CU(nbg_launch_parse_records(u32(tla.off_at), (const unsigned char*)(D + tla.bytes_at), nullptr, nullptr, nt,
+                                          tla.base, 0, (int64_t*)(D + s_tsec), u32(s_tnsf), (int32_t*)(D + s_tzone), d.s_run));
+      CU(nbg_launch_parse_records(u32(ann.off_at), (const unsigned char*)(D + ann.bytes_at), nullptr, nullptr, m, ann.base, 0,
+                                  (int64_t*)(D + s_asec), u32(s_ansf), nullptr, d.s_run));
+      CU(nbg_launch_parse_records(u32(chk.off_at), (const unsigned char*)(D + chk.bytes_at), nullptr, nullptr, m, chk.base, 0,
+                                  (int64_t*)(D + s_csec), u32(s_cnsf), nullptr, d.s_run));
+      CU(nbg_launch_cull_text_fixup((const uint8_t*)(D + a_flags), m, u32(s_ansf), u32(s_cnsf), (uint8_t*)(D + s_nbf), d.s_run));
+      nbg_cull_batch b;
+      b.k_off = u32(a_koff); b.k_sec = (const int64_t*)(D + s_ksec); b.k_nsf = u32(s_knsf);
+      b.t_off = u32(a_toff); b.t_sec = (const int64_t*)(D + s_tsec); b.t_nsf = u32(s_tnsf);
+      b.ann_sec = (const int64_t*)(D + s_asec); b.ann_nsf = u32(s_ansf);
+      b.chk_sec = (const int64_t*)(D + s_csec); b.chk_nsf = u32(s_cnsf);
+      b.nb_flags = (const uint8_t*)(D + s_nbf);
+      CU(nbg_launch_cull(&b, m, p, (unsigned)kb, (unsigned)tb, (uint8_t*)(D + o_act), u32(o_arg), (uint64_t*)(D + o_cull),
+                         (uint64_t*)(D + o_per), d.s_run));
+      CU(nbg_launch_cull_text_zone((const uint8_t*)(D + o_act), u32(o_arg), u32(a_koff), (const int32_t*)(D + s_kzone), (unsigned)kb,
+                                   u32(a_toff), (const int32_t*)(D + s_tzone), (unsigned)tb, m, (int32_t*)(D + o_zone), d.s_run));
+      ctx->launches += 5 + (nk ? 1 : 0) + (nt ? 1 : 0);
+      if (int rc = slot_download(d, sl, lay)) return rc;
     }
     return NBG_OK;
   });

@@ -171,7 +171,54 @@ cull_kernel(nbg_cull_batch in, unsigned long long n, nbg_cull_params p,
   }
 }
 
+// ---- glue for nbg_cull_text: device-parsed annotation words + presence flags -> cull inputs
+__global__ void __launch_bounds__(256)
+cull_text_fixup_kernel(const uint8_t* __restrict__ flags_in, unsigned long long n, uint32_t* __restrict__ ann_nsf,
+                       uint32_t* __restrict__ chk_nsf, uint8_t* __restrict__ nb_flags) {
+  const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned f = flags_in[i];
+  // a key that is absent cannot have parsed: keep only the words of present keys
+  unsigned a = (f & NBG_NB_LA_PRESENT) ? (ann_nsf[i] & (NBG_NSEC_MASK | NBG_ANN_PARSE_OK)) : 0u;
+  if (f & NBG_NBT_STOP_SET) a |= NBG_ANN_STOP_SET;
+  unsigned c = (f & NBG_NBT_CHK_PRESENT) ? ((chk_nsf[i] & (NBG_NSEC_MASK | NBG_CHK_PARSE_OK)) | NBG_CHK_PRESENT) : 0u;
+  ann_nsf[i] = a;
+  chk_nsf[i] = c;
+  nb_flags[i] = (uint8_t)(f & (NBG_NB_LA_PRESENT | NBG_NB_POD_MISSING));
+}
+
+// zone offset of the record that supplies the new last-activity (what Format(RFC3339) needs)
+__global__ void __launch_bounds__(256)
+cull_text_zone_kernel(const uint8_t* __restrict__ action, const uint32_t* __restrict__ argmax,
+                      const uint32_t* __restrict__ k_off, const int32_t* __restrict__ k_zone, unsigned k_base,
+                      const uint32_t* __restrict__ t_off, const int32_t* __restrict__ t_zone, unsigned t_base,
+                      unsigned long long n, int32_t* __restrict__ out) {
+  const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned src = action[i] & NBG_ACT_SRC_MASK;
+  int z = 0;
+  if (src == 2u) z = k_zone[k_off[i] - k_base + argmax[i]];
+  else if (src == 3u) z = t_zone[t_off[i] - t_base + argmax[i]];
+  out[i] = z;
+}
+
 }  // namespace nbg
+
+extern "C" cudaError_t nbg_launch_cull_text_fixup(const uint8_t* flags_in, unsigned long long n, uint32_t* ann_nsf,
+                                                  uint32_t* chk_nsf, uint8_t* nb_flags, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  nbg::cull_text_fixup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(flags_in, n, ann_nsf, chk_nsf, nb_flags);
+  return cudaGetLastError();
+}
+extern "C" cudaError_t nbg_launch_cull_text_zone(const uint8_t* action, const uint32_t* argmax, const uint32_t* k_off,
+                                                 const int32_t* k_zone, unsigned k_base, const uint32_t* t_off,
+                                                 const int32_t* t_zone, unsigned t_base, unsigned long long n, int32_t* out,
+                                                 cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  nbg::cull_text_zone_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(action, argmax, k_off, k_zone, k_base, t_off,
+                                                                               t_zone, t_base, n, out);
+  return cudaGetLastError();
+}
 
 // k_base / t_base: value of k_off[0] / t_off[0] when the record pointers in
 // `in` already point at the first record of this slice (host-buffer chunking);

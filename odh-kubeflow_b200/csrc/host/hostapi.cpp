@@ -393,6 +393,26 @@ NBH_API int nbh_parse_rfc3339(const char* s, int64_t* sec, int32_t* nsec, int32_
   if (offset_sec) *offset_sec = t.offset;
   return 1;
 }
+// Host-side counterpart of nbg_parse_records (same inputs, same outputs) on all host threads:
+// what a packer without the device parser has to do, and the CPU baseline of that kernel.
+NBH_API int nbh_parse_records(const uint32_t* off, const uint8_t* bytes, const uint32_t* s_off, const uint8_t* s_bytes,
+                              uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone) {
+  if (!off || !sec || !nsf) return -1;
+  const uint64_t kBlock = 16384, nblocks = (R + kBlock - 1) / kBlock;
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < R ? lo + kBlock : R;
+    for (uint64_t r = lo; r < hi; ++r) {
+      Instant t;
+      uint32_t w = 0;
+      if (parse_rfc3339((const char*)bytes + off[r], off[r + 1] - off[r], &t)) w = (uint32_t)t.nsec | NBG_REC_PARSE_OK;
+      else t = Instant();
+      if (s_off && s_off[r + 1] - s_off[r] == 4 && memcmp(s_bytes + s_off[r], "idle", 4) == 0) w |= NBG_REC_IDLE;
+      sec[r] = t.sec; nsf[r] = w;
+      if (zone) zone[r] = t.offset;
+    }
+  });
+  return 0;
+}
 NBH_API int nbh_format_rfc3339(int64_t sec, int32_t offset_sec, char* buf, size_t buflen) {
   const std::string s = format_rfc3339(sec, offset_sec);
   if (!buf || s.size() + 1 > buflen) return -1;

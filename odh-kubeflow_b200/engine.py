@@ -201,6 +201,73 @@ def _hash_strings(self, strings):
     return out
 
 
+LA_KEY = "notebooks.kubeflow.org/last-activity"
+CHK_KEY = "notebooks.kubeflow.org/last_activity_check_timestamp"
+STOP_KEY = "kubeflow-resource-stopped"
+
+
+class CullTextBatch:
+    """Culler inputs as the reference handles them — strings — laid out for nbg_cull_text.
+    notebooks: iterable of {"annotations": {...}|None, "kernels": [...], "terminals": [...], "pod_missing": bool}."""
+
+    def __init__(self, notebooks):
+        k_off, t_off, kla, kst, tla, ann, chk, flags = [0], [0], [], [], [], [], [], []
+        for nb in notebooks:
+            a = nb.get("annotations")
+            f = 0
+            la = ck = ""
+            if a is not None:
+                if LA_KEY in a:
+                    f |= N.NB_LA_PRESENT
+                    la = a[LA_KEY]
+                if CHK_KEY in a:
+                    f |= N.NBT_CHK_PRESENT
+                    ck = a[CHK_KEY]
+                if STOP_KEY in a:
+                    f |= N.NBT_STOP_SET
+            if nb.get("pod_missing"):
+                f |= N.NB_POD_MISSING
+            for k in nb.get("kernels") or []:
+                kla.append(k.get("last_activity", ""))
+                kst.append(k.get("execution_state", ""))
+            for t in nb.get("terminals") or []:
+                tla.append(t.get("last_activity", ""))
+            k_off.append(len(kla))
+            t_off.append(len(tla))
+            ann.append(la)
+            chk.append(ck)
+            flags.append(f)
+        self.n = len(flags)
+        self.k_off, self.t_off = np.array(k_off, np.uint32), np.array(t_off, np.uint32)
+        self.flags = np.array(flags, np.uint8)
+        self.tables = [StringTable(x) for x in (kla, kst, tla, ann, chk)]
+        self.kernel_texts, self.terminal_texts = kla, tla
+        v = N.nbg_cull_text_batch()
+        v.k_off, v.t_off = self.k_off.ctypes.data_as(N.u32p), self.t_off.ctypes.data_as(N.u32p)
+        v.k_last_activity, v.k_state, v.t_last_activity, v.ann_text, v.chk_text = (t.view for t in self.tables)
+        v.nb_flags = self.flags.ctypes.data_as(N.u8p)
+        self.view = v
+
+    def input_bytes(self):
+        return (self.k_off.nbytes + self.t_off.nbytes + self.flags.nbytes +
+                sum(t.off.nbytes + int(t.off[-1]) for t in self.tables))
+
+
+def _cull_text(self, batch, now_sec, now_nsec, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE):
+    """nbg_cull_text: the culler decision from raw strings; returns
+    (action, argmax, argmax_zone, cull_bitmap, period_bitmap)."""
+    n = batch.n
+    p = N.nbg_cull_params(now_sec, now_nsec, cull_idle_min, check_period_min, mode)
+    action, argmax, zone = np.zeros(n, np.uint8), np.zeros(n, np.uint32), np.zeros(n, np.int32)
+    words = (n + 63) // 64
+    cb, pb = np.zeros(words, np.uint64), np.zeros(words, np.uint64)
+    _check(self._lib.nbg_cull_text(self._h, C.byref(batch.view), n, C.byref(p), action.ctypes.data_as(C.c_void_p),
+                                   argmax.ctypes.data_as(C.c_void_p), zone.ctypes.data_as(C.c_void_p),
+                                   cb.ctypes.data_as(C.c_void_p), pb.ctypes.data_as(C.c_void_p)), "nbg_cull_text")
+    return action, argmax, zone, cb, pb
+
+
+Context.cull_text = _cull_text
 Context.parse_records = _parse_records
 Context.hash_strings = _hash_strings
 
