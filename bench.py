@@ -126,15 +126,15 @@ def struct_over(N, kind, arr):
         for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
             setattr(s, f, kv(f))
     elif kind == "svc":
-        s = N.nbg_svc_batch()
-        s.flags = p("flags", C.c_uint8)
-        s.ports_from, s.ports_to = p("ports_from", C.c_uint64), p("ports_to", C.c_uint64)
-        for f in ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"):
+        s = N.nbg_svc_gen_batch()
+        s.name_hash, s.target_port = p("name_hash", C.c_uint64), p("target_port", C.c_int32)
+        s.flags, s.ports_to = p("flags", C.c_uint8), p("ports_to", C.c_uint64)
+        for f in ("labels_to", "ann_to", "sel_to"):
             setattr(s, f, kv(f))
     elif kind == "vs":
-        s = N.nbg_vs_batch()
-        s.flags = p("flags", C.c_uint8)
-        s.spec_from, s.spec_to = p("spec_from", C.c_uint64), p("spec_to", C.c_uint64)
+        s = N.nbg_vs_gen_batch()
+        s.prefix_hash, s.rewrite_hash, s.host_hash = p("prefix_hash", C.c_uint64), p("rewrite_hash", C.c_uint64), p("host_hash", C.c_uint64)
+        s.flags, s.spec_to = p("flags", C.c_uint8), p("spec_to", C.c_uint64)
         s.hdr_from, s.hdr_to = kv("hdr_from"), kv("hdr_to")
     else:
         s = N.nbg_cull_batch()
@@ -249,8 +249,11 @@ def main():
     now = (cfleet.now_sec, cfleet.now_nsec)
 
     # the step compares StatefulSets on SPARSE PodSpec tiles (same answer as the dense tiles, ~4x fewer bytes)
-    sts_sp = sts.sparse()
-    d_sts, d_svc, d_vs, d_cull = (dev.DeviceBatch.from_host(b, device=local) for b in (sts_sp, svc, vs, cull))
+    # and Services / VirtualServices against a desired side generated on the device from the few
+    # Notebook words generateService / generateVirtualService depend on
+    sts_sp, svc_g, vs_g = sts.sparse(), svc.gen(), vs.gen()
+    vs_consts = host.vs_gen_consts()
+    d_sts, d_svc, d_vs, d_cull = (dev.DeviceBatch.from_host(b, device=local) for b in (sts_sp, svc_g, vs_g, cull))
     batches = [("diff_sts", d_sts), ("diff_svc", d_svc), ("diff_vs", d_vs), ("cull", d_cull)]
     alg_bytes = {name: b.algorithmic_bytes for name, b in batches}
 
@@ -326,7 +329,7 @@ def main():
     keep = []
     views, outs_h = {}, {}
     words = (per + 63) // 64
-    for kind, b in (("sts", sts_sp), ("svc", svc), ("vs", vs), ("cull", cull)):
+    for kind, b in (("sts", sts_sp), ("svc", svc_g), ("vs", vs_g), ("cull", cull)):
         views[kind] = (struct_over(N, kind, pinned_copy(lib, b.arrays(), keep)), sum(a.nbytes for a in b.arrays().values()))
     out_arr = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64), "a": np.zeros(per, np.uint32),
                                 "b2": np.zeros(words, np.uint64)}, keep)
@@ -335,8 +338,8 @@ def main():
 
     def e2e_step():
         rc = lib.nbg_diff_sts_sparse(ctx.handle, C.byref(views["sts"][0]), per, rp, bp)
-        rc |= lib.nbg_diff_svc(ctx.handle, C.byref(views["svc"][0]), per, rp, bp)
-        rc |= lib.nbg_diff_vs(ctx.handle, C.byref(views["vs"][0]), per, rp, bp)
+        rc |= lib.nbg_diff_svc_gen(ctx.handle, C.byref(views["svc"][0]), per, rp, bp)
+        rc |= lib.nbg_diff_vs_gen(ctx.handle, C.byref(views["vs"][0]), C.byref(vs_consts), per, rp, bp)
         rc |= lib.nbg_cull(ctx.handle, C.byref(views["cull"][0]), per, C.byref(params), rp, ap_, bp, b2p)
         if rc:
             raise SystemExit("bench: e2e call failed")
@@ -375,6 +378,8 @@ def main():
                                "decision per Notebook" % per,
                    "object": "one Notebook = 3 desired/live pairs + its kernel/terminal records",
                    "tiles": "PodSpec tiles stored sparsely (192-bit mask + non-zero slots); dense tiles reported under dense_tiles",
+                   "desired_side": "StatefulSet: packed from generateStatefulSet's output; Service and VirtualService: generated on the device "
+                                   "from name/port/prefix/rewrite/host words (same answer as shipping generateService/VirtualService outputs)",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
                    "l2": "inputs (%.1f GB per GPU) exceed L2; no flush needed" % (sum(alg_bytes.values()) / 1e9),
                    "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},

@@ -260,6 +260,36 @@ int nbg_owner_join(nbg_ctx* ctx, const uint64_t* nb_key, uint64_t n,
 /* never 0 */
 uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
 
+/* ---- desired Service / VirtualService generated ON THE DEVICE -------- */
+/* generateService (NBCTL:525-552) and generateVirtualService (NBCTL:558-658) are pure functions
+ * of a handful of Notebook fields, so their outputs need not be packed and shipped: these two
+ * entry points take only those fields for the desired side, synthesise the desired tile in
+ * registers and compare it with the live object — identical results to nbg_diff_svc /
+ * nbg_diff_vs on (generate*(notebook), live), ~45 % / ~30 % fewer bytes per object.
+ * (generateStatefulSet is NOT done this way: its PodSpec is the Notebook's own.) */
+typedef struct nbg_svc_gen_batch {
+  const uint64_t* name_hash;     /* n: hash64(notebook name) — selector {"statefulset": name}      */
+  const int32_t*  target_port;   /* n: containers[0].ports[0].containerPort, or 8888 (NBCTL:527-531) */
+  const uint8_t*  flags;         /* n: NBG_F_TO_SEL_NIL                                             */
+  const uint64_t* ports_to;      /* n * NBG_SVC_SLOTS                                               */
+  nbg_kvmap labels_to, ann_to, sel_to;
+} nbg_svc_gen_batch;
+typedef struct nbg_vs_gen_batch {
+  const uint64_t* prefix_hash;   /* n: hash64("/notebook/<ns>/<name>/")                             */
+  const uint64_t* rewrite_hash;  /* n: hash64(rewrite annotation, or the prefix) (NBCTL:569-574)    */
+  const uint64_t* host_hash;     /* n: hash64("<name>.<ns>.svc.<CLUSTER_DOMAIN>")                   */
+  nbg_kvmap hdr_from;            /* headers.request.set from the annotation JSON (NBCTL:602-618)    */
+  const uint8_t*  flags;         /* n: NBG_F_TO_SPEC_MISS, NBG_F_TO_HDR_NIL                         */
+  const uint64_t* spec_to;       /* n * NBG_VS_SLOTS                                                */
+  nbg_kvmap hdr_to;
+} nbg_vs_gen_batch;
+/* what does not depend on the notebook: hash64(ISTIO_HOST), hash64(ISTIO_GATEWAY) and the
+ * packer's residual digest of the generated spec's shape (nbh_vs_gen_consts computes them) */
+typedef struct nbg_vs_gen_consts { uint64_t istio_host_hash, gateway_hash, residual; } nbg_vs_gen_consts;
+int nbg_diff_svc_gen(nbg_ctx* ctx, const nbg_svc_gen_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap);
+int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts, uint64_t n,
+                    uint8_t* reason, uint64_t* bitmap);
+
 /* Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98) as a segmented
  * count: counts[ns] = number of StatefulSets j with ns_id[j] == ns whose pod-template label
  * "notebook-name" is present (flags[j] & 1) and equals the StatefulSet's name
@@ -373,6 +403,10 @@ int nbg_owner_join_device(nbg_ctx* ctx, int device, const uint64_t* nb_key, uint
                           void* scratch, size_t scratch_bytes, void* stream);
 int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* in, uint64_t n, int mode,
                             uint8_t* reason, uint64_t* bitmap, void* stream);
+int nbg_diff_svc_gen_device(nbg_ctx* ctx, int device, const nbg_svc_gen_batch* in, uint64_t n, uint8_t* reason,
+                            uint64_t* bitmap, void* stream);
+int nbg_diff_vs_gen_device(nbg_ctx* ctx, int device, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts,
+                           uint64_t n, uint8_t* reason, uint64_t* bitmap, void* stream);
 int nbg_count_running_device(nbg_ctx* ctx, int device, const uint32_t* ns_id, const uint64_t* name_hash,
                              const uint64_t* label_hash, const uint8_t* flags, uint64_t m, uint32_t n_namespaces,
                              uint32_t* counts, void* stream);

@@ -86,6 +86,12 @@ void nbh_svc_free(nbh_svc* b);
 int nbh_svc_add(nbh_svc* b, const nbh_obj* from, const nbh_obj* to);
 uint64_t nbh_svc_view(const nbh_svc* b, nbg_svc_batch* out);
 
+/* views for the device-generated desired side (nbg_diff_svc_gen / nbg_diff_vs_gen): valid when
+ * every `from` object was produced by generate_service / generate_virtualservice */
+uint64_t nbh_svc_view_gen(const nbh_svc* b, nbg_svc_gen_batch* out);
+uint64_t nbh_vs_view_gen(const nbh_vs* b, nbg_vs_gen_batch* out);
+int nbh_vs_gen_consts(const nbh_env* env /*NULL = defaults*/, nbg_vs_gen_consts* out);
+
 nbh_vs* nbh_vs_new(void);
 void nbh_vs_free(nbh_vs* b);
 int nbh_vs_add(nbh_vs* b, const nbh_obj* from, const nbh_obj* to);

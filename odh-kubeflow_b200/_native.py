@@ -69,6 +69,20 @@ class nbg_vs_batch(C.Structure):
                 ("hdr_from", nbg_kvmap), ("hdr_to", nbg_kvmap)]
 
 
+class nbg_svc_gen_batch(C.Structure):
+    _fields_ = [("name_hash", u64p), ("target_port", i32p), ("flags", u8p), ("ports_to", u64p),
+                ("labels_to", nbg_kvmap), ("ann_to", nbg_kvmap), ("sel_to", nbg_kvmap)]
+
+
+class nbg_vs_gen_batch(C.Structure):
+    _fields_ = [("prefix_hash", u64p), ("rewrite_hash", u64p), ("host_hash", u64p), ("hdr_from", nbg_kvmap),
+                ("flags", u8p), ("spec_to", u64p), ("hdr_to", nbg_kvmap)]
+
+
+class nbg_vs_gen_consts(C.Structure):
+    _fields_ = [("istio_host_hash", C.c_uint64), ("gateway_hash", C.c_uint64), ("residual", C.c_uint64)]
+
+
 class nbg_restart_batch(C.Structure):
     _fields_ = [("flags", u8p), ("old_spec", nbg_podsparse), ("updated_spec", nbg_podsparse), ("mutated_spec", nbg_podsparse)]
 
@@ -134,6 +148,7 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
+    "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
     "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
@@ -190,6 +205,14 @@ def _bind_nbg(lib):
     lib.nbg_restart_block.restype = C.c_int
     lib.nbg_restart_block_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_restart_batch), C.c_uint64, _vp, _vp, _vp]
     lib.nbg_restart_block_device.restype = C.c_int
+    lib.nbg_diff_svc_gen.argtypes = [_vp, C.POINTER(nbg_svc_gen_batch), C.c_uint64, _vp, _vp]
+    lib.nbg_diff_svc_gen.restype = C.c_int
+    lib.nbg_diff_svc_gen_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_svc_gen_batch), C.c_uint64, _vp, _vp, _vp]
+    lib.nbg_diff_svc_gen_device.restype = C.c_int
+    lib.nbg_diff_vs_gen.argtypes = [_vp, C.POINTER(nbg_vs_gen_batch), C.POINTER(nbg_vs_gen_consts), C.c_uint64, _vp, _vp]
+    lib.nbg_diff_vs_gen.restype = C.c_int
+    lib.nbg_diff_vs_gen_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_vs_gen_batch), C.POINTER(nbg_vs_gen_consts), C.c_uint64, _vp, _vp, _vp]
+    lib.nbg_diff_vs_gen_device.restype = C.c_int
     lib.nbg_count_running.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp]
     lib.nbg_count_running.restype = C.c_int
     lib.nbg_count_running_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]
@@ -235,6 +258,9 @@ def _bind_nbh(lib):
         "nbh_sts_view_sparse": ([_vp, P(nbg_sts_sparse_batch)], C.c_uint64),
         "nbh_svc_new": ([], _vp), "nbh_svc_free": ([_vp], None),
         "nbh_svc_add": ([_vp, _vp, _vp], C.c_int), "nbh_svc_view": ([_vp, P(nbg_svc_batch)], C.c_uint64),
+        "nbh_svc_view_gen": ([_vp, P(nbg_svc_gen_batch)], C.c_uint64),
+        "nbh_vs_view_gen": ([_vp, P(nbg_vs_gen_batch)], C.c_uint64),
+        "nbh_vs_gen_consts": ([P(nbh_env), P(nbg_vs_gen_consts)], C.c_int),
         "nbh_vs_new": ([], _vp), "nbh_vs_free": ([_vp], None),
         "nbh_vs_add": ([_vp, _vp, _vp], C.c_int), "nbh_vs_view": ([_vp, P(nbg_vs_batch)], C.c_uint64),
         "nbh_gen_new": ([], _vp), "nbh_gen_free": ([_vp], None),
@@ -276,7 +302,7 @@ NBH_SYMBOLS = [
     "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_erase", "nbh_obj_set_str", "nbh_obj_digest",
     "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate",
     "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_sts_view_sparse", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
-    "nbh_svc_view", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
+    "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
     "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",

@@ -33,6 +33,9 @@ cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const un
                                uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_generic(const nbg_generic_batch*, unsigned long long, int, const unsigned*, uint8_t*,
                                     uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_svc_gen(const nbg_svc_gen_batch*, unsigned long long, const unsigned*, uint8_t*, uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_vs_gen(const nbg_vs_gen_batch*, const nbg_vs_gen_consts*, unsigned long long, const unsigned*, uint8_t*,
+                                   uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_cull_text_fixup(const uint8_t*, unsigned long long, uint32_t*, uint32_t*, uint8_t*, cudaStream_t);
 cudaError_t nbg_launch_cull_text_zone(const uint8_t*, const uint32_t*, const uint32_t*, const int32_t*, unsigned,
                                       const uint32_t*, const int32_t*, unsigned, unsigned long long, int32_t*, cudaStream_t);
@@ -436,6 +439,32 @@ int nbg_diff_generic_device(nbg_ctx* ctx, int device, const nbg_generic_batch* i
   return NBG_OK;
 }
 
+int nbg_diff_svc_gen_device(nbg_ctx* ctx, int device, const nbg_svc_gen_batch* in, uint64_t n, uint8_t* reason,
+                            uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[3] = {0, 0, 0};
+  CU(nbg_launch_diff_svc_gen(in, n, bases, reason, bitmap, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_vs_gen_device(nbg_ctx* ctx, int device, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts,
+                           uint64_t n, uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in || !consts) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[2] = {0, 0};
+  CU(nbg_launch_diff_vs_gen(in, consts, n, bases, reason, bitmap, (cudaStream_t)stream));
+  ctx->launches++;
+  return NBG_OK;
+}
+
 int nbg_count_running_device(nbg_ctx* ctx, int device, const uint32_t* ns_id, const uint64_t* name_hash,
                              const uint64_t* label_hash, const uint8_t* flags, uint64_t m, uint32_t n_namespaces,
                              uint32_t* counts, void* stream) {
@@ -512,6 +541,67 @@ int nbg_diff_generic(nbg_ctx* ctx, const nbg_generic_batch* in, uint64_t n, int 
       b.spec_a = csr_ptr(sl, sa); b.spec_b = csr_ptr(sl, sb);
       const unsigned bases[4] = {la.base, lb.base, sa.base, sb.base};
       CU(nbg_launch_diff_generic(&b, m, mode, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_diff_svc_gen(nbg_ctx* ctx, const nbg_svc_gen_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->name_hash || !in->target_port || !in->flags || !in->ports_to) return NBG_E_INVAL;
+  if (!csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_to, n) || !csr_ptrs_ok(in->sel_to, n)) return NBG_E_INVAL;
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kSvcChunk, ++c) {
+      const uint64_t i1 = i0 + kSvcChunk < hi ? i0 + kSvcChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_to, i0, i1) || !csr_ok(in->sel_to, i0, i1)) return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_nm = lay.in(in->name_hash + i0, m * 8), a_tp = lay.in(in->target_port + i0, m * 4);
+      const size_t a_fl = lay.in(in->flags + i0, m), a_pt = lay.in(in->ports_to + i0 * NBG_SVC_SLOTS, m * NBG_SVC_SLOTS * 8);
+      const CsrDev lt = csr_in(lay, in->labels_to, i0, i1), at = csr_in(lay, in->ann_to, i0, i1), st = csr_in(lay, in->sel_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m), o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_svc_gen_batch b;
+      b.name_hash = (const uint64_t*)(sl.dev + a_nm); b.target_port = (const int32_t*)(sl.dev + a_tp);
+      b.flags = (const uint8_t*)(sl.dev + a_fl); b.ports_to = (const uint64_t*)(sl.dev + a_pt);
+      b.labels_to = csr_ptr(sl, lt); b.ann_to = csr_ptr(sl, at); b.sel_to = csr_ptr(sl, st);
+      const unsigned bases[3] = {lt.base, at.base, st.base};
+      CU(nbg_launch_diff_svc_gen(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+}
+
+int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts, uint64_t n, uint8_t* reason,
+                    uint64_t* bitmap) {
+  if (!ctx || !in || !consts) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->prefix_hash || !in->rewrite_hash || !in->host_hash || !in->flags || !in->spec_to) return NBG_E_INVAL;
+  if (!csr_ptrs_ok(in->hdr_from, n) || !csr_ptrs_ok(in->hdr_to, n)) return NBG_E_INVAL;
+  return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kVsChunk, ++c) {
+      const uint64_t i1 = i0 + kVsChunk < hi ? i0 + kVsChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->hdr_from, i0, i1) || !csr_ok(in->hdr_to, i0, i1)) return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_p = lay.in(in->prefix_hash + i0, m * 8), a_r = lay.in(in->rewrite_hash + i0, m * 8), a_h = lay.in(in->host_hash + i0, m * 8);
+      const size_t a_fl = lay.in(in->flags + i0, m), a_st = lay.in(in->spec_to + i0 * NBG_VS_SLOTS, m * NBG_VS_SLOTS * 8);
+      const CsrDev hf = csr_in(lay, in->hdr_from, i0, i1), ht = csr_in(lay, in->hdr_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m), o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_vs_gen_batch b;
+      b.prefix_hash = (const uint64_t*)(sl.dev + a_p); b.rewrite_hash = (const uint64_t*)(sl.dev + a_r);
+      b.host_hash = (const uint64_t*)(sl.dev + a_h); b.flags = (const uint8_t*)(sl.dev + a_fl);
+      b.spec_to = (const uint64_t*)(sl.dev + a_st); b.hdr_from = csr_ptr(sl, hf); b.hdr_to = csr_ptr(sl, ht);
+      const unsigned bases[2] = {hf.base, ht.base};
+      CU(nbg_launch_diff_vs_gen(&b, consts, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
       ctx->launches++;
       if (int r = slot_download(d, sl, lay)) return r;
     }

@@ -16,6 +16,7 @@
 // Nothing is reused between objects, so there is no shared-memory staging:
 // HBM -> registers -> vote.  No tensor cores: there is no contraction here.
 #include "common.cuh"
+#include "../hash.h"
 
 namespace nbg {
 
@@ -328,6 +329,117 @@ diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned
   store_results(base, n, lane, reason, update, reason_out, bitmap_half);
 }
 
+// ------------------------------- desired Service / VirtualService made on the device
+// Same votes as tiles_differ, but the desired vector of every lane is synthesised from a few
+// per-notebook words and constants instead of being loaded (generateService NBCTL:525-552,
+// generateVirtualService NBCTL:558-658; slot layout = csrc/host/pack.cpp).
+struct SvcGenConsts { unsigned long long port_name, proto_tcp, sel_key; };
+
+__global__ void __launch_bounds__(128)
+diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
+                    unsigned lt_base, unsigned at_base, unsigned st_base,
+                    uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  constexpr int VEC = NBG_SVC_SLOTS / 2;               // 8 lanes per object
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const uint4* pt = reinterpret_cast<const uint4*>(in.ports_to) + base * VEC;
+  const unsigned long long limit = (n - base) * VEC;
+  unsigned port_bits = 0;
+#pragma unroll
+  for (int r = 0; r < VEC; ++r) {
+    const unsigned idx = r * 32 + lane, part = lane & 7u;
+    const unsigned long long obj = base + (idx >> 3);
+    unsigned d = 0;
+    if (idx < limit) {
+      unsigned long long a = 0, b = 0;                 // desired slots 2*part, 2*part+1
+      if (part == 0) { a = k.port_name; b = k.proto_tcp; }                    // Name, Protocol
+      else if (part == 1) { b = 80ull; }                                      // AppProtocol nil; Port 80, NodePort 0
+      else if (part == 2) { a = (unsigned long long)(unsigned)__ldg(in.target_port + obj); }   // TargetPort Int
+      else if (part == 6) { a = 1ull; }                                       // one port, no overflow
+      const uint4 want = make_uint4((unsigned)a, (unsigned)(a >> 32), (unsigned)b, (unsigned)(b >> 32));
+      d = diff4(want, ld_stream(pt + idx));
+    }
+    const unsigned ballot = __ballot_sync(FULL, d != 0);
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+      if ((ballot >> (g * 8)) & 0xFFu) port_bits |= 1u << (r * 4 + g);
+  }
+  unsigned reason = 0;
+  if (i < n) {
+    const unsigned fl = __ldg(in.flags + i);
+    // desired has no labels and no annotations: any live entry with a non-empty value differs
+    for (unsigned t = __ldg(in.labels_to.off + i) - lt_base, e = __ldg(in.labels_to.off + i + 1) - lt_base; t < e; ++t)
+      if (ld_kv(in.labels_to.ent + t).val != 0ull) reason |= NBG_SVC_LABELS;
+    for (unsigned t = __ldg(in.ann_to.off + i) - at_base, e = __ldg(in.ann_to.off + i + 1) - at_base; t < e; ++t)
+      if (ld_kv(in.ann_to.ent + t).val != 0ull) reason |= NBG_SVC_ANNOTATIONS;
+    // desired selector = {"statefulset": name}, non-nil
+    const unsigned s0 = __ldg(in.sel_to.off + i) - st_base, s1 = __ldg(in.sel_to.off + i + 1) - st_base;
+    bool sel_ne = (fl & NBG_F_TO_SEL_NIL) != 0 || (s1 - s0) != 1u;
+    if (!sel_ne) {
+      const nbg_kv e = ld_kv(in.sel_to.ent + s0);
+      sel_ne = e.key != k.sel_key || e.val != __ldg(reinterpret_cast<const unsigned long long*>(in.name_hash) + i);
+    }
+    if (sel_ne) reason |= NBG_SVC_SELECTOR;
+    if ((port_bits >> lane) & 1u) reason |= NBG_SVC_PORTS;
+  }
+  store_results(base, n, lane, reason, (reason & NBG_SVC_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
+__global__ void __launch_bounds__(128)
+diff_vs_gen_kernel(nbg_vs_gen_batch in, nbg_vs_gen_consts k, unsigned long long n, unsigned hf_base, unsigned ht_base,
+                   uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  constexpr int VEC = NBG_VS_SLOTS / 2;                // 4 lanes per object
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const uint4* pt = reinterpret_cast<const uint4*>(in.spec_to) + base * VEC;
+  const unsigned long long limit = (n - base) * VEC;
+  const unsigned long long* prefix = reinterpret_cast<const unsigned long long*>(in.prefix_hash);
+  const unsigned long long* rewrite = reinterpret_cast<const unsigned long long*>(in.rewrite_hash);
+  const unsigned long long* host = reinterpret_cast<const unsigned long long*>(in.host_hash);
+  unsigned spec_bits = 0;
+#pragma unroll
+  for (int r = 0; r < VEC; ++r) {
+    const unsigned idx = r * 32 + lane, part = lane & 3u;
+    const unsigned long long obj = base + (idx >> 2);
+    unsigned d = 0;
+    if (idx < limit) {
+      unsigned long long a, b;
+      if (part == 0) { a = k.istio_host_hash; b = k.gateway_hash; }            // hosts[0], gateways[0]
+      else if (part == 1) { a = __ldg(prefix + obj); b = __ldg(rewrite + obj); } // match prefix, rewrite uri
+      else if (part == 2) { a = __ldg(host + obj); b = 80ull; }                // destination host, port number
+      else { a = 1ull; b = k.residual; }                                       // number is an int64; shape digest
+      const uint4 want = make_uint4((unsigned)a, (unsigned)(a >> 32), (unsigned)b, (unsigned)(b >> 32));
+      d = diff4(want, ld_stream(pt + idx));
+    }
+    const unsigned ballot = __ballot_sync(FULL, d != 0);
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+      if ((ballot >> (g * 4)) & 0xFu) spec_bits |= 1u << (r * 8 + g);
+  }
+  unsigned reason = 0;
+  bool update = false;
+  if (i < n) {
+    const unsigned fl = __ldg(in.flags + i);
+    if (fl & NBG_F_TO_SPEC_MISS) {                     // from.spec always exists here
+      reason = NBG_VS_TO_MISSING; update = true;
+    } else {
+      bool differs = (spec_bits >> lane) & 1u;
+      differs |= map_not_deep_equal(in.hdr_from.ent, __ldg(in.hdr_from.off + i) - hf_base,
+                                    __ldg(in.hdr_from.off + i + 1) - hf_base, false,
+                                    in.hdr_to.ent, __ldg(in.hdr_to.off + i) - ht_base,
+                                    __ldg(in.hdr_to.off + i + 1) - ht_base, (fl & NBG_F_TO_HDR_NIL) != 0);
+      if (differs) { reason = NBG_VS_SPEC_DIFFERS; update = true; }
+    }
+  }
+  store_results(base, n, lane, reason, update, reason_out, bitmap_half);
+}
+
 // ------------------------------------------------ ODH comparator family
 // One object pair per lane; both tests are short loops over small CSR vectors.
 __global__ void __launch_bounds__(128)
@@ -392,6 +504,27 @@ extern "C" cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch* in
   nbg::diff_sts_sparse_kernel<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
       reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_diff_svc_gen(const nbg_svc_gen_batch* in, unsigned long long n, const unsigned* bases /*3*/,
+                                               uint8_t* reason, uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  nbg::SvcGenConsts k;
+  k.port_name = nbg_hash_bytes("http-notebook", 13);   // NBCTL:541
+  k.proto_tcp = nbg_hash_bytes("TCP", 3);              // NBCTL:544
+  k.sel_key = nbg_hash_bytes("statefulset", 11);       // NBCTL:537
+  const unsigned block = 128;
+  nbg::diff_svc_gen_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+      *in, k, n, bases[0], bases[1], bases[2], reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+extern "C" cudaError_t nbg_launch_diff_vs_gen(const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts, unsigned long long n,
+                                              const unsigned* bases /*2*/, uint8_t* reason, uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const unsigned block = 128;
+  nbg::diff_vs_gen_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+      *in, *consts, n, bases[0], bases[1], reason, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
 

@@ -137,6 +137,14 @@ void SvcBatch::add(const GVal& from, const GVal& to) {
   labels_from.add(path(from, {"metadata", "labels"})); labels_to.add(path(to, {"metadata", "labels"}));
   ann_from.add(path(from, {"metadata", "annotations"})); ann_to.add(path(to, {"metadata", "annotations"}));
   sel_from.add(sf); sel_to.add(st);
+  // generateService's inputs, read back from the desired object it built
+  name_hash.push_back(hash_str(path(from, {"metadata", "name"}).s));
+  {
+    const GVal& fp = path(from, {"spec", "ports"});
+    int32_t tp = 8888;
+    if (fp.kind == GVal::List && !fp.items.empty()) tp = (int32_t)path(fp.items[0], {"targetPort", "IntVal"}).i;
+    target_port.push_back(tp);
+  }
   ++n;
 }
 void SvcBatch::append(const SvcBatch& o) {
@@ -144,6 +152,7 @@ void SvcBatch::append(const SvcBatch& o) {
   labels_from.append(o.labels_from); labels_to.append(o.labels_to);
   ann_from.append(o.ann_from); ann_to.append(o.ann_to);
   sel_from.append(o.sel_from); sel_to.append(o.sel_to);
+  extend(name_hash, o.name_hash); extend(target_port, o.target_port);
   n += o.n;
 }
 nbg_svc_batch SvcBatch::view() const {
@@ -152,6 +161,14 @@ nbg_svc_batch SvcBatch::view() const {
   b.labels_from = labels_from.view(); b.labels_to = labels_to.view();
   b.ann_from = ann_from.view(); b.ann_to = ann_to.view();
   b.sel_from = sel_from.view(); b.sel_to = sel_to.view();
+  return b;
+}
+
+nbg_svc_gen_batch SvcBatch::view_gen() const {
+  nbg_svc_gen_batch b;
+  b.name_hash = name_hash.data(); b.target_port = target_port.data();
+  b.flags = flags.data(); b.ports_to = ports_to.data();
+  b.labels_to = labels_to.view(); b.ann_to = ann_to.view(); b.sel_to = sel_to.view();
   return b;
 }
 
@@ -166,17 +183,28 @@ void VsBatch::add(const GVal& from, const GVal& to) {
                             (fnil ? NBG_F_FROM_HDR_NIL : 0) | (tnil ? NBG_F_TO_HDR_NIL : 0)));
   extend(hdr_from.ent, hf); hdr_from.off.push_back((uint32_t)hdr_from.ent.size());
   extend(hdr_to.ent, ht); hdr_to.off.push_back((uint32_t)hdr_to.ent.size());
+  prefix_hash.push_back(spec_from[n * NBG_VS_SLOTS + 2]);
+  rewrite_hash.push_back(spec_from[n * NBG_VS_SLOTS + 3]);
+  host_hash.push_back(spec_from[n * NBG_VS_SLOTS + 4]);
   ++n;
 }
 void VsBatch::append(const VsBatch& o) {
   extend(flags, o.flags); extend(spec_from, o.spec_from); extend(spec_to, o.spec_to);
   hdr_from.append(o.hdr_from); hdr_to.append(o.hdr_to);
+  extend(prefix_hash, o.prefix_hash); extend(rewrite_hash, o.rewrite_hash); extend(host_hash, o.host_hash);
   n += o.n;
 }
 nbg_vs_batch VsBatch::view() const {
   nbg_vs_batch b;
   b.flags = flags.data(); b.spec_from = spec_from.data(); b.spec_to = spec_to.data();
   b.hdr_from = hdr_from.view(); b.hdr_to = hdr_to.view();
+  return b;
+}
+
+nbg_vs_gen_batch VsBatch::view_gen() const {
+  nbg_vs_gen_batch b;
+  b.prefix_hash = prefix_hash.data(); b.rewrite_hash = rewrite_hash.data(); b.host_hash = host_hash.data();
+  b.hdr_from = hdr_from.view(); b.flags = flags.data(); b.spec_to = spec_to.data(); b.hdr_to = hdr_to.view();
   return b;
 }
 

@@ -57,19 +57,26 @@ struct SvcBatch {
   std::vector<uint8_t> flags;
   std::vector<uint64_t> ports_from, ports_to;
   KvCsr labels_from, labels_to, ann_from, ann_to, sel_from, sel_to;
+  // the few Notebook fields generateService depends on (nbg_svc_gen_batch)
+  std::vector<uint64_t> name_hash;
+  std::vector<int32_t> target_port;
   uint64_t n = 0;
   void add(const GVal& from, const GVal& to);
   void append(const SvcBatch& o);
   nbg_svc_batch view() const;
+  nbg_svc_gen_batch view_gen() const;
 };
 struct VsBatch {
   std::vector<uint8_t> flags;
   std::vector<uint64_t> spec_from, spec_to;
   KvCsr hdr_from, hdr_to;
+  // the per-notebook words of generateVirtualService (nbg_vs_gen_batch)
+  std::vector<uint64_t> prefix_hash, rewrite_hash, host_hash;
   uint64_t n = 0;
   void add(const GVal& from, const GVal& to);
   void append(const VsBatch& o);
   nbg_vs_batch view() const;
+  nbg_vs_gen_batch view_gen() const;
 };
 
 // Pairs for the ODH comparator family (nbg_generic_batch).

@@ -276,6 +276,35 @@ NBH_API uint64_t nbh_svc_view(const nbh_svc* b, nbg_svc_batch* out) {
   *out = b->b.view();
   return b->b.n;
 }
+NBH_API uint64_t nbh_svc_view_gen(const nbh_svc* b, nbg_svc_gen_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view_gen();
+  return b->b.n;
+}
+NBH_API uint64_t nbh_vs_view_gen(const nbh_vs* b, nbg_vs_gen_batch* out) {
+  if (!b || !out) return 0;
+  *out = b->b.view_gen();
+  return b->b.n;
+}
+// The notebook-independent words of a generated VirtualService for this environment.
+NBH_API int nbh_vs_gen_consts(const nbh_env* env, nbg_vs_gen_consts* out) {
+  if (!out) return -1;
+  GVal nb = GVal::strct(), meta = GVal::strct();
+  meta.set("name", GVal::str("x"));
+  meta.set("namespace", GVal::str("y"));
+  nb.set("metadata", std::move(meta));
+  GVal vs;
+  std::string err;
+  if (!generate_virtualservice(nb, to_env(env), &vs, &err)) return -1;
+  uint64_t slots[NBG_VS_SLOTS];
+  std::vector<nbg_kv> hdr;
+  bool hdr_nil;
+  if (!pack_vs_spec(vs, slots, &hdr, &hdr_nil)) return -1;
+  out->istio_host_hash = slots[0];
+  out->gateway_hash = slots[1];
+  out->residual = slots[7];
+  return 0;
+}
 NBH_API nbh_vs* nbh_vs_new(void) { return new nbh_vs(); }
 NBH_API void nbh_vs_free(nbh_vs* b) { delete b; }
 NBH_API int nbh_vs_add(nbh_vs* b, const nbh_obj* from, const nbh_obj* to) {

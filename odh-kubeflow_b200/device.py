@@ -27,7 +27,7 @@ class DeviceBatch:
     @classmethod
     def from_host(cls, batch, device=0, tile=1):
         self = cls()
-        self.device, self.kind = device, type(batch).__name__
+        self.device, self.kind = device, getattr(batch, "kind", type(batch).__name__)
         self.mode = getattr(batch, "mode", 0)
         arrays = batch.arrays()
         n0 = len(batch)
@@ -90,6 +90,18 @@ class DeviceBatch:
                 setattr(s, side, ps)
             for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
                 setattr(s, f, self._kv(f))
+        elif k == "svc_gen":
+            s = N.nbg_svc_gen_batch()
+            s.name_hash, s.target_port = self._p("name_hash", C.c_uint64), self._p("target_port", C.c_int32)
+            s.flags, s.ports_to = self._p("flags", C.c_uint8), self._p("ports_to", C.c_uint64)
+            for f in ("labels_to", "ann_to", "sel_to"):
+                setattr(s, f, self._kv(f))
+        elif k == "vs_gen":
+            s = N.nbg_vs_gen_batch()
+            s.prefix_hash, s.rewrite_hash, s.host_hash = (self._p("prefix_hash", C.c_uint64), self._p("rewrite_hash", C.c_uint64),
+                                                          self._p("host_hash", C.c_uint64))
+            s.flags, s.spec_to = self._p("flags", C.c_uint8), self._p("spec_to", C.c_uint64)
+            s.hdr_from, s.hdr_to = self._kv("hdr_from"), self._kv("hdr_to")
         elif k == "GenBatch":
             s = N.nbg_generic_batch()
             for f in ("labels_a", "labels_b", "spec_a", "spec_b"):
@@ -132,6 +144,14 @@ class DeviceBatch:
             p = N.nbg_cull_params(now[0], now[1], cull_idle_min, check_period_min, mode)
             rc = lib.nbg_cull_device(ctx.handle, 0, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
                                      C.c_void_p(stream))
+        elif self.kind == "svc_gen":
+            rc = lib.nbg_diff_svc_gen_device(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
+        elif self.kind == "vs_gen":
+            from . import host as _host
+            if not hasattr(self, "_consts"):
+                self._consts = _host.vs_gen_consts()
+            rc = lib.nbg_diff_vs_gen_device(ctx.handle, 0, C.byref(self._struct), C.byref(self._consts), self.n, o[0], o[1],
+                                            C.c_void_p(stream))
         elif self.kind == "GenBatch":
             rc = lib.nbg_diff_generic_device(ctx.handle, 0, C.byref(self._struct), self.n, self.mode, o[0], o[1], C.c_void_p(stream))
         elif self.kind == "RestartBatch":

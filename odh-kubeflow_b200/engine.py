@@ -97,6 +97,20 @@ class Context:
                                           bitmap.ctypes.data_as(C.c_void_p)), "nbg_diff_generic")
         return reason, bitmap
 
+    def diff_svc_gen(self, gen_view):
+        """CopyServiceFields against a desired Service generated on the device (batch = SvcBatch.gen())."""
+        return self._diff(self._lib.nbg_diff_svc_gen, gen_view)
+
+    def diff_vs_gen(self, gen_view, consts):
+        """CopyVirtualService against a desired VirtualService generated on the device (VsBatch.gen())."""
+        view = gen_view.view
+        n = gen_view.n
+        reason = np.zeros(n, dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        _check(self._lib.nbg_diff_vs_gen(self._h, C.byref(view), C.byref(consts), n, reason.ctypes.data_as(C.c_void_p),
+                                         bitmap.ctypes.data_as(C.c_void_p)), "nbg_diff_vs_gen")
+        return reason, bitmap
+
     def restart_block(self, batch):
         """Batched maybeRestartRunningNotebook (ODHWH:505-564) on a host.RestartBatch."""
         view = batch.view

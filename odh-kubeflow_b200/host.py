@@ -261,6 +261,14 @@ class StsSparseBatch:
 class SvcBatch(_Batch):
     _new, _free, _add, _view, _struct = "nbh_svc_new", "nbh_svc_free", "nbh_svc_add", "nbh_svc_view", N.nbg_svc_batch
 
+    def gen(self):
+        """Desired side generated on the device (valid when every `from` came from generate_service)."""
+        g = _GenView(self, "nbh_svc_view_gen", N.nbg_svc_gen_batch,
+                     [("name_hash", np.uint64, 1), ("target_port", np.int32, 1), ("flags", np.uint8, 1), ("ports_to", np.uint64, N.NBG_SVC_SLOTS)],
+                     ["labels_to", "ann_to", "sel_to"])
+        g.kind = "svc_gen"
+        return g
+
     def arrays(self):
         v, out = self.view, {}
         n = self.n
@@ -276,8 +284,57 @@ class SvcBatch(_Batch):
         return n + (n + 63) // 64 * 8
 
 
+class _GenView:
+    """Non-owning view of a Svc/Vs batch with the desired side reduced to the few Notebook words
+    generateService / generateVirtualService depend on (nbg_*_gen_batch)."""
+
+    def __init__(self, parent, fn, struct, names_fixed, names_kv):
+        self.parent, self._fn, self._struct, self._fixed, self._kv = parent, fn, struct, names_fixed, names_kv
+
+    @property
+    def view(self):
+        v = self._struct()
+        self.n = int(getattr(N.nbh(), self._fn)(self.parent._h, C.byref(v)))
+        return v
+
+    def __len__(self):
+        self.view
+        return self.n
+
+    def arrays(self):
+        v, out = self.view, {}
+        for name, dt, per in self._fixed:
+            out[name] = _arr(getattr(v, name), self.n * per, dt)
+        for name in self._kv:
+            _kv_arrays(getattr(v, name), self.n, name, out)
+        return out
+
+    @staticmethod
+    def output_bytes(n):
+        return n + (n + 63) // 64 * 8
+
+    def algorithmic_bytes(self):
+        n = len(self)
+        return sum(a.nbytes for a in self.arrays().values()) + self.output_bytes(n)
+
+
+def vs_gen_consts(env=None):
+    c = N.nbg_vs_gen_consts()
+    if N.nbh().nbh_vs_gen_consts(_env(env), C.byref(c)) != 0:
+        raise HostError("vs_gen_consts")
+    return c
+
+
 class VsBatch(_Batch):
     _new, _free, _add, _view, _struct = "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", N.nbg_vs_batch
+
+    def gen(self):
+        """Desired side generated on the device (valid when every `from` came from generate_virtualservice)."""
+        g = _GenView(self, "nbh_vs_view_gen", N.nbg_vs_gen_batch,
+                     [("prefix_hash", np.uint64, 1), ("rewrite_hash", np.uint64, 1), ("host_hash", np.uint64, 1),
+                      ("flags", np.uint8, 1), ("spec_to", np.uint64, N.NBG_VS_SLOTS)], ["hdr_from", "hdr_to"])
+        g.kind = "vs_gen"
+        return g
 
     def arrays(self):
         v, out = self.view, {}

@@ -388,3 +388,38 @@ def test_sparse_bad_runs_are_rejected(ctx):
     reason, bm = np.zeros(100, np.uint8), np.zeros(2, np.uint64)
     assert lib.nbg_diff_sts_sparse(ctx.handle, C.byref(view), 100, reason.ctypes.data_as(C.c_void_p),
                                    bm.ctypes.data_as(C.c_void_p)) == N.NBG_E_RANGE
+
+
+# ------------------------------------ desired Service / VirtualService made on the device
+@pytest.mark.parametrize("kind,n", [(host.FLEET_KUBEFLOW, 30001), (host.FLEET_ODH, 20000), (host.FLEET_ODH, 1), (host.FLEET_KUBEFLOW, 97)])
+def test_device_generated_desired_side_gives_the_same_answer(ctx, kind, n):
+    fleet = host.Fleet(kind, host.SEED_BASE + 15, n, max(n // 40, 1))
+    _, svc, vs = fleet.pack(sts=False)
+    want_svc, want_vs = ctx.diff_svc(svc), ctx.diff_vs(vs)
+    got_svc = ctx.diff_svc_gen(svc.gen())
+    got_vs = ctx.diff_vs_gen(vs.gen(), host.vs_gen_consts())
+    assert np.array_equal(got_svc[0], want_svc[0]) and np.array_equal(got_svc[1], want_svc[1])
+    assert np.array_equal(got_vs[0], want_vs[0]) and np.array_equal(got_vs[1], want_vs[1])
+    assert np.array_equal(got_svc[0], O.packed_diff_svc(svc)[0]) and np.array_equal(got_vs[0], O.packed_diff_vs(vs)[0])
+    if n > 1000:
+        assert svc.gen().algorithmic_bytes() < 0.62 * svc.algorithmic_bytes()
+        assert vs.gen().algorithmic_bytes() < 0.80 * vs.algorithmic_bytes()
+
+
+@pytest.mark.parametrize("name,frm,to,want", SVC_PAIRS, ids=[p[0][:60] for p in SVC_PAIRS])
+def test_derived_svc_device_generated(ctx, name, frm, to, want):
+    b = host.SvcBatch().add(host.Service(frm), host.Service(to))
+    reason, bm = ctx.diff_svc_gen(b.gen())
+    assert int(reason[0]) == want
+
+
+def test_vs_gen_respects_the_environment(ctx):
+    env = {"ISTIO_HOST": "nb.example.com", "ISTIO_GATEWAY": "istio-system/gw", "CLUSTER_DOMAIN": "corp.local"}
+    nb = host.Notebook(cases.BASE_NOTEBOOK)
+    desired = host.generate_virtualservice(nb, env)
+    other = host.generate_virtualservice(nb)                    # default env: hosts/gateways/host differ
+    b = host.VsBatch().add(desired, desired).add(desired, other)
+    r, _ = ctx.diff_vs_gen(b.gen(), host.vs_gen_consts(env))
+    assert r.tolist() == [0, 1]
+    r, _ = ctx.diff_vs_gen(b.gen(), host.vs_gen_consts())       # wrong constants for this desired side
+    assert r.tolist() == [1, 1] or r.tolist() == [1, 0]

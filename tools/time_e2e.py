@@ -10,15 +10,16 @@ ctx = pkg.Context([0]); lib = N.nbg()
 fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, per, max(200, per // 50))
 sts, svc, vs = fleet.pack(); cf = host.CullFleet(host.SEED_BASE + 5, per); cull = cf.pack()
 keep, views = [], {}
-for kind, b in (("sts", sts.sparse()), ("svc", svc), ("vs", vs), ("cull", cull)):
+vs_consts = host.vs_gen_consts()
+for kind, b in (("sts", sts.sparse()), ("svc", svc.gen()), ("vs", vs.gen()), ("cull", cull)):
     arr = b.arrays(); views[kind] = (bench.struct_over(N, kind, bench.pinned_copy(lib, arr, keep)), sum(a.nbytes for a in arr.values()))
 words = (per + 63) // 64
 out = bench.pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64), "a": np.zeros(per, np.uint32), "b2": np.zeros(words, np.uint64)}, keep)
 rp, bp, ap_, b2p = (out[k].ctypes.data_as(C.c_void_p) for k in ("r", "b", "a", "b2"))
 params = N.nbg_cull_params(cf.now_sec, cf.now_nsec, 1440, 1, 1)
 calls = {"sts": lambda: lib.nbg_diff_sts_sparse(ctx.handle, C.byref(views["sts"][0]), per, rp, bp),
-         "svc": lambda: lib.nbg_diff_svc(ctx.handle, C.byref(views["svc"][0]), per, rp, bp),
-         "vs": lambda: lib.nbg_diff_vs(ctx.handle, C.byref(views["vs"][0]), per, rp, bp),
+         "svc": lambda: lib.nbg_diff_svc_gen(ctx.handle, C.byref(views["svc"][0]), per, rp, bp),
+         "vs": lambda: lib.nbg_diff_vs_gen(ctx.handle, C.byref(views["vs"][0]), C.byref(vs_consts), per, rp, bp),
          "cull": lambda: lib.nbg_cull(ctx.handle, C.byref(views["cull"][0]), per, C.byref(params), rp, ap_, bp, b2p)}
 tot = 0
 for name, fn in calls.items():
