@@ -423,3 +423,26 @@ def test_vs_gen_respects_the_environment(ctx):
     assert r.tolist() == [0, 1]
     r, _ = ctx.diff_vs_gen(b.gen(), host.vs_gen_consts())       # wrong constants for this desired side
     assert r.tolist() == [1, 1] or r.tolist() == [1, 0]
+
+
+def test_one_context_over_two_devices():
+    """nbg_init(devices, 2): one process, the batch split in contiguous 64-aligned ranges, one per
+    device, results gathered by the call itself.  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    c2 = pkg.Context([0, 1])
+    try:
+        fleet = host.Fleet(host.FLEET_KUBEFLOW, 41, 50_001, 300)
+        sts, svc, vs = fleet.pack()
+        for got, want in ((c2.diff_sts(sts), O.packed_diff_sts(sts)), (c2.diff_sts_sparse(sts.sparse()), O.packed_diff_sts(sts)),
+                          (c2.diff_svc(svc), O.packed_diff_svc(svc)), (c2.diff_vs(vs), O.packed_diff_vs(vs)),
+                          (c2.diff_svc_gen(svc.gen()), O.packed_diff_svc(svc))):
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        cb = host.CullFleet(42, 300_001).pack()
+        got, want = c2.cull(cb, cases.NOW[0], cases.NOW[1], 1440, 1, 1), O.packed_cull(cb, cases.NOW, 1440, 1, 1)
+        for k in range(4):
+            assert np.array_equal(got[k], want[k])
+        assert c2.launch_count() >= 12
+    finally:
+        c2.close()
