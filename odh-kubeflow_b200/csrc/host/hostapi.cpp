@@ -68,7 +68,8 @@ void dump_json(const GVal& v, std::string* o) {
     case GVal::Bool: *o += v.i ? "true" : "false"; break;
     case GVal::Int: *o += std::to_string(v.i); break;
     case GVal::Float: { std::ostringstream os; os.precision(17); os << v.f; std::string t = os.str();
-                        if (t.find_first_of(".eEn") == std::string::npos) t += ".0"; *o += t; break; }
+                        if (t.find_first_of(".eEn") == std::string::npos) { t += ".0"; }
+                        *o += t; break; }
     case GVal::Str: esc(v.s); break;
     case GVal::List:
       o->push_back('[');
