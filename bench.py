@@ -365,13 +365,19 @@ def main():
     rp, bp, ap_, b2p = (out_arr[k].ctypes.data_as(C.c_void_p) for k in ("r", "b", "a", "b2"))
     params = N.nbg_cull_params(now[0], now[1], 1440, 1, N.CULL_RECONCILE)
 
+    o_sts = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64)}, keep)
+    o_svc = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64)}, keep)
+    o_vs = pinned_copy(lib, {"r": np.zeros(per, np.uint8), "b": np.zeros(words, np.uint64)}, keep)
+    step_out = N.nbg_step_outputs(o_sts["r"].ctypes.data, o_sts["b"].ctypes.data, o_svc["r"].ctypes.data, o_svc["b"].ctypes.data,
+                                  o_vs["r"].ctypes.data, o_vs["b"].ctypes.data, out_arr["r"].ctypes.data, out_arr["a"].ctypes.data,
+                                  out_arr["b"].ctypes.data, out_arr["b2"].ctypes.data)
+
     def e2e_step():
-        rc = lib.nbg_diff_sts_sparse(ctx.handle, C.byref(views["sts"][0]), per, rp, bp)
-        rc |= lib.nbg_diff_svc_gen(ctx.handle, C.byref(views["svc"][0]), per, rp, bp)
-        rc |= lib.nbg_diff_vs_gen(ctx.handle, C.byref(views["vs"][0]), C.byref(vs_consts), per, rp, bp)
-        rc |= lib.nbg_cull(ctx.handle, C.byref(views["cull"][0]), per, C.byref(params), rp, ap_, bp, b2p)
+        # the public one-call step: all four batches as one copy/compute pipeline
+        rc = lib.nbg_step(ctx.handle, C.byref(views["sts"][0]), C.byref(views["svc"][0]), C.byref(views["vs"][0]), C.byref(vs_consts),
+                          C.byref(views["cull"][0]), C.byref(params), per, C.byref(step_out))
         if rc:
-            raise SystemExit("bench: e2e call failed")
+            raise SystemExit("bench: e2e call failed (%d)" % rc)
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
         e2e_step()
@@ -389,6 +395,8 @@ def main():
     h2d = sum(v[1] for v in views.values())
     d2h = 3 * (per + words * 8) + (per + 4 * per + 2 * words * 8)  # 3x (reason + bitmap); action + argmax + 2 bitmaps
     assert np.array_equal(out_arr["r"], want["cull"][0]), "e2e cull action differs from the oracle"
+    assert np.array_equal(o_sts["r"], want["diff_sts"][0]) and np.array_equal(o_svc["r"], want["diff_svc"][0]) and \
+        np.array_equal(o_vs["r"], want["diff_vs"][0]), "e2e diff results differ from the oracle"
     for p in keep:
         lib.nbg_free_pinned(p)
 
@@ -417,14 +425,14 @@ def main():
                    "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI calls, max over ranks"},
+                "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI call nbg_step, max over ranks"},
         "gpu_launches": int(gpu_launches),
         "roofline": {"bound": "hbm", "kernel": "diff_sts_sparse_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
                      "frac": sts_gbs / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes["diff_sts"]), "avg_launch_ms": kernel_ms["diff_sts"]},
         "kernels": {name: {"avg_ms": kernel_ms[name], "GBps": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9,
                            "frac_of_peak": alg_bytes[name] / (kernel_ms[name] * 1e-3) / 1e9 / peak} for name, _ in batches},
-        "parity": "bit-exact vs packed oracle on all %d objects x 4 kernels (device path) and cull (e2e path); "
+        "parity": "bit-exact vs packed oracle on all %d objects x 4 kernels (device path and e2e path); "
                   "sparse-tile results == dense-tile results" % per,
         "dense_tiles": {"kernel": "diff_sts_kernel", "avg_ms": dense_ms, "GBps": dense_bytes / (dense_ms * 1e-3) / 1e9,
                         "frac_of_peak": dense_bytes / (dense_ms * 1e-3) / 1e9 / peak, "bytes_per_object": round(dense_bytes / per, 1),

@@ -290,6 +290,21 @@ int nbg_diff_svc_gen(nbg_ctx* ctx, const nbg_svc_gen_batch* in, uint64_t n, uint
 int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts, uint64_t n,
                     uint8_t* reason, uint64_t* bitmap);
 
+/* One reconcile step over n notebooks in ONE call: nbg_diff_sts_sparse + nbg_diff_svc_gen +
+ * nbg_diff_vs_gen + nbg_cull (any of the batches may be NULL to skip it), queued as a single
+ * copy/compute pipeline so the PCIe link stays busy across the four — the batch analogue of
+ * one pass of NotebookReconciler.Reconcile (NBCTL:152-240) and CullingReconciler.Reconcile
+ * (CULL:156-195) over the fleet.  Same outputs as the four separate calls. */
+typedef struct nbg_step_outputs {
+  uint8_t* sts_reason;  uint64_t* sts_bitmap;
+  uint8_t* svc_reason;  uint64_t* svc_bitmap;
+  uint8_t* vs_reason;   uint64_t* vs_bitmap;
+  uint8_t* action;      uint32_t* argmax;     uint64_t* cull_bitmap;  uint64_t* period_bitmap;
+} nbg_step_outputs;
+int nbg_step(nbg_ctx* ctx, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs,
+             const nbg_vs_gen_consts* vs_consts, const nbg_cull_batch* cull, const nbg_cull_params* params, uint64_t n,
+             const nbg_step_outputs* out);
+
 /* Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98) as a segmented
  * count: counts[ns] = number of StatefulSets j with ns_id[j] == ns whose pod-template label
  * "notebook-name" is present (flags[j] & 1) and equals the StatefulSet's name

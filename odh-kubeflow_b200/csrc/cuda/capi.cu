@@ -185,11 +185,25 @@ void device_range(uint64_t n, int ndev, int d, uint64_t* lo, uint64_t* hi) {
   *hi = w_hi * 64 < n ? w_hi * 64 : n;
 }
 
+// Set while nbg_step drives several entry points as ONE pipeline: they then only enqueue
+// (the caller holds the device locks and waits once at the end).
+thread_local bool tl_batched = false;
+
 template <class F>
 int for_each_device(nbg_ctx* ctx, uint64_t n, F&& run_range) {
   // Enqueue every device's chunks first, then wait: devices overlap.
   const int ndev = (int)ctx->devs.size();
   int rc = NBG_OK;
+  if (tl_batched) {
+    for (int d = 0; d < ndev && rc == NBG_OK; ++d) {
+      uint64_t lo, hi;
+      device_range(n, ndev, d, &lo, &hi);
+      if (hi <= lo) continue;
+      if (!cuda_ok(cudaSetDevice(ctx->devs[d]->id), "cudaSetDevice")) return NBG_E_CUDA;
+      rc = run_range(*ctx->devs[d], lo, hi);
+    }
+    return rc;
+  }
   std::vector<std::unique_lock<std::mutex>> locks;
   for (int d = 0; d < ndev; ++d) locks.emplace_back(ctx->devs[d]->mu);
   for (int d = 0; d < ndev && rc == NBG_OK; ++d) {
@@ -609,6 +623,36 @@ int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_c
   });
 }
 
+// One pipeline for a whole step: the four batches of the same n notebooks are queued back to
+// back, so the copy engine never drains between them, and the call waits once.
+int nbg_step(nbg_ctx* ctx, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs,
+             const nbg_vs_gen_consts* vs_consts, const nbg_cull_batch* cull, const nbg_cull_params* params, uint64_t n,
+             const nbg_step_outputs* out) {
+  if (!ctx || !out) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  const int ndev = (int)ctx->devs.size();
+  std::vector<std::unique_lock<std::mutex>> locks;
+  for (int d = 0; d < ndev; ++d) locks.emplace_back(ctx->devs[d]->mu);
+  int rc = NBG_OK;
+  tl_batched = true;
+  if (sts && rc == NBG_OK) rc = nbg_diff_sts_sparse(ctx, sts, n, out->sts_reason, out->sts_bitmap);
+  if (svc && rc == NBG_OK) rc = nbg_diff_svc_gen(ctx, svc, n, out->svc_reason, out->svc_bitmap);
+  if (vs && rc == NBG_OK) rc = nbg_diff_vs_gen(ctx, vs, vs_consts, n, out->vs_reason, out->vs_bitmap);
+  if (cull && rc == NBG_OK) rc = nbg_cull(ctx, cull, n, params, out->action, out->argmax, out->cull_bitmap, out->period_bitmap);
+  tl_batched = false;
+  for (int d = 0; d < ndev; ++d) {
+    cudaSetDevice(ctx->devs[d]->id);
+    if (!cuda_ok(cudaStreamSynchronize(ctx->devs[d]->s_run), "cudaStreamSynchronize") && rc == NBG_OK) rc = NBG_E_CUDA;
+    if (!cuda_ok(cudaStreamSynchronize(ctx->devs[d]->s_in), "cudaStreamSynchronize") && rc == NBG_OK) rc = NBG_E_CUDA;
+  }
+  if (rc == NBG_OK && sts) {
+    unsigned any = 0;
+    for (uint64_t i = 0; i < n; ++i) any |= out->sts_reason[i];
+    if (any & NBG_STS_NILREPLICAS) rc = NBG_E_NILREPLICAS;
+  }
+  return rc;
+}
+
 int nbg_count_running(nbg_ctx* ctx, const uint32_t* ns_id, const uint64_t* name_hash, const uint64_t* label_hash,
                       const uint8_t* flags, uint64_t m, uint32_t n_namespaces, uint32_t* counts) {
   if (!ctx) return NBG_E_INVAL;
@@ -1018,7 +1062,7 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
     }
     return NBG_OK;
   });
-  if (rc != NBG_OK) return rc;
+  if (rc != NBG_OK || tl_batched) return rc;
   unsigned any = 0;
   for (uint64_t i = 0; i < n; ++i) any |= reason[i];
   return (any & NBG_STS_NILREPLICAS) ? NBG_E_NILREPLICAS : NBG_OK;

@@ -446,3 +446,17 @@ def test_one_context_over_two_devices():
         assert c2.launch_count() >= 12
     finally:
         c2.close()
+
+
+@pytest.mark.parametrize("n", [1, 5000, 140_001])
+def test_step_in_one_call_equals_the_four_calls(ctx, n):
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 16, n, max(n // 40, 1))
+    sts, svc, vs = fleet.pack()
+    cf = host.CullFleet(host.SEED_BASE + 17, n)
+    cb = cf.pack()
+    r = ctx.step(sts.sparse(), svc.gen(), vs.gen(), host.vs_gen_consts(), cb, cf.now_sec, cf.now_nsec)
+    for k, want in (("sts", O.packed_diff_sts(sts)), ("svc", O.packed_diff_svc(svc)), ("vs", O.packed_diff_vs(vs))):
+        assert np.array_equal(r[k][0], want[0]) and np.array_equal(r[k][1], want[1]), k
+    want = O.packed_cull(cb, (cf.now_sec, cf.now_nsec), 1440, 1, 1)
+    for j in range(4):
+        assert np.array_equal(r["cull"][j], want[j])
