@@ -416,6 +416,13 @@ def main():
         return
 
     peak, peak_src = peaks()
+    traffic = None
+    try:  # per-launch DRAM bytes of the dominant kernel from the committed ncu capture (same launch size only)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))["diff_sts_sparse_kernel"]
+        if tr["objects_per_launch"] == per:
+            traffic = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+    except Exception:
+        pass
     sts_gbs = alg_bytes["diff_sts"] / (dom_ms * 1e-3) / 1e9
     iso_gbs = alg_bytes["diff_sts"] / (kernel_ms["diff_sts"] * 1e-3) / 1e9
     step_gbs = sum(alg_bytes.values()) / (ms_step * 1e-3) / 1e9 * (1.0 / world)
@@ -440,7 +447,7 @@ def main():
                 "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI call nbg_step, max over ranks"},
         "gpu_launches": int(gpu_launches),
         "roofline": {"bound": "hbm", "kernel": "diff_sts_sparse_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": sts_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": sts_gbs / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes["diff_sts"]), "avg_launch_ms": dom_ms,
                      "note": "timed inside the timed region on its own stream" + ("" if args.no_overlap else
                              ", while the three small kernels run concurrently on side streams and share HBM with it"),
