@@ -155,6 +155,10 @@ uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i);   /* nbg_hash64(name
 /* Pack objects idx[0..m) (idx == NULL: the range [i0, i0+m)) with all host threads. */
 int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                    nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
+/* CPU seconds, summed over threads, that the LAST nbh_fleet_pack spent (a) synthesising the objects
+ * (Notebook -> generateStatefulSet/Service/VirtualService -> drifted live copies) and (b) packing
+ * them into the batch arrays.  Only (b) is work a real caller has; the bench reports both. */
+void nbh_fleet_pack_timing(double* make_cpu_s, double* pack_cpu_s);
 
 /* Indices i in [0,n) whose namespace maps to `shard` of `n_shards` (nbg_shard_of), ascending.
  * Returns the count; writes at most cap of them (call with out=NULL to size). */

@@ -209,6 +209,77 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
 //   old != updated                          -> the user already restarts the pod (:548-551)
 //   old == updated == mutated               -> nothing changes                   (:554-557)
 //   old == updated != mutated               -> BLOCK: keep the updated spec      (:559-563)
+// Three sparse tiles a, b, c per object: which objects have b != a, which have c != a.  Same
+// scheme as sparse_tiles_differ, with a's run loaded ONCE and compared against both others; a side
+// whose mask already differs from a's is decided without its values being read.
+#ifndef NBG_RB_GROUP
+#define NBG_RB_GROUP 2
+#endif
+__device__ __forceinline__ void sparse_tiles_differ3(const nbg_podsparse& a, const nbg_podsparse& b, const nbg_podsparse& c,
+                                                     unsigned long long i, bool live, unsigned cnt, unsigned lane,
+                                                     unsigned a_base, unsigned b_base, unsigned c_base,
+                                                     unsigned& ab_bits, unsigned& ac_bits) {
+  constexpr unsigned G = NBG_RB_GROUP;
+  unsigned va0 = 0, vb0 = 0, vc0 = 0, vecs_b = 0, vecs_c = 0;
+  bool b_ne = false, c_ne = false;
+  if (live) {
+    const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
+    const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
+    const unsigned long long* mc = reinterpret_cast<const unsigned long long*>(c.mask) + i * 3;
+    const unsigned long long a0 = __ldg(ma), a1 = __ldg(ma + 1), a2 = __ldg(ma + 2);
+    b_ne = (a0 != __ldg(mb)) | (a1 != __ldg(mb + 1)) | (a2 != __ldg(mb + 2));
+    c_ne = (a0 != __ldg(mc)) | (a1 != __ldg(mc + 1)) | (a2 != __ldg(mc + 2));
+    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = __ldg(a.off + i + 1) - a_base;
+    va0 = f0 >> 1;
+    vb0 = (__ldg(b.off + i) - b_base) >> 1;
+    vc0 = (__ldg(c.off + i) - c_base) >> 1;
+    vecs_b = b_ne ? 0u : (f1 - f0) >> 1;
+    vecs_c = c_ne ? 0u : (f1 - f0) >> 1;
+  }
+  ab_bits = __ballot_sync(FULL, b_ne);
+  ac_bits = __ballot_sync(FULL, c_ne);
+  const uint4* av = reinterpret_cast<const uint4*>(a.val);
+  const uint4* bv = reinterpret_cast<const uint4*>(b.val);
+  const uint4* cv = reinterpret_cast<const uint4*>(c.val);
+  for (unsigned o = 0; o < cnt; o += G) {
+    unsigned db[G], dc[G];
+    uint4 x[G], y[G], z[G];
+    unsigned more = 0;
+#pragma unroll
+    for (unsigned g = 0; g < G; ++g) {
+      const unsigned src = min(o + g, 31u);
+      const unsigned nb = __shfl_sync(FULL, vecs_b, src), nc = __shfl_sync(FULL, vecs_c, src);
+      const unsigned ao = __shfl_sync(FULL, va0, src), bo = __shfl_sync(FULL, vb0, src), co = __shfl_sync(FULL, vc0, src);
+      x[g] = make_uint4(0, 0, 0, 0);
+      if (lane < max(nb, nc)) x[g] = ld_stream(av + ao + lane);
+      y[g] = x[g]; z[g] = x[g];                          // a side that is not read compares equal
+      if (lane < nb) y[g] = ld_stream(bv + bo + lane);
+      if (lane < nc) z[g] = ld_stream(cv + co + lane);
+      more |= max(nb, nc) > 32u;
+    }
+#pragma unroll
+    for (unsigned g = 0; g < G; ++g) { db[g] = diff4(x[g], y[g]); dc[g] = diff4(x[g], z[g]); }
+    if (more) {                                          // warp-uniform; runs of 65..192 values
+#pragma unroll
+      for (unsigned g = 0; g < G; ++g) {
+        const unsigned src = min(o + g, 31u);
+        const unsigned nb = __shfl_sync(FULL, vecs_b, src), nc = __shfl_sync(FULL, vecs_c, src);
+        const unsigned ao = __shfl_sync(FULL, va0, src), bo = __shfl_sync(FULL, vb0, src), co = __shfl_sync(FULL, vc0, src);
+        for (unsigned k = lane + 32u; k < max(nb, nc); k += 32u) {
+          const uint4 xa = ld_stream(av + ao + k);
+          if (k < nb) db[g] |= diff4(xa, ld_stream(bv + bo + k));
+          if (k < nc) dc[g] |= diff4(xa, ld_stream(cv + co + k));
+        }
+      }
+    }
+#pragma unroll
+    for (unsigned g = 0; g < G; ++g) {
+      if (__any_sync(FULL, db[g] != 0)) ab_bits |= 1u << min(o + g, 31u);
+      if (__any_sync(FULL, dc[g] != 0)) ac_bits |= 1u << min(o + g, 31u);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(128)
 restart_block_kernel(nbg_restart_batch in, unsigned long long n, unsigned o_base, unsigned u_base, unsigned m_base,
                      uint8_t* __restrict__ decision_out, uint32_t* __restrict__ bitmap_half) {
@@ -219,9 +290,9 @@ restart_block_kernel(nbg_restart_batch in, unsigned long long n, unsigned o_base
   const unsigned long long i = base + lane;
   const unsigned cnt = (unsigned)min(32ull, n - base);
   const bool live = i < n;
+  unsigned upd_bits, mut_bits;
+  sparse_tiles_differ3(in.old_spec, in.updated_spec, in.mutated_spec, i, live, cnt, lane, o_base, u_base, m_base, upd_bits, mut_bits);
   const unsigned fl = live ? __ldg(in.flags + i) : 0u;
-  const unsigned upd_bits = sparse_tiles_differ(in.old_spec, in.updated_spec, i, live, cnt, lane, o_base, u_base);
-  const unsigned mut_bits = sparse_tiles_differ(in.old_spec, in.mutated_spec, i, live, cnt, lane, o_base, m_base);
   unsigned decision = 0;
   if (live && !(fl & (NBG_RB_CREATE | NBG_RB_STOPPED | NBG_RB_RESTARTING))) {
     if ((upd_bits >> lane) & 1u) decision = NBG_RB_EXTERNAL_CHANGE;

@@ -1,5 +1,6 @@
 // hostapi.cpp — C ABI of libnbgraft_host.so (include/nbgraft_host.h).
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <sstream>
@@ -548,9 +549,18 @@ NBH_API int nbh_fleet_objects(const nbh_fleet* f, const uint64_t* idx, uint64_t 
   return 0;
 }
 
+// CPU seconds (summed over threads) the last nbh_fleet_pack spent synthesising objects and packing them.
+static std::atomic<uint64_t> g_make_ns{0}, g_pack_ns{0};
+NBH_API void nbh_fleet_pack_timing(double* make_cpu_s, double* pack_cpu_s) {
+  if (make_cpu_s) *make_cpu_s = g_make_ns.load() * 1e-9;
+  if (pack_cpu_s) *pack_cpu_s = g_pack_ns.load() * 1e-9;
+}
+
 NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                            nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
   if (!f) return -1;
+  g_make_ns = 0; g_pack_ns = 0;
+  typedef std::chrono::steady_clock clk;
   const uint64_t kBlock = 2048;
   const uint64_t nblocks = (m + kBlock - 1) / kBlock;
   std::vector<StsBatch> ps(sts ? nblocks : 0);
@@ -559,12 +569,19 @@ NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0,
   parallel_blocks(nblocks, [&](uint64_t blk) {
     const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
     Pair p;
+    uint64_t make_ns = 0, pack_ns = 0;
     for (uint64_t k = lo; k < hi; ++k) {
+      const auto t0 = clk::now();
       fleet_make(f->f, idx ? idx[k] : i0 + k, &p);
+      const auto t1 = clk::now();
       if (sts) ps[blk].add(p.sts_from, p.sts_to);
       if (svc) pv[blk].add(p.svc_from, p.svc_to);
       if (vs) pw[blk].add(p.vs_from, p.vs_to);
+      const auto t2 = clk::now();
+      make_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count();
+      pack_ns += std::chrono::duration_cast<std::chrono::nanoseconds>(t2 - t1).count();
     }
+    g_make_ns += make_ns; g_pack_ns += pack_ns;
   });
   if (sts) {
     nbh_sts* o = new nbh_sts();

@@ -511,6 +511,13 @@ class Fleet:
         return (StsBatch(a.value) if sts else None, SvcBatch(b.value) if svc else None,
                 VsBatch(c.value) if vs else None)
 
+    @staticmethod
+    def pack_timing():
+        """(synthesis, packing) CPU seconds, summed over threads, of the last pack() call."""
+        a, b = C.c_double(), C.c_double()
+        N.nbh().nbh_fleet_pack_timing(C.byref(a), C.byref(b))
+        return a.value, b.value
+
     def shard_indices(self, n_shards, shard=None):
         """Bucket object indices by nbg_shard_of(hash(namespace)) — SURVEY.md 8(e).
         Returns the list of all shards' index arrays, or one shard's array."""
