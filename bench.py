@@ -270,39 +270,25 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- value: inputs resident in HBM.  The four kernels of a step are independent; the three small,
-    # latency-bound ones run on side streams so that they overlap the bandwidth-bound StatefulSet kernel.
+    # ---- value: inputs resident in HBM.  One step = one nbg_step_device call: the StatefulSet kernel on the
+    # main stream, the three small latency-bound kernels beside it on the context's side streams (the
+    # library forks and joins them with events).  --no-overlap: four launches on one stream instead.
     main = torch.cuda.current_stream()
-    side = [torch.cuda.Stream() for _ in range(3)] if not args.no_overlap else None
-    fork = torch.cuda.Event()
-    joins = [torch.cuda.Event() for _ in range(3)]
+    resident = dev.ResidentStep(ctx, d_sts, d_svc, d_vs, d_cull, now=now, cull_idle_min=1440, check_period_min=1,
+                                mode=N.CULL_RECONCILE, time_sts=True) if not args.no_overlap else None
+    serial_ev = []
 
-    def launch_on(name, b, stream):
-        if name == "cull":
-            return b.run(ctx, now=now, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE, stream=stream.cuda_stream)
-        return b.run(ctx, stream=stream.cuda_stream)
-
-    def step(ev_pair=None):
-        if side is None:
-            for k, (name, b) in enumerate(batches):
-                if k == 0 and ev_pair:
-                    ev_pair[0].record(main)
-                launch_on(name, b, main)
-                if k == 0 and ev_pair:
-                    ev_pair[1].record(main)
+    def step(timed=False):
+        if resident is not None:
+            resident.run()
             return
-        fork.record(main)
-        for k, (name, b) in enumerate(batches[1:]):
-            side[k].wait_event(fork)
-            launch_on(name, b, side[k])
-            joins[k].record(side[k])
-        if ev_pair:
-            ev_pair[0].record(main)
-        launch_on(batches[0][0], batches[0][1], main)          # the dominant kernel, on the main stream
-        if ev_pair:
-            ev_pair[1].record(main)
-        for k in range(3):
-            main.wait_event(joins[k])
+        for k, (name, b) in enumerate(batches):
+            if k == 0 and timed:
+                serial_ev.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+                serial_ev[-1][0].record(main)
+            launch(name, b)
+            if k == 0 and timed:
+                serial_ev[-1][1].record(main)
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -310,13 +296,17 @@ def main():
     sampler = ClockSampler(local)
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = ctx.launch_count()
-    dom_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    if resident is not None:
+        resident.sts_ms()                                  # drop the warm-up pairs
+        resident.reserve(args.steps)
+        torch.cuda.synchronize()
     start.record()
     for s in range(args.steps):
-        step(dom_ev[s])
+        step(timed=True)
     stop.record()
     barrier()
-    dom_ms = statistics.mean(a.elapsed_time(b) for a, b in dom_ev)   # dominant kernel, in the timed region, on its stream
+    # dominant kernel, inside the timed region, on its stream (events recorded by the library around that launch)
+    dom_ms = statistics.mean(resident.sts_ms() if resident is not None else [a.elapsed_time(b) for a, b in serial_ev])
     gpu_launches = ctx.launch_count() - launches0
     ms_total = start.elapsed_time(stop)
     # per-kernel durations: a separate, serialised pass (same launches, one stream, CUDA events around each)
@@ -438,8 +428,8 @@ def main():
                    "desired_side": "StatefulSet: packed from generateStatefulSet's output; Service and VirtualService: generated on the device "
                                    "from name/port/prefix/rewrite/host words (same answer as shipping generateService/VirtualService outputs)",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
-                   "streams": "one stream" if args.no_overlap else "StatefulSet kernel on the main stream, the three small kernels on side streams "
-                              "(fork/join events every step); per-kernel times are from a separate serialised pass",
+                   "streams": "one stream" if args.no_overlap else "one nbg_step_device call per step: StatefulSet kernel on the main stream, the three small kernels "
+                              "on the context's side streams (event fork/join inside the library); per-kernel times are from a separate serialised pass",
                    "serial_sum_ms": sum(kernel_ms.values()),
                    "l2": "inputs (%.1f GB per GPU) exceed L2; no flush needed" % (sum(alg_bytes.values()) / 1e9),
                    "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},

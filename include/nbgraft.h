@@ -304,6 +304,17 @@ typedef struct nbg_step_outputs {
 int nbg_step(nbg_ctx* ctx, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs,
              const nbg_vs_gen_consts* vs_consts, const nbg_cull_batch* cull, const nbg_cull_params* params, uint64_t n,
              const nbg_step_outputs* out);
+/* The same step over batches that already live in device memory, asynchronous and ordered on
+ * `stream` like a single launch (work queued on `stream` afterwards sees every output).  Inside,
+ * the StatefulSet kernel runs on `stream` and the three small, latency-bound predicates run
+ * beside it on streams the context owns (event fork/join, no host synchronisation).  Any batch may
+ * be NULL.  Nil replicas are reported in sts_reason (NBG_STS_NILREPLICAS), not in the status.
+ * ev_sts_start / ev_sts_stop: optional cudaEvent_t handles recorded on `stream` right around the
+ * StatefulSet kernel, for callers that want that launch's duration inside a running step. */
+int nbg_step_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc,
+                    const nbg_vs_gen_batch* vs, const nbg_vs_gen_consts* vs_consts, const nbg_cull_batch* cull,
+                    const nbg_cull_params* params, uint64_t n, const nbg_step_outputs* out, void* stream,
+                    void* ev_sts_start /*nullable*/, void* ev_sts_stop /*nullable*/);
 
 /* Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98) as a segmented
  * count: counts[ns] = number of StatefulSets j with ns_id[j] == ns whose pod-template label

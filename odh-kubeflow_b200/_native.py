@@ -153,7 +153,7 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
-    "nbg_step", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
+    "nbg_step", "nbg_step_device", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
     "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
@@ -222,6 +222,10 @@ def _bind_nbg(lib):
                              C.POINTER(nbg_vs_gen_consts), C.POINTER(nbg_cull_batch), C.POINTER(nbg_cull_params), C.c_uint64,
                              C.POINTER(nbg_step_outputs)]
     lib.nbg_step.restype = C.c_int
+    lib.nbg_step_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_sts_sparse_batch), C.POINTER(nbg_svc_gen_batch),
+                                    C.POINTER(nbg_vs_gen_batch), C.POINTER(nbg_vs_gen_consts), C.POINTER(nbg_cull_batch),
+                                    C.POINTER(nbg_cull_params), C.c_uint64, C.POINTER(nbg_step_outputs), _vp, _vp, _vp]
+    lib.nbg_step_device.restype = C.c_int
     lib.nbg_count_running.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp]
     lib.nbg_count_running.restype = C.c_int
     lib.nbg_count_running_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]

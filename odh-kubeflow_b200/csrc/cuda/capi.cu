@@ -73,6 +73,8 @@ struct Slot {
 struct Dev {
   int id = 0;
   cudaStream_t s_in = nullptr, s_run = nullptr;
+  cudaStream_t s_side[3] = {nullptr, nullptr, nullptr};   // nbg_step_device: the three small predicates
+  cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
   Slot slot[2];
   char* scratch = nullptr;   // grow-only kernel scratch (the owner join's hash table)
   size_t scratch_cap = 0;
@@ -296,6 +298,10 @@ int nbg_init(const int* devices, int n_devices, nbg_ctx** out) {
     for (int s = 0; ok && s < 2; ++s)
       ok = cuda_ok(cudaEventCreateWithFlags(&d->slot[s].in_done, cudaEventDisableTiming), "cudaEventCreate") &&
            cuda_ok(cudaEventCreateWithFlags(&d->slot[s].free_ev, cudaEventDisableTiming), "cudaEventCreate");
+    ok = ok && cuda_ok(cudaEventCreateWithFlags(&d->ev_fork, cudaEventDisableTiming), "cudaEventCreate");
+    for (int k = 0; ok && k < 3; ++k)
+      ok = cuda_ok(cudaStreamCreateWithFlags(&d->s_side[k], cudaStreamNonBlocking), "cudaStreamCreate") &&
+           cuda_ok(cudaEventCreateWithFlags(&d->ev_join[k], cudaEventDisableTiming), "cudaEventCreate");
     if (!ok) { nbg_destroy(ctx); return NBG_E_CUDA; }
   }
   *out = ctx;
@@ -314,6 +320,11 @@ void nbg_destroy(nbg_ctx* ctx) {
       if (sl.in_done) cudaEventDestroy(sl.in_done);
       if (sl.free_ev) cudaEventDestroy(sl.free_ev);
     }
+    for (int k = 0; k < 3; ++k) {
+      if (d->s_side[k]) { cudaStreamSynchronize(d->s_side[k]); cudaStreamDestroy(d->s_side[k]); }
+      if (d->ev_join[k]) cudaEventDestroy(d->ev_join[k]);
+    }
+    if (d->ev_fork) cudaEventDestroy(d->ev_fork);
     if (d->s_in) cudaStreamDestroy(d->s_in);
     if (d->s_run) cudaStreamDestroy(d->s_run);
     delete d;
@@ -651,6 +662,53 @@ int nbg_step(nbg_ctx* ctx, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_ba
     if (any & NBG_STS_NILREPLICAS) rc = NBG_E_NILREPLICAS;
   }
   return rc;
+}
+
+// One step over RESIDENT batches.  The StatefulSet kernel streams ~0.8 KB per notebook and owns
+// `stream`; the three small predicates are latency-bound on their own, so they go to the context's
+// side streams, forked from and joined back into `stream` with events: to the caller the whole step
+// is ordered on `stream` like a single launch.
+int nbg_step_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc,
+                    const nbg_vs_gen_batch* vs, const nbg_vs_gen_consts* vs_consts, const nbg_cull_batch* cull,
+                    const nbg_cull_params* p, uint64_t n, const nbg_step_outputs* out, void* stream,
+                    void* ev_sts_start, void* ev_sts_stop) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!out || (vs && !vs_consts) || (cull && !p)) return NBG_E_INVAL;
+  if (n == 0 || !(sts || svc || vs || cull)) return NBG_OK;
+  if ((sts && (!out->sts_reason || !out->sts_bitmap)) || (svc && (!out->svc_reason || !out->svc_bitmap)) ||
+      (vs && (!out->vs_reason || !out->vs_bitmap)) ||
+      (cull && (!out->action || !out->argmax || !out->cull_bitmap || !out->period_bitmap)))
+    return NBG_E_INVAL;
+  if (cull) {
+    if (p->now_nsec < 0 || p->now_nsec > 999999999 || (p->mode != NBG_CULL_PREDICATES && p->mode != NBG_CULL_RECONCILE))
+      return NBG_E_INVAL;
+    if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
+        p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
+      return NBG_E_INVAL;
+  }
+  Dev& d = *ctx->devs[device];
+  std::unique_lock<std::mutex> lock(d.mu);             // the fork/join events are per device: one enqueue at a time
+  CU(cudaSetDevice(d.id));
+  cudaStream_t s = (cudaStream_t)stream;
+  const unsigned zero[6] = {0, 0, 0, 0, 0, 0};
+  CU(cudaEventRecord(d.ev_fork, s));
+  if (sts) {                                           // first in line for the SMs: it is the long one
+    if (ev_sts_start) CU(cudaEventRecord((cudaEvent_t)ev_sts_start, s));
+    CU(nbg_launch_diff_sts_sparse(sts, n, zero, out->sts_reason, out->sts_bitmap, s));
+    if (ev_sts_stop) CU(cudaEventRecord((cudaEvent_t)ev_sts_stop, s));
+    ctx->launches++;
+  }
+  for (int k = 0; k < 3; ++k) {
+    if (!(k == 0 ? (const void*)svc : k == 1 ? (const void*)vs : (const void*)cull)) continue;
+    CU(cudaStreamWaitEvent(d.s_side[k], d.ev_fork, 0));
+    if (k == 0) CU(nbg_launch_diff_svc_gen(svc, n, zero, out->svc_reason, out->svc_bitmap, d.s_side[k]));
+    if (k == 1) CU(nbg_launch_diff_vs_gen(vs, vs_consts, n, zero, out->vs_reason, out->vs_bitmap, d.s_side[k]));
+    if (k == 2) CU(nbg_launch_cull(cull, n, p, 0, 0, out->action, out->argmax, out->cull_bitmap, out->period_bitmap, d.s_side[k]));
+    CU(cudaEventRecord(d.ev_join[k], d.s_side[k]));
+    CU(cudaStreamWaitEvent(s, d.ev_join[k], 0));
+    ctx->launches++;
+  }
+  return NBG_OK;
 }
 
 int nbg_count_running(nbg_ctx* ctx, const uint32_t* ns_id, const uint64_t* name_hash, const uint64_t* label_hash,

@@ -165,3 +165,73 @@ class DeviceBatch:
             from .engine import NbgError
             raise NbgError(rc, "nbg_*_device")
         return self.outs
+
+
+class ResidentStep:
+    """One reconcile step over resident batches (nbg_step_device): `sts`, `svc`, `vs`, `cull` are
+    DeviceBatches of kinds StsSparseBatch, svc_gen, vs_gen and CullBatch over the same notebooks (any
+    may be None).  run() enqueues the step on `stream` (default: torch's current stream); results land
+    in each batch's own output tensors.  The argument structs are built once, so run() is one C call."""
+
+    def __init__(self, ctx, sts=None, svc=None, vs=None, cull=None, now=None, cull_idle_min=1440, check_period_min=1,
+                 mode=N.CULL_RECONCILE, time_sts=False):
+        given = [b for b in (sts, svc, vs, cull) if b is not None]
+        assert given and len({b.n for b in given}) == 1 and len({b.device for b in given}) == 1
+        assert sts is None or sts.kind == "StsSparseBatch"
+        assert svc is None or svc.kind == "svc_gen"
+        assert vs is None or vs.kind == "vs_gen"
+        assert cull is None or cull.kind == "CullBatch"
+        self.ctx, self.n, self.device = ctx, given[0].n, given[0].device
+        self.batches = {"sts": sts, "svc": svc, "vs": vs, "cull": cull}
+        self._consts = host.vs_gen_consts() if vs is not None else None
+        now = now or (host.NOW_SEC, host.NOW_NSEC)
+        self._p = N.nbg_cull_params(now[0], now[1], cull_idle_min, check_period_min, mode)
+        o = N.nbg_step_outputs()
+        if sts is not None:
+            o.sts_reason, o.sts_bitmap = sts.outs[0].data_ptr(), sts.outs[1].data_ptr()
+        if svc is not None:
+            o.svc_reason, o.svc_bitmap = svc.outs[0].data_ptr(), svc.outs[1].data_ptr()
+        if vs is not None:
+            o.vs_reason, o.vs_bitmap = vs.outs[0].data_ptr(), vs.outs[1].data_ptr()
+        if cull is not None:
+            o.action, o.argmax, o.cull_bitmap, o.period_bitmap = (t.data_ptr() for t in cull.outs)
+        self._o = o
+        self._refs = [C.byref(b._struct) if b is not None else None for b in (sts, svc, vs, cull)]
+        self.launches = len(given)
+        # optional timing of the StatefulSet kernel inside the running step: pairs of events the
+        # library records around that launch, read back with sts_ms()
+        self._pairs, self._free = [], []
+        self._time_sts = time_sts and sts is not None
+
+    def reserve(self, k):
+        """Create k event pairs ahead of time, so that timed run() calls create nothing."""
+        with torch.cuda.device(self.device):
+            while len(self._free) < k:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); b.record()                     # materialise the handles (the library re-records them)
+                self._free.append((a, b))
+
+    def run(self, stream=None):
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        e0 = e1 = None
+        if self._time_sts:
+            if not self._free:
+                self.reserve(1)
+            a, b = self._free.pop()
+            self._pairs.append((a, b))
+            e0, e1 = C.c_void_p(a.cuda_event), C.c_void_p(b.cuda_event)
+        rc = N.nbg().nbg_step_device(self.ctx.handle, 0, self._refs[0], self._refs[1], self._refs[2],
+                                     C.byref(self._consts) if self._consts is not None else None, self._refs[3],
+                                     C.byref(self._p), self.n, C.byref(self._o), C.c_void_p(stream), e0, e1)
+        if rc != N.NBG_OK:
+            from .engine import NbgError
+            raise NbgError(rc, "nbg_step_device")
+        return {k: b.outs for k, b in self.batches.items() if b is not None}
+
+    def sts_ms(self):
+        """Durations (ms) of the StatefulSet launches of the timed run() calls so far; call after a sync."""
+        out = [a.elapsed_time(b) for a, b in self._pairs]
+        self._free.extend(self._pairs)
+        self._pairs = []
+        return out

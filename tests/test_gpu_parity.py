@@ -460,3 +460,75 @@ def test_step_in_one_call_equals_the_four_calls(ctx, n):
     want = O.packed_cull(cb, (cf.now_sec, cf.now_nsec), 1440, 1, 1)
     for j in range(4):
         assert np.array_equal(r["cull"][j], want[j])
+
+
+def _masked(t, n):
+    """bits of a device bitmap (bits past n belong to nobody)"""
+    words = (n + 63) // 64
+    return pkg.engine.bitmap_to_bools(t.view(np.uint64)[:words], n)
+
+
+@pytest.mark.parametrize("n", [1, 33, 4097, 150_001])
+def test_resident_step_equals_the_stand_alone_kernels(ctx, n):
+    """nbg_step_device: StatefulSet kernel on the caller's stream, the three small predicates on the
+    context's side streams, joined back — same outputs as the four device calls, for every subset."""
+    import torch
+    devmod = importlib.import_module("odh-kubeflow_b200.device")
+    fleet = host.Fleet(host.FLEET_ODH if n % 2 else host.FLEET_KUBEFLOW, host.SEED_BASE + 18, n, max(n // 40, 1))
+    sts, svc, vs = fleet.pack()
+    cf = host.CullFleet(host.SEED_BASE + 19, n)
+    cb = cf.pack()
+    now = (cf.now_sec, cf.now_nsec)
+    d = dict(zip(("sts", "svc", "vs", "cull"), (devmod.DeviceBatch.from_host(b) for b in (sts.sparse(), svc.gen(), vs.gen(), cb))))
+    side = torch.cuda.Stream()
+    for mode, subset, stream in ((1, ("sts", "svc", "vs", "cull"), None), (0, ("sts", "svc", "vs", "cull"), side), (1, ("sts",), None),
+                                 (1, ("svc", "cull"), side), (1, ("vs",), None)):
+        want = {"sts": O.packed_diff_sts(sts), "svc": O.packed_diff_svc(svc), "vs": O.packed_diff_vs(vs),
+                "cull": O.packed_cull(cb, now, 1440, 1, mode)}
+        for b in d.values():
+            for o in b.outs:
+                o.fill_(0xA5)
+        torch.cuda.synchronize()
+        step = devmod.ResidentStep(ctx, now=now, mode=mode, time_sts=(stream is None), **{k: d[k] for k in subset})
+        before = ctx.launch_count()
+        for _ in range(3):                                   # back to back: the fork/join events are reused
+            if stream is None:
+                step.run()
+            else:
+                step.run(stream=stream.cuda_stream)
+        # ordered on the caller's stream like one launch: a copy queued behind it sees the results
+        if stream is None:
+            got_dev = {k: [o.clone() for o in d[k].outs] for k in d}
+        else:
+            with torch.cuda.stream(stream):
+                got_dev = {k: [o.clone() for o in d[k].outs] for k in d}
+        torch.cuda.synchronize()
+        assert ctx.launch_count() == before + 3 * len(subset)
+        if stream is None and "sts" in subset:
+            ms = step.sts_ms()
+            assert len(ms) == 3 and all(t > 0 for t in ms)
+        for k in d:
+            got = [o.cpu().numpy() for o in got_dev[k]]
+            if k not in subset:
+                assert all((g == 0xA5).all() for g in got), k          # untouched
+                continue
+            assert np.array_equal(got[0], want[k][0]), k
+            if k != "cull":
+                assert np.array_equal(_masked(got[1], n), _masked(want[k][1], n)), k
+            else:
+                assert np.array_equal(got[1].view(np.uint32), want[k][1])
+                assert np.array_equal(_masked(got[2], n), _masked(want[k][2], n))
+                assert np.array_equal(_masked(got[3], n), _masked(want[k][3], n))
+
+
+def test_step_device_rejects_bad_arguments(ctx):
+    lib = N.nbg()
+    out = N.nbg_step_outputs()
+    cb = N.nbg_cull_batch()
+    p = N.nbg_cull_params(0, 0, 1440, 1, 1)
+    none = [None] * 5
+    assert lib.nbg_step_device(ctx.handle, 0, *none, None, 10, None, None, None, None) == N.NBG_E_INVAL
+    assert lib.nbg_step_device(ctx.handle, 0, *none, None, 10, C.byref(out), None, None, None) == N.NBG_OK   # nothing to do
+    assert lib.nbg_step_device(ctx.handle, 0, None, None, None, None, C.byref(cb), None, 10, C.byref(out), None, None, None) == N.NBG_E_INVAL
+    assert lib.nbg_step_device(ctx.handle, 0, None, None, None, None, C.byref(cb), C.byref(p), 10, C.byref(out), None, None, None) == N.NBG_E_INVAL
+    assert lib.nbg_step_device(ctx.handle, 7, *none, None, 10, C.byref(out), None, None, None) != N.NBG_OK
