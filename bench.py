@@ -499,6 +499,38 @@ def other_configs(pkg, dev, ctx, torch, peak):
     sts, svc, _ = f2.pack(vs=False)
     ms = timed(dev.DeviceBatch.from_host(sts)) + timed(dev.DeviceBatch.from_host(svc))
     out["config2_10k_sts_svc"] = {"objects_per_s": 10_000 / (ms * 1e-3), "ms": ms, "roofline": "n/a (36 MB, launch-bound; L2 flushed between launches)"}
+    # the same 10 k notebooks as a whole step (sparse tiles, device-generated Service), issued directly and
+    # replayed from a captured CUDA graph: this size is launch-bound, so the graph is what helps
+    cf2 = host.CullFleet(host.SEED_BASE + 2, 10_000)
+    small = [dev.DeviceBatch.from_host(b) for b in (sts.sparse(), svc.gen(), cf2.pack())]
+    rstep = dev.ResidentStep(ctx, sts=small[0], svc=small[1], cull=small[2], now=(cf2.now_sec, cf2.now_nsec))
+    cap_stream = torch.cuda.Stream()
+    with torch.cuda.stream(cap_stream):
+        for _ in range(3):
+            rstep.run()
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=cap_stream):
+        rstep.run()
+    per_step = {}
+    for name, fn in (("direct", rstep.run), ("graph_replay", graph.replay)):
+        runs = []
+        with torch.cuda.stream(cap_stream):
+            for _ in range(7):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(50):
+                    fn()
+                b.record()
+                torch.cuda.synchronize()
+                runs.append(a.elapsed_time(b) / 50)
+        per_step[name] = statistics.median(runs)
+    out["config2_10k_step_back_to_back"] = {
+        "direct_us_per_step": per_step["direct"] * 1e3, "graph_replay_us_per_step": per_step["graph_replay"] * 1e3,
+        "objects_per_s_graph": 10_000 / (per_step["graph_replay"] * 1e-3),
+        "note": "StatefulSet + Service + culler over 10 k notebooks, 50 steps back to back, inputs L2-resident (no flush): "
+                "launch-bound; nbg_step_device captured once into a CUDA graph and replayed"}
+    del small, rstep, graph
     cf = host.CullFleet(host.SEED_BASE + 3, 250_000)
     cb = cf.pack()
     d = dev.DeviceBatch.from_host(cb)

@@ -532,3 +532,35 @@ def test_step_device_rejects_bad_arguments(ctx):
     assert lib.nbg_step_device(ctx.handle, 0, None, None, None, None, C.byref(cb), None, 10, C.byref(out), None, None, None) == N.NBG_E_INVAL
     assert lib.nbg_step_device(ctx.handle, 0, None, None, None, None, C.byref(cb), C.byref(p), 10, C.byref(out), None, None, None) == N.NBG_E_INVAL
     assert lib.nbg_step_device(ctx.handle, 7, *none, None, 10, C.byref(out), None, None, None) != N.NBG_OK
+
+
+def test_resident_step_replays_from_a_cuda_graph(ctx):
+    """nbg_step_device allocates nothing and synchronises nothing, so a caller can capture it (side
+    streams included) once and replay the step: same outputs as the direct call."""
+    import torch
+    devmod = importlib.import_module("odh-kubeflow_b200.device")
+    n = 10_000
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 2, n, 200)
+    sts, svc, vs = fleet.pack()
+    cf = host.CullFleet(host.SEED_BASE + 3, n)
+    cb = cf.pack()
+    d = [devmod.DeviceBatch.from_host(b) for b in (sts.sparse(), svc.gen(), vs.gen(), cb)]
+    step = devmod.ResidentStep(ctx, *d, now=(cf.now_sec, cf.now_nsec))
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        step.run()
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=s):
+        step.run()
+    for b in d:
+        for o in b.outs:
+            o.fill_(0xA5)
+    torch.cuda.synchronize()
+    graph.replay()
+    graph.replay()
+    torch.cuda.synchronize()
+    want = (O.packed_diff_sts(sts), O.packed_diff_svc(svc), O.packed_diff_vs(vs), O.packed_cull(cb, (cf.now_sec, cf.now_nsec), 1440, 1, 1))
+    for b, w in zip(d, want):
+        assert np.array_equal(b.outs[0].cpu().numpy(), w[0])
+        assert np.array_equal(_masked(b.outs[-1].cpu().numpy(), n), _masked(w[len(b.outs) - 1], n))
