@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <string>
+#include <string_view>
 #include <utility>
 #include <vector>
 
@@ -66,12 +67,17 @@ struct GVal {
   }
 
   // ---- Map / Struct access (sorted by name)
-  const GVal* find(const std::string& name) const {
+  // (string_view: looking a field up by a literal name builds no temporary std::string)
+  const GVal* find(std::string_view name) const {
     auto it = std::lower_bound(kv.begin(), kv.end(), name,
-                               [](const std::pair<std::string, GVal>& e, const std::string& n) { return e.first < n; });
-    return (it != kv.end() && it->first == name) ? &it->second : nullptr;
+                               [](const std::pair<std::string, GVal>& e, std::string_view n) { return std::string_view(e.first) < n; });
+    return (it != kv.end() && std::string_view(it->first) == name) ? &it->second : nullptr;
   }
-  GVal* find(const std::string& name) { return const_cast<GVal*>(static_cast<const GVal*>(this)->find(name)); }
+  GVal* find(std::string_view name) { return const_cast<GVal*>(static_cast<const GVal*>(this)->find(name)); }
+  const GVal* find(const std::string& name) const { return find(std::string_view(name)); }
+  GVal* find(const std::string& name) { return find(std::string_view(name)); }
+  const GVal* find(const char* name) const { return find(std::string_view(name)); }
+  GVal* find(const char* name) { return find(std::string_view(name)); }
   bool has(const std::string& name) const { return find(name) != nullptr; }
 
   // Insert or overwrite.  Struct fields holding a zero value are erased instead.
