@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--per-gpu", type=int, default=1_250_000, help="notebooks per GPU (10M / 8)")
     ap.add_argument("--cpu-sample", type=int, default=40_000, help="notebooks in the CPU baseline sample")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary configs (#2, #3, #4)")
+    ap.add_argument("--no-numa", action="store_true", help="multi-rank: do not bind each rank to the CPUs next to its GPU")
     ap.add_argument("--no-overlap", action="store_true", help="launch the four kernels of a step on one stream")
     return ap.parse_args()
 
@@ -210,6 +211,26 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def bind_near_gpu(torch, local):
+    """Multi-rank runs: keep this rank's threads (and so the pinned buffers it first-touches) on the CPUs
+    NVML reports as local to its GPU, so that eight ranks do not pull their H2D traffic across sockets.
+    Returns the CPU list, or None when the topology cannot be read (then nothing is changed)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        p = torch.cuda.get_device_properties(local)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)).encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 1) + 63) // 64)
+        cpus = [64 * i + bit for i, w in enumerate(words) for bit in range(64) if (w >> bit) & 1]
+        cpus = sorted(set(cpus) & os.sched_getaffinity(0))
+        if not cpus or len(cpus) == len(os.sched_getaffinity(0)):
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -230,6 +251,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    near = bind_near_gpu(torch, local) if (world > 1 and not args.no_numa) else None
     # host threads are shared by the ranks of this node
     if "NBH_THREADS" not in os.environ:
         os.environ["NBH_THREADS"] = str(max(1, (os.cpu_count() or 1) // world))
@@ -428,6 +450,7 @@ def main():
                    "desired_side": "StatefulSet: packed from generateStatefulSet's output; Service and VirtualService: generated on the device "
                                    "from name/port/prefix/rewrite/host words (same answer as shipping generateService/VirtualService outputs)",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
+                   "cpu_binding": ("rank 0 bound to the %d CPUs NVML lists next to its GPU" % len(near)) if near else "none",
                    "streams": "one stream" if args.no_overlap else "one nbg_step_device call per step: StatefulSet kernel on the main stream, the three small kernels "
                               "on the context's side streams (event fork/join inside the library); per-kernel times are from a separate serialised pass",
                    "serial_sum_ms": sum(kernel_ms.values()),
