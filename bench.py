@@ -438,7 +438,7 @@ def main():
         pass
     sts_gbs = alg_bytes["diff_sts"] / (dom_ms * 1e-3) / 1e9
     iso_gbs = alg_bytes["diff_sts"] / (kernel_ms["diff_sts"] * 1e-3) / 1e9
-    step_gbs = sum(alg_bytes.values()) / (ms_step * 1e-3) / 1e9 * (1.0 / world)
+    step_gbs = sum(alg_bytes.values()) / (ms_step * 1e-3) / 1e9          # this rank's bytes / max-over-ranks step time
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
