@@ -274,7 +274,34 @@ bool generate_virtualservice(const GVal& nb, const BuilderEnv& env, GVal* out, s
 }
 
 // --------------------------------------------------------------------- G4
-void odh_webhook_mutate(GVal* nb, const OdhInject& what) {
+// parseAndValidateAuthSidecarResources (ODHWH:124-172): defaults 100m / 64Mi, overridden by the four
+// auth-sidecar annotations (trimmed; empty = absent).  false where the Go function returns an error: a
+// value that does not parse or is negative, or a request above its limit.
+static bool auth_sidecar_resources(const GVal& nb, GVal* cpu_req, GVal* mem_req, GVal* cpu_lim, GVal* mem_lim) {
+  parse_quantity("100m", cpu_req); parse_quantity("64Mi", mem_req);
+  parse_quantity("100m", cpu_lim); parse_quantity("64Mi", mem_lim);
+  const GVal* meta = nb.find("metadata");
+  const GVal* ann = meta ? meta->find("annotations") : nullptr;
+  if (ann && ann->kind == GVal::Map) {
+    const std::pair<const char*, GVal*> keys[4] = {
+        {"notebooks.opendatahub.io/auth-sidecar-cpu-request", cpu_req},
+        {"notebooks.opendatahub.io/auth-sidecar-memory-request", mem_req},
+        {"notebooks.opendatahub.io/auth-sidecar-cpu-limit", cpu_lim},
+        {"notebooks.opendatahub.io/auth-sidecar-memory-limit", mem_lim}};
+    for (const auto& k : keys) {
+      std::string v = ann->get_str(k.first);
+      if (v.empty()) continue;
+      const size_t b = v.find_first_not_of(" \t\n\v\f\r"), e = v.find_last_not_of(" \t\n\v\f\r");
+      v = b == std::string::npos ? std::string() : v.substr(b, e - b + 1);      // strings.TrimSpace
+      GVal parsed;
+      if (!parse_quantity(v, &parsed) || quantity_sign(parsed) < 0) return false;
+      *k.second = std::move(parsed);
+    }
+  }
+  return quantity_cmp(*cpu_req, *cpu_lim) <= 0 && quantity_cmp(*mem_req, *mem_lim) <= 0;
+}
+
+bool odh_webhook_mutate(GVal* nb, const OdhInject& what) {
   // create every container we are going to reference BEFORE taking references:
   // inserting a field may move its siblings
   ensure_struct(*nb, "metadata");
@@ -371,10 +398,11 @@ void odh_webhook_mutate(GVal* nb, const OdhInject& what) {
       }
   }
   if (what.rbac_proxy) {                                   // InjectKubeRbacProxy ODHWH:177-326
-    auto q = [](const char* text) { GVal g; parse_quantity(text, &g); return g; };
+    GVal cpu_req, mem_req, cpu_lim, mem_lim;
+    if (!auth_sidecar_resources(*nb, &cpu_req, &mem_req, &cpu_lim, &mem_lim)) { nb->canon(); return false; }   // nothing injected
     GVal req = GVal::map(), lim = GVal::map();
-    req.set("cpu", q("100m")); req.set("memory", q("64Mi"));
-    lim.set("cpu", q("100m")); lim.set("memory", q("64Mi"));
+    req.set("cpu", std::move(cpu_req)); req.set("memory", std::move(mem_req));
+    lim.set("cpu", std::move(cpu_lim)); lim.set("memory", std::move(mem_lim));
     GVal res = GVal::strct();
     res.set("requests", std::move(req));
     res.set("limits", std::move(lim));
@@ -435,6 +463,7 @@ void odh_webhook_mutate(GVal* nb, const OdhInject& what) {
     pod.set("serviceAccountName", GVal::str(name));
   }
   nb->canon();
+  return true;
 }
 
 }  // namespace nbh

@@ -244,8 +244,7 @@ NBH_API int nbh_odh_mutate(nbh_obj* nb, int flags) {
   OdhInject inj;
   inj.lock = flags & 1; inj.ca_bundle = flags & 2; inj.runtime_images = flags & 4;
   inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16;
-  odh_webhook_mutate(&nb->v, inj);
-  return 0;
+  return odh_webhook_mutate(&nb->v, inj) ? 0 : 1;     // 1: kube-rbac-proxy injection refused (bad resource annotations)
 }
 
 // ------------------------------------------------------------------ batches

@@ -38,7 +38,9 @@ bool generate_virtualservice(const GVal& notebook, const BuilderEnv& env, GVal* 
 struct OdhInject {
   bool lock = false, ca_bundle = true, runtime_images = true, elyra_secret = true, rbac_proxy = true;
 };
-void odh_webhook_mutate(GVal* notebook, const OdhInject& what);
+// false when InjectKubeRbacProxy refuses the auth-sidecar resource annotations (the other injections
+// are still applied; no proxy container, volumes or service account are added — ODHWH:177-183)
+bool odh_webhook_mutate(GVal* notebook, const OdhInject& what);
 
 // ---- packing (pack.cpp) ---------------------------------------------------
 uint64_t hash_str(const std::string& s);

@@ -154,6 +154,37 @@ inline void quantity_number(const GVal& q, std::string* digits, int64_t* exponen
   *exponent = e;
 }
 
+// Quantity.Cmp(b): -1, 0, 1 by numeric value.
+inline int quantity_cmp(const GVal& a, const GVal& b) {
+  std::string da, db;
+  int64_t ea, eb;
+  quantity_number(a, &da, &ea);
+  quantity_number(b, &db, &eb);
+  const bool na = !da.empty() && da[0] == '-', nb = !db.empty() && db[0] == '-';
+  if (na) da.erase(0, 1);
+  if (nb) db.erase(0, 1);
+  const bool za = da == "0", zb = db == "0";
+  if (za || zb || na != nb) {
+    const int sa = za ? 0 : (na ? -1 : 1), sb = zb ? 0 : (nb ? -1 : 1);
+    return sa < sb ? -1 : sa > sb ? 1 : 0;
+  }
+  // same sign, both non-zero: compare magnitudes digits x 10^exponent
+  int mag;
+  const int64_t top_a = (int64_t)da.size() + ea, top_b = (int64_t)db.size() + eb;   // position of the leading digit
+  if (top_a != top_b) mag = top_a < top_b ? -1 : 1;
+  else {
+    const size_t n = da.size() > db.size() ? da.size() : db.size();
+    da.resize(n, '0'); db.resize(n, '0');
+    mag = da < db ? -1 : da > db ? 1 : 0;
+  }
+  return na ? -mag : mag;
+}
+inline int quantity_sign(const GVal& q) {
+  std::string d; int64_t e;
+  quantity_number(q, &d, &e);
+  return d == "0" ? 0 : (d[0] == '-' ? -1 : 1);
+}
+
 // ParseQuantity(str) -> GVal.  Returns false where the Go function returns an error.
 inline bool parse_quantity(const std::string& str, GVal* out) {
   using namespace qdetail;

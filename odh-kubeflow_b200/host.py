@@ -131,7 +131,11 @@ ODH_LOCK, ODH_CA_BUNDLE, ODH_RUNTIME_IMAGES, ODH_ELYRA_SECRET, ODH_RBAC_PROXY = 
 
 def odh_mutate(notebook, flags=2 | 4 | 8 | 16):
     """ODH mutating-webhook injections (ODHWH:105-114,177-326,666-781), in place."""
-    N.nbh().nbh_odh_mutate(notebook._h, flags)
+    rc = N.nbh().nbh_odh_mutate(notebook._h, flags)
+    if rc == 1:        # InjectKubeRbacProxy refused the auth-sidecar resource annotations: no proxy was injected
+        raise HostError("invalid kube-rbac-proxy resource configuration")
+    if rc != 0:
+        raise HostError("odh_mutate")
     return notebook
 
 

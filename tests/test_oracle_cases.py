@@ -330,3 +330,66 @@ def test_odh_webhook_shape():
     assert sorted(env_names) == sorted(["PIP_CERT", "REQUESTS_CA_BUNDLE", "SSL_CERT_FILE", "PIPELINES_SSL_SA_CERTS",
                                         "KF_PIPELINES_SSL_SA_CERTS", "GIT_SSL_CAINFO"])
     assert host.generate_statefulset(nb).to_python()["spec"]["replicas"] == 0
+
+
+def test_ref_kube_rbac_proxy_injection():
+    """notebook_webhook_test.go:339-417: what InjectKubeRbacProxy must leave in the Notebook — the shape
+    every config #4 object starts from (builders.cpp odh_webhook_mutate, flag 16)."""
+    g = GOLDEN["kube_rbac_proxy_injection"]
+    nb = host.Notebook(g["notebook"])
+    host.odh_mutate(nb, 16)
+    pod = nb.to_python()["spec"]["template"]["spec"]
+    e = g["expect"]
+    proxies = [c for c in pod["containers"] if c["name"] == e["container_name"]]
+    assert len(proxies) == 1 and len(pod["containers"]) == 2
+    c = proxies[0]
+    assert c["imagePullPolicy"] == e["imagePullPolicy"]
+    for side in ("requests", "limits"):
+        assert {k: _quantity_text(v) for k, v in c["resources"][side].items()} == e[side]      # .String() of each Quantity
+    assert [{"name": p["name"], "containerPort": p["containerPort"]} for p in c["ports"]] == e["ports"]
+    assert sorted(m["name"] for m in c["volumeMounts"]) == sorted(e["volumeMounts"])
+    assert sorted(v["name"] for v in pod["volumes"]) == sorted(e["volumes"])
+    assert pod["serviceAccountName"] == e["serviceAccountName"]
+    assert all(p in c for p in e["probes"])
+
+
+def test_ref_kube_rbac_proxy_custom_resources():
+    g = GOLDEN["kube_rbac_proxy_custom_resources"]
+    nb = host.Notebook(g["notebook"])
+    host.odh_mutate(nb, 16)
+    pod = nb.to_python()["spec"]["template"]["spec"]
+    e = g["expect"]
+    assert [c["name"] for c in pod["containers"]] == e["containers"]
+    c = pod["containers"][-1]
+    for side in ("requests", "limits"):
+        assert {k: _quantity_text(v) for k, v in c["resources"][side].items()} == e[side]
+    assert sorted(v["name"] for v in pod["volumes"]) == sorted(e["volumes"])
+
+
+def test_ref_kube_rbac_proxy_validation_failure():
+    g = GOLDEN["kube_rbac_proxy_validation_failure"]
+    nb = host.Notebook(g["notebook"])
+    before = nb.digest()
+    with pytest.raises(host.HostError, match=g["expect"]["error"]):
+        host.odh_mutate(nb, 16)
+    assert nb.digest() == before                                           # left exactly as it was
+    pod = nb.to_python()["spec"]["template"]["spec"]
+    assert [c["name"] for c in pod["containers"]] == g["expect"]["containers"]
+    assert pod.get("serviceAccountName", "") == g["expect"]["serviceAccountName"] and "volumes" not in pod
+
+
+@pytest.mark.parametrize("ann,ok", [({"cpu-request": " 50m "}, True), ({"cpu-request": "-1"}, False), ({"memory-limit": "sixty"}, False),
+                                    ({"memory-request": "65Mi"}, False), ({"memory-request": "64Mi"}, True),
+                                    ({"cpu-request": "0.1"}, True), ({"cpu-request": "0.11"}, False), ({"cpu-limit": ""}, True)])
+def test_auth_sidecar_resource_rules(ann, ok):
+    """parseAndValidateAuthSidecarResources (notebook_webhook.go:124-172): trimmed, empty = absent, no negatives,
+    request <= limit by VALUE (0.1 == 100m), defaults 100m / 64Mi fill what is missing."""
+    nb = host.Notebook({"metadata": {"name": "n", "namespace": "d", "annotations":
+                                      {"notebooks.opendatahub.io/auth-sidecar-" + k: v for k, v in ann.items()}},
+                        "spec": {"template": {"spec": {"containers": [{"name": "n", "image": "i"}]}}}})
+    if ok:
+        host.odh_mutate(nb, 16)
+        assert len(nb.to_python()["spec"]["template"]["spec"]["containers"]) == 2
+    else:
+        with pytest.raises(host.HostError):
+            host.odh_mutate(nb, 16)
