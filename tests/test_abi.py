@@ -77,7 +77,9 @@ def test_no_device_is_an_error_not_a_fallback():
 
 def test_product_never_references_the_oracle():
     bad = []
-    for dirpath, _, files in os.walk(os.path.join(ROOT, "odh-kubeflow_b200")):
+    walk = list(os.walk(os.path.join(ROOT, "odh-kubeflow_b200"))) + list(os.walk(os.path.join(ROOT, "tools"))) + \
+        list(os.walk(os.path.join(ROOT, "include")))
+    for dirpath, _, files in walk:
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", "Makefile")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()

@@ -1,7 +1,7 @@
 """One small launch of every SURVEY 8(f) kernel (for ncu captures)."""
 import importlib, json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 import numpy as np, torch
 pkg = importlib.import_module("odh-kubeflow_b200"); host, N = pkg.host, pkg._native
 dev = importlib.import_module("odh-kubeflow_b200.device")

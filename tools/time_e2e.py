@@ -1,7 +1,7 @@
 """Time the host-buffer C-ABI step (pinned buffers) — for tuning the copy pipeline."""
 import ctypes as C, importlib, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 import numpy as np
 import bench
 pkg = importlib.import_module("odh-kubeflow_b200"); host, N = pkg.host, pkg._native

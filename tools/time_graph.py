@@ -2,7 +2,7 @@
 usage: python tools/time_graph.py"""
 import importlib, os, statistics, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 import numpy as np, torch
 pkg = importlib.import_module("odh-kubeflow_b200")
 dev = importlib.import_module("odh-kubeflow_b200.device")

@@ -2,11 +2,9 @@
 usage: NBGRAFT_LIB=build/variants/libnbgraft_X.so python tools/time_kernel.py cull 1250000"""
 import importlib, os, statistics, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import numpy as np, torch
 pkg = importlib.import_module("odh-kubeflow_b200")
 dev = importlib.import_module("odh-kubeflow_b200.device")
-import oracle as O
 host = pkg.host
 kind, n = sys.argv[1], int(sys.argv[2])
 ctx = pkg.Context([0])
@@ -26,9 +24,8 @@ for mode in ((1, 0) if kind == "cull" else (None,)):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record(); outs = d.run(ctx, **kw); e.record(); torch.cuda.synchronize()
         if it >= 3: ms.append(s.elapsed_time(e))
-    want = O.packed_cull(b, kw["now"], 1440, 1, mode, threads=8)[0] if kind == "cull" else getattr(O, "packed_diff_" + kind)(b, threads=8)[0]
-    ok = np.array_equal(outs[0].cpu().numpy(), want)
+    digest = int(outs[0].cpu().numpy().astype(np.uint64).sum())      # to compare builds with each other; parity is tests' job
     med = statistics.median(ms)
-    print("%s %s mode=%s n=%d  median %.1f us  min %.1f us  %.0f GB/s  parity=%s" % (
+    print("%s %s mode=%s n=%d  median %.1f us  min %.1f us  %.0f GB/s  result-sum=%d" % (
         os.path.basename(os.environ.get("NBGRAFT_LIB", "default")), kind, mode, n, med * 1e3, min(ms) * 1e3,
-        d.algorithmic_bytes / (med * 1e-3) / 1e9, ok))
+        d.algorithmic_bytes / (med * 1e-3) / 1e9, digest))
