@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define NBG_ABI_VERSION 1
+#define NBG_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 #define NBG_OK              0
@@ -58,10 +58,13 @@ extern "C" {
  * sorted by key; duplicate keys cannot occur (they are Go map keys). */
 typedef struct nbg_kv { uint64_t key; uint64_t val; } nbg_kv;
 
-/* CSR of per-object string maps (labels, annotations, selector, headers):
- * object i owns ent[off[i] .. off[i+1]).  off has n+1 elements, off[0] may be
- * non-zero (a slice of a larger batch). */
-typedef struct nbg_kvmap { const uint32_t* off; const nbg_kv* ent; } nbg_kvmap;
+/* Per-object string maps (labels, annotations, selector, headers).
+ *   end == NULL (CSR): object i owns ent[off[i] .. off[i+1]).  off has n+1 elements, off[0] may
+ *     be non-zero (a slice of a larger batch).  The only form the host-buffer entry points take.
+ *   end != NULL (spans; *_device entry points only): object i owns ent[off[i] .. end[i]).  off and
+ *     end have n elements; runs may lie anywhere in `ent`, in any order, with gaps between them —
+ *     the layout of a resident fleet whose objects are replaced in place (nbg_store_*). */
+typedef struct nbg_kvmap { const uint32_t* off; const nbg_kv* ent; const uint32_t* end; } nbg_kvmap;
 
 /* ---- reason bits ------------------------------------------------------- */
 /* StatefulSet (COMMON:107-134 + caller pre-step NBCTL:188-194) */
@@ -120,6 +123,8 @@ typedef struct nbg_podsparse {
   const uint64_t* mask;   /* n * 3                                   */
   const uint32_t* off;    /* n + 1, in u64 units; off[0] may be != 0 */
   const uint64_t* val;    /* off[n] - off[0] values                  */
+  const uint32_t* end;    /* NULL (CSR) or n run ends, as in nbg_kvmap: run i = val[off[i] .. end[i]),
+                             every off[i] even (runs 16-byte aligned); *_device entry points only */
 } nbg_podsparse;
 typedef struct nbg_sts_sparse_batch {
   const int32_t*  replicas_from;
@@ -171,6 +176,9 @@ typedef struct nbg_cull_batch {
   const int64_t*  chk_sec; /* n: last_activity_check_timestamp annotation                */
   const uint32_t* chk_nsf; /* n                                                          */
   const uint8_t*  nb_flags;/* n                                                          */
+  const uint32_t* k_end;   /* NULL (CSR) or n: kernels of notebook i are k_off[i]..k_end[i) — spans, as in
+                              nbg_kvmap; *_device entry points only                       */
+  const uint32_t* t_end;   /* same for terminals                                          */
 } nbg_cull_batch;
 
 typedef struct nbg_cull_params {

@@ -36,7 +36,7 @@ class nbg_kv(C.Structure):
 
 
 class nbg_kvmap(C.Structure):
-    _fields_ = [("off", u32p), ("ent", C.POINTER(nbg_kv))]
+    _fields_ = [("off", u32p), ("ent", C.POINTER(nbg_kv)), ("end", u32p)]
 
 
 class nbg_sts_batch(C.Structure):
@@ -47,7 +47,7 @@ class nbg_sts_batch(C.Structure):
 
 
 class nbg_podsparse(C.Structure):
-    _fields_ = [("mask", u64p), ("off", u32p), ("val", u64p)]
+    _fields_ = [("mask", u64p), ("off", u32p), ("val", u64p), ("end", u32p)]
 
 
 class nbg_sts_sparse_batch(C.Structure):
@@ -119,7 +119,7 @@ class nbg_cull_batch(C.Structure):
     _fields_ = [("k_off", u32p), ("k_sec", i64p), ("k_nsf", u32p),
                 ("t_off", u32p), ("t_sec", i64p), ("t_nsf", u32p),
                 ("ann_sec", i64p), ("ann_nsf", u32p), ("chk_sec", i64p), ("chk_nsf", u32p),
-                ("nb_flags", u8p)]
+                ("nb_flags", u8p), ("k_end", u32p), ("t_end", u32p)]
 
 
 class nbg_cull_params(C.Structure):

@@ -160,7 +160,8 @@ bool off_ok(const uint32_t* off, uint64_t i0, uint64_t i1) {
   return bad == 0;
 }
 bool csr_ok(const nbg_kvmap& m, uint64_t i0, uint64_t i1) { return off_ok(m.off, i0, i1); }
-bool csr_ptrs_ok(const nbg_kvmap& m, uint64_t n) { return m.off && (m.ent || m.off[n] == m.off[0]); }
+// host-buffer entry points take CSR maps only (`end` must be NULL: chunking relies on contiguous runs)
+bool csr_ptrs_ok(const nbg_kvmap& m, uint64_t n) { return m.off && !m.end && (m.ent || m.off[n] == m.off[0]); }
 
 // Upload rows [i0,i1) of a CSR map; returns device pointers and the base offset.
 struct CsrDev { size_t off_at, ent_at; unsigned base; };
@@ -173,7 +174,7 @@ CsrDev csr_in(Layout& lay, const nbg_kvmap& m, uint64_t i0, uint64_t i1) {
   return c;
 }
 nbg_kvmap csr_ptr(const Slot& sl, const CsrDev& c) {
-  nbg_kvmap m;
+  nbg_kvmap m{};
   m.off = reinterpret_cast<const uint32_t*>(sl.dev + c.off_at);
   m.ent = reinterpret_cast<const nbg_kv*>(sl.dev + c.ent_at);
   return m;
@@ -561,7 +562,7 @@ int nbg_diff_generic(nbg_ctx* ctx, const nbg_generic_batch* in, uint64_t n, int 
       const size_t o_reason = lay.out(reason + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_generic_batch b;
+      nbg_generic_batch b{};
       b.labels_a = csr_ptr(sl, la); b.labels_b = csr_ptr(sl, lb);
       b.spec_a = csr_ptr(sl, sa); b.spec_b = csr_ptr(sl, sb);
       const unsigned bases[4] = {la.base, lb.base, sa.base, sb.base};
@@ -590,7 +591,7 @@ int nbg_diff_svc_gen(nbg_ctx* ctx, const nbg_svc_gen_batch* in, uint64_t n, uint
       const CsrDev lt = csr_in(lay, in->labels_to, i0, i1), at = csr_in(lay, in->ann_to, i0, i1), st = csr_in(lay, in->sel_to, i0, i1);
       const size_t o_reason = lay.out(reason + i0, m), o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_svc_gen_batch b;
+      nbg_svc_gen_batch b{};
       b.name_hash = (const uint64_t*)(sl.dev + a_nm); b.target_port = (const int32_t*)(sl.dev + a_tp);
       b.flags = (const uint8_t*)(sl.dev + a_fl); b.ports_to = (const uint64_t*)(sl.dev + a_pt);
       b.labels_to = csr_ptr(sl, lt); b.ann_to = csr_ptr(sl, at); b.sel_to = csr_ptr(sl, st);
@@ -621,7 +622,7 @@ int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_c
       const CsrDev hf = csr_in(lay, in->hdr_from, i0, i1), ht = csr_in(lay, in->hdr_to, i0, i1);
       const size_t o_reason = lay.out(reason + i0, m), o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_vs_gen_batch b;
+      nbg_vs_gen_batch b{};
       b.prefix_hash = (const uint64_t*)(sl.dev + a_p); b.rewrite_hash = (const uint64_t*)(sl.dev + a_r);
       b.host_hash = (const uint64_t*)(sl.dev + a_h); b.flags = (const uint8_t*)(sl.dev + a_fl);
       b.spec_to = (const uint64_t*)(sl.dev + a_st); b.hdr_from = csr_ptr(sl, hf); b.hdr_to = csr_ptr(sl, ht);
@@ -739,7 +740,7 @@ int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uin
   if (!decision || !bitmap || !in->flags) return NBG_E_INVAL;
   const nbg_podsparse* sp[3] = {&in->old_spec, &in->updated_spec, &in->mutated_spec};
   for (const nbg_podsparse* p : sp) {
-    if (!p->mask || !p->off || (p->off[n] > p->off[0] && !p->val) || ((uintptr_t)p->val & 15u)) return NBG_E_INVAL;
+    if (!p->mask || !p->off || p->end || (p->off[n] > p->off[0] && !p->val) || ((uintptr_t)p->val & 15u)) return NBG_E_INVAL;
   }
   return for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
     uint64_t c = 0;
@@ -766,7 +767,7 @@ int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uin
       const size_t o_dec = lay.out(decision + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_restart_batch b;
+      nbg_restart_batch b{};
       b.flags = (const uint8_t*)(sl.dev + a_fl);
       nbg_podsparse* dst[3] = {&b.old_spec, &b.updated_spec, &b.mutated_spec};
       for (int k = 0; k < 3; ++k) {
@@ -882,7 +883,7 @@ int nbg_cull_text(nbg_ctx* ctx, const nbg_cull_text_batch* in, uint64_t n, const
       CU(nbg_launch_parse_records(u32(chk.off_at), (const unsigned char*)(D + chk.bytes_at), nullptr, nullptr, m, chk.base, 0,
                                   (int64_t*)(D + s_csec), u32(s_cnsf), nullptr, d.s_run));
       CU(nbg_launch_cull_text_fixup((const uint8_t*)(D + a_flags), m, u32(s_ansf), u32(s_cnsf), (uint8_t*)(D + s_nbf), d.s_run));
-      nbg_cull_batch b;
+      nbg_cull_batch b{};
       b.k_off = u32(a_koff); b.k_sec = (const int64_t*)(D + s_ksec); b.k_nsf = u32(s_knsf);
       b.t_off = u32(a_toff); b.t_sec = (const int64_t*)(D + s_tsec); b.t_nsf = u32(s_tnsf);
       b.ann_sec = (const int64_t*)(D + s_asec); b.ann_nsf = u32(s_ansf);
@@ -965,7 +966,7 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_
   if (p->cull_idle_min > NBG_CULL_MAX_MINUTES || p->cull_idle_min < -NBG_CULL_MAX_MINUTES ||
       p->check_period_min > NBG_CULL_MAX_MINUTES || p->check_period_min < -NBG_CULL_MAX_MINUTES)
     return NBG_E_INVAL;
-  if (!in->k_off || !in->t_off) return NBG_E_INVAL;
+  if (!in->k_off || !in->t_off || in->k_end || in->t_end) return NBG_E_INVAL;
   if ((in->k_off[n] > in->k_off[0] && (!in->k_sec || !in->k_nsf)) ||
       (in->t_off[n] > in->t_off[0] && (!in->t_sec || !in->t_nsf)))
     return NBG_E_INVAL;
@@ -996,7 +997,7 @@ int nbg_cull(nbg_ctx* ctx, const nbg_cull_batch* in, uint64_t n, const nbg_cull_
       const size_t o_cull = lay.out(cull_bitmap + i0 / 64, words * 8);
       const size_t o_per = lay.out(period_bitmap + i0 / 64, words * 8);
       if (int rc = slot_upload(d, sl, lay)) return rc;
-      nbg_cull_batch b;
+      nbg_cull_batch b{};
       b.k_off = (const uint32_t*)(sl.dev + a_koff); b.k_sec = (const int64_t*)(sl.dev + a_ksec);
       b.k_nsf = (const uint32_t*)(sl.dev + a_knsf); b.t_off = (const uint32_t*)(sl.dev + a_toff);
       b.t_sec = (const int64_t*)(sl.dev + a_tsec); b.t_nsf = (const uint32_t*)(sl.dev + a_tnsf);
@@ -1042,7 +1043,7 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
       const size_t o_reason = lay.out(reason + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_sts_batch b;
+      nbg_sts_batch b{};
       b.replicas_from = (const int32_t*)(sl.dev + a_rf); b.replicas_to = (const int32_t*)(sl.dev + a_rt);
       b.tmpl_from = (const uint64_t*)(sl.dev + a_tf); b.tmpl_to = (const uint64_t*)(sl.dev + a_tt);
       b.pod_from = (const uint64_t*)(sl.dev + a_pf); b.pod_to = (const uint64_t*)(sl.dev + a_pt);
@@ -1068,7 +1069,7 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
       !in->pod_from.mask || !in->pod_to.mask)
     return NBG_E_INVAL;
   if (!csr_ptrs_ok(in->labels_from, n) || !csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_from, n) ||
-      !csr_ptrs_ok(in->ann_to, n) || !in->pod_from.off || !in->pod_to.off)
+      !csr_ptrs_ok(in->ann_to, n) || !in->pod_from.off || !in->pod_to.off || in->pod_from.end || in->pod_to.end)
     return NBG_E_INVAL;
   if ((in->pod_from.off[n] > in->pod_from.off[0] && !in->pod_from.val) ||
       (in->pod_to.off[n] > in->pod_to.off[0] && !in->pod_to.val))
@@ -1105,7 +1106,7 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
       const size_t o_reason = lay.out(reason + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_sts_sparse_batch b;
+      nbg_sts_sparse_batch b{};
       b.replicas_from = (const int32_t*)(sl.dev + a_rf); b.replicas_to = (const int32_t*)(sl.dev + a_rt);
       b.tmpl_from = (const uint64_t*)(sl.dev + a_tf); b.tmpl_to = (const uint64_t*)(sl.dev + a_tt);
       b.pod_from.mask = (const uint64_t*)(sl.dev + a_mf); b.pod_to.mask = (const uint64_t*)(sl.dev + a_mt);
@@ -1152,7 +1153,7 @@ int nbg_diff_svc(nbg_ctx* ctx, const nbg_svc_batch* in, uint64_t n, uint8_t* rea
       const size_t o_reason = lay.out(reason + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_svc_batch b;
+      nbg_svc_batch b{};
       b.flags = (const uint8_t*)(sl.dev + a_fl);
       b.ports_from = (const uint64_t*)(sl.dev + a_pf); b.ports_to = (const uint64_t*)(sl.dev + a_pt);
       b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt);
@@ -1187,7 +1188,7 @@ int nbg_diff_vs(nbg_ctx* ctx, const nbg_vs_batch* in, uint64_t n, uint8_t* reaso
       const size_t o_reason = lay.out(reason + i0, m);
       const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
       if (int r = slot_upload(d, sl, lay)) return r;
-      nbg_vs_batch b;
+      nbg_vs_batch b{};
       b.flags = (const uint8_t*)(sl.dev + a_fl);
       b.spec_from = (const uint64_t*)(sl.dev + a_sf); b.spec_to = (const uint64_t*)(sl.dev + a_st);
       b.hdr_from = csr_ptr(sl, hf); b.hdr_to = csr_ptr(sl, ht);

@@ -40,6 +40,21 @@ __device__ __forceinline__ nbg_kv ld_kv(const nbg_kv* p) {
 //   for k, v := range to { if from[k] != v { requireUpdate = true } }
 // A key missing from `from` reads as "" (hash 0).  Both segments are sorted by
 // key hash, so one merge pass answers every lookup.
+// End of object i's run: off[i+1] for a CSR map, end[i] for a map given as spans (nbgraft.h).
+// The choice depends on a kernel parameter only, so it is uniform across the grid.  The kernels of
+// the reconcile step are compiled twice: SPANS = false reads off[i+1] with no test at all (the
+// launcher picks it when every `end` of the batch is NULL), SPANS = true tests each map.
+template <bool SPANS = true>
+__device__ __forceinline__ uint32_t end_at(const nbg_kvmap& m, unsigned long long i) {
+  if (!SPANS) return __ldg(m.off + i + 1);
+  return __ldg((m.end ? m.end : m.off + 1) + i);
+}
+template <bool SPANS = true>
+__device__ __forceinline__ uint32_t end_at(const nbg_podsparse& m, unsigned long long i) {
+  if (!SPANS) return __ldg(m.off + i + 1);
+  return __ldg((m.end ? m.end : m.off + 1) + i);
+}
+
 __device__ __forceinline__ bool live_map_differs(const nbg_kv* __restrict__ from_ent,
                                                  uint32_t f_lo, uint32_t f_hi,
                                                  const nbg_kv* __restrict__ to_ent,

@@ -64,6 +64,7 @@ __device__ __forceinline__ Part scan_serial(const long long* __restrict__ sec, c
 #define NBG_CULL_MINBLOCKS 8   // 32 registers/thread: 64 resident warps per SM
 #endif
 
+template <bool SPANS>
 __global__ void __launch_bounds__(NBG_CULL_BLOCK, NBG_CULL_MINBLOCKS)
 cull_kernel(nbg_cull_batch in, unsigned long long n, nbg_cull_params p,
             unsigned k_base, unsigned t_base,
@@ -87,8 +88,8 @@ cull_kernel(nbg_cull_batch in, unsigned long long n, nbg_cull_params p,
     const unsigned annw = __ldg(in.ann_nsf + i);
     const unsigned chkw = __ldg(in.chk_nsf + i);
     const unsigned nbf = __ldg(in.nb_flags + i);
-    const unsigned k0 = __ldg(in.k_off + i), k1 = __ldg(in.k_off + i + 1);
-    const unsigned t0 = __ldg(in.t_off + i), t1 = __ldg(in.t_off + i + 1);
+    const unsigned k0 = __ldg(in.k_off + i), k1 = SPANS ? __ldg((in.k_end ? in.k_end : in.k_off + 1) + i) : __ldg(in.k_off + i + 1);
+    const unsigned t0 = __ldg(in.t_off + i), t1 = SPANS ? __ldg((in.t_end ? in.t_end : in.t_off + 1) + i) : __ldg(in.t_off + i + 1);
     ann.sec = __ldg(in.ann_sec + i); ann.nsec = annw & NBG_NSEC_MASK;
     chk.sec = __ldg(in.chk_sec + i); chk.nsec = chkw & NBG_NSEC_MASK;
     ann_ok = (annw & NBG_ANN_PARSE_OK) != 0;
@@ -230,7 +231,7 @@ extern "C" cudaError_t nbg_launch_cull(const nbg_cull_batch* in, unsigned long l
   if (n == 0) return cudaSuccess;
   const unsigned block = NBG_CULL_BLOCK;
   const unsigned long long grid = (n + block - 1) / block;
-  nbg::cull_kernel<<<(unsigned)grid, block, 0, stream>>>(
+  ((in->k_end || in->t_end) ? nbg::cull_kernel<true> : nbg::cull_kernel<false>)<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, *p, k_base, t_base, action, argmax, reinterpret_cast<uint32_t*>(cull_bitmap),
       reinterpret_cast<uint32_t*>(period_bitmap));
   return cudaGetLastError();

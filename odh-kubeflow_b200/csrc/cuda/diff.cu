@@ -60,14 +60,14 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
       if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
     }
     if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
-                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         end_at(in.labels_from, i) - lf_base,
                          in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
-                         __ldg(in.labels_to.off + i + 1) - lt_base))
+                         end_at(in.labels_to, i) - lt_base))
       reason |= NBG_STS_LABELS;                      // COMMON:109-113
     if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
-                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         end_at(in.ann_from, i) - af_base,
                          in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
-                         __ldg(in.ann_to.off + i + 1) - at_base))
+                         end_at(in.ann_to, i) - at_base))
       reason |= NBG_STS_ANNOTATIONS;                 // COMMON:116-120
   }
 
@@ -116,6 +116,7 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
 constexpr unsigned kSparseGroup = 4;
 
 // bit o of the result = the sparse tiles of object base+o differ (warp-cooperative)
+template <bool SPANS = true>
 __device__ __forceinline__ unsigned sparse_tiles_differ(const nbg_podsparse& a, const nbg_podsparse& b,
                                                         unsigned long long i, bool live, unsigned cnt, unsigned lane,
                                                         unsigned a_base, unsigned b_base) {
@@ -125,7 +126,7 @@ __device__ __forceinline__ unsigned sparse_tiles_differ(const nbg_podsparse& a, 
     const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
     const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
     mask_ne = (__ldg(ma) != __ldg(mb)) | (__ldg(ma + 1) != __ldg(mb + 1)) | (__ldg(ma + 2) != __ldg(mb + 2));
-    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = __ldg(a.off + i + 1) - a_base;
+    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = end_at<SPANS>(a, i) - a_base;
     va0 = f0 >> 1;
     vb0 = (__ldg(b.off + i) - b_base) >> 1;
     my_vecs = mask_ne ? 0u : (f1 - f0) >> 1;
@@ -164,6 +165,7 @@ __device__ __forceinline__ unsigned sparse_tiles_differ(const nbg_podsparse& a, 
   return bits;
 }
 
+template <bool SPANS>
 __global__ void __launch_bounds__(128)
 diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
                        unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
@@ -177,7 +179,7 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
   const unsigned cnt = (unsigned)min(32ull, n - base);
 
   // tiles first (the streaming part), then the per-lane scalar work: keeps the two register sets apart
-  const unsigned pod_bits = sparse_tiles_differ(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
+  const unsigned pod_bits = sparse_tiles_differ<SPANS>(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
   unsigned reason = ((pod_bits >> lane) & 1u) ? NBG_STS_PODSPEC : 0u;
   if (i < n) {
     const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
@@ -188,14 +190,14 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
       if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
     }
     if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
-                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         end_at<SPANS>(in.labels_from, i) - lf_base,
                          in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
-                         __ldg(in.labels_to.off + i + 1) - lt_base))
+                         end_at<SPANS>(in.labels_to, i) - lt_base))
       reason |= NBG_STS_LABELS;
     if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
-                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         end_at<SPANS>(in.ann_from, i) - af_base,
                          in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
-                         __ldg(in.ann_to.off + i + 1) - at_base))
+                         end_at<SPANS>(in.ann_to, i) - at_base))
       reason |= NBG_STS_ANNOTATIONS;
   }
   store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
@@ -229,7 +231,7 @@ __device__ __forceinline__ void sparse_tiles_differ3(const nbg_podsparse& a, con
     const unsigned long long a0 = __ldg(ma), a1 = __ldg(ma + 1), a2 = __ldg(ma + 2);
     b_ne = (a0 != __ldg(mb)) | (a1 != __ldg(mb + 1)) | (a2 != __ldg(mb + 2));
     c_ne = (a0 != __ldg(mc)) | (a1 != __ldg(mc + 1)) | (a2 != __ldg(mc + 2));
-    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = __ldg(a.off + i + 1) - a_base;
+    const unsigned f0 = __ldg(a.off + i) - a_base, f1 = end_at(a, i) - a_base;
     va0 = f0 >> 1;
     vb0 = (__ldg(b.off + i) - b_base) >> 1;
     vc0 = (__ldg(c.off + i) - c_base) >> 1;
@@ -348,19 +350,19 @@ diff_svc_kernel(nbg_svc_batch in, unsigned long long n,
   if (i < n) {
     const unsigned fl = __ldg(in.flags + i);
     if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base,
-                         __ldg(in.labels_from.off + i + 1) - lf_base,
+                         end_at(in.labels_from, i) - lf_base,
                          in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base,
-                         __ldg(in.labels_to.off + i + 1) - lt_base))
+                         end_at(in.labels_to, i) - lt_base))
       reason |= NBG_SVC_LABELS;                      // COMMON:168-172
     if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base,
-                         __ldg(in.ann_from.off + i + 1) - af_base,
+                         end_at(in.ann_from, i) - af_base,
                          in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base,
-                         __ldg(in.ann_to.off + i + 1) - at_base))
+                         end_at(in.ann_to, i) - at_base))
       reason |= NBG_SVC_ANNOTATIONS;                 // COMMON:175-179
     if (map_not_deep_equal(in.sel_from.ent, __ldg(in.sel_from.off + i) - sf_base,
-                           __ldg(in.sel_from.off + i + 1) - sf_base, (fl & NBG_F_FROM_SEL_NIL) != 0,
+                           end_at(in.sel_from, i) - sf_base, (fl & NBG_F_FROM_SEL_NIL) != 0,
                            in.sel_to.ent, __ldg(in.sel_to.off + i) - st_base,
-                           __ldg(in.sel_to.off + i + 1) - st_base, (fl & NBG_F_TO_SEL_NIL) != 0))
+                           end_at(in.sel_to, i) - st_base, (fl & NBG_F_TO_SEL_NIL) != 0))
       reason |= NBG_SVC_SELECTOR;                    // COMMON:184
     if ((port_bits >> lane) & 1u) reason |= NBG_SVC_PORTS;  // COMMON:189
   }
@@ -389,10 +391,10 @@ diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned
     } else {                                         // COMMON:214
       bool differs = (spec_bits >> lane) & 1u;
       differs |= map_not_deep_equal(in.hdr_from.ent, __ldg(in.hdr_from.off + i) - hf_base,
-                                    __ldg(in.hdr_from.off + i + 1) - hf_base,
+                                    end_at(in.hdr_from, i) - hf_base,
                                     (fl & NBG_F_FROM_HDR_NIL) != 0,
                                     in.hdr_to.ent, __ldg(in.hdr_to.off + i) - ht_base,
-                                    __ldg(in.hdr_to.off + i + 1) - ht_base,
+                                    end_at(in.hdr_to, i) - ht_base,
                                     (fl & NBG_F_TO_HDR_NIL) != 0);
       if (differs) { reason = NBG_VS_SPEC_DIFFERS; update = true; }
     }
@@ -406,6 +408,7 @@ diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned
 // generateVirtualService NBCTL:558-658; slot layout = csrc/host/pack.cpp).
 struct SvcGenConsts { unsigned long long port_name, proto_tcp, sel_key; };
 
+template <bool SPANS>
 __global__ void __launch_bounds__(128)
 diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
                     unsigned lt_base, unsigned at_base, unsigned st_base,
@@ -442,12 +445,12 @@ diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
   if (i < n) {
     const unsigned fl = __ldg(in.flags + i);
     // desired has no labels and no annotations: any live entry with a non-empty value differs
-    for (unsigned t = __ldg(in.labels_to.off + i) - lt_base, e = __ldg(in.labels_to.off + i + 1) - lt_base; t < e; ++t)
+    for (unsigned t = __ldg(in.labels_to.off + i) - lt_base, e = end_at<SPANS>(in.labels_to, i) - lt_base; t < e; ++t)
       if (ld_kv(in.labels_to.ent + t).val != 0ull) reason |= NBG_SVC_LABELS;
-    for (unsigned t = __ldg(in.ann_to.off + i) - at_base, e = __ldg(in.ann_to.off + i + 1) - at_base; t < e; ++t)
+    for (unsigned t = __ldg(in.ann_to.off + i) - at_base, e = end_at<SPANS>(in.ann_to, i) - at_base; t < e; ++t)
       if (ld_kv(in.ann_to.ent + t).val != 0ull) reason |= NBG_SVC_ANNOTATIONS;
     // desired selector = {"statefulset": name}, non-nil
-    const unsigned s0 = __ldg(in.sel_to.off + i) - st_base, s1 = __ldg(in.sel_to.off + i + 1) - st_base;
+    const unsigned s0 = __ldg(in.sel_to.off + i) - st_base, s1 = end_at<SPANS>(in.sel_to, i) - st_base;
     bool sel_ne = (fl & NBG_F_TO_SEL_NIL) != 0 || (s1 - s0) != 1u;
     if (!sel_ne) {
       const nbg_kv e = ld_kv(in.sel_to.ent + s0);
@@ -459,6 +462,7 @@ diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
   store_results(base, n, lane, reason, (reason & NBG_SVC_UPDATE_MASK) != 0, reason_out, bitmap_half);
 }
 
+template <bool SPANS>
 __global__ void __launch_bounds__(128)
 diff_vs_gen_kernel(nbg_vs_gen_batch in, nbg_vs_gen_consts k, unsigned long long n, unsigned hf_base, unsigned ht_base,
                    uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
@@ -502,9 +506,9 @@ diff_vs_gen_kernel(nbg_vs_gen_batch in, nbg_vs_gen_consts k, unsigned long long 
     } else {
       bool differs = (spec_bits >> lane) & 1u;
       differs |= map_not_deep_equal(in.hdr_from.ent, __ldg(in.hdr_from.off + i) - hf_base,
-                                    __ldg(in.hdr_from.off + i + 1) - hf_base, false,
+                                    end_at<SPANS>(in.hdr_from, i) - hf_base, false,
                                     in.hdr_to.ent, __ldg(in.hdr_to.off + i) - ht_base,
-                                    __ldg(in.hdr_to.off + i + 1) - ht_base, (fl & NBG_F_TO_HDR_NIL) != 0);
+                                    end_at<SPANS>(in.hdr_to, i) - ht_base, (fl & NBG_F_TO_HDR_NIL) != 0);
       if (differs) { reason = NBG_VS_SPEC_DIFFERS; update = true; }
     }
   }
@@ -524,10 +528,10 @@ diff_generic_kernel(nbg_generic_batch in, unsigned long long n, int mode,
   const unsigned long long i = base + lane;
   unsigned reason = 0;
   if (i < n) {
-    const unsigned la0 = __ldg(in.labels_a.off + i) - la_base, la1 = __ldg(in.labels_a.off + i + 1) - la_base;
-    const unsigned lb0 = __ldg(in.labels_b.off + i) - lb_base, lb1 = __ldg(in.labels_b.off + i + 1) - lb_base;
-    const unsigned sa0 = __ldg(in.spec_a.off + i) - sa_base, sa1 = __ldg(in.spec_a.off + i + 1) - sa_base;
-    const unsigned sb0 = __ldg(in.spec_b.off + i) - sb_base, sb1 = __ldg(in.spec_b.off + i + 1) - sb_base;
+    const unsigned la0 = __ldg(in.labels_a.off + i) - la_base, la1 = end_at(in.labels_a, i) - la_base;
+    const unsigned lb0 = __ldg(in.labels_b.off + i) - lb_base, lb1 = end_at(in.labels_b, i) - lb_base;
+    const unsigned sa0 = __ldg(in.spec_a.off + i) - sa_base, sa1 = end_at(in.spec_a, i) - sa_base;
+    const unsigned sb0 = __ldg(in.spec_b.off + i) - sb_base, sb1 = end_at(in.spec_b, i) - sb_base;
     if (mode == NBG_GEN_DEEPEQUAL) {
       // flattened trees: nil-ness, lengths and kinds are entries of the vectors themselves
       if (map_not_deep_equal(in.labels_a.ent, la0, la1, false, in.labels_b.ent, lb0, lb1, false)) reason |= NBG_GEN_LABELS;
@@ -572,7 +576,8 @@ extern "C" cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch* in
   if (n == 0) return cudaSuccess;
   const unsigned block = 128;
   const unsigned long long grid = (n + block - 1) / block;
-  nbg::diff_sts_sparse_kernel<<<(unsigned)grid, block, 0, stream>>>(
+  const bool spans = in->pod_from.end || in->pod_to.end || in->labels_from.end || in->labels_to.end || in->ann_from.end || in->ann_to.end;
+  (spans ? nbg::diff_sts_sparse_kernel<true> : nbg::diff_sts_sparse_kernel<false>)<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
       reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
@@ -586,7 +591,8 @@ extern "C" cudaError_t nbg_launch_diff_svc_gen(const nbg_svc_gen_batch* in, unsi
   k.proto_tcp = nbg_hash_bytes("TCP", 3);              // NBCTL:544
   k.sel_key = nbg_hash_bytes("statefulset", 11);       // NBCTL:537
   const unsigned block = 128;
-  nbg::diff_svc_gen_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+  const bool spans = in->labels_to.end || in->ann_to.end || in->sel_to.end;
+  (spans ? nbg::diff_svc_gen_kernel<true> : nbg::diff_svc_gen_kernel<false>)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
       *in, k, n, bases[0], bases[1], bases[2], reason, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
@@ -594,7 +600,8 @@ extern "C" cudaError_t nbg_launch_diff_vs_gen(const nbg_vs_gen_batch* in, const 
                                               const unsigned* bases /*2*/, uint8_t* reason, uint64_t* bitmap, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   const unsigned block = 128;
-  nbg::diff_vs_gen_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+  const bool spans = in->hdr_from.end || in->hdr_to.end;
+  (spans ? nbg::diff_vs_gen_kernel<true> : nbg::diff_vs_gen_kernel<false>)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
       *in, *consts, n, bases[0], bases[1], reason, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }

@@ -63,7 +63,7 @@ void RestartBatch::add(const GVal& old_nb, const GVal& updated_nb, const GVal& m
   ++n;
 }
 nbg_restart_batch RestartBatch::view() const {
-  nbg_restart_batch b;
+  nbg_restart_batch b{};
   b.flags = flags.data();
   nbg_podsparse* dst[3] = {&b.old_spec, &b.updated_spec, &b.mutated_spec};
   for (int k = 0; k < 3; ++k) { dst[k]->mask = mask[k].data(); dst[k]->off = off[k].data(); dst[k]->val = val[k].data(); }
@@ -107,7 +107,7 @@ void StsBatch::append(const StsBatch& o) {
   n += o.n;
 }
 nbg_sts_batch StsBatch::view() const {
-  nbg_sts_batch b;
+  nbg_sts_batch b{};
   b.replicas_from = replicas_from.data(); b.replicas_to = replicas_to.data();
   b.tmpl_from = tmpl_from.data(); b.tmpl_to = tmpl_to.data();
   b.pod_from = pod_from.data(); b.pod_to = pod_to.data();
@@ -117,7 +117,7 @@ nbg_sts_batch StsBatch::view() const {
 }
 
 nbg_sts_sparse_batch StsBatch::view_sparse() const {
-  nbg_sts_sparse_batch b;
+  nbg_sts_sparse_batch b{};
   b.replicas_from = replicas_from.data(); b.replicas_to = replicas_to.data();
   b.tmpl_from = tmpl_from.data(); b.tmpl_to = tmpl_to.data();
   b.pod_from.mask = mask_from.data(); b.pod_from.off = voff_from.data(); b.pod_from.val = val_from.data();
@@ -156,7 +156,7 @@ void SvcBatch::append(const SvcBatch& o) {
   n += o.n;
 }
 nbg_svc_batch SvcBatch::view() const {
-  nbg_svc_batch b;
+  nbg_svc_batch b{};
   b.flags = flags.data(); b.ports_from = ports_from.data(); b.ports_to = ports_to.data();
   b.labels_from = labels_from.view(); b.labels_to = labels_to.view();
   b.ann_from = ann_from.view(); b.ann_to = ann_to.view();
@@ -165,7 +165,7 @@ nbg_svc_batch SvcBatch::view() const {
 }
 
 nbg_svc_gen_batch SvcBatch::view_gen() const {
-  nbg_svc_gen_batch b;
+  nbg_svc_gen_batch b{};
   b.name_hash = name_hash.data(); b.target_port = target_port.data();
   b.flags = flags.data(); b.ports_to = ports_to.data();
   b.labels_to = labels_to.view(); b.ann_to = ann_to.view(); b.sel_to = sel_to.view();
@@ -195,14 +195,14 @@ void VsBatch::append(const VsBatch& o) {
   n += o.n;
 }
 nbg_vs_batch VsBatch::view() const {
-  nbg_vs_batch b;
+  nbg_vs_batch b{};
   b.flags = flags.data(); b.spec_from = spec_from.data(); b.spec_to = spec_to.data();
   b.hdr_from = hdr_from.view(); b.hdr_to = hdr_to.view();
   return b;
 }
 
 nbg_vs_gen_batch VsBatch::view_gen() const {
-  nbg_vs_gen_batch b;
+  nbg_vs_gen_batch b{};
   b.prefix_hash = prefix_hash.data(); b.rewrite_hash = rewrite_hash.data(); b.host_hash = host_hash.data();
   b.hdr_from = hdr_from.view(); b.flags = flags.data(); b.spec_to = spec_to.data(); b.hdr_to = hdr_to.view();
   return b;
@@ -217,7 +217,7 @@ void GenBatch::add(const GVal& la, const GVal& lb, const GVal& sa, const GVal& s
   ++n;
 }
 nbg_generic_batch GenBatch::view() const {
-  nbg_generic_batch b;
+  nbg_generic_batch b{};
   b.labels_a = labels_a.view(); b.labels_b = labels_b.view();
   b.spec_a = spec_a.view(); b.spec_b = spec_b.view();
   return b;
@@ -262,7 +262,7 @@ void CullBatch::append(const CullBatch& o) {
   n += o.n;
 }
 nbg_cull_batch CullBatch::view() const {
-  nbg_cull_batch b;
+  nbg_cull_batch b{};
   b.k_off = k_off.data(); b.k_sec = k_sec.data(); b.k_nsf = k_nsf.data();
   b.t_off = t_off.data(); b.t_sec = t_sec.data(); b.t_nsf = t_nsf.data();
   b.ann_sec = ann_sec.data(); b.ann_nsf = ann_nsf.data();

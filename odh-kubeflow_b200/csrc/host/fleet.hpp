@@ -37,7 +37,7 @@ struct KvCsr {
     ent.insert(ent.end(), o.ent.begin(), o.ent.end());
     for (size_t k = 1; k < o.off.size(); ++k) off.push_back(base + o.off[k]);
   }
-  nbg_kvmap view() const { nbg_kvmap m; m.off = off.data(); m.ent = ent.data(); return m; }
+  nbg_kvmap view() const { nbg_kvmap m{}; m.off = off.data(); m.ent = ent.data(); return m; }
 };
 
 struct StsBatch {

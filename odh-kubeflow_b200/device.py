@@ -34,7 +34,7 @@ class DeviceBatch:
         self.n = n0 * tile
         self.in_bytes = 0
         for name, a in arrays.items():
-            if name.endswith(".off") or name.endswith(".voff") or name in ("k_off", "t_off"):
+            if tile > 1 and (name.endswith(".off") or name.endswith(".voff") or name in ("k_off", "t_off")):
                 # CSR offsets of tile k are the base offsets shifted by k * (#entries)
                 base = a.astype(np.int64)
                 total = int(base[-1])
@@ -68,7 +68,17 @@ class DeviceBatch:
         m = N.nbg_kvmap()
         m.off = self._p(prefix + ".off", C.c_uint32)
         m.ent = C.cast(self.tensors[prefix + ".ent"].data_ptr(), C.POINTER(N.nbg_kv))
+        if prefix + ".end" in self.tensors:             # spans instead of CSR (include/nbgraft.h)
+            m.end = self._p(prefix + ".end", C.c_uint32)
         return m
+
+    def _sparse(self, side):
+        ps = N.nbg_podsparse()
+        ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
+                                   self._p(side + ".val", C.c_uint64))
+        if side + ".vend" in self.tensors:
+            ps.end = self._p(side + ".vend", C.c_uint32)
+        return ps
 
     def _build_struct(self):
         k = self.kind
@@ -84,10 +94,7 @@ class DeviceBatch:
             s.replicas_from, s.replicas_to = self._p("replicas_from", C.c_int32), self._p("replicas_to", C.c_int32)
             s.tmpl_from, s.tmpl_to = self._p("tmpl_from", C.c_uint64), self._p("tmpl_to", C.c_uint64)
             for side in ("pod_from", "pod_to"):
-                ps = N.nbg_podsparse()
-                ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
-                                           self._p(side + ".val", C.c_uint64))
-                setattr(s, side, ps)
+                setattr(s, side, self._sparse(side))
             for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
                 setattr(s, f, self._kv(f))
         elif k == "svc_gen":
@@ -110,10 +117,7 @@ class DeviceBatch:
             s = N.nbg_restart_batch()
             s.flags = self._p("flags", C.c_uint8)
             for side in ("old_spec", "updated_spec", "mutated_spec"):
-                ps = N.nbg_podsparse()
-                ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
-                                           self._p(side + ".val", C.c_uint64))
-                setattr(s, side, ps)
+                setattr(s, side, self._sparse(side))
         elif k == "SvcBatch":
             s = N.nbg_svc_batch()
             s.flags = self._p("flags", C.c_uint8)
@@ -131,6 +135,8 @@ class DeviceBatch:
                           ("t_sec", C.c_int64), ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32),
                           ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)):
                 setattr(s, f, self._p(f, ct))
+            if "k_end" in self.tensors:
+                s.k_end, s.t_end = self._p("k_end", C.c_uint32), self._p("t_end", C.c_uint32)
         return s
 
     def run(self, ctx, now=None, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE, stream=None):

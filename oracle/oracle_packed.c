@@ -29,12 +29,15 @@
 
 #define ORC_API __attribute__((visibility("default")))
 
+/* end of object i's run: off[i+1] (CSR) or end[i] (spans), see nbgraft.h */
+#define END_OF(m, i) ((m)->end ? (m)->end[i] : (m)->off[(i) + 1])
+
 static int live_differs(const nbg_kvmap* from, const nbg_kvmap* to, uint64_t i) {
   /* for k, v := range to { if from[k] != v { requireUpdate = true } } */
   int differs = 0;
-  for (uint32_t t = to->off[i]; t < to->off[i + 1]; ++t) {
+  for (uint32_t t = to->off[i]; t < END_OF(to, i); ++t) {
     uint64_t want = 0;
-    for (uint32_t f = from->off[i]; f < from->off[i + 1]; ++f)
+    for (uint32_t f = from->off[i]; f < END_OF(from, i); ++f)
       if (from->ent[f].key == to->ent[t].key) { want = from->ent[f].val; break; }
     if (want != to->ent[t].val) differs = 1;
   }
@@ -43,7 +46,7 @@ static int live_differs(const nbg_kvmap* from, const nbg_kvmap* to, uint64_t i) 
 
 static int map_not_equal(const nbg_kvmap* a, int a_nil, const nbg_kvmap* b, int b_nil, uint64_t i) {
   if (a_nil != b_nil) return 1;
-  const uint32_t na = a->off[i + 1] - a->off[i], nb = b->off[i + 1] - b->off[i];
+  const uint32_t na = END_OF(a, i) - a->off[i], nb = END_OF(b, i) - b->off[i];
   if (na != nb) return 1;
   for (uint32_t k = 0; k < na; ++k) {
     const nbg_kv* x = &a->ent[a->off[i] + k];
@@ -100,7 +103,7 @@ static void sts_sparse_range(const nbg_sts_sparse_batch* in, uint64_t lo, uint64
       for (unsigned s = 0; s < NBG_POD_SLOTS; ++s)
         t[s] = (p->mask[i * 3 + (s >> 6)] >> (s & 63) & 1) ? p->val[at++] : 0;
       if (at & 1) { if (p->val[at] != 0) r |= 0x40; ++at; }   /* runs are zero-padded to an even count */
-      if (at != p->off[i + 1]) r |= 0x40;                      /* malformed input: popcount(mask) != run length */
+      if (at != END_OF(p, i)) r |= 0x40;                      /* malformed input: popcount(mask) != run length */
     }
     if (memcmp(a, b, sizeof a) != 0) r |= NBG_STS_PODSPEC;
     reason[i] = (uint8_t)r;
@@ -180,13 +183,13 @@ static void cull_range(const nbg_cull_batch* in, const nbg_cull_params* p, uint6
       if (period) act |= NBG_ACT_PERIOD;
       if (p->mode == NBG_CULL_PREDICATES || period) {
         unsigned src = 0; int all_ok, all_idle; inst best; uint32_t idx;
-        if (in->k_off[i + 1] > in->k_off[i]) {
-          scan(in->k_sec, in->k_nsf, in->k_off[i], in->k_off[i + 1], &all_ok, &all_idle, &best, &idx);
+        if ((in->k_end ? in->k_end[i] : in->k_off[i + 1]) > in->k_off[i]) {
+          scan(in->k_sec, in->k_nsf, in->k_off[i], (in->k_end ? in->k_end[i] : in->k_off[i + 1]), &all_ok, &all_idle, &best, &idx);
           if (!all_idle) { ann = now_trunc; ann_ok = 1; src = 1; }
           else if (all_ok) { inst t = {best.sec, 0}; if (ann_ok && !after(ann, t)) { ann = t; src = 2; amax = idx; } }
         }
-        if (in->t_off[i + 1] > in->t_off[i]) {
-          scan(in->t_sec, in->t_nsf, in->t_off[i], in->t_off[i + 1], &all_ok, &all_idle, &best, &idx);
+        if ((in->t_end ? in->t_end[i] : in->t_off[i + 1]) > in->t_off[i]) {
+          scan(in->t_sec, in->t_nsf, in->t_off[i], (in->t_end ? in->t_end[i] : in->t_off[i + 1]), &all_ok, &all_idle, &best, &idx);
           if (all_ok) { inst t = {best.sec, 0}; if (ann_ok && !after(ann, t)) { ann = t; src = 3; amax = idx; } }
         }
         act |= src;
@@ -302,9 +305,9 @@ ORC_API void orc2_diff_generic(const nbg_generic_batch* in, uint64_t n, int mode
       if (map_not_equal(&in->labels_a, 0, &in->labels_b, 0, i)) r |= NBG_GEN_LABELS;
       if (map_not_equal(&in->spec_a, 0, &in->spec_b, 0, i)) r |= NBG_GEN_SPEC;
     } else {
-      if (in->labels_a.off[i + 1] - in->labels_a.off[i] != in->labels_b.off[i + 1] - in->labels_b.off[i] ||
+      if (END_OF(&in->labels_a, i) - in->labels_a.off[i] != END_OF(&in->labels_b, i) - in->labels_b.off[i] ||
           live_differs(&in->labels_b, &in->labels_a, i)) r |= NBG_GEN_LABELS;
-      if (in->spec_a.off[i + 1] - in->spec_a.off[i] != in->spec_b.off[i + 1] - in->spec_b.off[i] ||
+      if (END_OF(&in->spec_a, i) - in->spec_a.off[i] != END_OF(&in->spec_b, i) - in->spec_b.off[i] ||
           live_differs(&in->spec_b, &in->spec_a, i)) r |= NBG_GEN_SPEC;
     }
     reason[i] = (uint8_t)r;
@@ -315,8 +318,8 @@ ORC_API void orc2_diff_generic(const nbg_generic_batch* in, uint64_t n, int mode
 /* Webhook restart-block predicate on packed sparse tiles (nbg_restart_batch). */
 static int sparse_differs(const nbg_podsparse* a, const nbg_podsparse* b, uint64_t i) {
   if (memcmp(a->mask + i * 3, b->mask + i * 3, 24) != 0) return 1;
-  const uint32_t na = a->off[i + 1] - a->off[i];
-  if (na != b->off[i + 1] - b->off[i]) return 1;
+  const uint32_t na = END_OF(a, i) - a->off[i];
+  if (na != END_OF(b, i) - b->off[i]) return 1;
   return memcmp(a->val + a->off[i], b->val + b->off[i], (size_t)na * 8) != 0;
 }
 ORC_API void orc2_restart_block(const nbg_restart_batch* in, uint64_t n, uint8_t* decision, uint64_t* bitmap) {

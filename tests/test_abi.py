@@ -44,7 +44,35 @@ def test_schema_constants_match_header():
     assert const("NBG_VS_SLOTS") == N.NBG_VS_SLOTS == 8
     assert N.nbg().nbg_abi_version() == const("NBG_ABI_VERSION")
     assert C.sizeof(N.nbg_kv) == 16 and C.sizeof(N.nbg_cull_params) == 24
-    assert C.sizeof(N.nbg_sts_batch) == 6 * 8 + 4 * 16
+
+
+def test_ctypes_mirrors_have_the_c_compilers_layout(tmp_path):
+    """Every struct of include/nbgraft.h: size and every field offset as gcc lays it out == the ctypes
+    mirror in _native.py (a silent mismatch would shift every pointer after the first difference)."""
+    import subprocess
+    structs = [n for n in dir(N) if n.startswith("nbg_") and isinstance(getattr(N, n), type) and issubclass(getattr(N, n), C.Structure)]
+    assert len(structs) >= 15
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "nbgraft.h"', 'int main(void) {']
+    for n in structs:
+        lines.append('  printf("%s size %%zu\\n", sizeof(%s));' % (n, n))
+        for f, _ in getattr(N, n)._fields_:
+            lines.append('  printf("%s %s %%zu\\n", offsetof(%s, %s));' % (n, f, n, f))
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = str(tmp_path / "layout")
+    r = subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = subprocess.run([exe], capture_output=True, text=True).stdout.split("\n")
+    seen = 0
+    for line in out:
+        if not line:
+            continue
+        n, f, v = line.split()
+        cls = getattr(N, n)
+        assert int(v) == (C.sizeof(cls) if f == "size" else getattr(cls, f).offset), line
+        seen += 1
+    assert seen > 100
 
 
 def test_hash_contract():
