@@ -324,6 +324,45 @@ int nbg_step_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* sts, c
                     const nbg_cull_params* params, uint64_t n, const nbg_step_outputs* out, void* stream,
                     void* ev_sts_start /*nullable*/, void* ev_sts_stop /*nullable*/);
 
+/* ---- resident fleet ----------------------------------------------------------------------
+ * The four batches of a reconcile step for up to `capacity` notebooks, kept in device memory
+ * and edited IN PLACE: the caller packs an object when its informer delivers it (the expensive
+ * part, once per change), puts the packed row into its slot, and every tick runs the step over
+ * the whole resident fleet without moving it again.  The reference has no counterpart: it
+ * re-derives and re-compares one object per reconcile (NBCTL:152-240, CULL:86-203); this is the
+ * batch form of its informer cache + resync.
+ * Layout: fixed-width words in per-notebook arrays; every variable-length part (sparse PodSpec
+ * runs, label/annotation/selector/header maps, kernel and terminal records) in an append-only
+ * heap addressed by per-notebook spans (off,end) — a replaced run is appended and the old one
+ * becomes garbage; a heap that fills up is compacted (live runs copied in slot order) and grown
+ * when more than half of it is still live.  A store belongs to one device of the context. */
+typedef struct nbg_store nbg_store;
+int  nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** out);
+void nbg_store_destroy(nbg_store* st);
+/* Slots idx[0..m) take rows 0..m of the given HOST batches (CSR form, m objects each; a NULL batch
+ * leaves that predicate's rows as they are).  idx must be < capacity and free of duplicates.
+ * Returns when the rows are on the device (the host buffers may be reused at once). */
+int  nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_sparse_batch* sts,
+                   const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull);
+/* One step over slots [0,n): outputs as nbg_step, into HOST buffers (synchronous) ... */
+int  nbg_store_step(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts, const nbg_cull_params* params,
+                    const nbg_step_outputs* out);
+/* ... or into DEVICE buffers, enqueued on `stream` like nbg_step_device. */
+int  nbg_store_step_device(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts, const nbg_cull_params* params,
+                           const nbg_step_outputs* out, void* stream);
+typedef struct nbg_store_stats {
+  uint64_t capacity;        /* slots                                              */
+  uint64_t fixed_bytes;     /* per-slot arrays                                    */
+  uint64_t heap_bytes;      /* allocated for the heaps                            */
+  uint64_t live_bytes;      /* of which belong to a current run                   */
+  uint64_t garbage_bytes;   /* appended and since replaced                        */
+  uint64_t compactions;     /* heap compactions so far                            */
+  uint64_t puts, rows_put;  /* calls and rows since creation                      */
+} nbg_store_stats;
+int  nbg_store_get_stats(const nbg_store* st, nbg_store_stats* out);
+/* CUDA ordinal of the context's device `device` (for callers that allocate next to it). */
+int  nbg_device_id(const nbg_ctx* ctx, int device);
+
 /* Metrics.scrape (components/notebook-controller/pkg/metrics/metrics.go:82-98) as a segmented
  * count: counts[ns] = number of StatefulSets j with ns_id[j] == ns whose pod-template label
  * "notebook-name" is present (flags[j] & 1) and equals the StatefulSet's name

@@ -88,6 +88,11 @@ class nbg_step_outputs(C.Structure):
                                            "action", "argmax", "cull_bitmap", "period_bitmap")]
 
 
+class nbg_store_stats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("capacity", "fixed_bytes", "heap_bytes", "live_bytes", "garbage_bytes", "compactions",
+                                          "puts", "rows_put")]
+
+
 class nbg_restart_batch(C.Structure):
     _fields_ = [("flags", u8p), ("old_spec", nbg_podsparse), ("updated_spec", nbg_podsparse), ("mutated_spec", nbg_podsparse)]
 
@@ -153,7 +158,8 @@ NBG_SYMBOLS = [
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
-    "nbg_step", "nbg_step_device", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
+    "nbg_step", "nbg_step_device", "nbg_store_create", "nbg_store_destroy", "nbg_store_put", "nbg_store_step",
+    "nbg_store_step_device", "nbg_store_get_stats", "nbg_device_id", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
     "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
 ]
@@ -226,6 +232,22 @@ def _bind_nbg(lib):
                                     C.POINTER(nbg_vs_gen_batch), C.POINTER(nbg_vs_gen_consts), C.POINTER(nbg_cull_batch),
                                     C.POINTER(nbg_cull_params), C.c_uint64, C.POINTER(nbg_step_outputs), _vp, _vp, _vp]
     lib.nbg_step_device.restype = C.c_int
+    lib.nbg_store_create.argtypes = [_vp, C.c_int, C.c_uint64, C.POINTER(_vp)]
+    lib.nbg_store_create.restype = C.c_int
+    lib.nbg_store_destroy.argtypes = [_vp]
+    lib.nbg_store_destroy.restype = None
+    lib.nbg_store_put.argtypes = [_vp, u64p, C.c_uint64, C.POINTER(nbg_sts_sparse_batch), C.POINTER(nbg_svc_gen_batch),
+                                  C.POINTER(nbg_vs_gen_batch), C.POINTER(nbg_cull_batch)]
+    lib.nbg_store_put.restype = C.c_int
+    lib.nbg_store_step.argtypes = [_vp, C.c_uint64, C.POINTER(nbg_vs_gen_consts), C.POINTER(nbg_cull_params), C.POINTER(nbg_step_outputs)]
+    lib.nbg_store_step.restype = C.c_int
+    lib.nbg_store_step_device.argtypes = [_vp, C.c_uint64, C.POINTER(nbg_vs_gen_consts), C.POINTER(nbg_cull_params),
+                                          C.POINTER(nbg_step_outputs), _vp]
+    lib.nbg_store_step_device.restype = C.c_int
+    lib.nbg_store_get_stats.argtypes = [_vp, C.POINTER(nbg_store_stats)]
+    lib.nbg_store_get_stats.restype = C.c_int
+    lib.nbg_device_id.argtypes = [_vp, C.c_int]
+    lib.nbg_device_id.restype = C.c_int
     lib.nbg_count_running.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp]
     lib.nbg_count_running.restype = C.c_int
     lib.nbg_count_running_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]

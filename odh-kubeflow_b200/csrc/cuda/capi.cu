@@ -334,6 +334,9 @@ void nbg_destroy(nbg_ctx* ctx) {
 }
 
 int nbg_device_count(const nbg_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+int nbg_device_id(const nbg_ctx* ctx, int device) {
+  return (ctx && device >= 0 && device < (int)ctx->devs.size()) ? ctx->devs[device]->id : -1;
+}
 uint64_t nbg_launch_count(const nbg_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
 
 void* nbg_alloc_pinned(size_t bytes) {

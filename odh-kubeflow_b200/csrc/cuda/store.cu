@@ -1,0 +1,488 @@
+// store.cu — a resident fleet: the batches of a reconcile step kept in device memory and
+// edited in place (include/nbgraft.h, "resident fleet").
+//
+// Built on the public C ABI only: a step over the store is nbg_step_device on batch structs whose
+// variable-length parts are SPANS (off,end) into the store's heaps.
+//
+//   fixed arrays   one row per slot (replicas, masks, tiles, annotation instants, ...)
+//   heaps          one per variable-length array: payload buffer + per-slot start/end (device)
+//                  + per-slot length (host mirror, to account live/garbage and to plan compaction)
+//   put            H2D of the m rows into a staging arena, one scatter kernel per fixed array;
+//                  each heap's m runs arrive as ONE contiguous copy to the heap's tail (they are
+//                  contiguous in the caller's CSR batch) and only their start/end are scattered
+//   compaction     when a heap cannot take the next put: live runs are copied, slot by slot, into a
+//                  fresh buffer (twice the live size if more than half of the old one was live)
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../../include/nbgraft.h"
+
+namespace {
+
+// ---------------------------------------------------------------- kernels
+// dst row idx[k] <- src row k; rows are `words` 4-byte words wide.
+__global__ void __launch_bounds__(256)
+scatter_rows4_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, const uint64_t* __restrict__ idx,
+                     unsigned long long m, unsigned words) {
+  const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= m * words) return;
+  const unsigned long long k = t / words;
+  const unsigned w = (unsigned)(t - k * words);
+  dst[idx[k] * words + w] = src[t];
+}
+// one byte per row
+__global__ void __launch_bounds__(256)
+scatter_rows1_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, const uint64_t* __restrict__ idx,
+                     unsigned long long m) {
+  const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < m) dst[idx[k]] = src[k];
+}
+// Compaction: slot j's run moves from old[start[j] .. end[j]) to fresh[new_start[j] ..); a warp per
+// slot, `words` 4-byte words per element.  start/end are rewritten in place.
+__global__ void __launch_bounds__(256)
+compact_runs_kernel(uint32_t* __restrict__ fresh, const uint32_t* __restrict__ old, uint32_t* __restrict__ start,
+                    uint32_t* __restrict__ end, const uint32_t* __restrict__ new_start, unsigned long long slots,
+                    unsigned words, bool rewrite) {
+  const unsigned long long j = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned lane = threadIdx.x & 31u;
+  if (j >= slots) return;
+  const unsigned s = start[j], e = end[j], ns = new_start[j];
+  const unsigned long long n = (unsigned long long)(e - s) * words;
+  const uint32_t* from = old + (unsigned long long)s * words;
+  uint32_t* to = fresh + (unsigned long long)ns * words;
+  for (unsigned long long w = lane; w < n; w += 32u) to[w] = from[w];
+  __syncwarp();
+  if (rewrite && lane == 0) { start[j] = ns; end[j] = ns + (e - s); }
+}
+
+#define CUS(call) do { if ((call) != cudaSuccess) { cudaGetLastError(); return NBG_E_CUDA; } } while (0)
+
+// ---------------------------------------------------------------- data
+struct Fixed {                 // one fixed-width per-slot array
+  size_t width = 0;            // bytes per slot
+  char* data = nullptr;
+};
+
+struct Heap {                  // one variable-length array (or two that share an index space)
+  int payloads = 1;
+  size_t elem[2] = {0, 0};     // bytes per element of each payload
+  unsigned align = 1;          // every run starts at a multiple of `align` elements
+  char* data[2] = {nullptr, nullptr};
+  uint64_t cap = 0, used = 0, live = 0;      // elements
+  uint32_t *start = nullptr, *end = nullptr; // device, one per slot
+  std::vector<uint32_t> len;                 // host mirror of end - start
+};
+
+enum FixedId {
+  F_REP_F, F_REP_T, F_TMPL_F, F_TMPL_T, F_MASK_F, F_MASK_T,          // StatefulSet
+  F_SVC_NAME, F_SVC_PORT, F_SVC_FLAGS, F_SVC_PORTS,                  // Service
+  F_VS_PREFIX, F_VS_REWRITE, F_VS_HOST, F_VS_FLAGS, F_VS_SPEC,       // VirtualService
+  F_ANN_SEC, F_ANN_NSF, F_CHK_SEC, F_CHK_NSF, F_NB_FLAGS,            // culler
+  F_COUNT
+};
+const size_t kFixedWidth[F_COUNT] = {4, 4, 8, 8, 24, 24, 8, 4, 1, NBG_SVC_SLOTS * 8, 8, 8, 8, 1, NBG_VS_SLOTS * 8, 8, 4, 8, 4, 1};
+
+enum HeapId {
+  H_POD_F, H_POD_T, H_LAB_F, H_LAB_T, H_ANN_F, H_ANN_T,              // StatefulSet
+  H_SVC_LAB, H_SVC_ANN, H_SVC_SEL,                                   // Service
+  H_VS_HDR_F, H_VS_HDR_T,                                            // VirtualService
+  H_KERNELS, H_TERMINALS,                                            // culler (sec + nsf)
+  H_COUNT
+};
+
+}  // namespace
+
+struct nbg_store {
+  nbg_ctx* ctx = nullptr;
+  int device = 0, cuda_id = 0;
+  uint64_t capacity = 0;
+  cudaStream_t stream = nullptr;
+  Fixed fixed[F_COUNT];
+  Heap heap[H_COUNT];
+  char* stage = nullptr;       // grow-only staging arena for put
+  size_t stage_cap = 0, stage_at = 0;
+  char* outs = nullptr;        // grow-only device outputs of nbg_store_step
+  size_t outs_cap = 0;
+  uint64_t compactions = 0, puts = 0, rows_put = 0;
+  std::mutex mu;
+};
+
+namespace {
+
+constexpr size_t kStageAlign = 256;
+
+// Bump allocation in the staging arena (sized for the whole put before anything is queued).
+char* stage_take(nbg_store* st, size_t bytes) {
+  char* p = st->stage + st->stage_at;
+  st->stage_at += (bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
+  return p;
+}
+
+// src (host, m rows of `width` bytes) -> staging -> rows idx[] of dst
+int scatter_from_host(nbg_store* st, char* dst, const void* src, const uint64_t* idx_dev, uint64_t m, size_t width) {
+  if (!src) return NBG_E_INVAL;
+  char* tmp = stage_take(st, m * width);
+  CUS(cudaMemcpyAsync(tmp, src, m * width, cudaMemcpyHostToDevice, st->stream));
+  if (width == 1) {
+    scatter_rows1_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st->stream>>>(
+        reinterpret_cast<uint8_t*>(dst), reinterpret_cast<const uint8_t*>(tmp), idx_dev, m);
+  } else {
+    const unsigned words = (unsigned)(width / 4);
+    scatter_rows4_kernel<<<(unsigned)((m * words + 255) / 256), 256, 0, st->stream>>>(
+        reinterpret_cast<uint32_t*>(dst), reinterpret_cast<const uint32_t*>(tmp), idx_dev, m, words);
+  }
+  CUS(cudaGetLastError());
+  return NBG_OK;
+}
+
+uint64_t round_up(uint64_t x, unsigned a) { return (x + a - 1) / a * a; }
+
+// Make room for `need` more elements at the tail of a heap: compact (and grow) when it is full.
+int heap_reserve(nbg_store* st, Heap& h, uint64_t need) {
+  if (h.used + need <= h.cap) return NBG_OK;
+  // plan the compacted layout on the host: live runs in slot order, each aligned
+  std::vector<uint32_t> new_start(st->capacity);
+  uint64_t at = 0;
+  for (uint64_t j = 0; j < st->capacity; ++j) {
+    new_start[j] = (uint32_t)at;
+    at = round_up(at + h.len[j], h.align);
+  }
+  uint64_t cap = h.cap;
+  if (at + need > cap / 2) cap = 2 * (at + need) + 1024;      // mostly live: grow
+  cap = round_up(cap, 4);
+  if (cap > 0xFFFFFFF0ull) return NBG_E_TOOBIG;               // spans are 32-bit
+  char* fresh[2] = {nullptr, nullptr};
+  for (int p = 0; p < h.payloads; ++p)
+    if (cudaMalloc(&fresh[p], cap * h.elem[p]) != cudaSuccess) {
+      cudaGetLastError();
+      if (p) cudaFree(fresh[0]);
+      return NBG_E_NOMEM;
+    }
+  if (at) {
+    uint32_t* ns_dev = nullptr;
+    if (cudaMalloc(&ns_dev, st->capacity * sizeof(uint32_t)) != cudaSuccess) {
+      cudaGetLastError();
+      for (int p = 0; p < h.payloads; ++p) cudaFree(fresh[p]);
+      return NBG_E_NOMEM;
+    }
+    cudaError_t e = cudaMemcpyAsync(ns_dev, new_start.data(), st->capacity * sizeof(uint32_t), cudaMemcpyHostToDevice, st->stream);
+    const unsigned grid = (unsigned)((st->capacity * 32 + 255) / 256);
+    for (int p = 0; p < h.payloads && e == cudaSuccess; ++p) {
+      compact_runs_kernel<<<grid, 256, 0, st->stream>>>(
+          reinterpret_cast<uint32_t*>(fresh[p]), reinterpret_cast<const uint32_t*>(h.data[p]), h.start, h.end, ns_dev,
+          st->capacity, (unsigned)(h.elem[p] / 4), p == h.payloads - 1);     // spans rewritten after the last payload
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st->stream);            // new_start (host) and ns_dev die here
+    cudaFree(ns_dev);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      for (int p = 0; p < h.payloads; ++p) cudaFree(fresh[p]);
+      return NBG_E_CUDA;
+    }
+  } else {
+    CUS(cudaStreamSynchronize(st->stream));
+  }
+  for (int p = 0; p < h.payloads; ++p) {
+    if (h.data[p]) cudaFree(h.data[p]);
+    h.data[p] = fresh[p];
+  }
+  h.cap = cap;
+  h.used = at;
+  if (h.live) st->compactions++;
+  return NBG_OK;
+}
+
+// m runs, contiguous in the caller's CSR arrays, appended to the heap; slots idx_host[k] point at them.
+// `spans` (host scratch, 2*m) receives the new starts and ends, which are then scattered.
+int heap_put(nbg_store* st, Heap& h, const uint32_t* off, const void* payload0, const void* payload1,
+             const uint64_t* idx_host, const uint64_t* idx_dev, uint64_t m, std::vector<uint32_t>& spans) {
+  if (!off) return NBG_E_INVAL;
+  unsigned bad = 0;
+  for (uint64_t k = 0; k < m; ++k) bad |= (unsigned)(off[k] > off[k + 1]) | (off[k] % h.align != 0);
+  if (bad) return NBG_E_RANGE;
+  const uint64_t total = off[m] - off[0];
+  if (total && (!payload0 || (h.payloads > 1 && !payload1))) return NBG_E_INVAL;
+  const uint64_t need = round_up(total, h.align);
+  if (int rc = heap_reserve(st, h, need)) return rc;
+  const void* src[2] = {payload0, payload1};
+  for (int p = 0; p < h.payloads; ++p)
+    if (total)
+      CUS(cudaMemcpyAsync(h.data[p] + h.used * h.elem[p], static_cast<const char*>(src[p]) + (size_t)off[0] * h.elem[p],
+                          total * h.elem[p], cudaMemcpyHostToDevice, st->stream));
+  spans.resize(2 * m);
+  for (uint64_t k = 0; k < m; ++k) {
+    const uint32_t len = off[k + 1] - off[k];
+    spans[k] = (uint32_t)(h.used + (off[k] - off[0]));
+    spans[m + k] = spans[k] + len;
+    uint32_t& old = h.len[idx_host[k]];
+    h.live += len;
+    h.live -= old;
+    old = len;
+  }
+  h.used += need;
+  // the scatter copies `spans` into staging before this function's caller can touch it again
+  if (int rc = scatter_from_host(st, reinterpret_cast<char*>(h.start), spans.data(), idx_dev, m, 4)) return rc;
+  if (int rc = scatter_from_host(st, reinterpret_cast<char*>(h.end), spans.data() + m, idx_dev, m, 4)) return rc;
+  // `spans` is pageable memory: cudaMemcpyAsync from it has been staged by the driver on return
+  return NBG_OK;
+}
+
+nbg_kvmap span_map(const Heap& h) {
+  nbg_kvmap m{};
+  m.off = h.start;
+  m.end = h.end;
+  m.ent = reinterpret_cast<const nbg_kv*>(h.data[0]);
+  return m;
+}
+nbg_podsparse span_sparse(const Fixed& mask, const Heap& h) {
+  nbg_podsparse p{};
+  p.mask = reinterpret_cast<const uint64_t*>(mask.data);
+  p.off = h.start;
+  p.end = h.end;
+  p.val = reinterpret_cast<const uint64_t*>(h.data[0]);
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+void nbg_store_destroy(nbg_store* st) {
+  if (!st) return;
+  cudaSetDevice(st->cuda_id);
+  if (st->stream) cudaStreamSynchronize(st->stream);
+  for (auto& f : st->fixed) if (f.data) cudaFree(f.data);
+  for (auto& h : st->heap) {
+    for (int p = 0; p < h.payloads; ++p) if (h.data[p]) cudaFree(h.data[p]);
+    if (h.start) cudaFree(h.start);
+    if (h.end) cudaFree(h.end);
+  }
+  if (st->stage) cudaFree(st->stage);
+  if (st->outs) cudaFree(st->outs);
+  if (st->stream) cudaStreamDestroy(st->stream);
+  delete st;
+}
+
+int nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** out) {
+  if (!ctx || !out || capacity == 0) return NBG_E_INVAL;
+  *out = nullptr;
+  const int id = nbg_device_id(ctx, device);
+  if (id < 0) return NBG_E_INVAL;
+  if (capacity > 0x7FFFFFFFull) return NBG_E_TOOBIG;
+  nbg_store* st = new (std::nothrow) nbg_store();
+  if (!st) return NBG_E_NOMEM;
+  st->ctx = ctx; st->device = device; st->cuda_id = id; st->capacity = capacity;
+  bool ok = cudaSetDevice(id) == cudaSuccess && cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) == cudaSuccess;
+  for (int f = 0; ok && f < F_COUNT; ++f) {
+    st->fixed[f].width = kFixedWidth[f];
+    ok = cudaMalloc(&st->fixed[f].data, capacity * kFixedWidth[f]) == cudaSuccess &&
+         cudaMemsetAsync(st->fixed[f].data, 0, capacity * kFixedWidth[f], st->stream) == cudaSuccess;
+  }
+  for (int k = 0; ok && k < H_COUNT; ++k) {
+    Heap& h = st->heap[k];
+    const bool records = k == H_KERNELS || k == H_TERMINALS, pod = k == H_POD_F || k == H_POD_T;
+    h.payloads = records ? 2 : 1;
+    h.elem[0] = (records || pod) ? 8 : sizeof(nbg_kv);
+    h.elem[1] = records ? 4 : 0;
+    h.align = pod ? 2 : 1;                               // sparse runs stay 16-byte aligned
+    try { h.len.assign(capacity, 0u); } catch (...) { ok = false; break; }
+    ok = cudaMalloc(&h.start, capacity * 4) == cudaSuccess && cudaMalloc(&h.end, capacity * 4) == cudaSuccess &&
+         cudaMemsetAsync(h.start, 0, capacity * 4, st->stream) == cudaSuccess &&
+         cudaMemsetAsync(h.end, 0, capacity * 4, st->stream) == cudaSuccess;
+  }
+  ok = ok && cudaStreamSynchronize(st->stream) == cudaSuccess;
+  if (!ok) { cudaGetLastError(); nbg_store_destroy(st); return NBG_E_NOMEM; }
+  *out = st;
+  return NBG_OK;
+}
+
+int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_sparse_batch* sts,
+                  const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull) {
+  if (!st || (m && !idx)) return NBG_E_INVAL;
+  if (m == 0 || !(sts || svc || vs || cull)) return NBG_OK;
+  for (uint64_t k = 0; k < m; ++k) if (idx[k] >= st->capacity) return NBG_E_RANGE;
+  // spans are not accepted here: the rows arrive as plain CSR batches
+  if (sts && (sts->pod_from.end || sts->pod_to.end || sts->labels_from.end || sts->labels_to.end || sts->ann_from.end || sts->ann_to.end))
+    return NBG_E_INVAL;
+  if (svc && (svc->labels_to.end || svc->ann_to.end || svc->sel_to.end)) return NBG_E_INVAL;
+  if (vs && (vs->hdr_from.end || vs->hdr_to.end)) return NBG_E_INVAL;
+  if (cull && (cull->k_end || cull->t_end)) return NBG_E_INVAL;
+  std::unique_lock<std::mutex> lock(st->mu);
+  CUS(cudaSetDevice(st->cuda_id));
+  // staging: every fixed row + 2 span words per heap + the index list, each rounded to the arena alignment
+  size_t need = m * 8 + kStageAlign;
+  for (int f = 0; f < F_COUNT; ++f) need += m * kFixedWidth[f] + kStageAlign;
+  need += (size_t)H_COUNT * 2 * (m * 4 + kStageAlign);
+  if (need > st->stage_cap) {
+    CUS(cudaStreamSynchronize(st->stream));
+    if (st->stage) cudaFree(st->stage);
+    st->stage = nullptr; st->stage_cap = 0;
+    if (cudaMalloc(&st->stage, need + need / 2) != cudaSuccess) { cudaGetLastError(); return NBG_E_NOMEM; }
+    st->stage_cap = need + need / 2;
+  }
+  st->stage_at = 0;
+  uint64_t* idx_dev = reinterpret_cast<uint64_t*>(stage_take(st, m * 8));
+  CUS(cudaMemcpyAsync(idx_dev, idx, m * 8, cudaMemcpyHostToDevice, st->stream));
+  std::vector<uint32_t> spans;
+  int rc = NBG_OK;
+  auto fixed = [&](int f, const void* src) { if (rc == NBG_OK) rc = scatter_from_host(st, st->fixed[f].data, src, idx_dev, m, kFixedWidth[f]); };
+  auto heap = [&](int k, const uint32_t* off, const void* p0, const void* p1 = nullptr) {
+    if (rc == NBG_OK) rc = heap_put(st, st->heap[k], off, p0, p1, idx, idx_dev, m, spans);
+  };
+  if (sts) {
+    fixed(F_REP_F, sts->replicas_from); fixed(F_REP_T, sts->replicas_to);
+    fixed(F_TMPL_F, sts->tmpl_from); fixed(F_TMPL_T, sts->tmpl_to);
+    fixed(F_MASK_F, sts->pod_from.mask); fixed(F_MASK_T, sts->pod_to.mask);
+    heap(H_POD_F, sts->pod_from.off, sts->pod_from.val); heap(H_POD_T, sts->pod_to.off, sts->pod_to.val);
+    heap(H_LAB_F, sts->labels_from.off, sts->labels_from.ent); heap(H_LAB_T, sts->labels_to.off, sts->labels_to.ent);
+    heap(H_ANN_F, sts->ann_from.off, sts->ann_from.ent); heap(H_ANN_T, sts->ann_to.off, sts->ann_to.ent);
+  }
+  if (svc) {
+    fixed(F_SVC_NAME, svc->name_hash); fixed(F_SVC_PORT, svc->target_port);
+    fixed(F_SVC_FLAGS, svc->flags); fixed(F_SVC_PORTS, svc->ports_to);
+    heap(H_SVC_LAB, svc->labels_to.off, svc->labels_to.ent); heap(H_SVC_ANN, svc->ann_to.off, svc->ann_to.ent);
+    heap(H_SVC_SEL, svc->sel_to.off, svc->sel_to.ent);
+  }
+  if (vs) {
+    fixed(F_VS_PREFIX, vs->prefix_hash); fixed(F_VS_REWRITE, vs->rewrite_hash); fixed(F_VS_HOST, vs->host_hash);
+    fixed(F_VS_FLAGS, vs->flags); fixed(F_VS_SPEC, vs->spec_to);
+    heap(H_VS_HDR_F, vs->hdr_from.off, vs->hdr_from.ent); heap(H_VS_HDR_T, vs->hdr_to.off, vs->hdr_to.ent);
+  }
+  if (cull) {
+    fixed(F_ANN_SEC, cull->ann_sec); fixed(F_ANN_NSF, cull->ann_nsf);
+    fixed(F_CHK_SEC, cull->chk_sec); fixed(F_CHK_NSF, cull->chk_nsf); fixed(F_NB_FLAGS, cull->nb_flags);
+    heap(H_KERNELS, cull->k_off, cull->k_sec, cull->k_nsf); heap(H_TERMINALS, cull->t_off, cull->t_sec, cull->t_nsf);
+  }
+  // the caller's buffers (possibly pinned: truly asynchronous copies) are borrowed only until we return
+  if (cudaStreamSynchronize(st->stream) != cudaSuccess) { cudaGetLastError(); if (rc == NBG_OK) rc = NBG_E_CUDA; }
+  if (rc == NBG_OK) { st->puts++; st->rows_put += m; }
+  return rc;
+}
+
+static void store_views(const nbg_store* st, nbg_sts_sparse_batch* sts, nbg_svc_gen_batch* svc, nbg_vs_gen_batch* vs,
+                        nbg_cull_batch* cull) {
+  const Fixed* f = st->fixed;
+  const Heap* h = st->heap;
+  *sts = nbg_sts_sparse_batch{};
+  sts->replicas_from = reinterpret_cast<const int32_t*>(f[F_REP_F].data);
+  sts->replicas_to = reinterpret_cast<const int32_t*>(f[F_REP_T].data);
+  sts->tmpl_from = reinterpret_cast<const uint64_t*>(f[F_TMPL_F].data);
+  sts->tmpl_to = reinterpret_cast<const uint64_t*>(f[F_TMPL_T].data);
+  sts->pod_from = span_sparse(f[F_MASK_F], h[H_POD_F]);
+  sts->pod_to = span_sparse(f[F_MASK_T], h[H_POD_T]);
+  sts->labels_from = span_map(h[H_LAB_F]); sts->labels_to = span_map(h[H_LAB_T]);
+  sts->ann_from = span_map(h[H_ANN_F]); sts->ann_to = span_map(h[H_ANN_T]);
+  *svc = nbg_svc_gen_batch{};
+  svc->name_hash = reinterpret_cast<const uint64_t*>(f[F_SVC_NAME].data);
+  svc->target_port = reinterpret_cast<const int32_t*>(f[F_SVC_PORT].data);
+  svc->flags = reinterpret_cast<const uint8_t*>(f[F_SVC_FLAGS].data);
+  svc->ports_to = reinterpret_cast<const uint64_t*>(f[F_SVC_PORTS].data);
+  svc->labels_to = span_map(h[H_SVC_LAB]); svc->ann_to = span_map(h[H_SVC_ANN]); svc->sel_to = span_map(h[H_SVC_SEL]);
+  *vs = nbg_vs_gen_batch{};
+  vs->prefix_hash = reinterpret_cast<const uint64_t*>(f[F_VS_PREFIX].data);
+  vs->rewrite_hash = reinterpret_cast<const uint64_t*>(f[F_VS_REWRITE].data);
+  vs->host_hash = reinterpret_cast<const uint64_t*>(f[F_VS_HOST].data);
+  vs->flags = reinterpret_cast<const uint8_t*>(f[F_VS_FLAGS].data);
+  vs->spec_to = reinterpret_cast<const uint64_t*>(f[F_VS_SPEC].data);
+  vs->hdr_from = span_map(h[H_VS_HDR_F]); vs->hdr_to = span_map(h[H_VS_HDR_T]);
+  *cull = nbg_cull_batch{};
+  cull->k_off = h[H_KERNELS].start; cull->k_end = h[H_KERNELS].end;
+  cull->k_sec = reinterpret_cast<const int64_t*>(h[H_KERNELS].data[0]);
+  cull->k_nsf = reinterpret_cast<const uint32_t*>(h[H_KERNELS].data[1]);
+  cull->t_off = h[H_TERMINALS].start; cull->t_end = h[H_TERMINALS].end;
+  cull->t_sec = reinterpret_cast<const int64_t*>(h[H_TERMINALS].data[0]);
+  cull->t_nsf = reinterpret_cast<const uint32_t*>(h[H_TERMINALS].data[1]);
+  cull->ann_sec = reinterpret_cast<const int64_t*>(f[F_ANN_SEC].data);
+  cull->ann_nsf = reinterpret_cast<const uint32_t*>(f[F_ANN_NSF].data);
+  cull->chk_sec = reinterpret_cast<const int64_t*>(f[F_CHK_SEC].data);
+  cull->chk_nsf = reinterpret_cast<const uint32_t*>(f[F_CHK_NSF].data);
+  cull->nb_flags = reinterpret_cast<const uint8_t*>(f[F_NB_FLAGS].data);
+}
+
+int nbg_store_step_device(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts, const nbg_cull_params* params,
+                          const nbg_step_outputs* out, void* stream) {
+  if (!st || !out) return NBG_E_INVAL;
+  if (n > st->capacity) return NBG_E_RANGE;
+  if (n == 0) return NBG_OK;
+  nbg_sts_sparse_batch sts; nbg_svc_gen_batch svc; nbg_vs_gen_batch vs; nbg_cull_batch cull;
+  {
+    std::unique_lock<std::mutex> lock(st->mu);          // a put may be swapping heap buffers
+    store_views(st, &sts, &svc, &vs, &cull);
+  }
+  // a predicate takes part when its outputs are given
+  const bool do_sts = out->sts_reason && out->sts_bitmap, do_svc = out->svc_reason && out->svc_bitmap,
+             do_vs = out->vs_reason && out->vs_bitmap && vs_consts,
+             do_cull = out->action && out->argmax && out->cull_bitmap && out->period_bitmap && params;
+  return nbg_step_device(st->ctx, st->device, do_sts ? &sts : nullptr, do_svc ? &svc : nullptr, do_vs ? &vs : nullptr,
+                         vs_consts, do_cull ? &cull : nullptr, params, n, out, stream, nullptr, nullptr);
+}
+
+int nbg_store_step(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts, const nbg_cull_params* params,
+                   const nbg_step_outputs* out) {
+  if (!st || !out) return NBG_E_INVAL;
+  if (n > st->capacity) return NBG_E_RANGE;
+  if (n == 0) return NBG_OK;
+  const size_t words = (n + 63) / 64, bm = words * 8, row = (n + 255) / 256 * 256, bmr = (bm + 255) / 256 * 256;
+  const size_t need = 3 * (row + bmr) + row + (n * 4 + 255) / 256 * 256 + 2 * bmr;
+  char* base;
+  {
+    std::unique_lock<std::mutex> lock(st->mu);
+    CUS(cudaSetDevice(st->cuda_id));
+    if (need > st->outs_cap) {
+      CUS(cudaStreamSynchronize(st->stream));
+      if (st->outs) cudaFree(st->outs);
+      st->outs = nullptr; st->outs_cap = 0;
+      if (cudaMalloc(&st->outs, need) != cudaSuccess) { cudaGetLastError(); return NBG_E_NOMEM; }
+      st->outs_cap = need;
+    }
+    base = st->outs;
+  }
+  nbg_step_outputs d{};
+  char* at = base;
+  auto take = [&](size_t bytes) { char* p = at; at += (bytes + 255) / 256 * 256; return p; };
+  if (out->sts_reason && out->sts_bitmap) { d.sts_reason = (uint8_t*)take(n); d.sts_bitmap = (uint64_t*)take(bm); }
+  if (out->svc_reason && out->svc_bitmap) { d.svc_reason = (uint8_t*)take(n); d.svc_bitmap = (uint64_t*)take(bm); }
+  if (out->vs_reason && out->vs_bitmap) { d.vs_reason = (uint8_t*)take(n); d.vs_bitmap = (uint64_t*)take(bm); }
+  if (out->action && out->argmax && out->cull_bitmap && out->period_bitmap) {
+    d.action = (uint8_t*)take(n); d.argmax = (uint32_t*)take(n * 4);
+    d.cull_bitmap = (uint64_t*)take(bm); d.period_bitmap = (uint64_t*)take(bm);
+  }
+  if (int rc = nbg_store_step_device(st, n, vs_consts, params, &d, st->stream)) return rc;
+  auto back = [&](void* host, const void* dev, size_t bytes) {
+    return !dev || cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, st->stream) == cudaSuccess;
+  };
+  bool ok = back(out->sts_reason, d.sts_reason, n) && back(out->sts_bitmap, d.sts_bitmap, bm) &&
+            back(out->svc_reason, d.svc_reason, n) && back(out->svc_bitmap, d.svc_bitmap, bm) &&
+            back(out->vs_reason, d.vs_reason, n) && back(out->vs_bitmap, d.vs_bitmap, bm) &&
+            back(out->action, d.action, n) && back(out->argmax, d.argmax, n * 4) &&
+            back(out->cull_bitmap, d.cull_bitmap, bm) && back(out->period_bitmap, d.period_bitmap, bm);
+  if (cudaStreamSynchronize(st->stream) != cudaSuccess) ok = false;
+  if (!ok) { cudaGetLastError(); return NBG_E_CUDA; }
+  return NBG_OK;
+}
+
+int nbg_store_get_stats(const nbg_store* st, nbg_store_stats* out) {
+  if (!st || !out) return NBG_E_INVAL;
+  *out = nbg_store_stats{};
+  out->capacity = st->capacity;
+  for (const auto& f : st->fixed) out->fixed_bytes += st->capacity * f.width;
+  for (const auto& h : st->heap) {
+    const uint64_t per = h.elem[0] + h.elem[1];
+    out->fixed_bytes += st->capacity * 8;                 // the two span words of every slot
+    out->heap_bytes += h.cap * per;
+    out->live_bytes += h.live * per;
+    out->garbage_bytes += (h.used - h.live) * per;
+  }
+  out->compactions = st->compactions;
+  out->puts = st->puts;
+  out->rows_put = st->rows_put;
+  return NBG_OK;
+}
+
+}  // extern "C"

@@ -308,3 +308,56 @@ def bitmap_to_bools(bitmap, n):
     """uint64 words -> bool[n] (bit i of word i//64)."""
     bits = np.unpackbits(bitmap.view(np.uint8), bitorder="little")
     return bits[:n].astype(bool)
+
+
+class Store:
+    """A resident fleet (nbg_store_*): packed rows live in device memory, put() replaces the rows of given
+    slots from host batches of as many objects, step() runs the four predicates over slots [0, n)."""
+
+    def __init__(self, ctx, capacity, device=0):
+        self._lib, self.ctx, self.capacity = N.nbg(), ctx, capacity
+        h = C.c_void_p()
+        _check(self._lib.nbg_store_create(ctx.handle, device, capacity, C.byref(h)), "nbg_store_create")
+        self._h = h
+
+    def close(self):
+        if self._h:
+            self._lib.nbg_store_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def put(self, idx, sts_sparse=None, svc_gen=None, vs_gen=None, cull=None):
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        views = [b.view if b is not None else None for b in (sts_sparse, svc_gen, vs_gen, cull)]   # keep alive over the call
+        for b in (sts_sparse, svc_gen, vs_gen, cull):
+            assert b is None or len(b) == len(idx)
+        _check(self._lib.nbg_store_put(self._h, idx.ctypes.data_as(N.u64p), len(idx),
+                                       *[C.byref(v) if v is not None else None for v in views]), "nbg_store_put")
+
+    def step(self, n, vs_consts, now_sec, now_nsec, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE):
+        """-> the same dict as Context.step()."""
+        words = (n + 63) // 64
+        r = {k: (np.zeros(n, np.uint8), np.zeros(words, np.uint64)) for k in ("sts", "svc", "vs")}
+        action, argmax = np.zeros(n, np.uint8), np.zeros(n, np.uint32)
+        cb, pb = np.zeros(words, np.uint64), np.zeros(words, np.uint64)
+        o = N.nbg_step_outputs(*[a.ctypes.data for a in (r["sts"][0], r["sts"][1], r["svc"][0], r["svc"][1], r["vs"][0],
+                                                         r["vs"][1], action, argmax, cb, pb)])
+        p = N.nbg_cull_params(now_sec, now_nsec, cull_idle_min, check_period_min, mode)
+        _check(self._lib.nbg_store_step(self._h, n, C.byref(vs_consts), C.byref(p), C.byref(o)), "nbg_store_step")
+        r["cull"] = (action, argmax, cb, pb)
+        return r
+
+    def step_device(self, n, vs_consts, params, outputs, stream):
+        """Enqueue only: `outputs` is an nbg_step_outputs of DEVICE pointers, `stream` a cudaStream_t value."""
+        _check(self._lib.nbg_store_step_device(self._h, n, C.byref(vs_consts), C.byref(params), C.byref(outputs),
+                                               C.c_void_p(stream)), "nbg_store_step_device")
+
+    def stats(self):
+        s = N.nbg_store_stats()
+        _check(self._lib.nbg_store_get_stats(self._h, C.byref(s)), "nbg_store_get_stats")
+        return {k: getattr(s, k) for k, _ in s._fields_}
