@@ -495,9 +495,84 @@ def main():
                                 "packed_loops_note": "plain C loops over the same SoA batches, all %d objects, %d threads" % (per, threads)}
         if not args.no_extra:
             line["other_configs"] = other_configs(pkg, dev, ctx, torch, peak)
+            del d_sts, d_svc, d_vs, d_cull, batches, resident
+            torch.cuda.empty_cache()
+            line["other_configs"]["resident_store_1.25M"] = resident_store(
+                pkg, O, ctx, torch, fleet, per, (sts_sp, svc_g, vs_g, cull), now, want, sum(alg_bytes.values()), peak)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def resident_store(pkg, O, ctx, torch, fleet, per, host_batches, now, want, alg_bytes, peak):
+    """The same fleet held in an nbg_store: load, step from the store (spans instead of CSR), then ticks in which
+    1 % of the slots are replaced by other notebooks' rows before the step.  Parity after the last tick."""
+    host, N = pkg.host, pkg._native
+    sts_sp, svc_g, vs_g, cull = host_batches
+    store = pkg.engine.Store(ctx, per)
+    t0 = time.perf_counter()
+    store.put(np.arange(per, dtype=np.uint64), sts_sp, svc_g, vs_g, cull)
+    load_s = time.perf_counter() - t0
+    words = (per + 63) // 64
+    outs = {k: torch.empty(sz, dtype=torch.uint8, device="cuda") for k, sz in
+            (("sts_r", per), ("sts_b", words * 8), ("svc_r", per), ("svc_b", words * 8), ("vs_r", per), ("vs_b", words * 8),
+             ("act", per), ("amax", per * 4), ("cb", words * 8), ("pb", words * 8))}
+    o = N.nbg_step_outputs(*[outs[k].data_ptr() for k in ("sts_r", "sts_b", "svc_r", "svc_b", "vs_r", "vs_b", "act", "amax", "cb", "pb")])
+    consts = host.vs_gen_consts()
+    p = N.nbg_cull_params(now[0], now[1], 1440, 1, N.CULL_RECONCILE)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def device_step_ms(reps=20):
+        for _ in range(3):
+            store.step_device(per, consts, p, o, stream)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            store.step_device(per, consts, p, o, stream)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    fresh_ms = device_step_ms()
+    exp = {"sts": want["diff_sts"][0].copy(), "svc": want["diff_svc"][0].copy(), "vs": want["diff_vs"][0].copy(),
+           "act": want["cull"][0].copy(), "amax": want["cull"][1].copy()}
+    # ticks: 1 % of the slots take the rows of notebooks that were not in the fleet so far
+    rng = np.random.default_rng(7)
+    m = max(per // 100, 1)
+    ticks = []
+    for t in range(6):
+        slots = rng.choice(per, size=m, replace=False).astype(np.uint64)
+        alt = (per + t * m + np.arange(m)).astype(np.uint64) % np.uint64(fleet.n)
+        a_sts, a_svc, a_vs = fleet.pack(idx=alt)
+        a_cf = host.CullFleet(host.SEED_BASE + 900 + t, m)
+        a_cull = a_cf.pack()
+        rows = (a_sts.sparse(), a_svc.gen(), a_vs.gen(), a_cull)
+        t0 = time.perf_counter()
+        store.put(slots, *rows)
+        put_s = time.perf_counter() - t0
+        r = store.step(per, consts, now[0], now[1])                      # host outputs: the tick a controller would run
+        ticks.append((put_s, time.perf_counter() - t0))
+        exp["sts"][slots] = O.packed_diff_sts_sparse(rows[0])[0]
+        exp["svc"][slots] = O.packed_diff_svc(a_svc)[0]
+        exp["vs"][slots] = O.packed_diff_vs(a_vs)[0]
+        c = O.packed_cull(a_cull, now, 1440, 1, 1)
+        exp["act"][slots], exp["amax"][slots] = c[0], c[1]
+    ok = (np.array_equal(r["sts"][0], exp["sts"]) and np.array_equal(r["svc"][0], exp["svc"]) and np.array_equal(r["vs"][0], exp["vs"])
+          and np.array_equal(r["cull"][0], exp["act"]) and np.array_equal(r["cull"][1], exp["amax"]))
+    if not ok:
+        raise SystemExit("bench: the resident store differs from the packed oracle after replacements")
+    churned_ms = device_step_ms()
+    st = store.stats()
+    store.close()
+    put_ms = statistics.median(x[0] for x in ticks[1:]) * 1e3
+    tick_ms = statistics.median(x[1] for x in ticks[1:]) * 1e3
+    return {"load_seconds": load_s, "load_GBps": (alg_bytes / load_s) / 1e9,
+            "step_ms_fresh": fresh_ms, "step_objects_per_s_fresh": per / (fresh_ms * 1e-3), "step_frac_of_peak_fresh": alg_bytes / (fresh_ms * 1e-3) / 1e9 / peak,
+            "step_ms_after_6_ticks": churned_ms, "rows_replaced_per_tick": m,
+            "tick_ms": tick_ms, "tick_put_ms": put_ms, "tick_objects_per_s": per / (tick_ms * 1e-3),
+            "store": st, "parity": "bit-exact vs packed oracle after the last tick (replaced slots included)",
+            "note": "tick = nbg_store_put of 1 % of the rows (host buffers) + nbg_store_step over all 1.25 M slots with host outputs; "
+                    "packing the replaced rows is outside the tick (it happens when the informer delivers the object)"}
 
 
 def other_configs(pkg, dev, ctx, torch, peak):
