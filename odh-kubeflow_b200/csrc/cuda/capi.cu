@@ -58,7 +58,7 @@ thread_local char g_cuda_err[256] = "";
 
 bool cuda_ok(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return true;
-  snprintf(g_cuda_err, sizeof g_cuda_err, "%s: %s", what, cudaGetErrorString(e));
+  snprintf(g_cuda_err, sizeof g_cuda_err, "%.120s: %.120s", what, cudaGetErrorString(e));   // `what` may be a whole call
   return false;
 }
 #define CU(call) do { if (!cuda_ok((call), #call)) return NBG_E_CUDA; } while (0)

@@ -133,6 +133,47 @@ static void cull_known_answers(nbg_ctx* ctx) {
   }
 }
 
+/* The resident fleet from C: the StatefulSet rows of sts_known_answers() would need the sparse form, so this
+ * drives the culler rows only (a NULL batch leaves that predicate out): put three notebooks into slots 5, 0, 2
+ * of an 8-slot store, replace one of them, step. */
+static void store_known_answers(nbg_ctx* ctx) {
+  const int64_t now = 1767225600;
+  nbg_store* st = NULL;
+  uint64_t idx[3] = {5, 0, 2}, one[1] = {0};
+  /* last-activity: now-6 min, now-3 min, now (CULL_IDLE_TIME = 5) -> idle, not idle, not idle */
+  int64_t ann_sec[3] = {now - 360, now - 180, now}, chk_sec[3] = {0, 0, 0}, no_sec[1] = {0};
+  uint32_t ann_nsf[3] = {NBG_ANN_PARSE_OK, NBG_ANN_PARSE_OK, NBG_ANN_PARSE_OK}, chk_nsf[3] = {0, 0, 0}, off[4] = {0, 0, 0, 0}, no_nsf[1] = {0};
+  uint8_t nb_flags[3] = {NBG_NB_LA_PRESENT, NBG_NB_LA_PRESENT, NBG_NB_LA_PRESENT};
+  uint8_t action[8];
+  uint32_t argmax[8];
+  uint64_t cull_bits[1], period_bits[1];
+  nbg_cull_batch b;
+  nbg_cull_params p;
+  nbg_step_outputs out;
+  nbg_store_stats stats;
+
+  CHECK(nbg_store_create(ctx, 0, 8, &st) == NBG_OK && st != NULL, "nbg_store_create");
+  if (!st) return;
+  memset(&b, 0, sizeof b);
+  b.k_off = off; b.t_off = off; b.k_sec = no_sec; b.k_nsf = no_nsf; b.t_sec = no_sec; b.t_nsf = no_nsf;
+  b.ann_sec = ann_sec; b.ann_nsf = ann_nsf; b.chk_sec = chk_sec; b.chk_nsf = chk_nsf; b.nb_flags = nb_flags;
+  CHECK(nbg_store_put(st, idx, 3, NULL, NULL, NULL, &b) == NBG_OK, "nbg_store_put");
+  memset(&out, 0, sizeof out);
+  out.action = action; out.argmax = argmax; out.cull_bitmap = cull_bits; out.period_bitmap = period_bits;
+  p.now_sec = now; p.now_nsec = 0; p.cull_idle_min = 5; p.check_period_min = 1; p.mode = NBG_CULL_PREDICATES;
+  CHECK(nbg_store_step(st, 8, NULL, &p, &out) == NBG_OK, "nbg_store_step");
+  CHECK((action[5] & NBG_ACT_CULL) && !(action[0] & NBG_ACT_CULL) && !(action[2] & NBG_ACT_CULL), "idle slot is 5");
+  CHECK(cull_bits[0] == (1u << 5), "cull bitmap");
+  ann_sec[0] = now - 3600;                                    /* slot 0 now holds a notebook idle for an hour */
+  CHECK(nbg_store_put(st, one, 1, NULL, NULL, NULL, &b) == NBG_OK, "replace one row");
+  CHECK(nbg_store_step(st, 8, NULL, &p, &out) == NBG_OK, "step after the replacement");
+  CHECK(cull_bits[0] == ((1u << 5) | 1u), "slots 5 and 0 are idle now");
+  one[0] = 8;
+  CHECK(nbg_store_put(st, one, 1, NULL, NULL, NULL, &b) == NBG_E_RANGE, "slot past the capacity");
+  CHECK(nbg_store_get_stats(st, &stats) == NBG_OK && stats.puts == 2 && stats.rows_put == 4 && stats.capacity == 8, "stats");
+  nbg_store_destroy(st);
+}
+
 int main(void) {
   nbg_ctx* ctx = NULL;
   int rc;
@@ -151,7 +192,8 @@ int main(void) {
   if (rc != NBG_OK) return 1;
   sts_known_answers(ctx);
   cull_known_answers(ctx);
-  CHECK(nbg_launch_count(ctx) >= 4, "kernels were launched");
+  store_known_answers(ctx);
+  CHECK(nbg_launch_count(ctx) >= 6, "kernels were launched");
   nbg_destroy(ctx);
   if (failures) return 1;
   printf("ok %d checks\n", checks);
