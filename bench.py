@@ -109,42 +109,9 @@ def pinned_copy(lib, arrays, keep):
 
 
 def struct_over(N, kind, arr):
-    def p(name, ct):
-        return arr[name].ctypes.data_as(C.POINTER(ct))
-
-    def kv(prefix):
-        m = N.nbg_kvmap()
-        m.off = p(prefix + ".off", C.c_uint32)
-        m.ent = C.cast(arr[prefix + ".ent"].ctypes.data, C.POINTER(N.nbg_kv))
-        return m
-    if kind == "sts":
-        s = N.nbg_sts_sparse_batch()
-        s.replicas_from, s.replicas_to = p("replicas_from", C.c_int32), p("replicas_to", C.c_int32)
-        s.tmpl_from, s.tmpl_to = p("tmpl_from", C.c_uint64), p("tmpl_to", C.c_uint64)
-        for side in ("pod_from", "pod_to"):
-            ps = N.nbg_podsparse()
-            ps.mask, ps.off, ps.val = p(side + ".mask", C.c_uint64), p(side + ".voff", C.c_uint32), p(side + ".val", C.c_uint64)
-            setattr(s, side, ps)
-        for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
-            setattr(s, f, kv(f))
-    elif kind == "svc":
-        s = N.nbg_svc_gen_batch()
-        s.name_hash, s.target_port = p("name_hash", C.c_uint64), p("target_port", C.c_int32)
-        s.flags, s.ports_to = p("flags", C.c_uint8), p("ports_to", C.c_uint64)
-        for f in ("labels_to", "ann_to", "sel_to"):
-            setattr(s, f, kv(f))
-    elif kind == "vs":
-        s = N.nbg_vs_gen_batch()
-        s.prefix_hash, s.rewrite_hash, s.host_hash = p("prefix_hash", C.c_uint64), p("rewrite_hash", C.c_uint64), p("host_hash", C.c_uint64)
-        s.flags, s.spec_to = p("flags", C.c_uint8), p("spec_to", C.c_uint64)
-        s.hdr_from, s.hdr_to = kv("hdr_from"), kv("hdr_to")
-    else:
-        s = N.nbg_cull_batch()
-        for f, ct in (("k_off", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32), ("t_off", C.c_uint32),
-                      ("t_sec", C.c_int64), ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32),
-                      ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)):
-            setattr(s, f, p(f, ct))
-    return s
+    """The nbg_* batch struct over host arrays (here: pinned copies of a batch's arrays)."""
+    kind = {"sts": "StsSparseBatch", "svc": "svc_gen", "vs": "vs_gen", "cull": "CullBatch"}[kind]
+    return N.batch_struct(kind, lambda name, ct: arr[name].ctypes.data_as(C.POINTER(ct)), lambda name: name in arr)
 
 
 class CpuReference:

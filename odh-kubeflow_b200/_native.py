@@ -150,6 +150,58 @@ VS_SPEC_DIFFERS, VS_TO_MISSING, VS_FROM_MISSING = 1, 2, 4
 ACT_SRC_MASK, ACT_PERIOD, ACT_CULL, ACT_STOPPED, ACT_INIT, ACT_NOPOD = 3, 4, 8, 16, 32, 64
 CULL_PREDICATES, CULL_RECONCILE = 0, 1
 
+# ---- one place that knows which array goes into which field of which batch struct -----------------
+# Array names are those of host.*Batch.arrays(): "<map>.off/.ent[/.end]" for string maps,
+# "<side>.mask/.voff/.val[/.vend]" for sparse PodSpec tiles, plain field names otherwise.  `ptr(name, ctype)`
+# returns a ctypes pointer to that array wherever it lives (numpy, pinned memory, a device tensor), `has(name)`
+# says whether the optional span arrays exist.
+_KV_FIELDS = {"StsBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
+              "StsSparseBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
+              "SvcBatch": ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"),
+              "VsBatch": ("hdr_from", "hdr_to"), "svc_gen": ("labels_to", "ann_to", "sel_to"), "vs_gen": ("hdr_from", "hdr_to"),
+              "GenBatch": ("labels_a", "labels_b", "spec_a", "spec_b"), "RestartBatch": (), "CullBatch": ()}
+_SPARSE_FIELDS = {"StsSparseBatch": ("pod_from", "pod_to"), "RestartBatch": ("old_spec", "updated_spec", "mutated_spec")}
+_PLAIN_FIELDS = {
+    "StsBatch": (("replicas_from", C.c_int32), ("replicas_to", C.c_int32), ("tmpl_from", C.c_uint64), ("tmpl_to", C.c_uint64),
+                 ("pod_from", C.c_uint64), ("pod_to", C.c_uint64)),
+    "StsSparseBatch": (("replicas_from", C.c_int32), ("replicas_to", C.c_int32), ("tmpl_from", C.c_uint64), ("tmpl_to", C.c_uint64)),
+    "SvcBatch": (("flags", C.c_uint8), ("ports_from", C.c_uint64), ("ports_to", C.c_uint64)),
+    "VsBatch": (("flags", C.c_uint8), ("spec_from", C.c_uint64), ("spec_to", C.c_uint64)),
+    "svc_gen": (("name_hash", C.c_uint64), ("target_port", C.c_int32), ("flags", C.c_uint8), ("ports_to", C.c_uint64)),
+    "vs_gen": (("prefix_hash", C.c_uint64), ("rewrite_hash", C.c_uint64), ("host_hash", C.c_uint64), ("flags", C.c_uint8),
+               ("spec_to", C.c_uint64)),
+    "GenBatch": (), "RestartBatch": (("flags", C.c_uint8),),
+    "CullBatch": (("k_off", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32), ("t_off", C.c_uint32), ("t_sec", C.c_int64),
+                  ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32), ("chk_sec", C.c_int64),
+                  ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)),
+}
+
+
+def batch_struct(kind, ptr, has=lambda name: False):
+    cls = {"StsBatch": nbg_sts_batch, "StsSparseBatch": nbg_sts_sparse_batch, "SvcBatch": nbg_svc_batch, "VsBatch": nbg_vs_batch,
+           "svc_gen": nbg_svc_gen_batch, "vs_gen": nbg_vs_gen_batch, "GenBatch": nbg_generic_batch,
+           "RestartBatch": nbg_restart_batch, "CullBatch": nbg_cull_batch}[kind]
+    s = cls()
+    for name, ct in _PLAIN_FIELDS[kind]:
+        setattr(s, name, ptr(name, ct))
+    for name in _KV_FIELDS[kind]:
+        m = nbg_kvmap()
+        m.off = ptr(name + ".off", C.c_uint32)
+        m.ent = C.cast(ptr(name + ".ent", C.c_uint64), C.POINTER(nbg_kv))
+        if has(name + ".end"):
+            m.end = ptr(name + ".end", C.c_uint32)
+        setattr(s, name, m)
+    for side in _SPARSE_FIELDS.get(kind, ()):
+        ps = nbg_podsparse()
+        ps.mask, ps.off, ps.val = ptr(side + ".mask", C.c_uint64), ptr(side + ".voff", C.c_uint32), ptr(side + ".val", C.c_uint64)
+        if has(side + ".vend"):
+            ps.end = ptr(side + ".vend", C.c_uint32)
+        setattr(s, side, ps)
+    if kind == "CullBatch" and has("k_end"):
+        s.k_end, s.t_end = ptr("k_end", C.c_uint32), ptr("t_end", C.c_uint32)
+    return s
+
+
 NBG_SYMBOLS = [
     "nbg_init", "nbg_destroy", "nbg_strerror", "nbg_last_cuda_error", "nbg_abi_version", "nbg_device_count",
     "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of",

@@ -61,83 +61,10 @@ class DeviceBatch:
     def algorithmic_bytes(self):
         return self.in_bytes + self.out_bytes
 
-    def _p(self, name, ctype):
-        return C.cast(self.tensors[name].data_ptr(), C.POINTER(ctype))
-
-    def _kv(self, prefix):
-        m = N.nbg_kvmap()
-        m.off = self._p(prefix + ".off", C.c_uint32)
-        m.ent = C.cast(self.tensors[prefix + ".ent"].data_ptr(), C.POINTER(N.nbg_kv))
-        if prefix + ".end" in self.tensors:             # spans instead of CSR (include/nbgraft.h)
-            m.end = self._p(prefix + ".end", C.c_uint32)
-        return m
-
-    def _sparse(self, side):
-        ps = N.nbg_podsparse()
-        ps.mask, ps.off, ps.val = (self._p(side + ".mask", C.c_uint64), self._p(side + ".voff", C.c_uint32),
-                                   self._p(side + ".val", C.c_uint64))
-        if side + ".vend" in self.tensors:
-            ps.end = self._p(side + ".vend", C.c_uint32)
-        return ps
-
     def _build_struct(self):
-        k = self.kind
-        if k == "StsBatch":
-            s = N.nbg_sts_batch()
-            s.replicas_from, s.replicas_to = self._p("replicas_from", C.c_int32), self._p("replicas_to", C.c_int32)
-            s.tmpl_from, s.tmpl_to = self._p("tmpl_from", C.c_uint64), self._p("tmpl_to", C.c_uint64)
-            s.pod_from, s.pod_to = self._p("pod_from", C.c_uint64), self._p("pod_to", C.c_uint64)
-            for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
-                setattr(s, f, self._kv(f))
-        elif k == "StsSparseBatch":
-            s = N.nbg_sts_sparse_batch()
-            s.replicas_from, s.replicas_to = self._p("replicas_from", C.c_int32), self._p("replicas_to", C.c_int32)
-            s.tmpl_from, s.tmpl_to = self._p("tmpl_from", C.c_uint64), self._p("tmpl_to", C.c_uint64)
-            for side in ("pod_from", "pod_to"):
-                setattr(s, side, self._sparse(side))
-            for f in ("labels_from", "labels_to", "ann_from", "ann_to"):
-                setattr(s, f, self._kv(f))
-        elif k == "svc_gen":
-            s = N.nbg_svc_gen_batch()
-            s.name_hash, s.target_port = self._p("name_hash", C.c_uint64), self._p("target_port", C.c_int32)
-            s.flags, s.ports_to = self._p("flags", C.c_uint8), self._p("ports_to", C.c_uint64)
-            for f in ("labels_to", "ann_to", "sel_to"):
-                setattr(s, f, self._kv(f))
-        elif k == "vs_gen":
-            s = N.nbg_vs_gen_batch()
-            s.prefix_hash, s.rewrite_hash, s.host_hash = (self._p("prefix_hash", C.c_uint64), self._p("rewrite_hash", C.c_uint64),
-                                                          self._p("host_hash", C.c_uint64))
-            s.flags, s.spec_to = self._p("flags", C.c_uint8), self._p("spec_to", C.c_uint64)
-            s.hdr_from, s.hdr_to = self._kv("hdr_from"), self._kv("hdr_to")
-        elif k == "GenBatch":
-            s = N.nbg_generic_batch()
-            for f in ("labels_a", "labels_b", "spec_a", "spec_b"):
-                setattr(s, f, self._kv(f))
-        elif k == "RestartBatch":
-            s = N.nbg_restart_batch()
-            s.flags = self._p("flags", C.c_uint8)
-            for side in ("old_spec", "updated_spec", "mutated_spec"):
-                setattr(s, side, self._sparse(side))
-        elif k == "SvcBatch":
-            s = N.nbg_svc_batch()
-            s.flags = self._p("flags", C.c_uint8)
-            s.ports_from, s.ports_to = self._p("ports_from", C.c_uint64), self._p("ports_to", C.c_uint64)
-            for f in ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"):
-                setattr(s, f, self._kv(f))
-        elif k == "VsBatch":
-            s = N.nbg_vs_batch()
-            s.flags = self._p("flags", C.c_uint8)
-            s.spec_from, s.spec_to = self._p("spec_from", C.c_uint64), self._p("spec_to", C.c_uint64)
-            s.hdr_from, s.hdr_to = self._kv("hdr_from"), self._kv("hdr_to")
-        else:
-            s = N.nbg_cull_batch()
-            for f, ct in (("k_off", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32), ("t_off", C.c_uint32),
-                          ("t_sec", C.c_int64), ("t_nsf", C.c_uint32), ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32),
-                          ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32), ("nb_flags", C.c_uint8)):
-                setattr(s, f, self._p(f, ct))
-            if "k_end" in self.tensors:
-                s.k_end, s.t_end = self._p("k_end", C.c_uint32), self._p("t_end", C.c_uint32)
-        return s
+        def ptr(name, ctype):
+            return C.cast(self.tensors[name].data_ptr(), C.POINTER(ctype))
+        return N.batch_struct(self.kind, ptr, lambda name: name in self.tensors)
 
     def run(self, ctx, now=None, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE, stream=None):
         """Enqueue the kernel (asynchronous).  Returns the device output tensors."""

@@ -9,12 +9,7 @@ import oracle as O
 
 N = O.pkg._native
 
-KV = {"StsBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
-      "StsSparseBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
-      "SvcBatch": ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"),
-      "VsBatch": ("hdr_from", "hdr_to"), "svc_gen": ("labels_to", "ann_to", "sel_to"), "vs_gen": ("hdr_from", "hdr_to"),
-      "GenBatch": ("labels_a", "labels_b", "spec_a", "spec_b"), "RestartBatch": (), "CullBatch": ()}
-SPARSE = {"StsSparseBatch": ("pod_from", "pod_to"), "RestartBatch": ("old_spec", "updated_spec", "mutated_spec")}
+KV, SPARSE = N._KV_FIELDS, N._SPARSE_FIELDS
 
 
 def _scatter(off, payloads, rng, align, width):
@@ -74,57 +69,8 @@ class SpanBatch:
 
 def struct_over(sb):
     """The nbg_* batch struct over the HOST arrays of a SpanBatch (for the packed oracle)."""
-    a, k = sb.arrays(), sb.kind
-
-    def p(name, ct):
-        return a[name].ctypes.data_as(C.POINTER(ct))
-
-    def kv(prefix):
-        m = N.nbg_kvmap()
-        m.off, m.end = p(prefix + ".off", C.c_uint32), p(prefix + ".end", C.c_uint32)
-        m.ent = C.cast(a[prefix + ".ent"].ctypes.data, C.POINTER(N.nbg_kv))
-        return m
-
-    def sparse(side):
-        ps = N.nbg_podsparse()
-        ps.mask, ps.off, ps.end, ps.val = (p(side + ".mask", C.c_uint64), p(side + ".voff", C.c_uint32),
-                                           p(side + ".vend", C.c_uint32), p(side + ".val", C.c_uint64))
-        return ps
-    if k == "StsSparseBatch":
-        s = N.nbg_sts_sparse_batch()
-        s.replicas_from, s.replicas_to = p("replicas_from", C.c_int32), p("replicas_to", C.c_int32)
-        s.tmpl_from, s.tmpl_to = p("tmpl_from", C.c_uint64), p("tmpl_to", C.c_uint64)
-        s.pod_from, s.pod_to = sparse("pod_from"), sparse("pod_to")
-    elif k == "StsBatch":
-        s = N.nbg_sts_batch()
-        s.replicas_from, s.replicas_to = p("replicas_from", C.c_int32), p("replicas_to", C.c_int32)
-        s.tmpl_from, s.tmpl_to = p("tmpl_from", C.c_uint64), p("tmpl_to", C.c_uint64)
-        s.pod_from, s.pod_to = p("pod_from", C.c_uint64), p("pod_to", C.c_uint64)
-    elif k == "SvcBatch":
-        s = N.nbg_svc_batch()
-        s.flags, s.ports_from, s.ports_to = p("flags", C.c_uint8), p("ports_from", C.c_uint64), p("ports_to", C.c_uint64)
-    elif k == "VsBatch":
-        s = N.nbg_vs_batch()
-        s.flags, s.spec_from, s.spec_to = p("flags", C.c_uint8), p("spec_from", C.c_uint64), p("spec_to", C.c_uint64)
-    elif k == "GenBatch":
-        s = N.nbg_generic_batch()
-    elif k == "RestartBatch":
-        s = N.nbg_restart_batch()
-        s.flags = p("flags", C.c_uint8)
-        for side in SPARSE[k]:
-            setattr(s, side, sparse(side))
-    elif k == "CullBatch":
-        s = N.nbg_cull_batch()
-        for f, ct in (("k_off", C.c_uint32), ("k_end", C.c_uint32), ("k_sec", C.c_int64), ("k_nsf", C.c_uint32),
-                      ("t_off", C.c_uint32), ("t_end", C.c_uint32), ("t_sec", C.c_int64), ("t_nsf", C.c_uint32),
-                      ("ann_sec", C.c_int64), ("ann_nsf", C.c_uint32), ("chk_sec", C.c_int64), ("chk_nsf", C.c_uint32),
-                      ("nb_flags", C.c_uint8)):
-            setattr(s, f, p(f, ct))
-    else:
-        raise ValueError(k)
-    for name in KV[k]:
-        setattr(s, name, kv(name))
-    return s
+    a = sb.arrays()
+    return N.batch_struct(sb.kind, lambda name, ct: a[name].ctypes.data_as(C.POINTER(ct)), lambda name: name in a)
 
 
 class _Viewed:
