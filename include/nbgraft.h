@@ -336,9 +336,8 @@ int nbg_step_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* sts, c
  * heap addressed by per-notebook spans (off,end) — a replaced run is appended and the old one
  * becomes garbage; a heap that fills up is compacted (live runs copied in slot order) and grown
  * when more than half of it is still live.  A store belongs to one device of the context and must be
- * destroyed before it.  put and step may be called from different threads (the store serialises them);
- * a step enqueued with nbg_store_step_device must have finished before the next put that could compact
- * a heap (the caller orders them, e.g. by synchronising its stream once per tick). */
+ * destroyed before it.  put and step may be called from different threads (the store serialises them), and
+ * a put issued while a step enqueued with nbg_store_step_device is still running is ordered behind it. */
 typedef struct nbg_store nbg_store;
 int  nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** out);
 void nbg_store_destroy(nbg_store* st);

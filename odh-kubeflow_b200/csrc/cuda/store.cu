@@ -102,6 +102,8 @@ struct nbg_store {
   int device = 0, cuda_id = 0;
   uint64_t capacity = 0;
   cudaStream_t stream = nullptr;
+  cudaEvent_t step_done = nullptr;   // recorded on the caller's stream after every step: puts are ordered behind it
+  bool stepped = false;
   Fixed fixed[F_COUNT];
   Heap heap[H_COUNT];
   char* stage = nullptr;       // grow-only staging arena for put
@@ -110,6 +112,7 @@ struct nbg_store {
   size_t outs_cap = 0;
   uint64_t compactions = 0, puts = 0, rows_put = 0;
   std::mutex mu;
+  std::mutex step_mu;          // nbg_store_step: one user of `outs` at a time
 };
 
 namespace {
@@ -188,6 +191,7 @@ int heap_reserve(nbg_store* st, Heap& h, uint64_t need) {
   } else {
     CUS(cudaStreamSynchronize(st->stream));
   }
+  if (st->stepped) CUS(cudaEventSynchronize(st->step_done));   // a step still reading the old buffers must finish first
   for (int p = 0; p < h.payloads; ++p) {
     if (h.data[p]) cudaFree(h.data[p]);
     h.data[p] = fresh[p];
@@ -265,6 +269,7 @@ void nbg_store_destroy(nbg_store* st) {
   }
   if (st->stage) cudaFree(st->stage);
   if (st->outs) cudaFree(st->outs);
+  if (st->step_done) { cudaEventSynchronize(st->step_done); cudaEventDestroy(st->step_done); }
   if (st->stream) cudaStreamDestroy(st->stream);
   delete st;
 }
@@ -278,7 +283,8 @@ int nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** ou
   nbg_store* st = new (std::nothrow) nbg_store();
   if (!st) return NBG_E_NOMEM;
   st->ctx = ctx; st->device = device; st->cuda_id = id; st->capacity = capacity;
-  bool ok = cudaSetDevice(id) == cudaSuccess && cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) == cudaSuccess;
+  bool ok = cudaSetDevice(id) == cudaSuccess && cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaEventCreateWithFlags(&st->step_done, cudaEventDisableTiming) == cudaSuccess;
   for (int f = 0; ok && f < F_COUNT; ++f) {
     st->fixed[f].width = kFixedWidth[f];
     ok = cudaMalloc(&st->fixed[f].data, capacity * kFixedWidth[f]) == cudaSuccess &&
@@ -327,6 +333,7 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
     st->stage_cap = need + need / 2;
   }
   st->stage_at = 0;
+  if (st->stepped) CUS(cudaStreamWaitEvent(st->stream, st->step_done, 0));   // rows are rewritten only after the last step has read them
   uint64_t* idx_dev = reinterpret_cast<uint64_t*>(stage_take(st, m * 8));
   CUS(cudaMemcpyAsync(idx_dev, idx, m * 8, cudaMemcpyHostToDevice, st->stream));
   std::vector<uint32_t> spans;
@@ -411,16 +418,20 @@ int nbg_store_step_device(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs
   if (n > st->capacity) return NBG_E_RANGE;
   if (n == 0) return NBG_OK;
   nbg_sts_sparse_batch sts; nbg_svc_gen_batch svc; nbg_vs_gen_batch vs; nbg_cull_batch cull;
-  {
-    std::unique_lock<std::mutex> lock(st->mu);          // a put may be swapping heap buffers
-    store_views(st, &sts, &svc, &vs, &cull);
-  }
   // a predicate takes part when its outputs are given
   const bool do_sts = out->sts_reason && out->sts_bitmap, do_svc = out->svc_reason && out->svc_bitmap,
              do_vs = out->vs_reason && out->vs_bitmap && vs_consts,
              do_cull = out->action && out->argmax && out->cull_bitmap && out->period_bitmap && params;
-  return nbg_step_device(st->ctx, st->device, do_sts ? &sts : nullptr, do_svc ? &svc : nullptr, do_vs ? &vs : nullptr,
-                         vs_consts, do_cull ? &cull : nullptr, params, n, out, stream, nullptr, nullptr);
+  std::unique_lock<std::mutex> lock(st->mu);            // held over the enqueue: a put cannot swap a heap under it
+  CUS(cudaSetDevice(st->cuda_id));
+  store_views(st, &sts, &svc, &vs, &cull);
+  const int rc = nbg_step_device(st->ctx, st->device, do_sts ? &sts : nullptr, do_svc ? &svc : nullptr, do_vs ? &vs : nullptr,
+                                 vs_consts, do_cull ? &cull : nullptr, params, n, out, stream, nullptr, nullptr);
+  if (rc == NBG_OK) {
+    CUS(cudaEventRecord(st->step_done, (cudaStream_t)stream));
+    st->stepped = true;
+  }
+  return rc;
 }
 
 int nbg_store_step(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts, const nbg_cull_params* params,
@@ -428,6 +439,7 @@ int nbg_store_step(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts
   if (!st || !out) return NBG_E_INVAL;
   if (n > st->capacity) return NBG_E_RANGE;
   if (n == 0) return NBG_OK;
+  std::unique_lock<std::mutex> whole(st->step_mu);
   const size_t words = (n + 63) / 64, bm = words * 8, row = (n + 255) / 256 * 256, bmr = (bm + 255) / 256 * 256;
   const size_t need = 3 * (row + bmr) + row + (n * 4 + 255) / 256 * 256 + 2 * bmr;
   char* base;

@@ -104,3 +104,33 @@ def test_store_rejects_bad_arguments(ctx):
         assert np.array_equal(r["sts"][0], src.want["sts"][:8])
     finally:
         store.close()
+
+
+def test_put_right_behind_an_asynchronous_step(ctx):
+    """nbg_store_step_device only enqueues; a put issued straight after it (heap growth and compaction included)
+    must neither disturb that step's results nor free what it is reading."""
+    import torch
+    n = 30_000
+    a, b = Source(host.FLEET_KUBEFLOW, host.SEED_BASE + 51, n), Source(host.FLEET_ODH, host.SEED_BASE + 53, n)
+    store = pkg.engine.Store(ctx, n)
+    try:
+        all_slots = np.arange(n, dtype=np.uint64)
+        s1, s2, s3, s4, keep = a.rows(all_slots)
+        store.put(all_slots, s1, s2, s3, s4)
+        words = (n + 63) // 64
+        outs = [torch.full((sz,), 0xA5, dtype=torch.uint8, device="cuda") for sz in
+                (n, words * 8, n, words * 8, n, words * 8, n, n * 4, words * 8, words * 8)]
+        o = N.nbg_step_outputs(*[t.data_ptr() for t in outs])
+        p = N.nbg_cull_params(a.now[0], a.now[1], 1440, 1, 1)
+        big = b.rows(all_slots)                                   # ODH rows are larger: every heap has to grow
+        stream = torch.cuda.Stream()
+        for _ in range(3):
+            store.step_device(n, host.vs_gen_consts(), p, o, stream.cuda_stream)
+        store.put(all_slots, *big[:4])                            # returns after ITS copies; the steps were queued first
+        stream.synchronize()
+        assert np.array_equal(outs[0].cpu().numpy(), a.want["sts"])
+        assert np.array_equal(outs[6].cpu().numpy(), a.want["action"])
+        r = store.step(n, host.vs_gen_consts(), *a.now)
+        assert np.array_equal(r["sts"][0], b.want["sts"]) and np.array_equal(r["cull"][1], b.want["argmax"])
+    finally:
+        store.close()
