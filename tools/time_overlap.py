@@ -1,5 +1,5 @@
 """Step time with the three small kernels on side streams (fork/join), resident inputs.
-usage: [NBGRAFT_LIB=...] [NBG_SMALL_GRID_CAP=k] python tools/time_overlap.py 1250000"""
+usage: [NBGRAFT_LIB=...] [ORDER=sts_first] python tools/time_overlap.py 1250000"""
 import importlib, os, statistics, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -47,6 +47,6 @@ for rep in range(5):
     e.record(); torch.cuda.synchronize()
     ms.append(s.elapsed_time(e) / 20)
 med = statistics.median(ms)
-print("%s cap=%s order=%s  step %.1f us (min %.1f)  %.0f GB/s (%.3f of 6551)  %.2f G objects/s" % (
-    os.path.basename(os.environ.get("NBGRAFT_LIB", "default")), os.environ.get("NBG_SMALL_GRID_CAP", "0"), order,
+print("%s order=%s  step %.1f us (min %.1f)  %.0f GB/s (%.3f of 6551)  %.2f G objects/s" % (
+    os.path.basename(os.environ.get("NBGRAFT_LIB", "default")), order,
     med * 1e3, min(ms) * 1e3, total / (med * 1e-3) / 1e9, total / (med * 1e-3) / 1e9 / 6551, n / (med * 1e-3) / 1e9))
