@@ -165,6 +165,63 @@ __device__ __forceinline__ unsigned sparse_tiles_differ(const nbg_podsparse& a, 
   return bits;
 }
 
+// CSR form only.  There the value runs of a warp's 32 objects are ONE contiguous block per side, so the
+// warp sweeps the desired side's block 32 vectors per round, fully coalesced, instead of going object by
+// object: each lane finds the object its vector belongs to (binary search over the lanes' run starts, five
+// shuffles), reads the matching vector of the live side and records a difference under that object's bit.
+// Rounds do not depend on one another, so several are in flight at once.  Objects whose masks differ are
+// decided without their values being read, as above.
+#ifndef NBG_CSR_UNROLL
+#define NBG_CSR_UNROLL 2
+#endif
+constexpr int kCsrUnroll = NBG_CSR_UNROLL;
+__device__ __forceinline__ unsigned sparse_tiles_differ_csr(const nbg_podsparse& a, const nbg_podsparse& b,
+                                                            unsigned long long i, bool live, unsigned cnt, unsigned lane,
+                                                            unsigned a_base, unsigned b_base) {
+  unsigned fv0 = 0, fv1 = 0, tv0 = 0;                    // run start/end (desired) and start (live), in 16-byte vectors
+  bool mask_ne = false;
+  if (live) {
+    const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
+    const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
+    mask_ne = (__ldg(ma) != __ldg(mb)) | (__ldg(ma + 1) != __ldg(mb + 1)) | (__ldg(ma + 2) != __ldg(mb + 2));
+    fv0 = (__ldg(a.off + i) - a_base) >> 1;
+    fv1 = (__ldg(a.off + i + 1) - a_base) >> 1;
+    tv0 = (__ldg(b.off + i) - b_base) >> 1;
+  }
+  const unsigned ne_bits = __ballot_sync(FULL, mask_ne);
+  const unsigned first = __shfl_sync(FULL, fv0, 0), last = __shfl_sync(FULL, fv1, cnt - 1);
+  if (!live) fv0 = last;                                 // lanes past the end of the batch never own a vector
+  const uint4* av = reinterpret_cast<const uint4*>(a.val);
+  const uint4* bv = reinterpret_cast<const uint4*>(b.val);
+  unsigned mine = 0;
+  for (unsigned vb = first; vb < last; vb += 32u * kCsrUnroll) {   // warp-uniform trip count; kCsrUnroll rounds per trip
+    unsigned obj[kCsrUnroll];
+    uint4 x[kCsrUnroll], y[kCsrUnroll];
+#pragma unroll
+    for (int k = 0; k < kCsrUnroll; ++k) {               // all the rounds' loads are issued before any is compared
+      const unsigned v = vb + 32u * k + lane;
+      unsigned o = 0;                                    // largest lane whose run starts at or before v
+#pragma unroll
+      for (unsigned step = 16u; step; step >>= 1) {
+        const unsigned cand = __shfl_sync(FULL, fv0, o + step);
+        if (cand <= v) o += step;
+      }
+      const unsigned f_start = __shfl_sync(FULL, fv0, o), t_start = __shfl_sync(FULL, tv0, o);
+      obj[k] = o;
+      x[k] = make_uint4(0, 0, 0, 0);
+      y[k] = x[k];
+      if (v < last && !((ne_bits >> o) & 1u)) {
+        x[k] = ld_stream(av + v);
+        y[k] = ld_stream(bv + t_start + (v - f_start));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kCsrUnroll; ++k)
+      if (diff4(x[k], y[k])) mine |= 1u << obj[k];
+  }
+  return ne_bits | __reduce_or_sync(FULL, mine);
+}
+
 template <bool SPANS>
 __global__ void __launch_bounds__(128)
 diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
@@ -179,7 +236,9 @@ diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
   const unsigned cnt = (unsigned)min(32ull, n - base);
 
   // tiles first (the streaming part), then the per-lane scalar work: keeps the two register sets apart
-  const unsigned pod_bits = sparse_tiles_differ<SPANS>(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
+  unsigned pod_bits;
+  if constexpr (SPANS) pod_bits = sparse_tiles_differ<true>(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
+  else pod_bits = sparse_tiles_differ_csr(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
   unsigned reason = ((pod_bits >> lane) & 1u) ? NBG_STS_PODSPEC : 0u;
   if (i < n) {
     const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
