@@ -341,6 +341,56 @@ __device__ __forceinline__ void sparse_tiles_differ3(const nbg_podsparse& a, con
   }
 }
 
+// The same comparison for CSR batches, as a sweep over a's contiguous block (see sparse_tiles_differ_csr).
+__device__ __forceinline__ void sparse_tiles_differ3_csr(const nbg_podsparse& a, const nbg_podsparse& b, const nbg_podsparse& c,
+                                                         unsigned long long i, bool live, unsigned cnt, unsigned lane,
+                                                         unsigned a_base, unsigned b_base, unsigned c_base,
+                                                         unsigned& ab_bits, unsigned& ac_bits) {
+  unsigned av0 = 0, av1 = 0, bv0 = 0, cv0 = 0;
+  bool b_ne = false, c_ne = false;
+  if (live) {
+    const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
+    const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
+    const unsigned long long* mc = reinterpret_cast<const unsigned long long*>(c.mask) + i * 3;
+    const unsigned long long a0 = __ldg(ma), a1 = __ldg(ma + 1), a2 = __ldg(ma + 2);
+    b_ne = (a0 != __ldg(mb)) | (a1 != __ldg(mb + 1)) | (a2 != __ldg(mb + 2));
+    c_ne = (a0 != __ldg(mc)) | (a1 != __ldg(mc + 1)) | (a2 != __ldg(mc + 2));
+    av0 = (__ldg(a.off + i) - a_base) >> 1;
+    av1 = (__ldg(a.off + i + 1) - a_base) >> 1;
+    bv0 = (__ldg(b.off + i) - b_base) >> 1;
+    cv0 = (__ldg(c.off + i) - c_base) >> 1;
+  }
+  const unsigned b_skip = __ballot_sync(FULL, b_ne), c_skip = __ballot_sync(FULL, c_ne);
+  const unsigned first = __shfl_sync(FULL, av0, 0), last = __shfl_sync(FULL, av1, cnt - 1);
+  if (!live) av0 = last;
+  const uint4* av = reinterpret_cast<const uint4*>(a.val);
+  const uint4* bv = reinterpret_cast<const uint4*>(b.val);
+  const uint4* cv = reinterpret_cast<const uint4*>(c.val);
+  unsigned mine_b = 0, mine_c = 0;
+  for (unsigned vb = first; vb < last; vb += 32u) {      // warp-uniform trip count
+    const unsigned v = vb + lane;
+    unsigned o = 0;
+#pragma unroll
+    for (unsigned step = 16u; step; step >>= 1) {
+      const unsigned cand = __shfl_sync(FULL, av0, o + step);
+      if (cand <= v) o += step;
+    }
+    const unsigned a_start = __shfl_sync(FULL, av0, o), b_start = __shfl_sync(FULL, bv0, o), c_start = __shfl_sync(FULL, cv0, o);
+    const bool need_b = v < last && !((b_skip >> o) & 1u), need_c = v < last && !((c_skip >> o) & 1u);
+    if (need_b || need_c) {
+      const uint4 x = ld_stream(av + v);
+      uint4 y = x, z = x;
+      if (need_b) y = ld_stream(bv + b_start + (v - a_start));
+      if (need_c) z = ld_stream(cv + c_start + (v - a_start));
+      if (diff4(x, y)) mine_b |= 1u << o;
+      if (diff4(x, z)) mine_c |= 1u << o;
+    }
+  }
+  ab_bits = b_skip | __reduce_or_sync(FULL, mine_b);
+  ac_bits = c_skip | __reduce_or_sync(FULL, mine_c);
+}
+
+template <bool SPANS>
 __global__ void __launch_bounds__(128)
 restart_block_kernel(nbg_restart_batch in, unsigned long long n, unsigned o_base, unsigned u_base, unsigned m_base,
                      uint8_t* __restrict__ decision_out, uint32_t* __restrict__ bitmap_half) {
@@ -352,7 +402,10 @@ restart_block_kernel(nbg_restart_batch in, unsigned long long n, unsigned o_base
   const unsigned cnt = (unsigned)min(32ull, n - base);
   const bool live = i < n;
   unsigned upd_bits, mut_bits;
-  sparse_tiles_differ3(in.old_spec, in.updated_spec, in.mutated_spec, i, live, cnt, lane, o_base, u_base, m_base, upd_bits, mut_bits);
+  if constexpr (SPANS)
+    sparse_tiles_differ3(in.old_spec, in.updated_spec, in.mutated_spec, i, live, cnt, lane, o_base, u_base, m_base, upd_bits, mut_bits);
+  else
+    sparse_tiles_differ3_csr(in.old_spec, in.updated_spec, in.mutated_spec, i, live, cnt, lane, o_base, u_base, m_base, upd_bits, mut_bits);
   const unsigned fl = live ? __ldg(in.flags + i) : 0u;
   unsigned decision = 0;
   if (live && !(fl & (NBG_RB_CREATE | NBG_RB_STOPPED | NBG_RB_RESTARTING))) {
@@ -669,7 +722,8 @@ extern "C" cudaError_t nbg_launch_restart_block(const nbg_restart_batch* in, uns
                                                 uint8_t* decision, uint64_t* bitmap, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   const unsigned block = 128;
-  nbg::restart_block_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+  const bool spans = in->old_spec.end || in->updated_spec.end || in->mutated_spec.end;
+  (spans ? nbg::restart_block_kernel<true> : nbg::restart_block_kernel<false>)<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], decision, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
