@@ -3,6 +3,10 @@ import sys
 
 import pytest
 
+# The host-buffer entry points cut a batch into pipeline chunks; the smallest chunk size puts the most chunk
+# boundaries (and both staging slots, several times over) inside the test batches.  The library reads this once.
+os.environ.setdefault("NBG_CHUNK_SCALE", "1")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
