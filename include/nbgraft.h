@@ -343,7 +343,8 @@ int  nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** o
 void nbg_store_destroy(nbg_store* st);
 /* Slots idx[0..m) take rows 0..m of the given HOST batches (CSR form, m objects each; a NULL batch
  * leaves that predicate's rows as they are).  idx must be < capacity and free of duplicates.
- * Returns when the rows are on the device (the host buffers may be reused at once). */
+ * Returns when the rows are on the device (the host buffers may be reused at once).  After an error
+ * the slots named in this call hold unspecified rows (put them again); all other slots are intact. */
 int  nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_sparse_batch* sts,
                    const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull);
 /* One step over slots [0,n): outputs as nbg_step, into HOST buffers (synchronous) ... */
