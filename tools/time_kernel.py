@@ -1,5 +1,5 @@
 """Time one kernel of a given libnbgraft build on resident inputs (CUDA events, L2 > inputs).
-usage: NBGRAFT_LIB=build/variants/libnbgraft_X.so python tools/time_kernel.py cull 1250000"""
+usage: NBGRAFT_LIB=build/variants/libnbgraft_X.so python tools/time_kernel.py cull|sts|sts_sparse|svc|vs|svc_gen|vs_gen 1250000"""
 import importlib, os, statistics, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -12,8 +12,10 @@ if kind == "cull":
     cf = host.CullFleet(host.SEED_BASE + 3, n); b = cf.pack(); kw = dict(now=(cf.now_sec, cf.now_nsec))
 else:
     f = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, n, max(200, n // 50))
-    b = f.pack(sts=kind in ("sts", "sts_sparse"), svc=kind == "svc", vs=kind == "vs")[{"sts": 0, "sts_sparse": 0, "svc": 1, "vs": 2}[kind]]; kw = {}
+    base = kind.replace("_gen", "").replace("_sparse", "")
+    b = f.pack(sts=base == "sts", svc=base == "svc", vs=base == "vs")[{"sts": 0, "svc": 1, "vs": 2}[base]]; kw = {}
     if kind == "sts_sparse": b = b.sparse()
+    if kind.endswith("_gen"): b = b.gen()
 d = dev.DeviceBatch.from_host(b)
 flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 for mode in ((1, 0) if kind == "cull" else (None,)):
