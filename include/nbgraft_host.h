@@ -72,6 +72,14 @@ int nbh_generate_virtualservice(const nbh_obj* notebook, const nbh_env* env, nbh
  * 4 runtime images, 8 elyra secret, 16 kube-rbac-proxy. */
 int nbh_odh_mutate(nbh_obj* notebook, int flags);
 
+/* The COPY half of CopyStatefulSetFields / CopyServiceFields / CopyVirtualService (COMMON:114-131,173-192,
+ * 208-217): what the Go functions write into `to`, given the reason bits the compare kernel returned for the pair
+ * (nbg_diff_sts / nbg_diff_svc / nbg_diff_vs).  caller_prestep != 0 also copies the template labels when the
+ * kernel set NBG_STS_TMPL_LABELS, as Reconcile does before the call (NBCTL:190-194). */
+int nbh_apply_sts_fields(const nbh_obj* from, nbh_obj* to, unsigned reason, int caller_prestep);
+int nbh_apply_svc_fields(const nbh_obj* from, nbh_obj* to);
+int nbh_apply_vs_fields(const nbh_obj* from, nbh_obj* to, unsigned reason);
+
 /* ---- packed batches ---------------------------------------------------- */
 nbh_sts* nbh_sts_new(void);
 void nbh_sts_free(nbh_sts* b);

@@ -393,7 +393,7 @@ NBH_SYMBOLS = [
     "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
-    "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
+    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
     "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",
 ]

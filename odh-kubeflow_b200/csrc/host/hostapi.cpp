@@ -247,6 +247,23 @@ NBH_API int nbh_odh_mutate(nbh_obj* nb, int flags) {
   return odh_webhook_mutate(&nb->v, inj) ? 0 : 1;     // 1: kube-rbac-proxy injection refused (bad resource annotations)
 }
 
+// ---- what Copy*Fields does to `to` once the kernel has said how the pair compares (apply.cpp)
+NBH_API int nbh_apply_sts_fields(const nbh_obj* from, nbh_obj* to, unsigned reason, int caller_prestep) {
+  if (!from || !to) return -1;
+  apply_statefulset_fields(from->v, &to->v, reason, caller_prestep != 0);
+  return 0;
+}
+NBH_API int nbh_apply_svc_fields(const nbh_obj* from, nbh_obj* to) {
+  if (!from || !to) return -1;
+  apply_service_fields(from->v, &to->v);
+  return 0;
+}
+NBH_API int nbh_apply_vs_fields(const nbh_obj* from, nbh_obj* to, unsigned reason) {
+  if (!from || !to) return -1;
+  apply_virtualservice(from->v, &to->v, reason);
+  return 0;
+}
+
 // ------------------------------------------------------------------ batches
 NBH_API nbh_sts* nbh_sts_new(void) { return new nbh_sts(); }
 NBH_API void nbh_sts_free(nbh_sts* b) { delete b; }

@@ -42,6 +42,12 @@ struct OdhInject {
 // are still applied; no proxy container, volumes or service account are added — ODHWH:177-183)
 bool odh_webhook_mutate(GVal* notebook, const OdhInject& what);
 
+// ---- the copy half of Copy*Fields (apply.cpp) ------------------------------
+// `reason` = the bits the compare kernel returned for this pair (include/nbgraft.h).
+void apply_statefulset_fields(const GVal& from, GVal* to, unsigned reason, bool caller_prestep);
+void apply_service_fields(const GVal& from, GVal* to);
+void apply_virtualservice(const GVal& from, GVal* to, unsigned reason);
+
 // ---- packing (pack.cpp) ---------------------------------------------------
 uint64_t hash_str(const std::string& s);
 uint64_t digest(const GVal& v);                 // canonical 64-bit digest of a value tree
