@@ -340,6 +340,9 @@ def _bind_nbh(lib):
         "nbh_generate_service": ([_vp, P(_vp), cp, sz], C.c_int),
         "nbh_generate_virtualservice": ([_vp, P(nbh_env), P(_vp), cp, sz], C.c_int),
         "nbh_odh_mutate": ([_vp, C.c_int], C.c_int),
+        "nbh_apply_sts_fields": ([_vp, _vp, C.c_uint, C.c_int], C.c_int),
+        "nbh_apply_svc_fields": ([_vp, _vp], C.c_int),
+        "nbh_apply_vs_fields": ([_vp, _vp, C.c_uint], C.c_int),
         "nbh_sts_new": ([], _vp), "nbh_sts_free": ([_vp], None),
         "nbh_sts_add": ([_vp, _vp, _vp], C.c_int), "nbh_sts_view": ([_vp, P(nbg_sts_batch)], C.c_uint64),
         "nbh_sts_view_sparse": ([_vp, P(nbg_sts_sparse_batch)], C.c_uint64),

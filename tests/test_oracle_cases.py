@@ -393,3 +393,19 @@ def test_auth_sidecar_resource_rules(ann, ok):
     else:
         with pytest.raises(host.HostError):
             host.odh_mutate(nb, 16)
+
+
+@pytest.mark.parametrize("kind", [host.FLEET_KUBEFLOW, host.FLEET_ODH])
+def test_copy_half_of_copy_fields_matches_the_semantic_oracle(kind):
+    """Copy*Fields = compare (kernel) + copy (csrc/host/apply.cpp).  Given the reason bits, the product's copy must
+    leave `to` exactly as the object-level restatement of the Go functions leaves it (digest equality <=> DeepEqual)."""
+    lib = O.pkg._native.nbh()
+    fleet = host.Fleet(kind, host.SEED_BASE + 77, 600, 16)
+    for i in range(600):
+        for which, orc, apply in (("sts", lambda f, t: O.copy_statefulset_fields(f, t, 1), lambda f, t, r: lib.nbh_apply_sts_fields(f._h, t._h, r, 1)),
+                                  ("svc", O.copy_service_fields, lambda f, t, r: lib.nbh_apply_svc_fields(f._h, t._h)),
+                                  ("vs", O.copy_virtualservice, lambda f, t, r: lib.nbh_apply_vs_fields(f._h, t._h, r))):
+            frm, want_to, got_to = fleet.get(i, which + "_from"), fleet.get(i, which + "_to"), fleet.get(i, which + "_to")
+            reason = orc(frm, want_to)                        # mutates want_to like the Go code
+            assert apply(frm, got_to, reason) == 0
+            assert got_to.digest() == want_to.digest(), (which, i, fleet.drift_class(i), reason)
