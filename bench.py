@@ -451,14 +451,21 @@ def main():
     }
     if world == 1:
         threads = os.cpu_count() or 1
-        rate, info = CpuReference(pkg, O, args.cpu_sample, host.SEED_BASE + 5, threads).rate()
+        cpu_ref = CpuReference(pkg, O, args.cpu_sample, host.SEED_BASE + 5, threads)
+        rate, info = cpu_ref.rate()
+        cpu_ref.threads = 1                                   # the same port on ONE thread: the per-object cost (SURVEY 8d ii)
+        t1 = cpu_ref.step()
+        rate_1 = cpu_ref.sample / t1
+        t_packed_1 = sum(x[-1] for x in (O.packed_diff_sts_sparse(sts_sp, threads=1), O.packed_diff_svc(svc, threads=1),
+                                         O.packed_diff_vs(vs, threads=1), O.packed_cull(cull, now, 1440, 1, 1, threads=1)))
         # also the packed loops (the CPU version of OUR algorithm) for context
         t_packed = sum(x[-1] for x in (O.packed_diff_sts_sparse(sts_sp, threads=threads), O.packed_diff_svc(svc, threads=threads),
                                        O.packed_diff_vs(vs, threads=threads), O.packed_cull(cull, now, 1440, 1, 1, threads=threads)))
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": "%(sample_notebooks)d notebooks x %(repetitions)d repetitions (%(cpu_seconds)s CPU-s): "
                                           "object-level CopyStatefulSetFields/ServiceFields/VirtualService + culler on RFC3339 strings" % info,
-                                "packed_loops_value": per / t_packed,
+                                "single_thread_value": rate_1, "single_thread_us_per_object": 1e6 / rate_1,
+                                "packed_loops_value": per / t_packed, "packed_loops_single_thread_value": per / t_packed_1,
                                 "packed_loops_note": "plain C loops over the same SoA batches, all %d objects, %d threads" % (per, threads)}
         if not args.no_extra:
             line["other_configs"] = other_configs(pkg, dev, ctx, torch, peak)
