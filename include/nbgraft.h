@@ -233,6 +233,13 @@ uint32_t nbg_shard_of(uint64_t ns_hash, uint32_t n_shards);
  * i.e. the bool the Go function returns.  bitmap has ceil(n/64) words. */
 int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n,
                  uint8_t* reason, uint64_t* bitmap);
+/* CopyDeploymentSetFields (COMMON:136-163) on the same batch layout: labels, annotations and PodSpec as in
+ * CopyStatefulSetFields, but the Go code compares the Replicas POINTERS (COMMON:152), so NBG_STS_REPLICAS is set
+ * unless both are nil, nothing panics (NBG_STS_NILREPLICAS and NBG_STS_TMPL_LABELS are never set).  The reference
+ * itself has no caller for this function; it is here because the path's file defines it. */
+int nbg_diff_deploy(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap);
+int nbg_diff_deploy_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
+                           uint8_t* reason, uint64_t* bitmap, void* stream);
 /* The same predicate on sparsely stored PodSpec tiles (nbg_sts_sparse_batch): identical
  * outputs, ~4x fewer bytes per object to move over PCIe and to read from HBM. */
 int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n,

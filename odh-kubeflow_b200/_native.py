@@ -205,7 +205,7 @@ def batch_struct(kind, ptr, has=lambda name: False):
 NBG_SYMBOLS = [
     "nbg_init", "nbg_destroy", "nbg_strerror", "nbg_last_cuda_error", "nbg_abi_version", "nbg_device_count",
     "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of",
-    "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull",
+    "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull", "nbg_diff_deploy", "nbg_diff_deploy_device",
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
@@ -238,7 +238,7 @@ def _bind_nbg(lib):
     lib.nbg_shard_of.argtypes = [C.c_uint64, C.c_uint32]
     lib.nbg_shard_of.restype = C.c_uint32
     for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch),
-                     ("nbg_diff_sts_sparse", nbg_sts_sparse_batch)):
+                     ("nbg_diff_sts_sparse", nbg_sts_sparse_batch), ("nbg_diff_deploy", nbg_sts_batch)):
         f = getattr(lib, name)
         f.argtypes = [_vp, C.POINTER(bt), C.c_uint64, _vp, _vp]
         f.restype = C.c_int

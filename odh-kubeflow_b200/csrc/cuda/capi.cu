@@ -23,7 +23,7 @@ extern "C" {
 cudaError_t nbg_launch_cull(const nbg_cull_batch*, unsigned long long, const nbg_cull_params*,
                             unsigned, unsigned, uint8_t*, uint32_t*, uint64_t*, uint64_t*,
                             cudaStream_t);
-cudaError_t nbg_launch_diff_sts(const nbg_sts_batch*, unsigned long long, const unsigned*, uint8_t*,
+cudaError_t nbg_launch_diff_sts(const nbg_sts_batch*, unsigned long long, const unsigned*, int, uint8_t*,
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch*, unsigned long long, const unsigned*, uint8_t*,
                                        uint64_t*, cudaStream_t);
@@ -191,6 +191,8 @@ void device_range(uint64_t n, int ndev, int d, uint64_t* lo, uint64_t* hi) {
 // Set while nbg_step drives several entry points as ONE pipeline: they then only enqueue
 // (the caller holds the device locks and waits once at the end).
 thread_local bool tl_batched = false;
+// Set while nbg_diff_deploy[_device] drives the StatefulSet entry points with CopyDeploymentSetFields' replicas rule.
+thread_local bool tl_deployment = false;
 
 template <class F>
 int for_each_device(nbg_ctx* ctx, uint64_t n, F&& run_range) {
@@ -388,9 +390,24 @@ int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint6
   CU(cudaSetDevice(ctx->devs[device]->id));
   cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[4] = {0, 0, 0, 0};
-  CU(nbg_launch_diff_sts(in, n, bases, reason, bitmap, s));
+  CU(nbg_launch_diff_sts(in, n, bases, tl_deployment ? 1 : 0, reason, bitmap, s));
   ctx->launches++;
   return NBG_OK;
+}
+
+int nbg_diff_deploy_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
+                           uint8_t* reason, uint64_t* bitmap, void* stream) {
+  tl_deployment = true;
+  const int rc = nbg_diff_sts_device(ctx, device, in, n, reason, bitmap, stream);
+  tl_deployment = false;
+  return rc;
+}
+
+int nbg_diff_deploy(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  tl_deployment = true;
+  const int rc = nbg_diff_sts(ctx, in, n, reason, bitmap);
+  tl_deployment = false;
+  return rc;
 }
 
 int nbg_diff_sts_sparse_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* in, uint64_t n,
@@ -1054,7 +1071,7 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
       b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt);
       b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
       const unsigned bases[4] = {lf.base, lt.base, af.base, at.base};
-      CU(nbg_launch_diff_sts(&b, m, bases, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      CU(nbg_launch_diff_sts(&b, m, bases, tl_deployment ? 1 : 0, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
       ctx->launches++;
       if (int r = slot_download(d, sl, lay)) return r;
     }

@@ -39,7 +39,7 @@ constexpr int kPodVecPerLane = kPodVec / 32;          // 3
 
 __global__ void __launch_bounds__(128)
 diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
-                unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
+                unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base, unsigned deployment,
                 uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
   const unsigned lane = threadIdx.x & 31;
   const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -52,7 +52,11 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
   unsigned reason = 0;
   if (i < n) {
     const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
-    if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
+    if (deployment) {
+      // CopyDeploymentSetFields compares the Replicas POINTERS (COMMON:152): two objects never share one,
+      // so they are "different" unless both are nil; nothing is dereferenced, nothing panics
+      if (rf != NBG_REPLICAS_NIL || rt != NBG_REPLICAS_NIL) reason |= NBG_STS_REPLICAS;
+    } else if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
       reason |= NBG_STS_NILREPLICAS;                 // Go would panic at COMMON:123
     } else if (rf != rt) {
       reason |= NBG_STS_REPLICAS;                    // COMMON:123-126
@@ -672,13 +676,13 @@ extern "C" cudaError_t nbg_launch_diff_generic(const nbg_generic_batch* in, unsi
 // *_base: first CSR offset of the slice when the entry pointers already point
 // at the slice's first entry (host-buffer chunking); 0 for whole arrays.
 extern "C" cudaError_t nbg_launch_diff_sts(const nbg_sts_batch* in, unsigned long long n,
-                                           const unsigned* bases /*4*/, uint8_t* reason,
+                                           const unsigned* bases /*4*/, int deployment, uint8_t* reason,
                                            uint64_t* bitmap, cudaStream_t stream) {
   if (n == 0) return cudaSuccess;
   const unsigned block = 128;                          // 4 warps = 128 objects per CTA
   const unsigned long long grid = (n + block - 1) / block;
   nbg::diff_sts_kernel<<<(unsigned)grid, block, 0, stream>>>(
-      *in, n, bases[0], bases[1], bases[2], bases[3], reason, reinterpret_cast<uint32_t*>(bitmap));
+      *in, n, bases[0], bases[1], bases[2], bases[3], deployment ? 1u : 0u, reason, reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
 

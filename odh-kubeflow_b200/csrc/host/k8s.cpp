@@ -90,6 +90,8 @@ PodTemplateSpec: metadata:ObjectMeta spec:PodSpec
 LabelSelector: matchLabels:{s matchExpressions:any
 StatefulSetSpec: replicas:*i selector:*LabelSelector template:PodTemplateSpec volumeClaimTemplates:any serviceName:s podManagementPolicy:s updateStrategy:any revisionHistoryLimit:*i minReadySeconds:i persistentVolumeClaimRetentionPolicy:any ordinals:any
 StatefulSet: apiVersion:s kind:s metadata:ObjectMeta spec:StatefulSetSpec status:any
+DeploymentSpec: replicas:*i selector:*LabelSelector template:PodTemplateSpec strategy:any minReadySeconds:i revisionHistoryLimit:*i paused:b progressDeadlineSeconds:*i
+Deployment: apiVersion:s kind:s metadata:ObjectMeta spec:DeploymentSpec status:any
 ServicePort: name:s protocol:s appProtocol:*s port:i targetPort:ios nodePort:i
 ServiceSpec: ports:[ServicePort selector:{s clusterIP:s clusterIPs:[s type:s externalIPs:[s sessionAffinity:s loadBalancerIP:s loadBalancerSourceRanges:[s externalName:s externalTrafficPolicy:s healthCheckNodePort:i publishNotReadyAddresses:b sessionAffinityConfig:any ipFamilies:[s ipFamilyPolicy:*s allocateLoadBalancerNodePorts:*b loadBalancerClass:*s internalTrafficPolicy:*s trafficDistribution:*s
 Service: apiVersion:s kind:s metadata:ObjectMeta spec:ServiceSpec status:any

@@ -83,6 +83,11 @@ class Context:
         """Batched CopyStatefulSetFields (COMMON:107-134) + NBCTL:188-194."""
         return self._diff(self._lib.nbg_diff_sts, batch, allow_nil)
 
+    def diff_deploy(self, batch):
+        """Batched CopyDeploymentSetFields (COMMON:136-163) on a StsBatch of Deployment pairs: Replicas compared as
+        pointers (different unless both nil), no panic, no template-label pre-step."""
+        return self._diff(self._lib.nbg_diff_deploy, batch, True)
+
     def diff_sts_sparse(self, batch, allow_nil=False):
         """Same predicate on sparsely stored PodSpec tiles (batch = StsBatch.sparse())."""
         return self._diff(self._lib.nbg_diff_sts_sparse, batch, allow_nil)

@@ -83,6 +83,10 @@ def StatefulSet(obj):
     return Obj.from_json("StatefulSet", obj)
 
 
+def Deployment(obj):
+    return Obj.from_json("Deployment", obj)
+
+
 def Service(obj):
     return Obj.from_json("Service", obj)
 

@@ -251,6 +251,20 @@ static double run(int kind, const void* in, const nbg_cull_params* p, uint64_t n
 ORC_API double orc2_diff_sts(const nbg_sts_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
   return run(0, in, NULL, n, threads, reason, NULL, bitmap, NULL);
 }
+/* CopyDeploymentSetFields (COMMON:136-163): as sts_range, but Replicas are compared as POINTERS (:152) —
+ * different unless both nil — and there is neither a panic nor a template-label pre-step. */
+ORC_API void orc2_diff_deploy(const nbg_sts_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  for (uint64_t i = 0; i < n; ++i) {
+    unsigned r = 0;
+    if (in->replicas_from[i] != NBG_REPLICAS_NIL || in->replicas_to[i] != NBG_REPLICAS_NIL) r |= NBG_STS_REPLICAS;
+    if (live_differs(&in->labels_from, &in->labels_to, i)) r |= NBG_STS_LABELS;
+    if (live_differs(&in->ann_from, &in->ann_to, i)) r |= NBG_STS_ANNOTATIONS;
+    if (memcmp(in->pod_from + i * NBG_POD_SLOTS, in->pod_to + i * NBG_POD_SLOTS, NBG_POD_SLOTS * 8) != 0)
+      r |= NBG_STS_PODSPEC;
+    reason[i] = (uint8_t)r;
+    set_bit(bitmap, i, (r & NBG_STS_UPDATE_MASK) != 0);
+  }
+}
 ORC_API double orc2_diff_sts_sparse(const nbg_sts_sparse_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
   return run(4, in, NULL, n, threads, reason, NULL, bitmap, NULL);
 }

@@ -728,6 +728,35 @@ ORC_API int orc_strict_equal(const nbh_obj* a, const nbh_obj* b) { return strict
 ORC_API int orc_copy_statefulset_fields(const nbh_obj* from, nbh_obj* to, int caller_prestep) {
   return copy_statefulset_fields(from->v, to->v, caller_prestep);
 }
+// CopyDeploymentSetFields (COMMON:136-163) on two separately decoded objects: `from.Spec.Replicas != to.Spec.Replicas`
+// compares pointers (:152), which two objects never share, so it holds unless both are nil; then the POINTER is
+// assigned (:153), i.e. to.Spec.Replicas takes from's value (or nil).
+ORC_API int orc_copy_deployment_fields(const nbh_obj* from_o, nbh_obj* to_o) {
+  const GVal& from = from_o->v;
+  GVal& to = to_o->v;
+  int reason = 0;
+  ensure(to, "metadata", GVal::strct());
+  ensure(to, "spec", GVal::strct());
+  const GVal& from_meta = field(from, "metadata");
+  GVal& to_meta = *to.find("metadata");
+  GVal& to_spec = *to.find("spec");
+  ensure(to_spec, "template", GVal::strct());
+  if (live_entry_differs(field(from_meta, "labels"), field(to_meta, "labels"))) reason |= R_LABELS;        // :138-142
+  assign_field(to_meta, "labels", field(from_meta, "labels"));                                             // :143
+  if (live_entry_differs(field(from_meta, "annotations"), field(to_meta, "annotations"))) reason |= R_ANN; // :145-149
+  assign_field(to_meta, "annotations", field(from_meta, "annotations"));                                   // :150
+  const GVal& from_rep = field(field(from, "spec"), "replicas");
+  const GVal to_rep = field(to_spec, "replicas");
+  if (from_rep.kind == GVal::Ptr || to_rep.kind == GVal::Ptr) {                                             // :152
+    assign_field(to_spec, "replicas", from_rep);                                                            // :153
+    reason |= R_THIRD;
+  }
+  const GVal& from_pod = field(field(field(from, "spec"), "template"), "spec");
+  GVal& to_tmpl = *to_spec.find("template");
+  if (!deep_equal(field(to_tmpl, "spec"), from_pod)) reason |= R_FOURTH;                                    // :157
+  assign_field(to_tmpl, "spec", from_pod);                                                                  // :160
+  return reason;
+}
 ORC_API int orc_copy_service_fields(const nbh_obj* from, nbh_obj* to) { return copy_service_fields(from->v, to->v); }
 ORC_API int orc_copy_virtualservice(const nbh_obj* from, nbh_obj* to) { return copy_virtualservice(from->v, to->v); }
 

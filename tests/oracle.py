@@ -32,6 +32,9 @@ def lib():
         L.orc_strict_equal.argtypes = [vp, vp]
         L.orc_copy_statefulset_fields.argtypes = [vp, vp, C.c_int]
         L.orc_copy_service_fields.argtypes = [vp, vp]
+        L.orc_copy_deployment_fields.argtypes = [vp, vp]
+        L.orc2_diff_deploy.argtypes = [C.POINTER(N.nbg_sts_batch), C.c_uint64, vp, vp]
+        L.orc2_diff_deploy.restype = None
         L.orc_copy_virtualservice.argtypes = [vp, vp]
         L.orc_bench_pairs.argtypes = [C.c_int, C.POINTER(vp), C.POINTER(vp), C.c_uint64, C.c_int, vp]
         L.orc_bench_pairs.restype = C.c_double
@@ -78,6 +81,20 @@ def deep_equal(a, b):
 def copy_statefulset_fields(from_, to, prestep=1):
     """returns reason bits (NBG_STS_*); mutates `to` (a host.Obj) like the Go code."""
     return lib().orc_copy_statefulset_fields(from_._h, to._h, prestep)
+
+
+def copy_deployment_fields(from_, to):
+    """CopyDeploymentSetFields (COMMON:136-163) on two Deployment objects; mutates `to`."""
+    return lib().orc_copy_deployment_fields(from_._h, to._h)
+
+
+def packed_diff_deploy(batch):
+    view = batch.view
+    n = batch.n
+    reason = np.zeros(n, dtype=np.uint8)
+    bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+    lib().orc2_diff_deploy(C.byref(view), n, reason.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+    return reason, bitmap
 
 
 def copy_service_fields(from_, to):
