@@ -5,8 +5,8 @@
 // argument meaning, same side effects and failure behaviour — one object at a time, each call a
 // batch of one through the CUDA kernels:
 //
-//   nbgraft::reconcilehelper::CopyStatefulSetFields / CopyServiceFields / CopyVirtualService
-//        components/common/reconcilehelper/util.go:107-134, 166-195, 199-219
+//   nbgraft::reconcilehelper::CopyStatefulSetFields / CopyDeploymentSetFields / CopyServiceFields /
+//        CopyVirtualService        components/common/reconcilehelper/util.go:107-134, 136-163, 166-195, 199-219
 //   nbgraft::culler::Culler::{StopAnnotationIsSet, allKernelsAreIdle, notebookIsIdle,
 //        cullingCheckPeriodHasPassed, updateTimestampFromKernelsActivity,
 //        updateTimestampFromTerminalsActivity, setStopAnnotation}
@@ -126,6 +126,23 @@ inline bool CopyStatefulSetFields(Context& ctx, const Object& from, Object& to) 
   nbh_sts_free(b);
   if (rc == NBG_E_NILREPLICAS) throw Error(rc, "panic: runtime error: invalid memory address or nil pointer dereference (util.go:123)");
   if (rc != NBG_OK) throw Error(rc, std::string("nbg_diff_sts: ") + nbg_strerror(rc));
+  nbh_apply_sts_fields(from.get(), to.get(), reason, 0);
+  return (reason & NBG_STS_UPDATE_MASK) != 0;
+}
+
+// CopyDeploymentSetFields(from, to *appsv1.Deployment) bool — util.go:136-163.  As above, except that the Go
+// code compares the Replicas POINTERS (:152): an update is reported, and from's replicas assigned, unless both
+// are nil; nothing panics.
+inline bool CopyDeploymentSetFields(Context& ctx, const Object& from, Object& to) {
+  nbh_sts* b = nbh_sts_new();
+  nbh_sts_add(b, from.get(), to.get());
+  nbg_sts_batch view;
+  nbh_sts_view(b, &view);
+  uint8_t reason = 0;
+  uint64_t bitmap = 0;
+  const int rc = nbg_diff_deploy(ctx.get(), &view, 1, &reason, &bitmap);
+  nbh_sts_free(b);
+  if (rc != NBG_OK) throw Error(rc, std::string("nbg_diff_deploy: ") + nbg_strerror(rc));
   nbh_apply_sts_fields(from.get(), to.get(), reason, 0);
   return (reason & NBG_STS_UPDATE_MASK) != 0;
 }

@@ -135,6 +135,20 @@ static void reconcilehelper_tables(Context& ctx) {
              std::string("CopyStatefulSetFields copies unconditionally/") + tc.name);
     }
   }
+  {  // CopyDeploymentSetFields, util.go:136-163: Replicas are compared as pointers (:152)
+    const char* dep = R"({"apiVersion":"apps/v1","kind":"Deployment","metadata":{"name":"d","labels":{"app":"d"}},
+                          "spec":{"replicas":2,"template":{"spec":{"containers":[{"name":"c","image":"nginx"}]}}}})";
+    const Object desired("Deployment", dep);
+    Object live = desired;
+    expect(reconcilehelper::CopyDeploymentSetFields(ctx, desired, live), "CopyDeploymentSetFields/equal numbers, different pointers => update");
+    Object d_nil = desired, l_nil = desired;
+    nbh_obj_erase(d_nil.get(), "spec.replicas");
+    nbh_obj_erase(l_nil.get(), "spec.replicas");
+    expect(!reconcilehelper::CopyDeploymentSetFields(ctx, d_nil, l_nil), "CopyDeploymentSetFields/both nil => nothing to do");
+    Object l3 = desired;
+    expect(reconcilehelper::CopyDeploymentSetFields(ctx, d_nil, l3) && !l3.has("spec.replicas"),
+           "CopyDeploymentSetFields/desired nil: no panic, the nil pointer is assigned");
+  }
   {  // CopyServiceFields, util.go:166-195
     const std::vector<Edit> cases = {{"identical", [](Object&) {}, false},
                                      {"selector changed", set("spec.selector.statefulset", "other"), true},
