@@ -230,7 +230,16 @@ def main():
     per = args.per_gpu
     fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, per * world * 4, max(200, per * world // 50))
     t0 = time.time()
-    idx = fleet.shard_indices(world, rank)[:per] if world > 1 else np.arange(per, dtype=np.uint64)
+    shard_imbalance = None
+    if world > 1:
+        shard = fleet.shard_indices(world, rank)
+        sizes = torch.zeros(world, dtype=torch.float64, device="cuda")
+        sizes[rank] = float(len(shard))
+        dist.all_reduce(sizes)                                   # set-up only, not in any timed region
+        shard_imbalance = float(sizes.max() / sizes.mean())      # what hash sharding of Zipf namespaces gives
+        idx = shard[:per]
+    else:
+        idx = np.arange(per, dtype=np.uint64)
     assert len(idx) == per, "shard too small"
     sts, svc, vs = fleet.pack(idx=idx)
     make_cpu_s, pack_cpu_s = fleet.pack_timing()
@@ -417,6 +426,7 @@ def main():
                    "desired_side": "StatefulSet: packed from generateStatefulSet's output; Service and VirtualService: generated on the device "
                                    "from name/port/prefix/rewrite/host words (same answer as shipping generateService/VirtualService outputs)",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
+                   "shard_imbalance_max_over_mean": shard_imbalance,
                    "cpu_binding": ("rank 0 bound to the %d CPUs NVML lists next to its GPU" % len(near)) if near else "none",
                    "streams": "one stream" if args.no_overlap else "one nbg_step_device call per step: StatefulSet kernel on the main stream, the three small kernels "
                               "on the context's side streams (event fork/join inside the library); per-kernel times are from a separate serialised pass",
@@ -424,11 +434,13 @@ def main():
                    "l2": "inputs (%.1f GB per GPU) exceed L2; no flush needed" % (sum(alg_bytes.values()) / 1e9),
                    "bytes_per_object": {k: round(v / per, 1) for k, v in alg_bytes.items()}},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": te.item() * 1e3, "timer": "host wall clock around the synchronous C-ABI call nbg_step, max over ranks"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
+                "ms_per_step": te.item() * 1e3, "effective_h2d_GBps_per_gpu": h2d / te.item() / 1e9,
+                "bytes_note": "whole job: rank 0's bytes x ranks (every shard holds the same number of notebooks)",
+                "timer": "host wall clock around the synchronous C-ABI call nbg_step, max over ranks"},
         "gpu_launches": int(gpu_launches),
         "roofline": {"bound": "hbm", "kernel": "diff_sts_sparse_kernel", "achieved": sts_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": sts_gbs / peak, "traffic": traffic, "peak_source": peak_src,
+                     "frac": sts_gbs / peak, "frac_of_nominal_8TBps": sts_gbs / 8000.0, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": int(alg_bytes["diff_sts"]), "avg_launch_ms": dom_ms,
                      "note": "timed inside the timed region on its own stream" + ("" if args.no_overlap else
                              ", while the three small kernels run concurrently on side streams and share HBM with it"),
