@@ -483,11 +483,43 @@ def main():
             line["other_configs"] = other_configs(pkg, dev, ctx, torch, peak)
             del d_sts, d_svc, d_vs, d_cull, batches, resident
             torch.cuda.empty_cache()
+            line["other_configs"]["config5_10M_on_one_gpu"] = ten_million_on_one_gpu(
+                pkg, dev, ctx, torch, (sts_sp, svc_g, vs_g, cull), now, want, per, peak)
             line["other_configs"]["resident_store_1.25M"] = resident_store(
                 pkg, O, ctx, torch, fleet, per, (sts_sp, svc_g, vs_g, cull), now, want, sum(alg_bytes.values()), peak)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def ten_million_on_one_gpu(pkg, dev, ctx, torch, host_batches, now, want, per, peak):
+    """BASELINE config #5 at its full size on ONE GPU: the 1.25 M-notebook batches tiled 8x on the device (10 M
+    notebooks, ~11 GB resident), one nbg_step_device per step.  Parity through the tiling property: every tile must
+    repeat the 1.25 M results the oracle was checked against."""
+    N = pkg._native
+    tiles = 8
+    d = [dev.DeviceBatch.from_host(b, tile=tiles) for b in host_batches]
+    n = d[0].n
+    step = dev.ResidentStep(ctx, *d, now=now, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE)
+    for _ in range(3):
+        step.run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        step.run()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    ok = True
+    for b, w in zip(d, (want["diff_sts"][0], want["diff_svc"][0], want["diff_vs"][0], want["cull"][0])):
+        ok &= bool((b.outs[0].cpu().numpy().reshape(tiles, per) == w[None, :]).all())
+    if not ok:
+        raise SystemExit("bench: 10 M-notebook results do not repeat the checked 1.25 M results tile by tile")
+    nbytes = sum(b.algorithmic_bytes for b in d)
+    return {"notebooks": n, "ms_per_step": ms, "objects_per_s": n / (ms * 1e-3), "resident_GB": nbytes / 1e9,
+            "GBps": nbytes / (ms * 1e-3) / 1e9, "frac_of_peak": nbytes / (ms * 1e-3) / 1e9 / peak,
+            "frac_of_nominal_8TBps": nbytes / (ms * 1e-3) / 1e9 / 8000.0,
+            "parity": "every one of the 8 tiles repeats the 1.25 M results that were checked against the packed oracle"}
 
 
 def resident_store(pkg, O, ctx, torch, fleet, per, host_batches, now, want, alg_bytes, peak):
