@@ -564,3 +564,32 @@ def test_resident_step_replays_from_a_cuda_graph(ctx):
     for b, w in zip(d, want):
         assert np.array_equal(b.outs[0].cpu().numpy(), w[0])
         assert np.array_equal(_masked(b.outs[-1].cpu().numpy(), n), _masked(w[len(b.outs) - 1], n))
+
+
+def test_ten_million_notebooks_repeat_the_checked_tile(ctx):
+    """BASELINE config #5 at its full size (10 M notebooks on one GPU, ~11 GB resident) through the size-independent
+    property the layout offers: a fleet of 156 250 notebooks checked against the oracle, tiled 64x on the device,
+    must give the same 156 250 answers 64 times — for all four predicates of the step."""
+    import torch
+    devmod = importlib.import_module("odh-kubeflow_b200.device")
+    base, tiles = 156_250, 64
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, base, 3000)
+    sts, svc, vs = fleet.pack()
+    cf = host.CullFleet(host.SEED_BASE + 6, base)
+    cb = cf.pack()
+    now = (cf.now_sec, cf.now_nsec)
+    want = (O.packed_diff_sts(sts, threads=4)[0], O.packed_diff_svc(svc, threads=4)[0], O.packed_diff_vs(vs, threads=4)[0],
+            O.packed_cull(cb, now, 1440, 1, 1, threads=4))
+    d = [devmod.DeviceBatch.from_host(b, tile=tiles) for b in (sts.sparse(), svc.gen(), vs.gen(), cb)]
+    assert d[0].n == 10_000_000
+    devmod.ResidentStep(ctx, *d, now=now).run()
+    torch.cuda.synchronize()
+    for k in range(3):
+        assert (d[k].outs[0].cpu().numpy().reshape(tiles, base) == want[k][None, :]).all(), k
+    assert (d[3].outs[0].cpu().numpy().reshape(tiles, base) == want[3][0][None, :]).all()
+    assert (d[3].outs[1].cpu().numpy().view(np.uint32).reshape(tiles, base) == want[3][1][None, :]).all()
+    # bitmaps: 156 250 is not a multiple of 64, so tiles are not word-aligned: compare bit by bit
+    bits = pkg.engine.bitmap_to_bools(d[0].outs[1].cpu().numpy().view(np.uint64), 10_000_000).reshape(tiles, base)
+    assert (bits == ((want[0] & 0x0F) != 0)[None, :]).all()
+    del d
+    torch.cuda.empty_cache()
