@@ -596,6 +596,10 @@ def resident_store(pkg, O, ctx, torch, fleet, per, host_batches, now, want, alg_
 def other_configs(pkg, dev, ctx, torch, peak):
     """Device-timed numbers for BASELINE configs #2, #3, #4 (parity for these is in tests/)."""
     host, N = pkg.host, pkg._native
+    import oracle as O   # the checker of these side measurements
+
+    def O_packed_cull(batch, now):
+        return O.packed_cull(batch, now, 1440, 1, 1, threads=8)[0]
     out = {}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
@@ -653,6 +657,20 @@ def other_configs(pkg, dev, ctx, torch, peak):
     ms = timed(d, now=(cf.now_sec, cf.now_nsec))
     out["config3_1M_kernel_records"] = {"records_per_s": sum(cb.records()) / (ms * 1e-3), "notebooks_per_s": 250_000 / (ms * 1e-3), "ms": ms,
                                         "GBps": d.algorithmic_bytes / (ms * 1e-3) / 1e9, "roofline": "n/a (22 MB, launch-bound; L2 flushed)"}
+    # the same culler batch scaled to ~1 G kernel/terminal records (SURVEY 8d, config #3 note): tiled 1000x on the device
+    del d
+    big = dev.DeviceBatch.from_host(cb, tile=1000)
+    ms_big = timed(big, reps=5, now=(cf.now_sec, cf.now_nsec))
+    got = big.outs[0].cpu().numpy().reshape(1000, -1)
+    want_c = O_packed_cull(cb, (cf.now_sec, cf.now_nsec))
+    assert (got == want_c[None, :]).all(), "1 G-record culler run does not repeat the checked 250 k results"
+    out["config3_1G_kernel_records"] = {"records": int(sum(cb.records())) * 1000, "notebooks": big.n, "ms": ms_big,
+                                        "records_per_s": sum(cb.records()) * 1000 / (ms_big * 1e-3),
+                                        "resident_GB": big.algorithmic_bytes / 1e9, "GBps": big.algorithmic_bytes / (ms_big * 1e-3) / 1e9,
+                                        "frac_of_peak": big.algorithmic_bytes / (ms_big * 1e-3) / 1e9 / peak,
+                                        "parity": "every one of the 1000 tiles repeats the 250 k results checked against the packed oracle"}
+    del big
+    torch.cuda.empty_cache()
     f4 = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 100_000, 2000)
     sts, _, vs = f4.pack(svc=False)
     d1, d2 = dev.DeviceBatch.from_host(sts), dev.DeviceBatch.from_host(vs)
@@ -660,7 +678,6 @@ def other_configs(pkg, dev, ctx, torch, peak):
     out["config4_100k_odh_sts_vs"] = {"objects_per_s": 100_000 / ((m1 + m2) * 1e-3), "ms": m1 + m2,
                                       "sts_GBps": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9, "sts_frac_of_peak": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9 / peak}
     # the owner-reference join (NBCTL:157-170) as a hash join, 1.25 M notebooks
-    import oracle as O
     lib = N.nbg()
     n = 1_250_000
     fj = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 6, n, n // 50)
