@@ -160,6 +160,18 @@ bool off_ok(const uint32_t* off, uint64_t i0, uint64_t i1) {
   return bad == 0;
 }
 bool csr_ok(const nbg_kvmap& m, uint64_t i0, uint64_t i1) { return off_ok(m.off, i0, i1); }
+// Sparse tiles of rows [i0,i1): offsets even, every run as long as its mask says (popcount, rounded up to even).
+// The kernels size their reads of BOTH sides by one side's run when the masks agree, so this is what keeps a
+// malformed batch from reading outside the arrays.  Branch-free, runs per chunk like off_ok.
+bool sparse_ok(const nbg_podsparse& p, uint64_t i0, uint64_t i1) {
+  unsigned bad = p.off[i0] & 1u;
+  for (uint64_t i = i0; i < i1; ++i) {
+    const unsigned bits = (unsigned)(__builtin_popcountll(p.mask[3 * i]) + __builtin_popcountll(p.mask[3 * i + 1]) +
+                                     __builtin_popcountll(p.mask[3 * i + 2]));
+    bad |= (unsigned)(p.off[i + 1] - p.off[i] != ((bits + 1u) & ~1u));
+  }
+  return bad == 0;
+}
 // host-buffer entry points take CSR maps only (`end` must be NULL: chunking relies on contiguous runs)
 bool csr_ptrs_ok(const nbg_kvmap& m, uint64_t n) { return m.off && !m.end && (m.ent || m.off[n] == m.off[0]); }
 
@@ -768,10 +780,7 @@ int nbg_restart_block(nbg_ctx* ctx, const nbg_restart_batch* in, uint64_t n, uin
     for (uint64_t i0 = lo; i0 < hi; i0 += kStsSparseChunk, ++c) {
       const uint64_t i1 = i0 + kStsSparseChunk < hi ? i0 + kStsSparseChunk : hi, m = i1 - i0;
       for (const nbg_podsparse* p : sp) {
-        if (!off_ok(p->off, i0, i1)) return NBG_E_RANGE;
-        unsigned bad = p->off[i0] & 1u;
-        for (uint64_t i = i0; i < i1; ++i) bad |= (p->off[i + 1] & 1u) | (unsigned)(p->off[i + 1] - p->off[i] > NBG_POD_SLOTS);
-        if (bad) return NBG_E_RANGE;
+        if (!off_ok(p->off, i0, i1) || !sparse_ok(*p, i0, i1)) return NBG_E_RANGE;
       }
       Slot& sl = d.slot[c & 1];
       Layout lay;
@@ -1104,14 +1113,7 @@ int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n
       if (!csr_ok(in->labels_from, i0, i1) || !csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_from, i0, i1) ||
           !csr_ok(in->ann_to, i0, i1) || !off_ok(in->pod_from.off, i0, i1) || !off_ok(in->pod_to.off, i0, i1))
         return NBG_E_RANGE;
-      {  // runs are even-padded and never longer than a tile
-        const uint32_t *of = in->pod_from.off, *ot = in->pod_to.off;
-        unsigned bad = (of[i0] | ot[i0]) & 1u;
-        for (uint64_t i = i0; i < i1; ++i)
-          bad |= ((of[i + 1] | ot[i + 1]) & 1u) | (unsigned)(of[i + 1] - of[i] > NBG_POD_SLOTS) |
-                 (unsigned)(ot[i + 1] - ot[i] > NBG_POD_SLOTS);
-        if (bad) return NBG_E_RANGE;
-      }
+      if (!sparse_ok(in->pod_from, i0, i1) || !sparse_ok(in->pod_to, i0, i1)) return NBG_E_RANGE;
       Slot& sl = d.slot[c & 1];
       Layout lay;
       const size_t a_rf = lay.in(in->replicas_from + i0, m * 4), a_rt = lay.in(in->replicas_to + i0, m * 4);

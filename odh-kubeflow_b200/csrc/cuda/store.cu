@@ -319,6 +319,19 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
   if (svc && (svc->labels_to.end || svc->ann_to.end || svc->sel_to.end)) return NBG_E_INVAL;
   if (vs && (vs->hdr_from.end || vs->hdr_to.end)) return NBG_E_INVAL;
   if (cull && (cull->k_end || cull->t_end)) return NBG_E_INVAL;
+  if (sts) {                                             // every run as long as its mask says (as the host-buffer calls check)
+    const nbg_podsparse* sides[2] = {&sts->pod_from, &sts->pod_to};
+    for (const nbg_podsparse* p : sides) {
+      if (!p->mask || !p->off) return NBG_E_INVAL;
+      unsigned bad = 0;
+      for (uint64_t k = 0; k < m; ++k) {
+        const unsigned bits = (unsigned)(__builtin_popcountll(p->mask[3 * k]) + __builtin_popcountll(p->mask[3 * k + 1]) +
+                                         __builtin_popcountll(p->mask[3 * k + 2]));
+        bad |= (unsigned)(p->off[k + 1] - p->off[k] != ((bits + 1u) & ~1u));
+      }
+      if (bad) return NBG_E_RANGE;
+    }
+  }
   std::unique_lock<std::mutex> lock(st->mu);
   CUS(cudaSetDevice(st->cuda_id));
   // staging: every fixed row + 2 span words per heap + the index list, each rounded to the arena alignment

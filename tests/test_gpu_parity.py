@@ -388,6 +388,19 @@ def test_sparse_bad_runs_are_rejected(ctx):
     reason, bm = np.zeros(100, np.uint8), np.zeros(2, np.uint64)
     assert lib.nbg_diff_sts_sparse(ctx.handle, C.byref(view), 100, reason.ctypes.data_as(C.c_void_p),
                                    bm.ctypes.data_as(C.c_void_p)) == N.NBG_E_RANGE
+    # a run two values shorter than its mask says (the next run moved up): monotone, even, and still refused —
+    # the kernels size their reads of both sides by the masks
+    off = sp.arrays()["pod_to.voff"].copy()
+    off[11:] -= 2
+    view.pod_to.off = off.ctypes.data_as(N.u32p)
+    assert lib.nbg_diff_sts_sparse(ctx.handle, C.byref(view), 100, reason.ctypes.data_as(C.c_void_p),
+                                   bm.ctypes.data_as(C.c_void_p)) == N.NBG_E_RANGE
+    store = pkg.engine.Store(ctx, 100)
+    try:
+        idx = np.arange(100, dtype=np.uint64)
+        assert lib.nbg_store_put(store._h, idx.ctypes.data_as(N.u64p), 100, C.byref(view), None, None, None) == N.NBG_E_RANGE
+    finally:
+        store.close()
 
 
 # ------------------------------------ desired Service / VirtualService made on the device
