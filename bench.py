@@ -396,6 +396,25 @@ def main():
     assert np.array_equal(out_arr["r"], want["cull"][0]), "e2e cull action differs from the oracle"
     assert np.array_equal(o_sts["r"], want["diff_sts"][0]) and np.array_equal(o_svc["r"], want["diff_svc"][0]) and \
         np.array_equal(o_vs["r"], want["diff_vs"][0]), "e2e diff results differ from the oracle"
+    # ---- gather (outside every timed region): the shards' StatefulSet bitmaps come together on the host through the
+    # per-shard index maps, as a sharded controller would assemble its fleet-wide "needs update" list
+    gathered = None
+    if world > 1:
+        idx_t = torch.from_numpy(idx.astype(np.int64)).cuda()
+        upd_t = torch.from_numpy(((o_sts["r"] & 0x0F) != 0).astype(np.uint8)).cuda()
+        all_idx = [torch.empty_like(idx_t) for _ in range(world)]
+        all_upd = [torch.empty_like(upd_t) for _ in range(world)]
+        dist.all_gather(all_idx, idx_t)            # plumbing only: 11 bytes per notebook, once, after the measurements
+        dist.all_gather(all_upd, upd_t)
+        if rank == 0:
+            fleet_bits = np.zeros(fleet.n, dtype=np.uint8)
+            seen = np.zeros(fleet.n, dtype=np.uint8)
+            for gi, gu in zip(all_idx, all_upd):
+                gi = gi.cpu().numpy()
+                seen[gi] += 1
+                fleet_bits[gi] = gu.cpu().numpy()
+            gathered = {"notebooks": int(seen.sum()), "each_notebook_in_exactly_one_shard": bool((seen <= 1).all() and seen.sum() == per * world),
+                        "statefulsets_needing_update": int(fleet_bits.sum())}
     for p in keep:
         lib.nbg_free_pinned(p)
 
@@ -426,7 +445,7 @@ def main():
                    "desired_side": "StatefulSet: packed from generateStatefulSet's output; Service and VirtualService: generated on the device "
                                    "from name/port/prefix/rewrite/host words (same answer as shipping generateService/VirtualService outputs)",
                    "sharding": "namespace hash (nbg_shard_of), no collective, equal notebooks per shard",
-                   "shard_imbalance_max_over_mean": shard_imbalance,
+                   "shard_imbalance_max_over_mean": shard_imbalance, "gathered_on_rank0": gathered,
                    "cpu_binding": ("rank 0 bound to the %d CPUs NVML lists next to its GPU" % len(near)) if near else "none",
                    "streams": "one stream" if args.no_overlap else "one nbg_step_device call per step: StatefulSet kernel on the main stream, the three small kernels "
                               "on the context's side streams (event fork/join inside the library); per-kernel times are from a separate serialised pass",
