@@ -134,3 +134,46 @@ def test_put_right_behind_an_asynchronous_step(ctx):
         assert np.array_equal(r["sts"][0], b.want["sts"]) and np.array_equal(r["cull"][1], b.want["argmax"])
     finally:
         store.close()
+
+
+def test_put_and_step_from_two_threads(ctx):
+    """A controller's informer thread puts rows while its tick thread steps: whatever the interleaving, every slot's
+    answer must be the oracle's answer for one of the two rows that slot can hold — never a torn mixture."""
+    import threading
+    n = 8192
+    a, b = Source(host.FLEET_KUBEFLOW, host.SEED_BASE + 71, n), Source(host.FLEET_ODH, host.SEED_BASE + 73, n)
+    store = pkg.engine.Store(ctx, n)
+    errors, stop = [], threading.Event()
+    try:
+        all_slots = np.arange(n, dtype=np.uint64)
+        rows = {"a": a.rows(all_slots), "b": b.rows(all_slots)}
+        store.put(all_slots, *rows["a"][:4])
+
+        def writer():
+            rng = np.random.default_rng(1)
+            try:
+                for k in range(40):
+                    src = "b" if k % 2 == 0 else "a"
+                    lo = int(rng.integers(0, n - 512))
+                    sub = np.arange(lo, lo + 512, dtype=np.uint64)
+                    s = (a if src == "a" else b).rows(sub)
+                    store.put(sub, *s[:4])
+            except Exception as e:                                   # noqa: BLE001
+                errors.append(e)
+            finally:
+                stop.set()
+
+        t = threading.Thread(target=writer)
+        t.start()
+        steps = 0
+        while not stop.is_set() or steps < 3:
+            r = store.step(n, host.vs_gen_consts(), *a.now)
+            for key, got in (("sts", r["sts"][0]), ("svc", r["svc"][0]), ("vs", r["vs"][0]), ("action", r["cull"][0])):
+                ok = (got == a.want[key]) | (got == b.want[key])
+                assert ok.all(), (key, int((~ok).sum()))
+            steps += 1
+        t.join()
+        assert not errors, errors
+        assert steps >= 3
+    finally:
+        store.close()
