@@ -44,7 +44,8 @@ extern "C" {
 #define NBG_E_CUDA        (-4) /* a CUDA call failed; nbg_last_cuda_error()       */
 #define NBG_E_NILREPLICAS (-5) /* an object had a nil Spec.Replicas: the Go code
                                   would panic at COMMON:123; reason bit7 marks it */
-#define NBG_E_RANGE       (-6) /* CSR offsets not monotone or past the entry array */
+#define NBG_E_RANGE       (-6) /* CSR offsets not monotone, a sparse run that disagrees with its
+                                  mask, or a slot index past a store's capacity             */
 #define NBG_E_TOOBIG      (-7) /* batch exceeds a documented maximum              */
 
 /* ---- schema constants (frozen; tests/test_abi.py checks them) ---------- */
@@ -240,8 +241,9 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n,
 int nbg_diff_deploy(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* reason, uint64_t* bitmap);
 int nbg_diff_deploy_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint64_t n,
                            uint8_t* reason, uint64_t* bitmap, void* stream);
-/* The same predicate on sparsely stored PodSpec tiles (nbg_sts_sparse_batch): identical
- * outputs, ~4x fewer bytes per object to move over PCIe and to read from HBM. */
+/* CopyStatefulSetFields again, on sparsely stored PodSpec tiles (nbg_sts_sparse_batch): outputs identical to
+ * nbg_diff_sts, ~4x fewer bytes per object to move over PCIe and to read from HBM.  Every run must be as long
+ * as its mask says (popcount, rounded up to even): NBG_E_RANGE otherwise. */
 int nbg_diff_sts_sparse(nbg_ctx* ctx, const nbg_sts_sparse_batch* in, uint64_t n,
                         uint8_t* reason, uint64_t* bitmap);
 /* Batched CopyServiceFields (COMMON:166-195). */

@@ -280,7 +280,7 @@ const char* nbg_strerror(int status) {
     case NBG_E_NOMEM: return "device or pinned-host allocation failed";
     case NBG_E_CUDA: return "CUDA call failed (see nbg_last_cuda_error)";
     case NBG_E_NILREPLICAS: return "an object has a nil Spec.Replicas (the Go reference would panic)";
-    case NBG_E_RANGE: return "CSR offsets are not monotone";
+    case NBG_E_RANGE: return "offsets not monotone, run length disagrees with its mask, or slot out of range";
     case NBG_E_TOOBIG: return "batch exceeds a documented maximum";
     default: return "unknown status";
   }
