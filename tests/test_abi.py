@@ -114,3 +114,14 @@ def test_product_never_references_the_oracle():
                 if re.search(r"oracle[/_.]|liboracle|import oracle", text):
                     bad.append(os.path.join(dirpath, f))
     assert not bad, bad
+
+
+def test_libraries_stand_alone():
+    """The product is two plain shared libraries: no Python, no torch, no CUDA runtime .so to find at load time
+    (cudart is linked statically; the driver's libcuda is opened by it on first use)."""
+    import subprocess
+    allowed = ("linux-vdso", "libc.so", "libm.so", "libstdc++", "libgcc_s", "libdl", "librt", "libpthread", "ld-linux")
+    for name in ("libnbgraft.so", "libnbgraft_host.so"):
+        out = subprocess.run(["ldd", os.path.join(ROOT, "odh-kubeflow_b200", name)], capture_output=True, text=True).stdout
+        deps = [line.split()[0] for line in out.splitlines() if line.strip()]
+        assert deps and all(any(d.startswith(a) or ("/" + a) in d for a in allowed) for d in deps), (name, deps)
