@@ -1,0 +1,45 @@
+// Driver for tools/asan_host.sh: walks the host library (fleets, builders, ODH injections, packers, the copy half of
+// Copy*Fields, JSON rendering, culler packing) under AddressSanitizer + UBSan + LeakSanitizer.
+#include <cstdio>
+#include <cstdlib>
+#include <cstdint>
+#include <vector>
+#include "../include/nbgraft_host.h"
+int main() {
+  setenv("NBH_THREADS", "4", 1);
+  for (int kind : {2, 4}) {
+    nbh_fleet* f = nbh_fleet_new(kind, 0x6E62677261667405ull + kind, 6000, 100);
+    nbh_sts* a; nbh_svc* b; nbh_vs* c;
+    if (nbh_fleet_pack(f, nullptr, 0, 6000, &a, &b, &c)) return 1;
+    nbg_sts_sparse_batch sv; nbh_sts_view_sparse(a, &sv);
+    nbg_svc_gen_batch gv; nbh_svc_view_gen(b, &gv);
+    nbg_vs_gen_batch vv; nbh_vs_view_gen(c, &vv);
+    for (uint64_t i = 0; i < 300; ++i) {
+      nbh_obj *from, *to, *nb;
+      for (int which = 1; which <= 5; which += 2) {
+        nbh_fleet_get(f, i, which, &from); nbh_fleet_get(f, i, which + 1, &to);
+        if (which == 1) nbh_apply_sts_fields(from, to, 0x1F, 1);
+        if (which == 3) nbh_apply_svc_fields(from, to);
+        if (which == 5) nbh_apply_vs_fields(from, to, 1);
+        nbh_obj_digest(to);
+        char* j = nbh_obj_to_json(to); nbh_str_free(j);
+        nbh_obj_free(from); nbh_obj_free(to);
+      }
+      nbh_fleet_get(f, i, 0, &nb);
+      nbh_obj* m = nbh_obj_clone(nb);
+      nbh_odh_mutate(m, 31);
+      nbh_obj* s; char err[128];
+      nbh_generate_statefulset(m, nullptr, &s, err, sizeof err); nbh_obj_free(s);
+      nbh_generate_service(m, &s, err, sizeof err); nbh_obj_free(s);
+      nbh_generate_virtualservice(m, nullptr, &s, err, sizeof err); nbh_obj_free(s);
+      nbh_obj_free(m); nbh_obj_free(nb);
+    }
+    nbh_sts_free(a); nbh_svc_free(b); nbh_vs_free(c);
+    nbh_cullfleet* cf = nbh_cullfleet_new(7, 5000, 1767225600, 0, 4.0);
+    nbh_cull* cb; nbh_cullfleet_pack(cf, nullptr, 0, 5000, &cb);
+    nbh_cull_free(cb); nbh_cullfleet_free(cf);
+    nbh_fleet_free(f);
+  }
+  printf("asan driver done\n");
+  return 0;
+}
