@@ -226,6 +226,16 @@ uint64_t nbg_hash64(const void* data, size_t len);
 /* namespace -> shard (GPU) map, the batch analogue of the per-namespace List
  * at NBCTL:159: shard = mix64(ns_hash) % n_shards. */
 uint32_t nbg_shard_of(uint64_t ns_hash, uint32_t n_shards);
+/* Size-aware namespace -> shard table for fleets whose namespaces are very unequal (a Zipf fleet hashed into 8
+ * shards is 1.9x out of balance, and the step ends when the largest shard does).  The partition unit stays the
+ * namespace, as the per-namespace List of NBCTL:159 requires: every namespace goes to exactly one shard.
+ * Longest-processing-time rule: namespaces in order of decreasing size (ties: increasing ns_hash) each go to the
+ * shard that is lightest so far (ties: lowest shard number), so the result depends only on the (hash, size)
+ * pairs, not on their order in the arrays.  shard_out[k] in [0, n_shards) for namespace k; load_out (nullable,
+ * n_shards entries) receives the shards' total sizes.  Max load <= mean + largest namespace.  Host side, pure;
+ * needs no context. */
+int nbg_balance_shards(const uint64_t* ns_hash, const uint64_t* ns_size, uint64_t n_namespaces, uint32_t n_shards,
+                       uint32_t* shard_out, uint64_t* load_out);
 
 /* ---- host-buffer entry points (H2D + kernel + D2H inside the call) ----- */
 /* Batched CopyStatefulSetFields (COMMON:107-134) with the caller's template-

@@ -163,6 +163,12 @@ uint64_t nbh_fleet_ns_hash(const nbh_fleet* f, uint64_t i);   /* nbg_hash64(name
 /* Pack objects idx[0..m) (idx == NULL: the range [i0, i0+m)) with all host threads. */
 int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                    nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
+/* The same, keeping only what the reconcile step reads of the StatefulSet pairs: the SPARSE PodSpec tiles
+ * (nbh_sts_view_sparse); the dense tiles are not stored and nbh_sts_view returns NULL for pod_from / pod_to.
+ * 0.8 KB instead of 3.9 KB per pair: what lets the 10 M-notebook fleet of BASELINE config #5 sit in host memory. */
+int nbh_fleet_pack_lean(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                        nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
+int nbh_sts_is_lean(const nbh_sts* b);
 /* CPU seconds, summed over threads, that the LAST nbh_fleet_pack spent (a) synthesising the objects
  * (Notebook -> generateStatefulSet/Service/VirtualService -> drifted live copies) and (b) packing
  * them into the batch arrays.  Only (b) is work a real caller has; the bench reports both. */
@@ -171,6 +177,12 @@ void nbh_fleet_pack_timing(double* make_cpu_s, double* pack_cpu_s);
 /* Indices i in [0,n) whose namespace maps to `shard` of `n_shards` (nbg_shard_of), ascending.
  * Returns the count; writes at most cap of them (call with out=NULL to size). */
 uint64_t nbh_fleet_shard_indices(const nbh_fleet* f, uint32_t n_shards, uint32_t shard, uint64_t* out, uint64_t cap);
+/* The fleet's namespaces: ns_hash[k] = nbg_hash64(name of namespace k), ns_size[k] = notebooks in it (either may
+ * be NULL).  Returns the number of namespaces.  Input of nbg_shard_of / nbg_balance_shards. */
+uint32_t nbh_fleet_ns_table(const nbh_fleet* f, uint64_t* ns_hash, uint64_t* ns_size);
+/* As nbh_fleet_shard_indices, for an explicit namespace -> shard table (shard_of_ns[k] for namespace k). */
+uint64_t nbh_fleet_shard_indices_by_table(const nbh_fleet* f, const uint32_t* shard_of_ns, uint32_t shard,
+                                          uint64_t* out, uint64_t cap);
 /* Materialise objects of m notebooks at once: out[k*7 + which] (see nbh_fleet_get). */
 int nbh_fleet_objects(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m, nbh_obj** out);
 

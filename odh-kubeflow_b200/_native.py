@@ -204,7 +204,7 @@ def batch_struct(kind, ptr, has=lambda name: False):
 
 NBG_SYMBOLS = [
     "nbg_init", "nbg_destroy", "nbg_strerror", "nbg_last_cuda_error", "nbg_abi_version", "nbg_device_count",
-    "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of",
+    "nbg_alloc_pinned", "nbg_free_pinned", "nbg_hash64", "nbg_shard_of", "nbg_balance_shards",
     "nbg_diff_sts", "nbg_diff_svc", "nbg_diff_vs", "nbg_cull", "nbg_diff_deploy", "nbg_diff_deploy_device",
     "nbg_diff_sts_device", "nbg_diff_svc_device", "nbg_diff_vs_device", "nbg_cull_device",
     "nbg_sync", "nbg_launch_count", "nbg_ctx_stream",
@@ -237,6 +237,8 @@ def _bind_nbg(lib):
     lib.nbg_hash64.restype = C.c_uint64
     lib.nbg_shard_of.argtypes = [C.c_uint64, C.c_uint32]
     lib.nbg_shard_of.restype = C.c_uint32
+    lib.nbg_balance_shards.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]
+    lib.nbg_balance_shards.restype = C.c_int
     for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch),
                      ("nbg_diff_sts_sparse", nbg_sts_sparse_batch), ("nbg_diff_deploy", nbg_sts_batch)):
         f = getattr(lib, name)
@@ -370,6 +372,10 @@ def _bind_nbh(lib):
         "nbh_fleet_drift_class": ([_vp, C.c_uint64], C.c_int),
         "nbh_fleet_ns_hash": ([_vp, C.c_uint64], C.c_uint64),
         "nbh_fleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
+        "nbh_fleet_pack_lean": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
+        "nbh_sts_is_lean": ([_vp], C.c_int),
+        "nbh_fleet_ns_table": ([_vp, u64p, u64p], C.c_uint32),
+        "nbh_fleet_shard_indices_by_table": ([_vp, u32p, C.c_uint32, u64p, C.c_uint64], C.c_uint64),
         "nbh_fleet_pack_timing": ([P(C.c_double), P(C.c_double)], None),
         "nbh_cullfleet_new": ([C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_double], _vp),
         "nbh_cullfleet_free": ([_vp], None),
@@ -396,7 +402,7 @@ NBH_SYMBOLS = [
     "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
-    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
+    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_lean", "nbh_sts_is_lean", "nbh_fleet_ns_table", "nbh_fleet_shard_indices_by_table", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
     "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",
 ]

@@ -8,12 +8,14 @@
 // fails and every other entry point rejects the null context.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <queue>
 #include <vector>
 
 #include "../../../include/nbgraft.h"
@@ -288,6 +290,32 @@ const char* nbg_strerror(int status) {
 
 uint64_t nbg_hash64(const void* data, size_t len) { return nbg_hash_bytes(data, len); }
 uint32_t nbg_shard_of(uint64_t ns_hash, uint32_t n_shards) { return nbg_shard_of_inline(ns_hash, n_shards); }
+
+int nbg_balance_shards(const uint64_t* ns_hash, const uint64_t* ns_size, uint64_t n_ns, uint32_t n_shards,
+                       uint32_t* shard_out, uint64_t* load_out) {
+  if (n_shards == 0 || (n_ns && (!ns_hash || !ns_size || !shard_out))) return NBG_E_INVAL;
+  std::vector<uint64_t> order(n_ns);
+  for (uint64_t k = 0; k < n_ns; ++k) order[k] = k;
+  std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+    if (ns_size[a] != ns_size[b]) return ns_size[a] > ns_size[b];
+    if (ns_hash[a] != ns_hash[b]) return ns_hash[a] < ns_hash[b];
+    return a < b;
+  });
+  // lightest shard first; ties go to the lowest shard number
+  typedef std::pair<uint64_t, uint32_t> Load;
+  std::priority_queue<Load, std::vector<Load>, std::greater<Load>> heap;
+  for (uint32_t s = 0; s < n_shards; ++s) heap.push(Load(0, s));
+  for (uint64_t k : order) {
+    Load l = heap.top();
+    heap.pop();
+    shard_out[k] = l.second;
+    l.first += ns_size[k];
+    heap.push(l);
+  }
+  if (load_out)
+    for (; !heap.empty(); heap.pop()) load_out[heap.top().second] = heap.top().first;
+  return NBG_OK;
+}
 
 int nbg_init(const int* devices, int n_devices, nbg_ctx** out) {
   if (!out) return NBG_E_INVAL;

@@ -127,7 +127,13 @@ cull_kernel(nbg_cull_batch in, unsigned long long n, nbg_cull_params p,
 
   // ---- record scans, one notebook per lane.  (Tried and measured slower on B200 at 1.25 M
   // notebooks: four-lane groups with butterfly merges, 85 us; staging each warp's record run in
-  // shared memory first, 54-65 us; this plain loop with every per-notebook load hoisted, 43 us.)
+  // shared memory first, 54-65 us; the whole warp in lockstep over the longest list with predicated
+  // loads and selects, 16 instructions per slot and no branch, 45-49 us; the same with kernel and
+  // terminal records in one loop, 56-66 us; this plain loop with every per-notebook load hoisted, 43 us
+  // (unchanged by 64- or 128-thread blocks and by prefetching the terminal records' lines before the kernel scan).
+  // ncu source counters: 404 of the 687 warp instructions per 32 notebooks are these two loops, but the
+  // warps wait on three dependent memory round trips (offsets -> kernel records -> terminal records)
+  // whatever the loops cost: DESIGN.md section 3.)
   const Part ks = scan_serial((const long long*)in.k_sec, in.k_nsf, k_lo, k_hi);
   const Part ts = scan_serial((const long long*)in.t_sec, in.t_nsf, t_lo, t_hi);
 

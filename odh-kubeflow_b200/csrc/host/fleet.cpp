@@ -79,16 +79,19 @@ void StsBatch::add(const GVal& from, const GVal& to) {
   replicas_to.push_back(replicas(to));
   tmpl_from.push_back(digest_string_map(path(from, {"spec", "template", "metadata", "labels"})));
   tmpl_to.push_back(digest_string_map(path(to, {"spec", "template", "metadata", "labels"})));
-  pod_from.resize(pod_from.size() + NBG_POD_SLOTS);
-  pod_to.resize(pod_to.size() + NBG_POD_SLOTS);
-  pack_podspec(path(from, {"spec", "template", "spec"}), &pod_from[n * NBG_POD_SLOTS]);
-  pack_podspec(path(to, {"spec", "template", "spec"}), &pod_to[n * NBG_POD_SLOTS]);
+  uint64_t tile_from[NBG_POD_SLOTS], tile_to[NBG_POD_SLOTS];
+  pack_podspec(path(from, {"spec", "template", "spec"}), tile_from);
+  pack_podspec(path(to, {"spec", "template", "spec"}), tile_to);
+  if (!lean) {
+    pod_from.insert(pod_from.end(), tile_from, tile_from + NBG_POD_SLOTS);
+    pod_to.insert(pod_to.end(), tile_to, tile_to + NBG_POD_SLOTS);
+  }
   labels_from.add(path(from, {"metadata", "labels"}));
   labels_to.add(path(to, {"metadata", "labels"}));
   ann_from.add(path(from, {"metadata", "annotations"}));
   ann_to.add(path(to, {"metadata", "annotations"}));
-  sparsify_tile(&pod_from[n * NBG_POD_SLOTS], mask_from, val_from, voff_from);
-  sparsify_tile(&pod_to[n * NBG_POD_SLOTS], mask_to, val_to, voff_to);
+  sparsify_tile(tile_from, mask_from, val_from, voff_from);
+  sparsify_tile(tile_to, mask_to, val_to, voff_to);
   ++n;
 }
 void StsBatch::append(const StsBatch& o) {
@@ -101,7 +104,7 @@ void StsBatch::append(const StsBatch& o) {
   }
   extend(replicas_from, o.replicas_from); extend(replicas_to, o.replicas_to);
   extend(tmpl_from, o.tmpl_from); extend(tmpl_to, o.tmpl_to);
-  extend(pod_from, o.pod_from); extend(pod_to, o.pod_to);
+  if (!lean) { extend(pod_from, o.pod_from); extend(pod_to, o.pod_to); }
   labels_from.append(o.labels_from); labels_to.append(o.labels_to);
   ann_from.append(o.ann_from); ann_to.append(o.ann_to);
   n += o.n;
@@ -110,7 +113,7 @@ nbg_sts_batch StsBatch::view() const {
   nbg_sts_batch b{};
   b.replicas_from = replicas_from.data(); b.replicas_to = replicas_to.data();
   b.tmpl_from = tmpl_from.data(); b.tmpl_to = tmpl_to.data();
-  b.pod_from = pod_from.data(); b.pod_to = pod_to.data();
+  b.pod_from = lean ? nullptr : pod_from.data(); b.pod_to = lean ? nullptr : pod_to.data();
   b.labels_from = labels_from.view(); b.labels_to = labels_to.view();
   b.ann_from = ann_from.view(); b.ann_to = ann_to.view();
   return b;

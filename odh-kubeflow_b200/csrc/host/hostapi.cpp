@@ -572,8 +572,9 @@ NBH_API void nbh_fleet_pack_timing(double* make_cpu_s, double* pack_cpu_s) {
   if (pack_cpu_s) *pack_cpu_s = g_pack_ns.load() * 1e-9;
 }
 
-NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
-                           nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
+namespace {
+int fleet_pack_impl(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                    nbh_sts** sts, nbh_svc** svc, nbh_vs** vs, bool lean) {
   if (!f) return -1;
   g_make_ns = 0; g_pack_ns = 0;
   typedef std::chrono::steady_clock clk;
@@ -582,6 +583,7 @@ NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0,
   std::vector<StsBatch> ps(sts ? nblocks : 0);
   std::vector<SvcBatch> pv(svc ? nblocks : 0);
   std::vector<VsBatch> pw(vs ? nblocks : 0);
+  for (auto& b : ps) b.lean = lean;
   parallel_blocks(nblocks, [&](uint64_t blk) {
     const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
     Pair p;
@@ -601,13 +603,84 @@ NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0,
   });
   if (sts) {
     nbh_sts* o = new nbh_sts();
-    o->b.pod_from.reserve(m * NBG_POD_SLOTS); o->b.pod_to.reserve(m * NBG_POD_SLOTS);
+    o->b.lean = lean;
+    if (!lean) { o->b.pod_from.reserve(m * NBG_POD_SLOTS); o->b.pod_to.reserve(m * NBG_POD_SLOTS); }
+    // the value runs are the bulk of a sparse batch: size them once instead of letting the vectors double
+    size_t vf = 0, vt = 0;
+    for (const auto& b : ps) { vf += b.val_from.size(); vt += b.val_to.size(); }
+    if (vf >= (1ull << 32) || vt >= (1ull << 32)) { delete o; return -1; }   // run offsets are 32-bit (nbgraft.h)
+    o->b.val_from.reserve(vf); o->b.val_to.reserve(vt);
+    o->b.mask_from.reserve(3 * m); o->b.mask_to.reserve(3 * m);
     for (auto& b : ps) { o->b.append(b); b = StsBatch(); }
     *sts = o;
   }
-  if (svc) { nbh_svc* o = new nbh_svc(); for (auto& b : pv) { o->b.append(b); b = SvcBatch(); } *svc = o; }
-  if (vs) { nbh_vs* o = new nbh_vs(); for (auto& b : pw) { o->b.append(b); b = VsBatch(); } *vs = o; }
+  if (svc) {
+    nbh_svc* o = new nbh_svc();
+    o->b.ports_from.reserve(m * NBG_SVC_SLOTS); o->b.ports_to.reserve(m * NBG_SVC_SLOTS);
+    for (auto& b : pv) { o->b.append(b); b = SvcBatch(); }
+    *svc = o;
+  }
+  if (vs) {
+    nbh_vs* o = new nbh_vs();
+    o->b.spec_from.reserve(m * NBG_VS_SLOTS); o->b.spec_to.reserve(m * NBG_VS_SLOTS);
+    for (auto& b : pw) { o->b.append(b); b = VsBatch(); }
+    *vs = o;
+  }
   return 0;
+}
+}  // namespace
+
+NBH_API int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                           nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
+  return fleet_pack_impl(f, idx, i0, m, sts, svc, vs, false);
+}
+NBH_API int nbh_fleet_pack_lean(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
+                                nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
+  return fleet_pack_impl(f, idx, i0, m, sts, svc, vs, true);
+}
+NBH_API int nbh_sts_is_lean(const nbh_sts* b) { return b && b->b.lean ? 1 : 0; }
+
+// Namespace table of the fleet: ns_hash[k] = nbg_hash64 of namespace k's name, ns_size[k] = notebooks in it.
+NBH_API uint32_t nbh_fleet_ns_table(const nbh_fleet* f, uint64_t* ns_hash, uint64_t* ns_size) {
+  if (!f) return 0;
+  const uint32_t K = f->f.n_namespaces;
+  if (ns_hash)
+    for (uint32_t k = 0; k < K; ++k) {
+      char buf[32];
+      snprintf(buf, sizeof buf, "ns-%06u", k);
+      ns_hash[k] = nbg_hash_bytes(buf, strlen(buf));
+    }
+  if (ns_size) {
+    const uint64_t n = f->f.n, kBlock = 65536, nblocks = (n + kBlock - 1) / kBlock;
+    std::vector<std::atomic<uint64_t>> cnt(K);
+    for (auto& c : cnt) c = 0;
+    parallel_blocks(nblocks, [&](uint64_t blk) {
+      const uint64_t lo = blk * kBlock, hi = lo + kBlock < n ? lo + kBlock : n;
+      std::vector<uint32_t> local(K, 0);
+      for (uint64_t i = lo; i < hi; ++i) ++local[f->f.namespace_of(i)];
+      for (uint32_t k = 0; k < K; ++k) if (local[k]) cnt[k] += local[k];
+    });
+    for (uint32_t k = 0; k < K; ++k) ns_size[k] = cnt[k].load();
+  }
+  return K;
+}
+
+// Indices i in [0,n) whose namespace k has shard_of_ns[k] == shard, ascending (any namespace -> shard table:
+// nbg_shard_of per namespace, or the size-aware one of nbg_balance_shards).
+NBH_API uint64_t nbh_fleet_shard_indices_by_table(const nbh_fleet* f, const uint32_t* shard_of_ns, uint32_t shard,
+                                                  uint64_t* out, uint64_t cap) {
+  if (!f || !shard_of_ns) return 0;
+  const uint64_t n = f->f.n, kBlock = 65536, nblocks = (n + kBlock - 1) / kBlock;
+  std::vector<std::vector<uint64_t>> parts(nblocks);
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < n ? lo + kBlock : n;
+    for (uint64_t i = lo; i < hi; ++i)
+      if (shard_of_ns[f->f.namespace_of(i)] == shard) parts[blk].push_back(i);
+  });
+  uint64_t count = 0;
+  for (const auto& v : parts)
+    for (uint64_t i : v) { if (out && count < cap) out[count] = i; ++count; }
+  return count;
 }
 
 // A synthetic "List(StatefulSets)" for notebooks [0,n): most notebooks have one StatefulSet,

@@ -201,7 +201,13 @@ class _Batch:
 class StsBatch(_Batch):
     _new, _free, _add, _view, _struct = "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", N.nbg_sts_batch
 
+    @property
+    def lean(self):
+        return bool(N.nbh().nbh_sts_is_lean(self._h))
+
     def arrays(self):
+        if self.lean:
+            raise HostError("a lean StsBatch has no dense tiles: use .sparse()")
         v, out = self.view, {}
         n = self.n
         out["replicas_from"] = _arr(v.replicas_from, n, np.int32)
@@ -505,16 +511,19 @@ class Fleet:
     def ns_hash(self, i):
         return N.nbh().nbh_fleet_ns_hash(self._h, i)
 
-    def pack(self, i0=0, m=None, idx=None, sts=True, svc=True, vs=True):
-        """Pack objects [i0, i0+m) (or the explicit index list) on all host threads."""
+    def pack(self, i0=0, m=None, idx=None, sts=True, svc=True, vs=True, lean=False):
+        """Pack objects [i0, i0+m) (or the explicit index list) on all host threads.
+        lean=True keeps only the sparse PodSpec tiles of the StatefulSet pairs (what the step reads):
+        the StsBatch then has no dense arrays (use .sparse())."""
         if idx is not None:
             idx = np.ascontiguousarray(idx, dtype=np.uint64)
             m, ip = len(idx), idx.ctypes.data_as(N.u64p)
         else:
             m, ip = (self.n - i0 if m is None else m), None
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
-        if N.nbh().nbh_fleet_pack(self._h, ip, i0, m, C.byref(a) if sts else None, C.byref(b) if svc else None,
-                                  C.byref(c) if vs else None) != 0:
+        fn = N.nbh().nbh_fleet_pack_lean if lean else N.nbh().nbh_fleet_pack
+        if fn(self._h, ip, i0, m, C.byref(a) if sts else None, C.byref(b) if svc else None,
+              C.byref(c) if vs else None) != 0:
             raise HostError("fleet_pack")
         return (StsBatch(a.value) if sts else None, SvcBatch(b.value) if svc else None,
                 VsBatch(c.value) if vs else None)
@@ -535,6 +544,39 @@ class Fleet:
             N.nbh().nbh_fleet_shard_indices(self._h, n_shards, s, out.ctypes.data_as(N.u64p), cnt)
             return out
         return one(shard) if shard is not None else [one(s) for s in range(n_shards)]
+
+    def ns_table(self):
+        """(ns_hash[K], ns_size[K]) of the fleet's K namespaces: the input of nbg_shard_of / nbg_balance_shards."""
+        K = self.n_namespaces
+        h, sz = np.empty(K, np.uint64), np.empty(K, np.uint64)
+        got = N.nbh().nbh_fleet_ns_table(self._h, h.ctypes.data_as(N.u64p), sz.ctypes.data_as(N.u64p))
+        assert got == K
+        return h, sz
+
+    def shard_table(self, n_shards, balanced=False):
+        """namespace -> shard table (uint32[K]) and the shards' sizes: nbg_shard_of per namespace, or the
+        size-aware assignment of nbg_balance_shards (still one namespace -> one shard, NBCTL:159)."""
+        h, sz = self.ns_table()
+        table = np.empty(len(h), np.uint32)
+        load = np.zeros(n_shards, np.uint64)
+        if balanced:
+            rc = N.nbg().nbg_balance_shards(h.ctypes.data, sz.ctypes.data, len(h), n_shards, table.ctypes.data, load.ctypes.data)
+            if rc != 0:
+                raise HostError("nbg_balance_shards: %d" % rc)
+        else:
+            lib = N.nbg()
+            for k in range(len(h)):
+                table[k] = lib.nbg_shard_of(int(h[k]), n_shards)
+            load = np.bincount(table, weights=sz.astype(np.float64), minlength=n_shards).astype(np.uint64)
+        return table, load
+
+    def shard_indices_by_table(self, table, shard):
+        table = np.ascontiguousarray(table, dtype=np.uint32)
+        assert len(table) == self.n_namespaces
+        cnt = N.nbh().nbh_fleet_shard_indices_by_table(self._h, table.ctypes.data_as(N.u32p), shard, None, 0)
+        out = np.empty(cnt, dtype=np.uint64)
+        N.nbh().nbh_fleet_shard_indices_by_table(self._h, table.ctypes.data_as(N.u32p), shard, out.ctypes.data_as(N.u64p), cnt)
+        return out
 
     def join_lists(self, n):
         """Synthetic StatefulSet list for notebooks [0,n): (nb_keys[n], sts_keys[m], sts_owner[m])."""
