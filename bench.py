@@ -278,7 +278,8 @@ def timed_resident_steps(torch, dist, world, resident, steps, warmup):
         resident.run()
     stop.record()
     barrier()
-    return start.elapsed_time(stop), statistics.mean(resident.sts_ms())
+    dom = resident.sts_ms()
+    return start.elapsed_time(stop), (statistics.mean(dom) if dom else None)
 
 
 def main():

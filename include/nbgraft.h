@@ -361,9 +361,12 @@ typedef struct nbg_store nbg_store;
 int  nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** out);
 void nbg_store_destroy(nbg_store* st);
 /* Slots idx[0..m) take rows 0..m of the given HOST batches (CSR form, m objects each; a NULL batch
- * leaves that predicate's rows as they are).  idx must be < capacity and free of duplicates.
- * Returns when the rows are on the device (the host buffers may be reused at once).  After an error
- * the slots named in this call hold unspecified rows (put them again); all other slots are intact. */
+ * leaves that predicate's rows as they are).  Every idx must be < capacity (NBG_E_RANGE) and named once
+ * (NBG_E_INVAL for a duplicate: two rows would race for the slot); both are checked before anything is
+ * touched.  The rows travel as ONE pinned staging copy and ONE kernel launch per chunk of up to 65 536 rows /
+ * 48 MB (two staging slots, so the gather of a chunk overlaps the copy of the one before).
+ * Returns when the rows are on the device (the host buffers may be reused at once).  After an error other
+ * than those two the slots named in this call hold unspecified rows (put them again); all other slots are intact. */
 int  nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_sparse_batch* sts,
                    const nbg_svc_gen_batch* svc, const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull);
 /* One step over slots [0,n): outputs as nbg_step, into HOST buffers (synchronous) ... */

@@ -226,6 +226,139 @@ __device__ __forceinline__ unsigned sparse_tiles_differ_csr(const nbg_podsparse&
   return ne_bits | __reduce_or_sync(FULL, mine);
 }
 
+#ifdef NBG_STS_BULK
+// ---- experiment (tools/build_variant.sh ... -DNBG_STS_BULK): the same sweep with each warp's two value blocks
+// brought into shared memory by the bulk-copy engine (cp.async.bulk global -> shared, completion on an mbarrier)
+// instead of per-lane 128-bit loads.  One elected lane issues two copies per tile; address generation for the
+// bulk of the bytes leaves the issue slots.  A tile whose blocks exceed the budget, or whose value arrays are not
+// 16-byte aligned, takes the register path.  Measured against the register path in DESIGN.md section 3.
+#ifndef NBG_BULK_VECS
+#define NBG_BULK_VECS 640                      // 16-byte vectors per side and warp (10 KB)
+#endif
+constexpr unsigned kBulkVecs = NBG_BULK_VECS;
+constexpr unsigned kBulkWarps = 4;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ unsigned sparse_tiles_differ_bulk(const nbg_podsparse& a, const nbg_podsparse& b,
+                                                             unsigned long long i, bool live, unsigned cnt, unsigned lane,
+                                                             unsigned a_base, unsigned b_base, uint4* sa, uint4* sb,
+                                                             unsigned long long* bar, bool& staged) {
+  unsigned fv0 = 0, fv1 = 0, tv0 = 0, tv1 = 0;
+  bool mask_ne = false;
+  if (live) {
+    const unsigned long long* ma = reinterpret_cast<const unsigned long long*>(a.mask) + i * 3;
+    const unsigned long long* mb = reinterpret_cast<const unsigned long long*>(b.mask) + i * 3;
+    mask_ne = (__ldg(ma) != __ldg(mb)) | (__ldg(ma + 1) != __ldg(mb + 1)) | (__ldg(ma + 2) != __ldg(mb + 2));
+    fv0 = (__ldg(a.off + i) - a_base) >> 1;
+    fv1 = (__ldg(a.off + i + 1) - a_base) >> 1;
+    tv0 = (__ldg(b.off + i) - b_base) >> 1;
+    tv1 = (__ldg(b.off + i + 1) - b_base) >> 1;
+  }
+  const unsigned ne_bits = __ballot_sync(FULL, mask_ne);
+  const unsigned first = __shfl_sync(FULL, fv0, 0), last = __shfl_sync(FULL, fv1, cnt - 1);
+  const unsigned tfirst = __shfl_sync(FULL, tv0, 0), tlast = __shfl_sync(FULL, tv1, cnt - 1);
+  if (!live) fv0 = last;
+  const uint4* av = reinterpret_cast<const uint4*>(a.val);
+  const uint4* bv = reinterpret_cast<const uint4*>(b.val);
+  staged = (last - first) <= kBulkVecs && (tlast - tfirst) <= kBulkVecs &&
+           ((reinterpret_cast<unsigned long long>(av) | reinterpret_cast<unsigned long long>(bv)) & 15ull) == 0;
+  if (!staged) return ~0u;                               // caller takes the register path
+  const unsigned bytes_a = (last - first) * 16u, bytes_b = (tlast - tfirst) * 16u;
+  if (lane == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes_a + bytes_b) : "memory");
+    if (bytes_a)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(smem_u32(sa)), "l"(av + first), "r"(bytes_a), "r"(smem_u32(bar)) : "memory");
+    if (bytes_b)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(smem_u32(sb)), "l"(bv + tfirst), "r"(bytes_b), "r"(smem_u32(bar)) : "memory");
+  }
+  return ne_bits;                                        // the copies are in flight; finish with sparse_bulk_compare
+}
+
+__device__ __forceinline__ unsigned sparse_bulk_compare(const nbg_podsparse& a, const nbg_podsparse& b, unsigned long long i,
+                                                        bool live, unsigned cnt, unsigned lane, unsigned a_base, unsigned b_base,
+                                                        const uint4* sa, const uint4* sb, unsigned long long* bar, unsigned ne_bits) {
+  unsigned fv0 = 0, fv1 = 0, tv0 = 0;
+  if (live) {                                            // the offsets again (L1 hits): cheaper than keeping them alive
+    fv0 = (__ldg(a.off + i) - a_base) >> 1;
+    fv1 = (__ldg(a.off + i + 1) - a_base) >> 1;
+    tv0 = (__ldg(b.off + i) - b_base) >> 1;
+  }
+  const unsigned first = __shfl_sync(FULL, fv0, 0), last = __shfl_sync(FULL, fv1, cnt - 1);
+  const unsigned tfirst = __shfl_sync(FULL, tv0, 0);
+  if (!live) fv0 = last;
+  unsigned done = 0;
+  while (!done)                                          // phase 0 of a barrier used once per kernel
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_u32(bar)) : "memory");
+  unsigned mine = 0;
+  for (unsigned vb = first; vb < last; vb += 32u) {
+    const unsigned v = vb + lane;
+    unsigned o = 0;
+#pragma unroll
+    for (unsigned step = 16u; step; step >>= 1) {
+      const unsigned cand = __shfl_sync(FULL, fv0, o + step);
+      if (cand <= v) o += step;
+    }
+    const unsigned f_start = __shfl_sync(FULL, fv0, o), t_start = __shfl_sync(FULL, tv0, o);
+    if (v < last && !((ne_bits >> o) & 1u)) {
+      const uint4 x = sa[v - first];
+      const uint4 y = sb[t_start + (v - f_start) - tfirst];
+      if (diff4(x, y)) mine |= 1u << o;
+    }
+  }
+  return ne_bits | __reduce_or_sync(FULL, mine);
+}
+
+__global__ void __launch_bounds__(32 * kBulkWarps)
+diff_sts_sparse_bulk_kernel(nbg_sts_sparse_batch in, unsigned long long n,
+                            unsigned lf_base, unsigned lt_base, unsigned af_base, unsigned at_base,
+                            unsigned vf_base, unsigned vt_base,
+                            uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint4* sa = reinterpret_cast<uint4*>(smem_raw) + (size_t)wid * 2 * kBulkVecs;
+  uint4* sb = sa + kBulkVecs;
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem_raw + (size_t)kBulkWarps * 2 * kBulkVecs * 16) + wid;
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(bar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const unsigned cnt = (unsigned)min(32ull, n - base);
+  bool staged;
+  const unsigned ne_bits = sparse_tiles_differ_bulk(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base, sa, sb, bar, staged);
+  // the scalar work runs while the copies are in flight
+  unsigned reason = 0;
+  if (i < n) {
+    const int rf = __ldg(in.replicas_from + i), rt = __ldg(in.replicas_to + i);
+    if (rf == NBG_REPLICAS_NIL || rt == NBG_REPLICAS_NIL) {
+      reason |= NBG_STS_NILREPLICAS;
+    } else if (rf != rt) {
+      reason |= NBG_STS_REPLICAS;
+      if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
+    }
+    if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base, end_at<false>(in.labels_from, i) - lf_base,
+                         in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base, end_at<false>(in.labels_to, i) - lt_base))
+      reason |= NBG_STS_LABELS;
+    if (live_map_differs(in.ann_from.ent, __ldg(in.ann_from.off + i) - af_base, end_at<false>(in.ann_from, i) - af_base,
+                         in.ann_to.ent, __ldg(in.ann_to.off + i) - at_base, end_at<false>(in.ann_to, i) - at_base))
+      reason |= NBG_STS_ANNOTATIONS;
+  }
+  __syncwarp();
+  const unsigned pod_bits = staged ? sparse_bulk_compare(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base, sa, sb, bar, ne_bits)
+                                   : sparse_tiles_differ_csr(in.pod_from, in.pod_to, i, i < n, cnt, lane, vf_base, vt_base);
+  if ((pod_bits >> lane) & 1u) reason |= NBG_STS_PODSPEC;
+  store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+#endif  // NBG_STS_BULK
+
 template <bool SPANS>
 __global__ void __launch_bounds__(128)
 diff_sts_sparse_kernel(nbg_sts_sparse_batch in, unsigned long long n,
@@ -693,6 +826,20 @@ extern "C" cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch* in
   const unsigned block = 128;
   const unsigned long long grid = (n + block - 1) / block;
   const bool spans = in->pod_from.end || in->pod_to.end || in->labels_from.end || in->labels_to.end || in->ann_from.end || in->ann_to.end;
+#ifdef NBG_STS_BULK
+  if (!spans) {
+    const size_t smem = (size_t)nbg::kBulkWarps * 2 * nbg::kBulkVecs * 16 + nbg::kBulkWarps * 8;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(nbg::diff_sts_sparse_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      attr_set = true;
+    }
+    const unsigned bblock = 32 * nbg::kBulkWarps;
+    nbg::diff_sts_sparse_bulk_kernel<<<(unsigned)((n + bblock - 1) / bblock), bblock, smem, stream>>>(
+        *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason, reinterpret_cast<uint32_t*>(bitmap));
+    return cudaGetLastError();
+  }
+#endif
   (spans ? nbg::diff_sts_sparse_kernel<true> : nbg::diff_sts_sparse_kernel<false>)<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], bases[4], bases[5], reason,
       reinterpret_cast<uint32_t*>(bitmap));

@@ -7,17 +7,23 @@
 //   fixed arrays   one row per slot (replicas, masks, tiles, annotation instants, ...)
 //   heaps          one per variable-length array: payload buffer + per-slot start/end (device)
 //                  + per-slot length (host mirror, to account live/garbage and to plan compaction)
-//   put            H2D of the m rows into a staging arena, one scatter kernel per fixed array;
-//                  each heap's m runs arrive as ONE contiguous copy to the heap's tail (they are
-//                  contiguous in the caller's CSR batch) and only their start/end are scattered
+//   put            the m rows are gathered (host threads) into a PINNED staging slot laid out like its
+//                  device twin: descriptor table, slot list, every fixed array's rows, every heap's new
+//                  spans and payload.  ONE asynchronous H2D copy of the slot and ONE kernel over the
+//                  descriptor table then place everything: fixed rows and spans are scattered to their
+//                  slots, each heap's payload (contiguous in the caller's CSR batch) lands at the heap's
+//                  tail.  Large puts run as a sequence of such chunks over two slots, so the gather of
+//                  one chunk overlaps the copy of the one before
 //   compaction     when a heap cannot take the next put: live runs are copied, slot by slot, into a
 //                  fresh buffer (twice the live size if more than half of the old one was live)
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "../../../include/nbgraft.h"
@@ -25,22 +31,40 @@
 namespace {
 
 // ---------------------------------------------------------------- kernels
-// dst row idx[k] <- src row k; rows are `words` 4-byte words wide.
+// One entry of a put's descriptor table (lives at the start of the staging slot).
+struct PutDesc {
+  unsigned long long dst;   // device address of the array (kinds 0, 1) or of the heap's tail (kind 2)
+  unsigned src;             // byte offset of the source inside the staging slot
+  unsigned words;           // kind 0: 4-byte words per row; kind 2: 4-byte words in all
+  unsigned kind;            // 0 row k -> row idx[k], 1 the same for 1-byte rows, 2 contiguous copy
+  unsigned pad;
+};
+static_assert(sizeof(PutDesc) == 24, "descriptor layout");
+constexpr unsigned kMaxDesc = 96;
+
+// The whole put in one launch: blockIdx.y picks the descriptor, the blocks of a row stride over its items.
 __global__ void __launch_bounds__(256)
-scatter_rows4_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, const uint64_t* __restrict__ idx,
-                     unsigned long long m, unsigned words) {
-  const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= m * words) return;
-  const unsigned long long k = t / words;
-  const unsigned w = (unsigned)(t - k * words);
-  dst[idx[k] * words + w] = src[t];
-}
-// one byte per row
-__global__ void __launch_bounds__(256)
-scatter_rows1_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, const uint64_t* __restrict__ idx,
-                     unsigned long long m) {
-  const unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < m) dst[idx[k]] = src[k];
+put_kernel(const char* __restrict__ stage, unsigned long long m, unsigned idx_off) {
+  const PutDesc d = reinterpret_cast<const PutDesc*>(stage)[blockIdx.y];
+  const unsigned long long* idx = reinterpret_cast<const unsigned long long*>(stage + idx_off);
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d.kind == 0u) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(stage + d.src);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(d.dst);
+    for (const unsigned long long total = m * d.words; t < total; t += stride) {
+      const unsigned long long k = t / d.words;
+      dst[idx[k] * d.words + (t - k * d.words)] = src[t];
+    }
+  } else if (d.kind == 1u) {
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(stage + d.src);
+    uint8_t* dst = reinterpret_cast<uint8_t*>(d.dst);
+    for (; t < m; t += stride) dst[idx[t]] = src[t];
+  } else {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(stage + d.src);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(d.dst);
+    for (; t < d.words; t += stride) dst[t] = src[t];
+  }
 }
 // Compaction: slot j's run moves from old[start[j] .. end[j]) to fresh[new_start[j] ..); a warp per
 // slot, `words` 4-byte words per element.  start/end are rewritten in place.
@@ -106,8 +130,16 @@ struct nbg_store {
   bool stepped = false;
   Fixed fixed[F_COUNT];
   Heap heap[H_COUNT];
-  char* stage = nullptr;       // grow-only staging arena for put
-  size_t stage_cap = 0, stage_at = 0;
+  struct Slot {                // staging for put: a pinned host buffer and its device twin, same layout
+    char* host = nullptr;
+    char* dev = nullptr;
+    size_t cap = 0;
+    cudaEvent_t done = nullptr;   // recorded behind the kernel that read the device twin
+    bool used = false;
+  } slot[2];
+  unsigned next_slot = 0;
+  std::vector<uint32_t> stamp;    // duplicate check of a put's slot list: stamp[j] == epoch <=> j was named already
+  uint32_t epoch = 0;
   char* outs = nullptr;        // grow-only device outputs of nbg_store_step
   size_t outs_cap = 0;
   uint64_t compactions = 0, puts = 0, rows_put = 0;
@@ -118,30 +150,7 @@ struct nbg_store {
 namespace {
 
 constexpr size_t kStageAlign = 256;
-
-// Bump allocation in the staging arena (sized for the whole put before anything is queued).
-char* stage_take(nbg_store* st, size_t bytes) {
-  char* p = st->stage + st->stage_at;
-  st->stage_at += (bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
-  return p;
-}
-
-// src (host, m rows of `width` bytes) -> staging -> rows idx[] of dst
-int scatter_from_host(nbg_store* st, char* dst, const void* src, const uint64_t* idx_dev, uint64_t m, size_t width) {
-  if (!src) return NBG_E_INVAL;
-  char* tmp = stage_take(st, m * width);
-  CUS(cudaMemcpyAsync(tmp, src, m * width, cudaMemcpyHostToDevice, st->stream));
-  if (width == 1) {
-    scatter_rows1_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st->stream>>>(
-        reinterpret_cast<uint8_t*>(dst), reinterpret_cast<const uint8_t*>(tmp), idx_dev, m);
-  } else {
-    const unsigned words = (unsigned)(width / 4);
-    scatter_rows4_kernel<<<(unsigned)((m * words + 255) / 256), 256, 0, st->stream>>>(
-        reinterpret_cast<uint32_t*>(dst), reinterpret_cast<const uint32_t*>(tmp), idx_dev, m, words);
-  }
-  CUS(cudaGetLastError());
-  return NBG_OK;
-}
+size_t stage_round(size_t bytes) { return (bytes + kStageAlign - 1) / kStageAlign * kStageAlign; }
 
 uint64_t round_up(uint64_t x, unsigned a) { return (x + a - 1) / a * a; }
 
@@ -202,39 +211,101 @@ int heap_reserve(nbg_store* st, Heap& h, uint64_t need) {
   return NBG_OK;
 }
 
-// m runs, contiguous in the caller's CSR arrays, appended to the heap; slots idx_host[k] point at them.
-// `spans` (host scratch, 2*m) receives the new starts and ends, which are then scattered.
-int heap_put(nbg_store* st, Heap& h, const uint32_t* off, const void* payload0, const void* payload1,
-             const uint64_t* idx_host, const uint64_t* idx_dev, uint64_t m, std::vector<uint32_t>& spans) {
-  if (!off) return NBG_E_INVAL;
-  unsigned bad = 0;
-  for (uint64_t k = 0; k < m; ++k) bad |= (unsigned)(off[k] > off[k + 1]) | (off[k] % h.align != 0);
-  if (bad) return NBG_E_RANGE;
-  const uint64_t total = off[m] - off[0];
-  if (total && (!payload0 || (h.payloads > 1 && !payload1))) return NBG_E_INVAL;
-  const uint64_t need = round_up(total, h.align);
-  if (int rc = heap_reserve(st, h, need)) return rc;
-  const void* src[2] = {payload0, payload1};
-  for (int p = 0; p < h.payloads; ++p)
-    if (total)
-      CUS(cudaMemcpyAsync(h.data[p] + h.used * h.elem[p], static_cast<const char*>(src[p]) + (size_t)off[0] * h.elem[p],
-                          total * h.elem[p], cudaMemcpyHostToDevice, st->stream));
-  spans.resize(2 * m);
-  for (uint64_t k = 0; k < m; ++k) {
-    const uint32_t len = off[k + 1] - off[k];
-    spans[k] = (uint32_t)(h.used + (off[k] - off[0]));
-    spans[m + k] = spans[k] + len;
-    uint32_t& old = h.len[idx_host[k]];
-    h.live += len;
-    h.live -= old;
-    old = len;
+// A chunk of a put while it is being laid out in a staging slot.
+struct Gather { char* dst; const char* src; size_t bytes; };
+struct Chunk {
+  nbg_store* st;
+  nbg_store::Slot* slot;
+  const uint64_t* idx;          // the chunk's slot list (host)
+  uint64_t k0, m;               // rows [k0, k0+m) of the caller's batches
+  size_t at = 0;                // bump pointer inside the slot
+  std::vector<PutDesc> desc;
+  std::vector<Gather> gather;
+  size_t take(size_t bytes) { const size_t o = at; at += stage_round(bytes); return o; }
+  void add(unsigned kind, void* dst, size_t off, unsigned words) {
+    PutDesc d{};
+    d.dst = (unsigned long long)dst; d.src = (unsigned)off; d.words = words; d.kind = kind;
+    desc.push_back(d);
   }
-  h.used += need;
-  // the scatter copies `spans` into staging before this function's caller can touch it again
-  if (int rc = scatter_from_host(st, reinterpret_cast<char*>(h.start), spans.data(), idx_dev, m, 4)) return rc;
-  if (int rc = scatter_from_host(st, reinterpret_cast<char*>(h.end), spans.data() + m, idx_dev, m, 4)) return rc;
-  // `spans` is pageable memory: cudaMemcpyAsync from it has been staged by the driver on return
-  return NBG_OK;
+  // rows [k0, k0+m) of a fixed-width host array -> rows idx[] of a store array
+  int fixed(int f, const void* src) {
+    if (!src) return NBG_E_INVAL;
+    const size_t width = kFixedWidth[f], off = take(m * width);
+    gather.push_back({slot->host + off, static_cast<const char*>(src) + k0 * width, m * width});
+    add(width == 1 ? 1u : 0u, st->fixed[f].data, off, (unsigned)(width / 4));
+    return NBG_OK;
+  }
+  // the chunk's runs of one heap: payload to the heap's tail, new spans to the slots
+  int heap(Heap& h, const uint32_t* off_all, const void* payload0, const void* payload1) {
+    const uint32_t* off = off_all + k0;
+    const uint64_t total = off[m] - off[0];
+    if (total && (!payload0 || (h.payloads > 1 && !payload1))) return NBG_E_INVAL;
+    const uint64_t need = round_up(total, h.align);
+    if (int rc = heap_reserve(st, h, need)) return rc;
+    const void* src[2] = {payload0, payload1};
+    for (int p = 0; p < h.payloads && total; ++p) {
+      const size_t o = take(total * h.elem[p]);
+      gather.push_back({slot->host + o, static_cast<const char*>(src[p]) + (size_t)off[0] * h.elem[p], total * h.elem[p]});
+      add(2u, h.data[p] + h.used * h.elem[p], o, (unsigned)(total * h.elem[p] / 4));
+    }
+    const size_t o_start = take(m * 4), o_end = take(m * 4);
+    uint32_t* starts = reinterpret_cast<uint32_t*>(slot->host + o_start);
+    uint32_t* ends = reinterpret_cast<uint32_t*>(slot->host + o_end);
+    for (uint64_t k = 0; k < m; ++k) {
+      const uint32_t len = off[k + 1] - off[k];
+      starts[k] = (uint32_t)(h.used + (off[k] - off[0]));
+      ends[k] = starts[k] + len;
+      uint32_t& old = h.len[idx[k]];
+      h.live += len;
+      h.live -= old;
+      old = len;
+    }
+    h.used += need;
+    add(0u, h.start, o_start, 1u);
+    add(0u, h.end, o_end, 1u);
+    return NBG_OK;
+  }
+};
+
+// Bytes a chunk of rows [k0, k1) needs in a staging slot (upper bound: every piece rounded up).
+size_t chunk_bytes(uint64_t k0, uint64_t k1, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc,
+                   const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull) {
+  const uint64_t m = k1 - k0;
+  size_t fixed = 0;
+  for (int f = 0; f < F_COUNT; ++f) fixed += m * kFixedWidth[f] + kStageAlign;
+  size_t bytes = stage_round(kMaxDesc * sizeof(PutDesc)) + stage_round(m * 8) + fixed + (size_t)H_COUNT * 2 * (m * 4 + kStageAlign);
+  auto run = [&](const uint32_t* off, size_t elem) { if (off) bytes += (size_t)(off[k1] - off[k0]) * elem + 2 * kStageAlign; };
+  if (sts) {
+    run(sts->pod_from.off, 8); run(sts->pod_to.off, 8);
+    run(sts->labels_from.off, 16); run(sts->labels_to.off, 16); run(sts->ann_from.off, 16); run(sts->ann_to.off, 16);
+  }
+  if (svc) { run(svc->labels_to.off, 16); run(svc->ann_to.off, 16); run(svc->sel_to.off, 16); }
+  if (vs) { run(vs->hdr_from.off, 16); run(vs->hdr_to.off, 16); }
+  if (cull) { run(cull->k_off, 12); run(cull->t_off, 12); }
+  return bytes;
+}
+
+// Copy the listed pieces into the pinned slot; large chunks are split over a few threads by bytes.
+void run_gather(const std::vector<Gather>& g) {
+  size_t total = 0;
+  for (const auto& t : g) total += t.bytes;
+  unsigned threads = 1;
+  if (total > (4u << 20)) threads = std::min(4u, std::max(1u, std::thread::hardware_concurrency()));
+  auto part = [&](unsigned who) {
+    const size_t lo = total * who / threads, hi = total * (who + 1) / threads;
+    size_t at = 0;
+    for (const auto& t : g) {
+      const size_t b = std::max(lo, at), e = std::min(hi, at + t.bytes);
+      if (b < e) memcpy(t.dst + (b - at), t.src + (b - at), e - b);
+      at += t.bytes;
+      if (at >= hi) break;
+    }
+  };
+  if (threads == 1) { part(0); return; }
+  std::vector<std::thread> pool;
+  for (unsigned w = 1; w < threads; ++w) pool.emplace_back(part, w);
+  part(0);
+  for (auto& th : pool) th.join();
 }
 
 nbg_kvmap span_map(const Heap& h) {
@@ -267,7 +338,11 @@ void nbg_store_destroy(nbg_store* st) {
     if (h.start) cudaFree(h.start);
     if (h.end) cudaFree(h.end);
   }
-  if (st->stage) cudaFree(st->stage);
+  for (auto& sl : st->slot) {
+    if (sl.done) { cudaEventSynchronize(sl.done); cudaEventDestroy(sl.done); }
+    if (sl.host) cudaFreeHost(sl.host);
+    if (sl.dev) cudaFree(sl.dev);
+  }
   if (st->outs) cudaFree(st->outs);
   if (st->step_done) { cudaEventSynchronize(st->step_done); cudaEventDestroy(st->step_done); }
   if (st->stream) cudaStreamDestroy(st->stream);
@@ -285,6 +360,8 @@ int nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** ou
   st->ctx = ctx; st->device = device; st->cuda_id = id; st->capacity = capacity;
   bool ok = cudaSetDevice(id) == cudaSuccess && cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreateWithFlags(&st->step_done, cudaEventDisableTiming) == cudaSuccess;
+  for (auto& sl : st->slot) ok = ok && cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) == cudaSuccess;
+  try { st->stamp.assign(capacity, 0u); } catch (...) { ok = false; }
   for (int f = 0; ok && f < F_COUNT; ++f) {
     st->fixed[f].width = kFixedWidth[f];
     ok = cudaMalloc(&st->fixed[f].data, capacity * kFixedWidth[f]) == cudaSuccess &&
@@ -319,10 +396,27 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
   if (svc && (svc->labels_to.end || svc->ann_to.end || svc->sel_to.end)) return NBG_E_INVAL;
   if (vs && (vs->hdr_from.end || vs->hdr_to.end)) return NBG_E_INVAL;
   if (cull && (cull->k_end || cull->t_end)) return NBG_E_INVAL;
-  if (sts) {                                             // every run as long as its mask says (as the host-buffer calls check)
+  // every offset array present and monotone, sparse runs aligned and as long as their masks say
+  {
+    const uint32_t* offs[H_COUNT] = {
+        sts ? sts->pod_from.off : nullptr, sts ? sts->pod_to.off : nullptr, sts ? sts->labels_from.off : nullptr,
+        sts ? sts->labels_to.off : nullptr, sts ? sts->ann_from.off : nullptr, sts ? sts->ann_to.off : nullptr,
+        svc ? svc->labels_to.off : nullptr, svc ? svc->ann_to.off : nullptr, svc ? svc->sel_to.off : nullptr,
+        vs ? vs->hdr_from.off : nullptr, vs ? vs->hdr_to.off : nullptr, cull ? cull->k_off : nullptr, cull ? cull->t_off : nullptr};
+    const bool wanted[H_COUNT] = {!!sts, !!sts, !!sts, !!sts, !!sts, !!sts, !!svc, !!svc, !!svc, !!vs, !!vs, !!cull, !!cull};
+    for (int h = 0; h < H_COUNT; ++h) {
+      if (!wanted[h]) continue;
+      if (!offs[h]) return NBG_E_INVAL;
+      const unsigned align = st->heap[h].align;
+      unsigned bad = 0;
+      for (uint64_t k = 0; k < m; ++k) bad |= (unsigned)(offs[h][k] > offs[h][k + 1]) | (offs[h][k] % align != 0);
+      if (bad) return NBG_E_RANGE;
+    }
+  }
+  if (sts) {
     const nbg_podsparse* sides[2] = {&sts->pod_from, &sts->pod_to};
     for (const nbg_podsparse* p : sides) {
-      if (!p->mask || !p->off) return NBG_E_INVAL;
+      if (!p->mask) return NBG_E_INVAL;
       unsigned bad = 0;
       for (uint64_t k = 0; k < m; ++k) {
         const unsigned bits = (unsigned)(__builtin_popcountll(p->mask[3 * k]) + __builtin_popcountll(p->mask[3 * k + 1]) +
@@ -333,53 +427,84 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
     }
   }
   std::unique_lock<std::mutex> lock(st->mu);
+  // a slot named twice would be scattered to by two rows at once (either may win on the device while the host
+  // mirror keeps the last), so it is refused before anything is touched
+  if (++st->epoch == 0) { std::fill(st->stamp.begin(), st->stamp.end(), 0u); st->epoch = 1; }
+  for (uint64_t k = 0; k < m; ++k) {
+    if (st->stamp[idx[k]] == st->epoch) return NBG_E_INVAL;
+    st->stamp[idx[k]] = st->epoch;
+  }
   CUS(cudaSetDevice(st->cuda_id));
-  // staging: every fixed row + 2 span words per heap + the index list, each rounded to the arena alignment
-  size_t need = m * 8 + kStageAlign;
-  for (int f = 0; f < F_COUNT; ++f) need += m * kFixedWidth[f] + kStageAlign;
-  need += (size_t)H_COUNT * 2 * (m * 4 + kStageAlign);
-  if (need > st->stage_cap) {
-    CUS(cudaStreamSynchronize(st->stream));
-    if (st->stage) cudaFree(st->stage);
-    st->stage = nullptr; st->stage_cap = 0;
-    if (cudaMalloc(&st->stage, need + need / 2) != cudaSuccess) { cudaGetLastError(); return NBG_E_NOMEM; }
-    st->stage_cap = need + need / 2;
-  }
-  st->stage_at = 0;
   if (st->stepped) CUS(cudaStreamWaitEvent(st->stream, st->step_done, 0));   // rows are rewritten only after the last step has read them
-  uint64_t* idx_dev = reinterpret_cast<uint64_t*>(stage_take(st, m * 8));
-  CUS(cudaMemcpyAsync(idx_dev, idx, m * 8, cudaMemcpyHostToDevice, st->stream));
-  std::vector<uint32_t> spans;
+  constexpr size_t kChunkBytes = 48u << 20;
   int rc = NBG_OK;
-  auto fixed = [&](int f, const void* src) { if (rc == NBG_OK) rc = scatter_from_host(st, st->fixed[f].data, src, idx_dev, m, kFixedWidth[f]); };
-  auto heap = [&](int k, const uint32_t* off, const void* p0, const void* p1 = nullptr) {
-    if (rc == NBG_OK) rc = heap_put(st, st->heap[k], off, p0, p1, idx, idx_dev, m, spans);
-  };
-  if (sts) {
-    fixed(F_REP_F, sts->replicas_from); fixed(F_REP_T, sts->replicas_to);
-    fixed(F_TMPL_F, sts->tmpl_from); fixed(F_TMPL_T, sts->tmpl_to);
-    fixed(F_MASK_F, sts->pod_from.mask); fixed(F_MASK_T, sts->pod_to.mask);
-    heap(H_POD_F, sts->pod_from.off, sts->pod_from.val); heap(H_POD_T, sts->pod_to.off, sts->pod_to.val);
-    heap(H_LAB_F, sts->labels_from.off, sts->labels_from.ent); heap(H_LAB_T, sts->labels_to.off, sts->labels_to.ent);
-    heap(H_ANN_F, sts->ann_from.off, sts->ann_from.ent); heap(H_ANN_T, sts->ann_to.off, sts->ann_to.ent);
+  for (uint64_t k0 = 0; k0 < m && rc == NBG_OK;) {
+    uint64_t rows = std::min<uint64_t>(m - k0, 1u << 16);
+    while (rows > 1 && chunk_bytes(k0, k0 + rows, sts, svc, vs, cull) > kChunkBytes) rows = (rows + 1) / 2;
+    const size_t need = chunk_bytes(k0, k0 + rows, sts, svc, vs, cull);
+    nbg_store::Slot& sl = st->slot[st->next_slot];
+    st->next_slot ^= 1u;
+    if (sl.used) CUS(cudaEventSynchronize(sl.done));      // the copy and the kernel that read this slot are done
+    if (need > sl.cap) {
+      if (sl.host) cudaFreeHost(sl.host);
+      if (sl.dev) cudaFree(sl.dev);
+      sl.host = sl.dev = nullptr; sl.cap = 0;
+      const size_t cap = need + need / 4;
+      if (cudaHostAlloc(&sl.host, cap, cudaHostAllocDefault) != cudaSuccess || cudaMalloc(&sl.dev, cap) != cudaSuccess) {
+        cudaGetLastError();
+        if (sl.host) { cudaFreeHost(sl.host); sl.host = nullptr; }
+        return NBG_E_NOMEM;
+      }
+      sl.cap = cap;
+    }
+    Chunk c;
+    c.st = st; c.slot = &sl; c.idx = idx + k0; c.k0 = k0; c.m = rows;
+    c.take(kMaxDesc * sizeof(PutDesc));                   // the descriptor table sits at offset 0
+    const size_t idx_off = c.take(rows * 8);
+    c.gather.push_back({sl.host + idx_off, reinterpret_cast<const char*>(idx + k0), rows * 8});
+    auto fixed = [&](int f, const void* src) { if (rc == NBG_OK) rc = c.fixed(f, src); };
+    auto heap = [&](int k, const uint32_t* off, const void* p0, const void* p1 = nullptr) {
+      if (rc == NBG_OK) rc = c.heap(st->heap[k], off, p0, p1);
+    };
+    if (sts) {
+      fixed(F_REP_F, sts->replicas_from); fixed(F_REP_T, sts->replicas_to);
+      fixed(F_TMPL_F, sts->tmpl_from); fixed(F_TMPL_T, sts->tmpl_to);
+      fixed(F_MASK_F, sts->pod_from.mask); fixed(F_MASK_T, sts->pod_to.mask);
+      heap(H_POD_F, sts->pod_from.off, sts->pod_from.val); heap(H_POD_T, sts->pod_to.off, sts->pod_to.val);
+      heap(H_LAB_F, sts->labels_from.off, sts->labels_from.ent); heap(H_LAB_T, sts->labels_to.off, sts->labels_to.ent);
+      heap(H_ANN_F, sts->ann_from.off, sts->ann_from.ent); heap(H_ANN_T, sts->ann_to.off, sts->ann_to.ent);
+    }
+    if (svc) {
+      fixed(F_SVC_NAME, svc->name_hash); fixed(F_SVC_PORT, svc->target_port);
+      fixed(F_SVC_FLAGS, svc->flags); fixed(F_SVC_PORTS, svc->ports_to);
+      heap(H_SVC_LAB, svc->labels_to.off, svc->labels_to.ent); heap(H_SVC_ANN, svc->ann_to.off, svc->ann_to.ent);
+      heap(H_SVC_SEL, svc->sel_to.off, svc->sel_to.ent);
+    }
+    if (vs) {
+      fixed(F_VS_PREFIX, vs->prefix_hash); fixed(F_VS_REWRITE, vs->rewrite_hash); fixed(F_VS_HOST, vs->host_hash);
+      fixed(F_VS_FLAGS, vs->flags); fixed(F_VS_SPEC, vs->spec_to);
+      heap(H_VS_HDR_F, vs->hdr_from.off, vs->hdr_from.ent); heap(H_VS_HDR_T, vs->hdr_to.off, vs->hdr_to.ent);
+    }
+    if (cull) {
+      fixed(F_ANN_SEC, cull->ann_sec); fixed(F_ANN_NSF, cull->ann_nsf);
+      fixed(F_CHK_SEC, cull->chk_sec); fixed(F_CHK_NSF, cull->chk_nsf); fixed(F_NB_FLAGS, cull->nb_flags);
+      heap(H_KERNELS, cull->k_off, cull->k_sec, cull->k_nsf); heap(H_TERMINALS, cull->t_off, cull->t_sec, cull->t_nsf);
+    }
+    if (rc != NBG_OK) break;
+    if (c.desc.size() > kMaxDesc || c.at > sl.cap) { rc = NBG_E_TOOBIG; break; }   // cannot happen: sized above
+    run_gather(c.gather);
+    memcpy(sl.host, c.desc.data(), c.desc.size() * sizeof(PutDesc));
+    // widest descriptor decides the row of blocks; the others stride or idle
+    unsigned long long widest = rows;
+    for (const auto& d : c.desc) widest = std::max<unsigned long long>(widest, d.kind == 0u ? rows * d.words : d.kind == 2u ? d.words : rows);
+    const unsigned gx = (unsigned)std::min<unsigned long long>((widest + 256ull * 8 - 1) / (256ull * 8), 1024ull);
+    if (cudaMemcpyAsync(sl.dev, sl.host, c.at, cudaMemcpyHostToDevice, st->stream) != cudaSuccess) { cudaGetLastError(); rc = NBG_E_CUDA; break; }
+    put_kernel<<<dim3(gx ? gx : 1u, (unsigned)c.desc.size()), 256, 0, st->stream>>>(sl.dev, rows, (unsigned)idx_off);
+    if (cudaGetLastError() != cudaSuccess || cudaEventRecord(sl.done, st->stream) != cudaSuccess) { cudaGetLastError(); rc = NBG_E_CUDA; break; }
+    sl.used = true;
+    k0 += rows;
   }
-  if (svc) {
-    fixed(F_SVC_NAME, svc->name_hash); fixed(F_SVC_PORT, svc->target_port);
-    fixed(F_SVC_FLAGS, svc->flags); fixed(F_SVC_PORTS, svc->ports_to);
-    heap(H_SVC_LAB, svc->labels_to.off, svc->labels_to.ent); heap(H_SVC_ANN, svc->ann_to.off, svc->ann_to.ent);
-    heap(H_SVC_SEL, svc->sel_to.off, svc->sel_to.ent);
-  }
-  if (vs) {
-    fixed(F_VS_PREFIX, vs->prefix_hash); fixed(F_VS_REWRITE, vs->rewrite_hash); fixed(F_VS_HOST, vs->host_hash);
-    fixed(F_VS_FLAGS, vs->flags); fixed(F_VS_SPEC, vs->spec_to);
-    heap(H_VS_HDR_F, vs->hdr_from.off, vs->hdr_from.ent); heap(H_VS_HDR_T, vs->hdr_to.off, vs->hdr_to.ent);
-  }
-  if (cull) {
-    fixed(F_ANN_SEC, cull->ann_sec); fixed(F_ANN_NSF, cull->ann_nsf);
-    fixed(F_CHK_SEC, cull->chk_sec); fixed(F_CHK_NSF, cull->chk_nsf); fixed(F_NB_FLAGS, cull->nb_flags);
-    heap(H_KERNELS, cull->k_off, cull->k_sec, cull->k_nsf); heap(H_TERMINALS, cull->t_off, cull->t_sec, cull->t_nsf);
-  }
-  // the caller's buffers (possibly pinned: truly asynchronous copies) are borrowed only until we return
+  // the rows are on the device when the call returns (the caller's buffers were only read by the gather)
   if (cudaStreamSynchronize(st->stream) != cudaSuccess) { cudaGetLastError(); if (rc == NBG_OK) rc = NBG_E_CUDA; }
   if (rc == NBG_OK) { st->puts++; st->rows_put += m; }
   return rc;

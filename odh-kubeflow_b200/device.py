@@ -71,29 +71,30 @@ class DeviceBatch:
         lib = N.nbg()
         if stream is None:
             stream = torch.cuda.current_stream(self.device).cuda_stream
+        di = ctx.index_of(self.device)        # the C ABI wants the context's index of the device the batch lives on
         o = [C.c_void_p(t.data_ptr()) for t in self.outs]
         if self.kind == "CullBatch":
             now = now or (host.NOW_SEC, host.NOW_NSEC)
             p = N.nbg_cull_params(now[0], now[1], cull_idle_min, check_period_min, mode)
-            rc = lib.nbg_cull_device(ctx.handle, 0, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
+            rc = lib.nbg_cull_device(ctx.handle, di, C.byref(self._struct), self.n, C.byref(p), o[0], o[1], o[2], o[3],
                                      C.c_void_p(stream))
         elif self.kind == "svc_gen":
-            rc = lib.nbg_diff_svc_gen_device(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
+            rc = lib.nbg_diff_svc_gen_device(ctx.handle, di, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
         elif self.kind == "vs_gen":
             from . import host as _host
             if not hasattr(self, "_consts"):
                 self._consts = _host.vs_gen_consts()
-            rc = lib.nbg_diff_vs_gen_device(ctx.handle, 0, C.byref(self._struct), C.byref(self._consts), self.n, o[0], o[1],
+            rc = lib.nbg_diff_vs_gen_device(ctx.handle, di, C.byref(self._struct), C.byref(self._consts), self.n, o[0], o[1],
                                             C.c_void_p(stream))
         elif self.kind == "GenBatch":
-            rc = lib.nbg_diff_generic_device(ctx.handle, 0, C.byref(self._struct), self.n, self.mode, o[0], o[1], C.c_void_p(stream))
+            rc = lib.nbg_diff_generic_device(ctx.handle, di, C.byref(self._struct), self.n, self.mode, o[0], o[1], C.c_void_p(stream))
         elif self.kind == "RestartBatch":
-            rc = lib.nbg_restart_block_device(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
+            rc = lib.nbg_restart_block_device(ctx.handle, di, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
         else:
             fn = {"StsBatch": lib.nbg_diff_sts_device, "StsSparseBatch": lib.nbg_diff_sts_sparse_device,
                   "SvcBatch": lib.nbg_diff_svc_device,
                   "VsBatch": lib.nbg_diff_vs_device}[self.kind]
-            rc = fn(ctx.handle, 0, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
+            rc = fn(ctx.handle, di, C.byref(self._struct), self.n, o[0], o[1], C.c_void_p(stream))
         if rc != N.NBG_OK:
             from .engine import NbgError
             raise NbgError(rc, "nbg_*_device")
@@ -131,6 +132,7 @@ class ResidentStep:
         self._o = o
         self._refs = [C.byref(b._struct) if b is not None else None for b in (sts, svc, vs, cull)]
         self.launches = len(given)
+        self._di = ctx.index_of(self.device)  # the context's index of the device the batches live on
         # optional timing of the StatefulSet kernel inside the running step: pairs of events the
         # library records around that launch, read back with sts_ms()
         self._pairs, self._free = [], []
@@ -154,7 +156,7 @@ class ResidentStep:
             a, b = self._free.pop()
             self._pairs.append((a, b))
             e0, e1 = C.c_void_p(a.cuda_event), C.c_void_p(b.cuda_event)
-        rc = N.nbg().nbg_step_device(self.ctx.handle, 0, self._refs[0], self._refs[1], self._refs[2],
+        rc = N.nbg().nbg_step_device(self.ctx.handle, self._di, self._refs[0], self._refs[1], self._refs[2],
                                      C.byref(self._consts) if self._consts is not None else None, self._refs[3],
                                      C.byref(self._p), self.n, C.byref(self._o), C.c_void_p(stream), e0, e1)
         if rc != N.NBG_OK:

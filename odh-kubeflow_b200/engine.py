@@ -68,6 +68,17 @@ class Context:
     def launch_count(self):
         return int(self._lib.nbg_launch_count(self._h))
 
+    def index_of(self, cuda_ordinal):
+        """Position of CUDA device `cuda_ordinal` in this context (what the nbg_*_device calls take as
+        `device`); raises when the context was not created on that device."""
+        cache = self.__dict__.setdefault("_index_of", {})
+        if cuda_ordinal not in cache:
+            for k in range(self._lib.nbg_device_count(self._h)):
+                cache[self._lib.nbg_device_id(self._h, k)] = k
+        if cuda_ordinal not in cache:
+            raise ValueError("CUDA device %d is not part of this context" % cuda_ordinal)
+        return cache[cuda_ordinal]
+
     # ---- host-buffer calls (H2D + kernel + D2H inside) -------------------
     def _diff(self, fn, batch, allow_nil=False):
         view = batch.view

@@ -461,6 +461,49 @@ def test_one_context_over_two_devices():
         c2.close()
 
 
+def test_resident_batches_on_the_second_device_of_a_context():
+    """Context([0, 1]) with batches resident on CUDA device 1: the *_device calls must be given the context's index
+    of that device (1), not 0 — the kernels run on device 1's stream over device 1's pointers.  Skipped on a
+    one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    devmod = importlib.import_module("odh-kubeflow_b200.device")
+    c2 = pkg.Context([0, 1])
+    try:
+        assert c2.index_of(1) == 1 and c2.index_of(0) == 0
+        with pytest.raises(ValueError):
+            c2.index_of(5)
+        n = 40_003
+        fleet = host.Fleet(host.FLEET_KUBEFLOW, 43, n, 300)
+        sts, svc, vs = fleet.pack()
+        cf = host.CullFleet(44, n)
+        cb = cf.pack()
+        now = (cf.now_sec, cf.now_nsec)
+        want = (O.packed_diff_sts(sts)[0], O.packed_diff_svc(svc)[0], O.packed_diff_vs(vs)[0], O.packed_cull(cb, now, 1440, 1, 1)[0])
+        d = [devmod.DeviceBatch.from_host(b, device=1) for b in (sts.sparse(), svc.gen(), vs.gen(), cb)]
+        for b, w in zip(d, want):                       # each kernel alone ...
+            outs = b.run(c2, now=now) if b.kind == "CullBatch" else b.run(c2)
+            torch.cuda.synchronize(1)
+            assert np.array_equal(outs[0].cpu().numpy(), w)
+            outs[0].zero_()
+        devmod.ResidentStep(c2, *d, now=now).run()      # ... and the four as one step
+        torch.cuda.synchronize(1)
+        for b, w in zip(d, want):
+            assert np.array_equal(b.outs[0].cpu().numpy(), w)
+        one = pkg.Context([1])                          # a context on device 1 alone calls it index 0
+        try:
+            assert one.index_of(1) == 0
+            d[0].outs[0].zero_()
+            d[0].run(one)
+            torch.cuda.synchronize(1)
+            assert np.array_equal(d[0].outs[0].cpu().numpy(), want[0])
+        finally:
+            one.close()
+    finally:
+        c2.close()
+
+
 @pytest.mark.parametrize("n", [1, 5000, 140_001])
 def test_step_in_one_call_equals_the_four_calls(ctx, n):
     fleet = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 16, n, max(n // 40, 1))

@@ -102,6 +102,38 @@ def test_store_rejects_bad_arguments(ctx):
         store.put(np.arange(8), s1, s2, s3, s4)
         r = store.step(8, host.vs_gen_consts(), *src.now)
         assert np.array_equal(r["sts"][0], src.want["sts"][:8])
+        # a slot named twice in one put is refused (two rows would race for it), and nothing is changed by the call
+        before = store.stats()
+        with pytest.raises(pkg.engine.NbgError) as e:
+            store.put(np.array([1, 2, 3, 4, 5, 6, 7, 1]), s1, s2, s3, s4)
+        assert e.value.status == N.NBG_E_INVAL
+        assert store.stats() == before
+        r = store.step(8, host.vs_gen_consts(), *src.now)
+        assert np.array_equal(r["sts"][0], src.want["sts"][:8])
+        store.put(np.array([7, 6, 5, 4, 3, 2, 1, 0]), s1, s2, s3, s4)         # the same slots again in another order: fine
+        r = store.step(8, host.vs_gen_consts(), *src.now)
+        assert np.array_equal(r["sts"][0], src.want["sts"][:8][::-1])
+    finally:
+        store.close()
+
+
+def test_a_large_put_runs_as_several_chunks(ctx):
+    """A put of more rows than one staging slot takes (> 65 536 rows, or > 48 MB) is cut into chunks that
+    alternate between the two slots; slots are written in a scrambled order so that every chunk scatters all
+    over the store.  The step over the store must equal the oracle on the rows the slots hold."""
+    n = 150_001
+    src = Source(host.FLEET_KUBEFLOW, host.SEED_BASE + 47, n)
+    perm = np.random.default_rng(11).permutation(n).astype(np.uint64)
+    s1, s2, s3, s4, keep = src.rows(np.arange(n, dtype=np.uint64))
+    store = pkg.engine.Store(ctx, n)
+    try:
+        store.put(perm, s1, s2, s3, s4)                                       # row k -> slot perm[k]
+        want = {k: np.zeros(n, v.dtype) for k, v in src.want.items()}
+        for k, v in src.want.items():
+            want[k][perm.astype(np.int64)] = v
+        check(store, n, want, src.now)
+        st = store.stats()
+        assert st["puts"] == 1 and st["rows_put"] == n and st["garbage_bytes"] == 0
     finally:
         store.close()
 
