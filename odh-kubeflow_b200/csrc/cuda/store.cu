@@ -5,25 +5,27 @@
 // variable-length parts are SPANS (off,end) into the store's heaps.
 //
 //   fixed arrays   one row per slot (replicas, masks, tiles, annotation instants, ...)
-//   heaps          one per variable-length array: payload buffer + per-slot start/end (device)
-//                  + per-slot length (host mirror, to account live/garbage and to plan compaction)
-//   put            the m rows are gathered (host threads) into a PINNED staging slot laid out like its
+//   heaps          one per variable-length array: payload buffer + per-slot start/end, all on the device; the
+//                  host keeps three numbers per heap (capacity, used, live).  What a put replaces is added up
+//                  by the put's own kernel and read back with it, so no per-slot state lives on the host
+//   put            the m rows are gathered into a PINNED staging slot laid out like its
 //                  device twin: descriptor table, slot list, every fixed array's rows, every heap's new
 //                  spans and payload.  ONE asynchronous H2D copy of the slot and ONE kernel over the
 //                  descriptor table then place everything: fixed rows and spans are scattered to their
 //                  slots, each heap's payload (contiguous in the caller's CSR batch) lands at the heap's
 //                  tail.  Large puts run as a sequence of such chunks over two slots, so the gather of
 //                  one chunk overlaps the copy of the one before
-//   compaction     when a heap cannot take the next put: live runs are copied, slot by slot, into a
-//                  fresh buffer (twice the live size if more than half of the old one was live)
+//   compaction     when a heap cannot take the next put: the spans are read back, live runs are copied, slot by
+//                  slot, into a fresh buffer (twice the live size if more than half of the old one was live)
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <new>
-#include <thread>
 #include <vector>
 
 #include "../../../include/nbgraft.h"
@@ -33,18 +35,21 @@ namespace {
 // ---------------------------------------------------------------- kernels
 // One entry of a put's descriptor table (lives at the start of the staging slot).
 struct PutDesc {
-  unsigned long long dst;   // device address of the array (kinds 0, 1) or of the heap's tail (kind 2)
-  unsigned src;             // byte offset of the source inside the staging slot
-  unsigned words;           // kind 0: 4-byte words per row; kind 2: 4-byte words in all
-  unsigned kind;            // 0 row k -> row idx[k], 1 the same for 1-byte rows, 2 contiguous copy
-  unsigned pad;
+  unsigned long long dst;   // device address of the array (kinds 0, 1), of the heap's tail (2) or of the heap's start[] (3)
+  unsigned long long dst2;  // kind 3: device address of the heap's end[]
+  unsigned src;             // byte offset of the source inside the staging slot (kind 3: the new starts)
+  unsigned words;           // kind 0: 4-byte words per row; kind 2: 4-byte words in all; kind 3: byte offset of the new ends
+  unsigned kind;            // 0 row k -> row idx[k], 1 the same for 1-byte rows, 2 contiguous copy, 3 a heap's spans
+  unsigned heap;            // kind 3: which heap (index into the replaced-length counters)
 };
-static_assert(sizeof(PutDesc) == 24, "descriptor layout");
+static_assert(sizeof(PutDesc) == 32, "descriptor layout");
 constexpr unsigned kMaxDesc = 96;
 
 // The whole put in one launch: blockIdx.y picks the descriptor, the blocks of a row stride over its items.
+// Kind 3 also adds up the lengths of the runs it replaces (replaced[heap]), which is how the store knows how much
+// of a heap is garbage without keeping a host copy of every slot's length.
 __global__ void __launch_bounds__(256)
-put_kernel(const char* __restrict__ stage, unsigned long long m, unsigned idx_off) {
+put_kernel(const char* __restrict__ stage, unsigned long long m, unsigned idx_off, unsigned long long* __restrict__ replaced) {
   const PutDesc d = reinterpret_cast<const PutDesc*>(stage)[blockIdx.y];
   const unsigned long long* idx = reinterpret_cast<const unsigned long long*>(stage + idx_off);
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -60,10 +65,24 @@ put_kernel(const char* __restrict__ stage, unsigned long long m, unsigned idx_of
     const uint8_t* src = reinterpret_cast<const uint8_t*>(stage + d.src);
     uint8_t* dst = reinterpret_cast<uint8_t*>(d.dst);
     for (; t < m; t += stride) dst[idx[t]] = src[t];
-  } else {
+  } else if (d.kind == 2u) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(stage + d.src);
     uint32_t* dst = reinterpret_cast<uint32_t*>(d.dst);
     for (; t < d.words; t += stride) dst[t] = src[t];
+  } else {
+    const uint32_t* ns = reinterpret_cast<const uint32_t*>(stage + d.src);
+    const uint32_t* ne = reinterpret_cast<const uint32_t*>(stage + d.words);
+    uint32_t* start = reinterpret_cast<uint32_t*>(d.dst);
+    uint32_t* end = reinterpret_cast<uint32_t*>(d.dst2);
+    unsigned long long gone = 0;
+    for (; t < m; t += stride) {                          // a slot is named once per put: no two threads share one
+      const unsigned long long j = idx[t];
+      gone += end[j] - start[j];
+      start[j] = ns[t];
+      end[j] = ne[t];
+    }
+    for (unsigned o = 16; o; o >>= 1) gone += __shfl_xor_sync(0xFFFFFFFFu, gone, o);
+    if ((threadIdx.x & 31u) == 0 && gone) atomicAdd(replaced + d.heap, gone);
   }
 }
 // Compaction: slot j's run moves from old[start[j] .. end[j]) to fresh[new_start[j] ..); a warp per
@@ -99,7 +118,6 @@ struct Heap {                  // one variable-length array (or two that share a
   char* data[2] = {nullptr, nullptr};
   uint64_t cap = 0, used = 0, live = 0;      // elements
   uint32_t *start = nullptr, *end = nullptr; // device, one per slot
-  std::vector<uint32_t> len;                 // host mirror of end - start
 };
 
 enum FixedId {
@@ -138,6 +156,7 @@ struct nbg_store {
     bool used = false;
   } slot[2];
   unsigned next_slot = 0;
+  unsigned long long* replaced = nullptr;   // device, H_COUNT counters: lengths of the runs the current put replaces
   std::vector<uint32_t> stamp;    // duplicate check of a put's slot list: stamp[j] == epoch <=> j was named already
   uint32_t epoch = 0;
   char* outs = nullptr;        // grow-only device outputs of nbg_store_step
@@ -157,12 +176,17 @@ uint64_t round_up(uint64_t x, unsigned a) { return (x + a - 1) / a * a; }
 // Make room for `need` more elements at the tail of a heap: compact (and grow) when it is full.
 int heap_reserve(nbg_store* st, Heap& h, uint64_t need) {
   if (h.used + need <= h.cap) return NBG_OK;
-  // plan the compacted layout on the host: live runs in slot order, each aligned
-  std::vector<uint32_t> new_start(st->capacity);
+  // plan the compacted layout on the host from the spans as they are on the device once everything queued so far
+  // has run: live runs in slot order, each aligned.  (Compaction is rare and already costs an allocation and a copy
+  // of the whole heap; reading the spans back here is what lets a put do without a host copy of every run length.)
+  std::vector<uint32_t> new_start(st->capacity), cur_start(st->capacity), cur_end(st->capacity);
+  CUS(cudaStreamSynchronize(st->stream));
+  CUS(cudaMemcpy(cur_start.data(), h.start, st->capacity * 4, cudaMemcpyDeviceToHost));
+  CUS(cudaMemcpy(cur_end.data(), h.end, st->capacity * 4, cudaMemcpyDeviceToHost));
   uint64_t at = 0;
   for (uint64_t j = 0; j < st->capacity; ++j) {
     new_start[j] = (uint32_t)at;
-    at = round_up(at + h.len[j], h.align);
+    at = round_up(at + (cur_end[j] - cur_start[j]), h.align);
   }
   uint64_t cap = h.cap;
   if (at + need > cap / 2) cap = 2 * (at + need) + 1024;      // mostly live: grow
@@ -207,7 +231,7 @@ int heap_reserve(nbg_store* st, Heap& h, uint64_t need) {
   }
   h.cap = cap;
   h.used = at;
-  if (h.live) st->compactions++;
+  if (at) st->compactions++;
   return NBG_OK;
 }
 
@@ -251,18 +275,14 @@ struct Chunk {
     const size_t o_start = take(m * 4), o_end = take(m * 4);
     uint32_t* starts = reinterpret_cast<uint32_t*>(slot->host + o_start);
     uint32_t* ends = reinterpret_cast<uint32_t*>(slot->host + o_end);
-    for (uint64_t k = 0; k < m; ++k) {
-      const uint32_t len = off[k + 1] - off[k];
-      starts[k] = (uint32_t)(h.used + (off[k] - off[0]));
-      ends[k] = starts[k] + len;
-      uint32_t& old = h.len[idx[k]];
-      h.live += len;
-      h.live -= old;
-      old = len;
-    }
+    const uint32_t base = (uint32_t)h.used - off[0];
+    for (uint64_t k = 0; k < m; ++k) { starts[k] = base + off[k]; ends[k] = base + off[k + 1]; }
     h.used += need;
-    add(0u, h.start, o_start, 1u);
-    add(0u, h.end, o_end, 1u);
+    h.live += total;                                     // what the put replaces is subtracted when it has run
+    PutDesc d{};
+    d.dst = (unsigned long long)h.start; d.dst2 = (unsigned long long)h.end;
+    d.src = (unsigned)o_start; d.words = (unsigned)o_end; d.kind = 3u; d.heap = (unsigned)(&h - st->heap);
+    desc.push_back(d);
     return NBG_OK;
   }
 };
@@ -285,27 +305,11 @@ size_t chunk_bytes(uint64_t k0, uint64_t k1, const nbg_sts_sparse_batch* sts, co
   return bytes;
 }
 
-// Copy the listed pieces into the pinned slot; large chunks are split over a few threads by bytes.
+// Copy the listed pieces into the pinned slot.  One thread: measured on the B200 host, three more gather threads
+// (a pool living with the store) cut the gather of a 14 MB put from 1.1 to 0.8 ms but slowed the planning loop
+// and the DMA running beside it by more (2.0 ms per put against 1.45): the host's memory system is the shared limit.
 void run_gather(const std::vector<Gather>& g) {
-  size_t total = 0;
-  for (const auto& t : g) total += t.bytes;
-  unsigned threads = 1;
-  if (total > (4u << 20)) threads = std::min(4u, std::max(1u, std::thread::hardware_concurrency()));
-  auto part = [&](unsigned who) {
-    const size_t lo = total * who / threads, hi = total * (who + 1) / threads;
-    size_t at = 0;
-    for (const auto& t : g) {
-      const size_t b = std::max(lo, at), e = std::min(hi, at + t.bytes);
-      if (b < e) memcpy(t.dst + (b - at), t.src + (b - at), e - b);
-      at += t.bytes;
-      if (at >= hi) break;
-    }
-  };
-  if (threads == 1) { part(0); return; }
-  std::vector<std::thread> pool;
-  for (unsigned w = 1; w < threads; ++w) pool.emplace_back(part, w);
-  part(0);
-  for (auto& th : pool) th.join();
+  for (const auto& t : g) memcpy(t.dst, t.src, t.bytes);
 }
 
 nbg_kvmap span_map(const Heap& h) {
@@ -344,6 +348,7 @@ void nbg_store_destroy(nbg_store* st) {
     if (sl.dev) cudaFree(sl.dev);
   }
   if (st->outs) cudaFree(st->outs);
+  if (st->replaced) cudaFree(st->replaced);
   if (st->step_done) { cudaEventSynchronize(st->step_done); cudaEventDestroy(st->step_done); }
   if (st->stream) cudaStreamDestroy(st->stream);
   delete st;
@@ -361,6 +366,7 @@ int nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** ou
   bool ok = cudaSetDevice(id) == cudaSuccess && cudaStreamCreateWithFlags(&st->stream, cudaStreamNonBlocking) == cudaSuccess &&
             cudaEventCreateWithFlags(&st->step_done, cudaEventDisableTiming) == cudaSuccess;
   for (auto& sl : st->slot) ok = ok && cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaMalloc(&st->replaced, H_COUNT * sizeof(unsigned long long)) == cudaSuccess;
   try { st->stamp.assign(capacity, 0u); } catch (...) { ok = false; }
   for (int f = 0; ok && f < F_COUNT; ++f) {
     st->fixed[f].width = kFixedWidth[f];
@@ -374,7 +380,6 @@ int nbg_store_create(nbg_ctx* ctx, int device, uint64_t capacity, nbg_store** ou
     h.elem[0] = (records || pod) ? 8 : sizeof(nbg_kv);
     h.elem[1] = records ? 4 : 0;
     h.align = pod ? 2 : 1;                               // sparse runs stay 16-byte aligned
-    try { h.len.assign(capacity, 0u); } catch (...) { ok = false; break; }
     ok = cudaMalloc(&h.start, capacity * 4) == cudaSuccess && cudaMalloc(&h.end, capacity * 4) == cudaSuccess &&
          cudaMemsetAsync(h.start, 0, capacity * 4, st->stream) == cudaSuccess &&
          cudaMemsetAsync(h.end, 0, capacity * 4, st->stream) == cudaSuccess;
@@ -436,8 +441,30 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
   }
   CUS(cudaSetDevice(st->cuda_id));
   if (st->stepped) CUS(cudaStreamWaitEvent(st->stream, st->step_done, 0));   // rows are rewritten only after the last step has read them
-  constexpr size_t kChunkBytes = 48u << 20;
+  CUS(cudaMemsetAsync(st->replaced, 0, H_COUNT * sizeof(unsigned long long), st->stream));
+  // chunk size: a quarter of the put (so that gathering one chunk overlaps the copy of the one before), within 2..48 MB
+  const size_t kChunkBytes = std::min<size_t>(48u << 20, std::max<size_t>(2u << 20, chunk_bytes(0, m, sts, svc, vs, cull) / 4));
   int rc = NBG_OK;
+  {
+    // room for the WHOLE put in every heap before the first chunk is queued: a large put then costs each heap at
+    // most one compaction, however many chunks carry it (each chunk pads its runs' total up to the heap's alignment)
+    const uint32_t* offs[H_COUNT] = {
+        sts ? sts->pod_from.off : nullptr, sts ? sts->pod_to.off : nullptr, sts ? sts->labels_from.off : nullptr,
+        sts ? sts->labels_to.off : nullptr, sts ? sts->ann_from.off : nullptr, sts ? sts->ann_to.off : nullptr,
+        svc ? svc->labels_to.off : nullptr, svc ? svc->ann_to.off : nullptr, svc ? svc->sel_to.off : nullptr,
+        vs ? vs->hdr_from.off : nullptr, vs ? vs->hdr_to.off : nullptr, cull ? cull->k_off : nullptr, cull ? cull->t_off : nullptr};
+    const uint64_t chunks = m / 256 + 2;                // generous bound on the number of chunks (a short reserve only costs a compaction)
+    for (int h = 0; h < H_COUNT && rc == NBG_OK; ++h)
+      if (offs[h]) rc = heap_reserve(st, st->heap[h], (uint64_t)(offs[h][m] - offs[h][0]) + chunks * st->heap[h].align);
+    if (rc != NBG_OK) return rc;
+  }
+#ifdef NBG_STORE_TIMING
+  auto tick = [] { return std::chrono::steady_clock::now(); };
+  auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return (double)std::chrono::duration_cast<std::chrono::nanoseconds>(b - a).count() * 1e-3; };
+  const auto t_begin = tick();
+  double t_layout = 0, t_gather = 0, t_queue = 0;
+#endif
   for (uint64_t k0 = 0; k0 < m && rc == NBG_OK;) {
     uint64_t rows = std::min<uint64_t>(m - k0, 1u << 16);
     while (rows > 1 && chunk_bytes(k0, k0 + rows, sts, svc, vs, cull) > kChunkBytes) rows = (rows + 1) / 2;
@@ -457,6 +484,9 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
       }
       sl.cap = cap;
     }
+#ifdef NBG_STORE_TIMING
+    const auto t0 = tick();
+#endif
     Chunk c;
     c.st = st; c.slot = &sl; c.idx = idx + k0; c.k0 = k0; c.m = rows;
     c.take(kMaxDesc * sizeof(PutDesc));                   // the descriptor table sits at offset 0
@@ -492,20 +522,40 @@ int nbg_store_put(nbg_store* st, const uint64_t* idx, uint64_t m, const nbg_sts_
     }
     if (rc != NBG_OK) break;
     if (c.desc.size() > kMaxDesc || c.at > sl.cap) { rc = NBG_E_TOOBIG; break; }   // cannot happen: sized above
+#ifdef NBG_STORE_TIMING
+    const auto t1 = tick();
+#endif
     run_gather(c.gather);
     memcpy(sl.host, c.desc.data(), c.desc.size() * sizeof(PutDesc));
+#ifdef NBG_STORE_TIMING
+    const auto t2 = tick();
+#endif
     // widest descriptor decides the row of blocks; the others stride or idle
     unsigned long long widest = rows;
     for (const auto& d : c.desc) widest = std::max<unsigned long long>(widest, d.kind == 0u ? rows * d.words : d.kind == 2u ? d.words : rows);
     const unsigned gx = (unsigned)std::min<unsigned long long>((widest + 256ull * 8 - 1) / (256ull * 8), 1024ull);
     if (cudaMemcpyAsync(sl.dev, sl.host, c.at, cudaMemcpyHostToDevice, st->stream) != cudaSuccess) { cudaGetLastError(); rc = NBG_E_CUDA; break; }
-    put_kernel<<<dim3(gx ? gx : 1u, (unsigned)c.desc.size()), 256, 0, st->stream>>>(sl.dev, rows, (unsigned)idx_off);
+    put_kernel<<<dim3(gx ? gx : 1u, (unsigned)c.desc.size()), 256, 0, st->stream>>>(sl.dev, rows, (unsigned)idx_off, st->replaced);
     if (cudaGetLastError() != cudaSuccess || cudaEventRecord(sl.done, st->stream) != cudaSuccess) { cudaGetLastError(); rc = NBG_E_CUDA; break; }
     sl.used = true;
     k0 += rows;
+#ifdef NBG_STORE_TIMING
+    const auto t3 = tick();
+    t_layout += us(t0, t1); t_gather += us(t1, t2); t_queue += us(t2, t3);
+#endif
   }
   // the rows are on the device when the call returns (the caller's buffers were only read by the gather)
-  if (cudaStreamSynchronize(st->stream) != cudaSuccess) { cudaGetLastError(); if (rc == NBG_OK) rc = NBG_E_CUDA; }
+#ifdef NBG_STORE_TIMING
+  const auto t_sync0 = tick();
+#endif
+  unsigned long long gone[H_COUNT] = {};
+  if (cudaMemcpyAsync(gone, st->replaced, sizeof gone, cudaMemcpyDeviceToHost, st->stream) != cudaSuccess ||
+      cudaStreamSynchronize(st->stream) != cudaSuccess) { cudaGetLastError(); if (rc == NBG_OK) rc = NBG_E_CUDA; }
+  else for (int h = 0; h < H_COUNT; ++h) st->heap[h].live -= gone[h];
+#ifdef NBG_STORE_TIMING
+  fprintf(stderr, "put m=%llu: layout %.0f us, gather %.0f us, queue %.0f us, final sync %.0f us, total %.0f us\n",
+          (unsigned long long)m, t_layout, t_gather, t_queue, us(t_sync0, tick()), us(t_begin, tick()));
+#endif
   if (rc == NBG_OK) { st->puts++; st->rows_put += m; }
   return rc;
 }

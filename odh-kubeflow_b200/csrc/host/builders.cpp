@@ -397,6 +397,42 @@ bool odh_webhook_mutate(GVal* nb, const OdhInject& what) {
         if (!exists) append(&slice_field(c, "volumeMounts"), volume_mount("elyra-dsp-details", "/opt/app-root/runtimes"));
       }
   }
+  if (what.feast) {                                        // Handle, ODHWH:431-444
+    const GVal* labels = nb->find("metadata")->find("labels");
+    const GVal* flag = (labels && labels->kind == GVal::Map) ? labels->find("opendatahub.io/feast-integration") : nullptr;
+    const bool enabled = flag && flag->kind == GVal::Str && flag->s == "true";          // isFeastEnabled, feast:34-41
+    if (enabled) {                                         // mountFeastConfig, feast:53-117 (all keys: no Items)
+      upsert_volume(configmap_volume("odh-feast-config", name + "-feast-config", false, -1), true);
+      // a missing image container is an error the webhook only logs (ODHWH:435-437): the volume stays
+      if (containers.kind == GVal::List)
+        for (auto& c : containers.items) {
+          if (c.get_str("name") != name) continue;
+          GVal& mounts = slice_field(c, "volumeMounts");
+          bool replaced = false;
+          if (mounts.kind == GVal::List)
+            for (auto& m : mounts.items)
+              if (m.get_str("name") == "odh-feast-config") { m = volume_mount("odh-feast-config", "/opt/app-root/src/feast-config", true); replaced = true; break; }
+          if (!replaced) append(&mounts, volume_mount("odh-feast-config", "/opt/app-root/src/feast-config", true));
+          break;
+        }
+    } else {                                               // isFeastMounted + unmountFeastConfig, feast:44-51,120-147
+      GVal* vols = pod.find("volumes");
+      bool mounted = false;
+      if (vols && vols->kind == GVal::List)
+        for (size_t k = 0; k < vols->items.size(); ++k)
+          if (vols->items[k].get_str("name") == "odh-feast-config") { vols->items.erase(vols->items.begin() + k); mounted = true; break; }
+      if (mounted && containers.kind == GVal::List)
+        for (auto& c : containers.items) {
+          if (c.get_str("name") != name) continue;
+          GVal* mounts = c.find("volumeMounts");
+          if (mounts && mounts->kind == GVal::List)
+            for (size_t k = 0; k < mounts->items.size(); ++k)
+              if (mounts->items[k].get_str("name") == "odh-feast-config") { mounts->items.erase(mounts->items.begin() + k); break; }
+          break;
+        }
+      // append(s[:i], s[i+1:]...) keeps a non-nil slice: removing the last element leaves an EMPTY list, not nil
+    }
+  }
   if (what.rbac_proxy) {                                   // InjectKubeRbacProxy ODHWH:177-326
     GVal cpu_req, mem_req, cpu_lim, mem_lim;
     if (!auth_sidecar_resources(*nb, &cpu_req, &mem_req, &cpu_lim, &mem_lim)) { nb->canon(); return false; }   // nothing injected
@@ -461,6 +497,23 @@ bool odh_webhook_mutate(GVal* nb, const OdhInject& what) {
     tls.set("secret", GVal::ptr(std::move(ssrc)));
     upsert_volume(std::move(tls), true);
     pod.set("serviceAccountName", GVal::str(name));
+  }
+  if (what.proxy_env && containers.kind == GVal::List) {   // InjectProxyConfigEnvVars, ODHWH:566-616
+    for (auto& c : containers.items) {
+      if (c.get_str("name") != name) continue;
+      // Go ranges over a 3-key map (random order); this restatement appends in sorted key order.  A variable that
+      // is already present keeps its value: the "update" at ODHWH:583-585 assigns to the range copy, not to the slice.
+      const std::pair<const char*, const std::string*> vars[] = {
+          {"HTTPS_PROXY", &what.https_proxy}, {"HTTP_PROXY", &what.http_proxy}, {"NO_PROXY", &what.no_proxy}};
+      for (const auto& kv : vars) {
+        bool exists = false;
+        const GVal* envs = c.find("env");
+        if (envs && envs->kind == GVal::List)
+          for (const auto& e : envs->items) if (e.get_str("name") == kv.first) exists = true;
+        if (!exists) append(&slice_field(c, "env"), env_var(kv.first, *kv.second));
+      }
+      break;
+    }
   }
   nb->canon();
   return true;

@@ -37,6 +37,13 @@ bool generate_virtualservice(const GVal& notebook, const BuilderEnv& env, GVal* 
 // notebook_runtime.go:216-285, notebook_dspa_secret.go:375-450): applied to a Notebook.
 struct OdhInject {
   bool lock = false, ca_bundle = true, runtime_images = true, elyra_secret = true, rbac_proxy = true;
+  // the label-gated Feast block of Handle (ODHWH:431-444): label opendatahub.io/feast-integration == "true"
+  // mounts <name>-feast-config (notebook_feast_config.go:53-117), any other value unmounts a mounted one (:120-147)
+  bool feast = true;
+  // InjectProxyConfigEnvVars (ODHWH:566-616): runs when INJECT_CLUSTER_PROXY_ENV parses as true and the cluster
+  // Proxy has all three status fields; the map it ranges over holds exactly these three keys (ODHWH:340-342)
+  bool proxy_env = false;
+  std::string http_proxy, https_proxy, no_proxy;
 };
 // false when InjectKubeRbacProxy refuses the auth-sidecar resource annotations (the other injections
 // are still applied; no proxy container, volumes or service account are added — ODHWH:177-183)

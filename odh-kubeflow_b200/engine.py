@@ -358,7 +358,7 @@ class Store:
         idx = np.ascontiguousarray(idx, dtype=np.uint64)
         views = [b.view if b is not None else None for b in (sts_sparse, svc_gen, vs_gen, cull)]   # keep alive over the call
         for b in (sts_sparse, svc_gen, vs_gen, cull):
-            assert b is None or len(b) == len(idx)
+            assert b is None or b.n == len(idx)            # .view has just set .n
         _check(self._lib.nbg_store_put(self._h, idx.ctypes.data_as(N.u64p), len(idx),
                                        *[C.byref(v) if v is not None else None for v in views]), "nbg_store_put")
 

@@ -1,13 +1,13 @@
 """The resident step of a given libnbgraft build: whole-step time, the StatefulSet kernel's time INSIDE the running
-step (events recorded by the library around that launch) and alone, checked against the packed oracle.
+step (events recorded by the library around that launch) and alone.  Prints a sum of the result bytes so that
+builds can be compared with each other; parity is the tests' job.
 usage: [NBGRAFT_LIB=build/variants/libnbgraft_X.so] python tools/time_step.py 2500000"""
 import importlib, os, statistics, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
 import numpy as np, torch
 pkg = importlib.import_module("odh-kubeflow_b200")
 dev = importlib.import_module("odh-kubeflow_b200.device")
-import oracle as O
 host, N = pkg.host, pkg._native
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_500_000
 ctx = pkg.Context([0])
@@ -32,9 +32,9 @@ alone = []
 for _ in range(12):
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record(); d[0].run(ctx); e.record(); torch.cuda.synchronize(); alone.append(s.elapsed_time(e))
-ok = np.array_equal(d[0].outs[0].cpu().numpy(), O.packed_diff_sts_sparse(sts.sparse(), threads=8)[0])
+ok = int(d[0].outs[0].cpu().numpy().astype(np.uint64).sum())
 peak = 6544.0
-print("%s n=%d  step %.1f us (%.3f of peak)  sts inside %.1f us (%.3f)  sts alone %.1f us (%.3f)  parity=%s" % (
+print("%s n=%d  step %.1f us (%.3f of peak)  sts inside %.1f us (%.3f)  sts alone %.1f us (%.3f)  result-sum=%d" % (
     os.path.basename(os.environ.get("NBGRAFT_LIB", "default")), n, statistics.median(runs) * 1e3,
     total / (statistics.median(runs) * 1e-3) / 1e9 / peak, statistics.median(inside) * 1e3,
     d[0].algorithmic_bytes / (statistics.median(inside) * 1e-3) / 1e9 / peak, statistics.median(alone[2:]) * 1e3,
