@@ -68,9 +68,14 @@ int nbh_generate_service(const nbh_obj* notebook, nbh_obj** out, char* err, size
 /* generateVirtualService (NBCTL:558-658) */
 int nbh_generate_virtualservice(const nbh_obj* notebook, const nbh_env* env, nbh_obj** out, char* err, size_t errlen);
 /* ODH mutating-webhook injections (ODHWH:105-114,177-326,666-781; notebook_runtime.go:216-285;
- * notebook_dspa_secret.go:375-450) applied in place. flags: 1 lock, 2 CA bundle,
- * 4 runtime images, 8 elyra secret, 16 kube-rbac-proxy. */
+ * notebook_dspa_secret.go:375-450; notebook_feast_config.go:34-147) applied in place. flags: 1 lock, 2 CA bundle,
+ * 4 runtime images, 8 elyra secret, 16 kube-rbac-proxy, 32 the label-gated Feast block of Handle (ODHWH:431-444:
+ * label opendatahub.io/feast-integration == "true" mounts <name>-feast-config, otherwise a mounted one is removed). */
 int nbh_odh_mutate(nbh_obj* notebook, int flags);
+/* The same, followed by InjectProxyConfigEnvVars (ODHWH:566-616) with the cluster Proxy's three status fields:
+ * HTTP_PROXY / HTTPS_PROXY / NO_PROXY are appended to the image container's env unless already present (a present
+ * one keeps its value: the reference's update at :583-585 writes to the range copy). */
+int nbh_odh_mutate_proxy(nbh_obj* notebook, int flags, const char* http_proxy, const char* https_proxy, const char* no_proxy);
 
 /* The COPY half of CopyStatefulSetFields / CopyServiceFields / CopyVirtualService (COMMON:114-131,173-192,
  * 208-217): what the Go functions write into `to`, given the reason bits the compare kernel returned for the pair

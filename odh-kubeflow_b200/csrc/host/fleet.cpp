@@ -447,11 +447,50 @@ void apply_api_defaults(GVal* pod) {
 void fleet_make(const Fleet& f, uint64_t i, Pair* out) {
   Rng r(f.seed ^ nbg_mix64(i * 2));
   out->notebook = make_notebook(f, i, r);
+  // a second stream for the Feast / cluster-proxy decisions, so that adding them left every other draw as it was
+  Rng r2(f.seed ^ nbg_mix64(i * 2 + 1) ^ 0x6665617374ull);
+  bool feast_on = false, proxy_on = false;
   if (f.kind == FLEET_ODH) {
     OdhInject inj;
     inj.lock = r.chance(0.2);
     inj.elyra_secret = r.chance(0.7);
     inj.runtime_images = r.chance(0.8);
+    // Feast (ODHWH:431-444): 12 % of the notebooks carry the label and get the 6th volume; 3 % had it once —
+    // the label now says "false" and the user's spec still holds the volume and mount, which the webhook removes
+    const double uf = r2.unit();
+    GVal* labels = mpath(out->notebook, {"metadata", "labels"});
+    if (uf < 0.12) {
+      feast_on = true;
+      labels->set("opendatahub.io/feast-integration", GVal::str("true"));
+    } else if (uf < 0.15) {
+      labels->set("opendatahub.io/feast-integration", GVal::str("false"));
+      OdhInject once;
+      once.ca_bundle = once.runtime_images = once.elyra_secret = once.rbac_proxy = false;
+      GVal was = out->notebook;
+      mpath(was, {"metadata", "labels"})->set("opendatahub.io/feast-integration", GVal::str("true"));
+      odh_webhook_mutate(&was, once);
+      *mpath(out->notebook, {"spec", "template", "spec"}) = *mpath(was, {"spec", "template", "spec"});
+    }
+    // cluster-wide proxy (ODHWH:457-473): a quarter of the notebooks were admitted while it was switched on;
+    // one in ten of those already had an HTTP_PROXY of their own, which the injector leaves alone (:583-585)
+    if (r2.chance(0.25)) {
+      proxy_on = true;
+      inj.proxy_env = true;
+      inj.http_proxy = "http://proxy.corp.example:3128";
+      inj.https_proxy = "http://proxy.corp.example:3129";
+      inj.no_proxy = ".cluster.local,.svc,10.0.0.0/8,localhost";
+      if (r2.chance(0.1)) {
+        GVal* cs = mpath(out->notebook, {"spec", "template", "spec", "containers"});
+        if (cs && cs->kind == GVal::List && !cs->items.empty()) {
+          GVal e = GVal::strct();
+          e.set("name", GVal::str("HTTP_PROXY"));
+          e.set("value", GVal::str("http://my-own-proxy:8080"));
+          GVal* env = cs->items[0].find("env");
+          if (!env || env->kind != GVal::List) { cs->items[0].set("env", GVal::list()); env = cs->items[0].find("env"); }
+          env->items.push_back(std::move(e));
+        }
+      }
+    }
     odh_webhook_mutate(&out->notebook, inj);
     GVal* ann = mpath(out->notebook, {"metadata", "annotations"});
     if (ann && ann->kind == GVal::Map) {
@@ -539,6 +578,26 @@ void fleet_make(const Fleet& f, uint64_t i, Pair* out) {
     // Notebook would have asked for 1024Mi)
     req->set("memory", quantity("1Gi"));
     mpath(out->sts_from, {"spec", "template", "spec"})->find("containers")->items[0].find("resources")->find("requests")->set("memory", quantity("1024Mi"));
+  }
+  // ODH only, on top of the class above: StatefulSets created before the webhook learnt a mutation.  Both make
+  // the PodSpecs differ (P), so they are applied only where the class already expects P or nothing else is checked.
+  if (f.kind == FLEET_ODH && (cls == 1 || cls == 7)) {
+    if (feast_on && r2.chance(0.5)) {                                // live pod still without the Feast volume and mount
+      GVal* vols = to_pod->find("volumes");
+      if (vols && vols->kind == GVal::List)
+        for (size_t k = 0; k < vols->items.size(); ++k)
+          if (vols->items[k].get_str("name") == "odh-feast-config") { vols->items.erase(vols->items.begin() + k); break; }
+      GVal* ms = to_c0->find("volumeMounts");
+      if (ms && ms->kind == GVal::List)
+        for (size_t k = 0; k < ms->items.size(); ++k)
+          if (ms->items[k].get_str("name") == "odh-feast-config") { ms->items.erase(ms->items.begin() + k); break; }
+    }
+    if (proxy_on && r2.chance(0.5)) {                                // live pod with the proxy of an earlier cluster config
+      GVal* env = to_c0->find("env");
+      if (env && env->kind == GVal::List)
+        for (auto& e : env->items)
+          if (e.get_str("name") == "NO_PROXY") e.set("value", GVal::str(".cluster.local,.svc,localhost"));
+    }
   }
   out->drift_class = cls;
 

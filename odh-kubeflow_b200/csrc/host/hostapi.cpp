@@ -243,8 +243,16 @@ NBH_API int nbh_odh_mutate(nbh_obj* nb, int flags) {
   if (!nb) return -1;
   OdhInject inj;
   inj.lock = flags & 1; inj.ca_bundle = flags & 2; inj.runtime_images = flags & 4;
-  inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16;
+  inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16; inj.feast = flags & 32;
   return odh_webhook_mutate(&nb->v, inj) ? 0 : 1;     // 1: kube-rbac-proxy injection refused (bad resource annotations)
+}
+NBH_API int nbh_odh_mutate_proxy(nbh_obj* nb, int flags, const char* http_proxy, const char* https_proxy, const char* no_proxy) {
+  if (!nb || !http_proxy || !https_proxy || !no_proxy) return -1;
+  OdhInject inj;
+  inj.lock = flags & 1; inj.ca_bundle = flags & 2; inj.runtime_images = flags & 4;
+  inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16; inj.feast = flags & 32;
+  inj.proxy_env = true; inj.http_proxy = http_proxy; inj.https_proxy = https_proxy; inj.no_proxy = no_proxy;
+  return odh_webhook_mutate(&nb->v, inj) ? 0 : 1;
 }
 
 // ---- what Copy*Fields does to `to` once the kernel has said how the pair compares (apply.cpp)

@@ -130,12 +130,16 @@ def generate_virtualservice(notebook, env=None):
     return Obj(out.value)
 
 
-ODH_LOCK, ODH_CA_BUNDLE, ODH_RUNTIME_IMAGES, ODH_ELYRA_SECRET, ODH_RBAC_PROXY = 1, 2, 4, 8, 16
+ODH_LOCK, ODH_CA_BUNDLE, ODH_RUNTIME_IMAGES, ODH_ELYRA_SECRET, ODH_RBAC_PROXY, ODH_FEAST = 1, 2, 4, 8, 16, 32
 
 
-def odh_mutate(notebook, flags=2 | 4 | 8 | 16):
-    """ODH mutating-webhook injections (ODHWH:105-114,177-326,666-781), in place."""
-    rc = N.nbh().nbh_odh_mutate(notebook._h, flags)
+def odh_mutate(notebook, flags=2 | 4 | 8 | 16 | 32, proxy=None):
+    """ODH mutating-webhook injections (ODHWH:105-114,177-326,431-444,666-781), in place.
+    proxy = (http_proxy, https_proxy, no_proxy): also InjectProxyConfigEnvVars (ODHWH:566-616)."""
+    if proxy is not None:
+        rc = N.nbh().nbh_odh_mutate_proxy(notebook._h, flags, *[p.encode() for p in proxy])
+    else:
+        rc = N.nbh().nbh_odh_mutate(notebook._h, flags)
     if rc == 1:        # InjectKubeRbacProxy refused the auth-sidecar resource annotations: no proxy was injected
         raise HostError("invalid kube-rbac-proxy resource configuration")
     if rc != 0:

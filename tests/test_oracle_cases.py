@@ -409,3 +409,106 @@ def test_copy_half_of_copy_fields_matches_the_semantic_oracle(kind):
             reason = orc(frm, want_to)                        # mutates want_to like the Go code
             assert apply(frm, got_to, reason) == 0
             assert got_to.digest() == want_to.digest(), (which, i, fleet.drift_class(i), reason)
+
+
+# ---- Feast config mount and cluster-proxy env injection (config #4 input shape, G4) -------------------------
+def _feast_state(nb_obj):
+    pod = nb_obj.to_python()["spec"]["template"]["spec"]
+    vols = [v for v in pod.get("volumes") or [] if v["name"] == "odh-feast-config"]
+    mounts = {c["name"]: [{k: m.get(k, False if k == "readOnly" else None) for k in ("name", "mountPath", "readOnly")}
+                          for m in c.get("volumeMounts") or [] if m["name"] == "odh-feast-config"]
+              for c in pod["containers"]}
+    return pod, vols, mounts
+
+
+def test_ref_feast_label_gate():
+    """notebook_feast_config_test.go:40-105 (isFeastEnabled): only the exact label value "true" mounts."""
+    g = GOLDEN["feast_config"]
+    for case in g["is_enabled"]:
+        body = {"metadata": {"name": "test-notebook", "namespace": "default"},
+                "spec": {"template": {"spec": {"containers": [{"name": "test-notebook", "image": "i"}]}}}}
+        if case["labels"] is not None:
+            body["metadata"]["labels"] = case["labels"]
+        nb = host.Notebook(body)
+        host.odh_mutate(nb, host.ODH_FEAST)
+        _, vols, _ = _feast_state(nb)
+        assert bool(vols) == case["want"], case["at"]
+
+
+@pytest.mark.parametrize("k", range(4))
+def test_ref_feast_mount(k):
+    """notebook_feast_config_test.go:108-301 (mountFeastConfig), reached the way the webhook reaches it: label "true"
+    and the config map named <notebook>-feast-config (NewFeastConfig, notebook_feast_config.go:149-158)."""
+    case = GOLDEN["feast_config"]["mount"][k]
+    body = json.loads(json.dumps(case["notebook"]))
+    body["metadata"]["labels"] = {"opendatahub.io/feast-integration": "true"}
+    nb = host.Notebook(body)
+    host.odh_mutate(nb, host.ODH_FEAST)
+    pod, vols, mounts = _feast_state(nb)
+    e = case["expect"]
+    assert [v["name"] for v in pod.get("volumes") or []] == e["volumes"], case["at"]
+    assert len(vols) == 1 and vols[0]["configMap"]["name"] == e["configMap"]
+    assert ("items" not in vols[0]["configMap"]) == e["items_nil"]           # all keys of the ConfigMap, mounted dynamically
+    assert mounts == e["mounts"], case["at"]
+    assert len(pod["containers"]) == len(case["notebook"]["spec"]["template"]["spec"]["containers"])
+
+
+@pytest.mark.parametrize("k", range(2))
+def test_ref_feast_unmount(k):
+    """notebook_feast_config_test.go:304-397 (unmountFeastConfig), reached the way the webhook reaches it: the label
+    is not "true" and the volume is still there (notebook_webhook.go:440-444)."""
+    case = GOLDEN["feast_config"]["unmount"][k]
+    nb = host.Notebook(case["notebook"])
+    host.odh_mutate(nb, host.ODH_FEAST)
+    pod, vols, mounts = _feast_state(nb)
+    assert vols == [] and mounts == case["expect"]["mounts"], case["at"]
+    if k == 0:
+        # append(s[:i], s[i+1:]...) leaves EMPTY, non-nil slices behind: reflect.DeepEqual tells them from nil ones
+        assert pod["volumes"] == [] and pod["containers"][0]["volumeMounts"] == []
+    else:
+        assert pod.get("volumes") is None                                      # untouched: still nil
+
+
+def test_proxy_env_injection_quirks():
+    """InjectProxyConfigEnvVars (notebook_webhook.go:566-616; no spec of its own in the reference, so these
+    expectations are derived from the cited lines): the three variables are appended to the IMAGE container only;
+    one that is already present keeps its value, because the update at :583-585 assigns to the range variable."""
+    body = {"metadata": {"name": "wb", "namespace": "ns"},
+            "spec": {"template": {"spec": {"containers": [
+                {"name": "sidecar", "image": "s"},
+                {"name": "wb", "image": "i", "env": [{"name": "A", "value": "1"}, {"name": "HTTP_PROXY", "value": "http://mine:1"}]}]}}}}
+    nb = host.Notebook(body)
+    host.odh_mutate(nb, 0, proxy=("http://p:3128", "http://p:3129", ".svc"))
+    cs = nb.to_python()["spec"]["template"]["spec"]["containers"]
+    assert "env" not in cs[0] or not cs[0]["env"]
+    env = [(e["name"], e["value"]) for e in cs[1]["env"]]
+    assert env[:2] == [("A", "1"), ("HTTP_PROXY", "http://mine:1")]             # kept, not updated
+    assert sorted(env[2:]) == [("HTTPS_PROXY", "http://p:3129"), ("NO_PROXY", ".svc")]
+    # no container carries the notebook's name: nothing happens (the loop at :570 never matches)
+    nb2 = host.Notebook({"metadata": {"name": "other", "namespace": "ns"},
+                         "spec": {"template": {"spec": {"containers": [{"name": "wb", "image": "i"}]}}}})
+    before = nb2.digest()
+    host.odh_mutate(nb2, 0, proxy=("a", "b", "c"))
+    assert nb2.digest() == before
+
+
+def test_odh_fleet_carries_feast_and_proxy_shapes():
+    """Config #4's fleet: a labelled fraction with the sixth volume, a fraction whose label went back to "false"
+    (volume removed again), a fraction admitted under a cluster-wide proxy; packed and object-level oracles agree on
+    all of them (the drift on top includes live pods that predate either mutation)."""
+    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 4, 2500, 50)
+    feast = off = proxy = 0
+    for i in range(0, 2500, 5):
+        nb = fleet.get(i, "notebook").to_python()
+        lab = (nb["metadata"].get("labels") or {}).get("opendatahub.io/feast-integration")
+        pod = nb["spec"]["template"]["spec"]
+        has = any(v["name"] == "odh-feast-config" for v in pod.get("volumes") or [])
+        assert has == (lab == "true"), i
+        feast += has
+        off += lab == "false"
+        proxy += any(e["name"] == "NO_PROXY" for e in pod["containers"][0].get("env") or [])
+    assert 30 < feast < 100 and 5 < off < 35 and 80 < proxy < 170
+    sts, svc, vs = fleet.pack()
+    l1 = O.l1_diff_all(fleet)
+    assert np.array_equal(O.packed_diff_sts(sts)[0], l1["sts"])
+    assert np.array_equal(O.packed_diff_vs(vs)[0], l1["vs"])
