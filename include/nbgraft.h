@@ -385,6 +385,9 @@ typedef struct nbg_store_stats {
   uint64_t puts, rows_put;  /* calls and rows since creation                      */
 } nbg_store_stats;
 int  nbg_store_get_stats(const nbg_store* st, nbg_store_stats* out);
+/* nbg_check_step_device (below) on the store's own view of slots [0,n): every span inside the used part of its
+ * heap, sparse runs aligned and as long as their masks say.  A self-check for tests and debug builds. */
+int  nbg_store_check(nbg_store* st, uint64_t n, unsigned* what /*nullable*/);
 /* CUDA ordinal of the context's device `device` (for callers that allocate next to it). */
 int  nbg_device_id(const nbg_ctx* ctx, int device);
 
@@ -514,6 +517,26 @@ int nbg_parse_records_device(nbg_ctx* ctx, int device, const nbg_strings* last_a
                              uint64_t R, int64_t* sec, uint32_t* nsf, int32_t* zone, void* stream);
 int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings, uint64_t R, uint64_t* out,
                             void* stream);
+/* The checks the host-buffer entry points make on their arguments, for batches that are already on the device
+ * (the *_device entry points above only enqueue and therefore trust what they are given: a run that ends past its
+ * payload array makes a kernel read outside it).  One thread per object looks at every (start, end) pair of its
+ * rows: start <= end, end <= the payload's length as stated in `ext`, sparse runs even-aligned and as long as their
+ * mask says.  Synchronous (it waits for its own kernel); returns NBG_E_RANGE when anything is wrong, with the kinds
+ * of fault OR-ed into *what (nullable): 1 start > end, 2 past the payload, 4 misaligned, 8 length != mask.
+ * Any batch may be NULL.  No counterpart in the reference (Go slices carry their bounds).  Meant for the moments
+ * where a host-buffer call would have checked for free: after uploading a batch from a new packer, in tests, in a
+ * debug build of the caller. */
+typedef struct nbg_step_extents {          /* lengths, in elements, of the payload arrays the batches point into */
+  uint64_t sts_val_from, sts_val_to;                                    /* u64 values   */
+  uint64_t sts_labels_from, sts_labels_to, sts_ann_from, sts_ann_to;    /* nbg_kv       */
+  uint64_t svc_labels_to, svc_ann_to, svc_sel_to;                       /* nbg_kv       */
+  uint64_t vs_hdr_from, vs_hdr_to;                                      /* nbg_kv       */
+  uint64_t cull_kernels, cull_terminals;                                /* records      */
+} nbg_step_extents;
+int nbg_check_step_device(nbg_ctx* ctx, int device, const nbg_sts_sparse_batch* sts, const nbg_svc_gen_batch* svc,
+                          const nbg_vs_gen_batch* vs, const nbg_cull_batch* cull, uint64_t n,
+                          const nbg_step_extents* ext, void* stream, unsigned* what);
+
 /* Owner join that allocates nothing — it has no counterpart in the reference.
  * For callers that may not call the CUDA allocator while they run: code on a
  * reconcile path with a latency bound (cudaMalloc/cudaFree synchronise the whole
@@ -524,9 +547,14 @@ int nbg_hash_strings_device(nbg_ctx* ctx, int device, const nbg_strings* strings
  * hash table is a fixed array inside the library, so:
  *   - at most NBG_JOIN_STATIC_MAX_STS StatefulSets per call; more is rejected
  *     with NBG_E_TOOBIG and nothing is launched;
- *   - every GPU that loads the library holds the table (3 MiB) until exit;
- *   - the first call on each device looks the table's address up
- *     (cudaGetSymbolAddress); make that first call before any stream capture;
+ *   - every GPU the entry point has been called on holds the table (3 MiB) until exit;
+ *   - the FIRST call on each device is the set-up: it looks the table's address up
+ *     (cudaGetSymbolAddress), and with CUDA's lazy module loading that lookup is what makes
+ *     the driver load this part of the library and claim the 3 MiB on that device.  It can
+ *     therefore block, or fail with NBG_E_NOMEM when the device is already full.  Make it a
+ *     warm-up call at start-up (n = 1 is enough; or run with CUDA_MODULE_LOADING=EAGER),
+ *     before memory gets tight and before any stream capture.  Later calls touch neither the
+ *     loader nor the allocator;
  *   - all calls on a device share the one table (each call clears it before
  *     use): two calls whose GPU work overlaps — different streams, or several
  *     threads — race.  Order them on one stream or with events.

@@ -211,12 +211,18 @@ NBG_SYMBOLS = [
     "nbg_owner_join", "nbg_join_key", "nbg_owner_join_scratch_bytes", "nbg_owner_join_device",
     "nbg_owner_join_static", "nbg_diff_sts_sparse", "nbg_diff_sts_sparse_device",
     "nbg_step", "nbg_step_device", "nbg_store_create", "nbg_store_destroy", "nbg_store_put", "nbg_store_step",
-    "nbg_store_step_device", "nbg_store_get_stats", "nbg_device_id", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
+    "nbg_store_step_device", "nbg_store_get_stats", "nbg_store_check", "nbg_device_id", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
-    "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device",
+    "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device", "nbg_check_step_device",
 ]
 
 _vp = C.c_void_p
+
+
+class nbg_step_extents(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("sts_val_from", "sts_val_to", "sts_labels_from", "sts_labels_to", "sts_ann_from",
+                                          "sts_ann_to", "svc_labels_to", "svc_ann_to", "svc_sel_to", "vs_hdr_from", "vs_hdr_to",
+                                          "cull_kernels", "cull_terminals")]
 
 
 def _bind_nbg(lib):
@@ -239,6 +245,11 @@ def _bind_nbg(lib):
     lib.nbg_shard_of.restype = C.c_uint32
     lib.nbg_balance_shards.argtypes = [_vp, _vp, C.c_uint64, C.c_uint32, _vp, _vp]
     lib.nbg_balance_shards.restype = C.c_int
+    lib.nbg_check_step_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.POINTER(nbg_step_extents), _vp,
+                                          C.POINTER(C.c_uint)]
+    lib.nbg_check_step_device.restype = C.c_int
+    lib.nbg_store_check.argtypes = [_vp, C.c_uint64, C.POINTER(C.c_uint)]
+    lib.nbg_store_check.restype = C.c_int
     for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch),
                      ("nbg_diff_sts_sparse", nbg_sts_sparse_batch), ("nbg_diff_deploy", nbg_sts_batch)):
         f = getattr(lib, name)

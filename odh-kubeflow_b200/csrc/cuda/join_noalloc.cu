@@ -8,13 +8,17 @@
 // controller that shares its GPU with the notebooks it manages and comes up
 // after they have claimed the memory, so an allocation made "when needed" may
 // simply fail.  For those callers the table lives in this file, in a fixed-size
-// array that is part of the loaded library image: it exists from the moment the
-// library is loaded on a device until the process exits, and using it costs no
-// allocator call at all.
+// array that is part of the library image, and a call costs no allocator call.
+//
+// When the memory is claimed: CUDA loads a module lazily, and nothing in this
+// file runs on the device, so the first cudaGetSymbolAddress on a device — the
+// set-up inside the first nbg_owner_join_static call there — is what loads the
+// module and reserves the array.  That one call can block or run out of memory
+// (NBG_E_NOMEM); callers make it once at start-up, as a warm-up, and every later
+// call finds the address cached.  The table then stays until the process exits.
 //
 // The price is a hard limit (NBG_JOIN_STATIC_MAX_STS StatefulSets per call) and
-// 3 MiB of device memory held on every GPU that loads libnbgraft.so, whether or
-// not this entry point is ever used.
+// 3 MiB of device memory on every GPU the entry point has been used on.
 #include <cuda_runtime.h>
 
 #include <mutex>
@@ -49,9 +53,11 @@ int table_for_current_device(void** out) {
   std::lock_guard<std::mutex> lock(g_mu);
   if (!g_table_addr[dev]) {
     void* p = nullptr;
-    if (cudaGetSymbolAddress(&p, g_join_table) != cudaSuccess || !p) {
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_join_table);
+    if (e != cudaSuccess || !p) {
       cudaGetLastError();
-      return NBG_E_CUDA;
+      // this lookup is where the module is loaded and the array gets its memory: a full device fails here
+      return e == cudaErrorMemoryAllocation ? NBG_E_NOMEM : NBG_E_CUDA;
     }
     g_table_addr[dev] = p;
   }

@@ -667,6 +667,25 @@ int nbg_store_step(nbg_store* st, uint64_t n, const nbg_vs_gen_consts* vs_consts
   return NBG_OK;
 }
 
+int nbg_store_check(nbg_store* st, uint64_t n, unsigned* what) {
+  if (what) *what = 0;
+  if (!st) return NBG_E_INVAL;
+  if (n > st->capacity) return NBG_E_RANGE;
+  if (n == 0) return NBG_OK;
+  nbg_sts_sparse_batch sts; nbg_svc_gen_batch svc; nbg_vs_gen_batch vs; nbg_cull_batch cull;
+  std::unique_lock<std::mutex> lock(st->mu);
+  store_views(st, &sts, &svc, &vs, &cull);
+  const Heap* h = st->heap;
+  nbg_step_extents ext{};
+  ext.sts_val_from = h[H_POD_F].used; ext.sts_val_to = h[H_POD_T].used;
+  ext.sts_labels_from = h[H_LAB_F].used; ext.sts_labels_to = h[H_LAB_T].used;
+  ext.sts_ann_from = h[H_ANN_F].used; ext.sts_ann_to = h[H_ANN_T].used;
+  ext.svc_labels_to = h[H_SVC_LAB].used; ext.svc_ann_to = h[H_SVC_ANN].used; ext.svc_sel_to = h[H_SVC_SEL].used;
+  ext.vs_hdr_from = h[H_VS_HDR_F].used; ext.vs_hdr_to = h[H_VS_HDR_T].used;
+  ext.cull_kernels = h[H_KERNELS].used; ext.cull_terminals = h[H_TERMINALS].used;
+  return nbg_check_step_device(st->ctx, st->device, &sts, &svc, &vs, &cull, n, &ext, st->stream, what);
+}
+
 int nbg_store_get_stats(const nbg_store* st, nbg_store_stats* out) {
   if (!st || !out) return NBG_E_INVAL;
   *out = nbg_store_stats{};

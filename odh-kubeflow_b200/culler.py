@@ -7,6 +7,7 @@ and terminals are lists of dicts as /api/kernels and /api/terminals return them.
 `now` is (unix_sec, nsec); default = the wall clock, as time.Now() in Go.
 """
 import os
+import re
 import time
 
 from . import _native as N
@@ -24,11 +25,31 @@ CULL_IDLE_TIME = 0           # minutes; CULL:37
 IDLENESS_CHECK_PERIOD = 0    # minutes; CULL:39
 
 
+_ATOI = re.compile(r"[+-]?[0-9]+\Z")
+
+
+def _atoi(text):
+    """strconv.Atoi: an optional sign and decimal digits, nothing else (no spaces, no underscores, no
+    empty string) and the value must fit a 64-bit int; None where Go returns an error."""
+    if not _ATOI.match(text):
+        return None
+    v = int(text)
+    return v if -(1 << 63) <= v < (1 << 63) else None
+
+
 def initGlobalVars():
-    """CULL:525-558 (the two variables the predicates read)."""
+    """CULL:525-558 (the two variables the predicates read).  As there: an empty variable means the default
+    (GetEnvDefault, CULL:505-511); a CULL_IDLE_TIME that is not an integer is logged and replaced by the default
+    1440 (:535-542); an IDLENESS_CHECK_PERIOD that is not an integer is an error, which stops the controller's
+    set-up (:550-554, :566-569) — ValueError here."""
     global CULL_IDLE_TIME, IDLENESS_CHECK_PERIOD
-    CULL_IDLE_TIME = int(os.environ.get("CULL_IDLE_TIME") or "1440")
-    IDLENESS_CHECK_PERIOD = int(os.environ.get("IDLENESS_CHECK_PERIOD") or "1")
+    idle = _atoi(os.environ.get("CULL_IDLE_TIME") or "1440")
+    CULL_IDLE_TIME = 1440 if idle is None else idle
+    text = os.environ.get("IDLENESS_CHECK_PERIOD") or "1"
+    period = _atoi(text)
+    if period is None:
+        raise ValueError('strconv.Atoi: parsing "%s": invalid syntax' % text)
+    IDLENESS_CHECK_PERIOD = period
 
 
 def _now(now):
@@ -96,7 +117,9 @@ def updateTimestampFromTerminalsActivity(meta, terminals, now=None):
 
 
 def setStopAnnotation(meta, now=None):
-    """CULL:475-491 (host-side write; metrics are out of scope)."""
+    """CULL:475-491 (host-side write; metrics are out of scope).  The reference formats time.Now() in the process's
+    LOCAL zone (t.Format(time.RFC3339)); this writes UTC ("...Z"), which is the same string only where TZ is UTC, as
+    it is in the controller's container image.  The instant is the same either way, and that is all C7 reads back."""
     if meta is None:
         return
     sec, _ = _now(now)

@@ -170,3 +170,34 @@ class ResidentStep:
         self._free.extend(self._pairs)
         self._pairs = []
         return out
+
+
+def check_step(ctx, sts=None, svc=None, vs=None, cull=None, stream=None):
+    """nbg_check_step_device on resident batches: the argument checks a host-buffer call would have made (offsets
+    monotone and inside their payload arrays, sparse runs aligned and as long as their masks say).  The payload
+    lengths are taken from the tensors the batches own.  Returns the fault bits (0 = fine)."""
+    given = [b for b in (sts, svc, vs, cull) if b is not None]
+    assert given and len({b.n for b in given}) == 1 and len({b.device for b in given}) == 1
+    device = given[0].device
+    if stream is None:
+        stream = torch.cuda.current_stream(device).cuda_stream
+    ext = N.nbg_step_extents()
+
+    def elems(b, name, size):
+        return b.tensors[name].numel() // size if b is not None else 0
+    ext.sts_val_from, ext.sts_val_to = elems(sts, "pod_from.val", 8), elems(sts, "pod_to.val", 8)
+    for field, (b, name) in {"sts_labels_from": (sts, "labels_from.ent"), "sts_labels_to": (sts, "labels_to.ent"),
+                             "sts_ann_from": (sts, "ann_from.ent"), "sts_ann_to": (sts, "ann_to.ent"),
+                             "svc_labels_to": (svc, "labels_to.ent"), "svc_ann_to": (svc, "ann_to.ent"),
+                             "svc_sel_to": (svc, "sel_to.ent"), "vs_hdr_from": (vs, "hdr_from.ent"),
+                             "vs_hdr_to": (vs, "hdr_to.ent")}.items():
+        setattr(ext, field, elems(b, name, 16))
+    ext.cull_kernels, ext.cull_terminals = elems(cull, "k_sec", 8), elems(cull, "t_sec", 8)
+    what = C.c_uint(0)
+    refs = [C.byref(b._struct) if b is not None else None for b in (sts, svc, vs, cull)]
+    rc = N.nbg().nbg_check_step_device(ctx.handle, ctx.index_of(device), refs[0], refs[1], refs[2], refs[3], given[0].n,
+                                       C.byref(ext), C.c_void_p(stream), C.byref(what))
+    if rc not in (N.NBG_OK, N.NBG_E_RANGE):
+        from .engine import NbgError
+        raise NbgError(rc, "nbg_check_step_device")
+    return int(what.value)

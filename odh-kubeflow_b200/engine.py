@@ -380,6 +380,14 @@ class Store:
         _check(self._lib.nbg_store_step_device(self._h, n, C.byref(vs_consts), C.byref(params), C.byref(outputs),
                                                C.c_void_p(stream)), "nbg_store_step_device")
 
+    def check(self, n):
+        """nbg_store_check: fault bits of the store's own spans over slots [0, n) (0 = consistent)."""
+        what = C.c_uint(0)
+        rc = self._lib.nbg_store_check(self._h, n, C.byref(what))
+        if rc not in (N.NBG_OK, N.NBG_E_RANGE):
+            _check(rc, "nbg_store_check")
+        return int(what.value)
+
     def stats(self):
         s = N.nbg_store_stats()
         _check(self._lib.nbg_store_get_stats(self._h, C.byref(s)), "nbg_store_get_stats")

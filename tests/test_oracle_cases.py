@@ -1,6 +1,7 @@
 """CPU tests: the oracle against the reference's own known-answer cases
 (tests/golden/reference_cases.json) and against the derived cases of cases.py;
 the host packer + packed oracle (L2) against the semantic oracle (L1)."""
+import importlib
 import json
 import os
 import time
@@ -512,3 +513,25 @@ def test_odh_fleet_carries_feast_and_proxy_shapes():
     l1 = O.l1_diff_all(fleet)
     assert np.array_equal(O.packed_diff_sts(sts)[0], l1["sts"])
     assert np.array_equal(O.packed_diff_vs(vs)[0], l1["vs"])
+
+
+def test_culler_env_parsing_follows_strconv_atoi(monkeypatch):
+    """initGlobalVars (CULL:525-558): Atoi accepts a sign and digits only; a bad CULL_IDLE_TIME falls back to 1440,
+    a bad IDLENESS_CHECK_PERIOD is an error; empty means default (GetEnvDefault, CULL:505-511)."""
+    culler = importlib.import_module("odh-kubeflow_b200.culler")
+    for text, want in (("", 1440), ("30", 30), ("+5", 5), ("-3", -3), (" 5", 1440), ("5 ", 1440), ("1_000", 1440),
+                       ("abc", 1440), ("1.5", 1440), ("9223372036854775808", 1440), ("007", 7)):
+        monkeypatch.setenv("CULL_IDLE_TIME", text)
+        monkeypatch.delenv("IDLENESS_CHECK_PERIOD", raising=False)
+        culler.initGlobalVars()
+        assert culler.CULL_IDLE_TIME == want and culler.IDLENESS_CHECK_PERIOD == 1, text
+    monkeypatch.delenv("CULL_IDLE_TIME", raising=False)
+    for text in (" 2", "2m", "1_0", "one"):
+        monkeypatch.setenv("IDLENESS_CHECK_PERIOD", text)
+        with pytest.raises(ValueError):
+            culler.initGlobalVars()
+    monkeypatch.setenv("IDLENESS_CHECK_PERIOD", "15")
+    culler.initGlobalVars()
+    assert (culler.CULL_IDLE_TIME, culler.IDLENESS_CHECK_PERIOD) == (1440, 15)
+    monkeypatch.delenv("IDLENESS_CHECK_PERIOD")
+    culler.initGlobalVars()

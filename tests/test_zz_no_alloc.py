@@ -56,6 +56,30 @@ def test_static_join_matches_the_scratch_variant_twice_in_a_row(ctx):
     assert np.array_equal(got, O.packed_owner_join(probe, st2)[0])
 
 
+def test_static_join_claims_no_memory_after_its_first_call(ctx):
+    """The first call on a device is the set-up (it may load the module and claim the table); from then on a call
+    must leave the device's free memory exactly as it found it — no cudaMalloc behind the caller's back."""
+    import torch
+    lib = N.nbg()
+    torch.cuda.set_device(0)
+    f = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 9, 20_000, 400)
+    nb, st, _ = f.join_lists(20_000)
+    d_nb = torch.from_numpy(nb.view(np.int64)).cuda()
+    d_st = torch.from_numpy(st.view(np.int64)).cuda()
+    out = torch.empty(len(nb), dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    call = lambda: lib.nbg_owner_join_static(d_nb.data_ptr(), len(nb), d_st.data_ptr(), len(st), out.data_ptr(), stream)
+    assert call() == N.NBG_OK                      # warm-up: set-up done by now at the latest
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(0)          # cudaMemGetInfo: the driver's view, not torch's cache
+    for _ in range(3):
+        assert call() == N.NBG_OK
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(0)
+    assert free1 == free0
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), O.packed_owner_join(nb, st)[0])
+
+
 def test_static_join_rejects_lists_beyond_its_limit(ctx):
     import torch
     lib = N.nbg()

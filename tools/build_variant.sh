@@ -10,7 +10,7 @@ mkdir -p $out
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-mpopcnt -Xptxas -v "$@" \
   -c cuda/$src -o $out/${name}_${src%.cu}.o 2> $out/${name}_${src%.cu}.ptxas.log
 objs=""
-for f in capi cull diff join join_noalloc store text; do
+for f in capi cull diff join join_noalloc store text validate; do
   if [ "$f.cu" = "$src" ]; then objs="$objs $out/${name}_${src%.cu}.o"; else objs="$objs cuda/$f.o"; fi
 done
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/libnbgraft_$name.so $objs -cudart static
