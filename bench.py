@@ -1,17 +1,22 @@
 #!/usr/bin/env python
 """bench.py — the graft's one headline measurement (contract: README of the task).
 
-A "step" is one pass of the hot path over one GPU's share of the fleet:
-diff_sts + diff_svc + diff_vs (Copy*Fields, COMMON:107-219) + cull (CULL:86-241,
-315-428) over the same notebooks.  Unit: objects/s where one object = one Notebook
-(its StatefulSet pair, Service pair, VirtualService pair and culler record set).
+Workload: BASELINE config #5 as stated — 10 M DISTINCT synthetic Notebooks in 200 k Zipf(1.1) namespaces.  A "step"
+is one pass of the hot path over the whole fleet: diff_sts + diff_svc + diff_vs (Copy*Fields, COMMON:107-219) +
+cull (CULL:86-241, 315-428).  Unit: objects/s where one object = one Notebook (its StatefulSet pair, Service pair,
+VirtualService pair and culler record set).  One GPU holds the whole fleet; N GPUs split the SAME fleet by
+namespace (NBCTL:159), at the sizes the partition gives (strong scaling): headline with the size-aware table of
+nbg_balance_shards, and beside it the stateless nbg_shard_of hash.
 
-  value      inputs resident in HBM, CUDA-event timed, max over ranks
-  e2e        the same step through the host-buffer C ABI (nbg_diff_*, nbg_cull):
-             pinned host buffers -> H2D -> kernel -> D2H inside the timed region
-  roofline   dominant kernel (diff_sts): algorithmic bytes / its own CUDA-event time
-  cpu_baseline  the semantic oracle (CPU restatement of the Go predicates on whole
-             objects) on all host threads, bounded sample; N=1, rank 0 only
+  value      fleet / slowest rank's step time; inputs resident in HBM, CUDA events on the launch stream
+  e2e        the same step through the host-buffer C ABI (nbg_step): pinned host buffers -> H2D -> kernels -> D2H
+             inside the timed region, max over ranks
+  roofline   dominant kernel (diff_sts_sparse): algorithmic bytes / its own CUDA-event time inside the step;
+             frac_by_traffic uses the DRAM bytes ncu saw for that launch (profiles/r2_traffic.json)
+  parity     L2: every object of every shard against the packed oracle; L1: a sample of the same fleet
+             (100 k notebooks at N=1) against the object-level port of the Go predicates — the bench fails on a difference
+  cpu_baseline  that port (CPU restatement of the Go predicates on whole objects) on all host threads, on the
+             same sample; like_for_like: the two ratios that start both sides from the same place
 
 --impl reference times that CPU restatement alone (the reference is Go and cannot
 be built here: no toolchain, un-vendored modules — see DESIGN.md).
@@ -823,8 +828,15 @@ def other_configs(pkg, dev, ctx, torch, peak):
     sts, _, vs = f4.pack(svc=False)
     d1, d2 = dev.DeviceBatch.from_host(sts), dev.DeviceBatch.from_host(vs)
     m1, m2 = timed(d1), timed(d2)
+    th = os.cpu_count() or 1
+    ok4 = (np.array_equal(d1.outs[0].cpu().numpy(), O.packed_diff_sts(sts, threads=th)[0]) and
+           np.array_equal(d2.outs[0].cpu().numpy(), O.packed_diff_vs(vs, threads=th)[0]))
+    if not ok4:
+        raise SystemExit("bench: config #4 results differ from the packed oracle")
     out["config4_100k_odh_sts_vs"] = {"objects_per_s": 100_000 / ((m1 + m2) * 1e-3), "ms": m1 + m2,
-                                      "sts_GBps": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9, "sts_frac_of_peak": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9 / peak}
+                                      "sts_GBps": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9, "sts_frac_of_peak": d1.algorithmic_bytes / (m1 * 1e-3) / 1e9 / peak,
+                                      "parity": "bit-exact vs packed oracle on all 100 000 StatefulSet and VirtualService pairs "
+                                                "(tests/test_gpu_parity.py::test_config4_odh_notebooks adds the object-level oracle on all of them)"}
     # the owner-reference join (NBCTL:157-170) as a hash join, 1.25 M notebooks
     lib = N.nbg()
     n = 1_250_000
