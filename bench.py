@@ -570,7 +570,6 @@ def main():
                               "from_objects below packs objects that sit in memory",
                       "synthesis_us_per_object_per_thread": make_cpu_s / per * 1e6, "wall_seconds_with_synthesis": pack_wall_s},
     }
-    del shard
     # ---- CPU legs on rank 0: the port of the Go predicates on whole objects (L1) over a sample of the SAME fleet.  Its
     # verdicts are compared with the GPU's bytes for the same notebooks: this is the check that ties packer + kernel to
     # the Go semantics.  world > 1: rank 0's shard only supplies the GPU bytes, so the sample is drawn from it.
@@ -640,7 +639,12 @@ def main():
     if world == 1 and not args.no_extra:
         torch.cuda.empty_cache()
         line["other_configs"] = other_configs(pkg, dev, ctx, torch, peak)
-        line["other_configs"]["resident_store_1.25M"] = resident_store(pkg, O, ctx, torch, fleet, cfleet, min(total, 1_250_000), now, peak)
+        # the deployment this graft argues for, at the size of the headline: the whole fleet resident in an nbg_store
+        del resident, d_sts, d_svc, d_vs, d_cull, batches
+        shard.dev_batches = shard.named = None
+        torch.cuda.empty_cache()
+        line["other_configs"]["resident_store"] = resident_store(pkg, O, ctx, torch, fleet, cfleet, total, now, peak,
+                                                                 prepacked=(shard.host_batches, shard.svc, shard.vs, want))
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -669,17 +673,22 @@ def multi_device_context_check(pkg, O, n_devices):
     return "bit-exact (nbg_init with %d devices, %d notebooks through nbg_step)" % (n_devices, n)
 
 
-def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak):
-    """A 1.25 M-notebook slice of the fleet held in an nbg_store: load, step from the store (spans instead of CSR),
-    then ticks in which 1 % of the slots are replaced by other notebooks' rows before the step.  Parity after the last tick."""
+def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak, prepacked=None):
+    """The first `per` notebooks of the fleet held in an nbg_store: load, step from the store (spans instead of CSR),
+    then ticks in which 1 % of the slots are replaced by other notebooks' rows before the step.  Parity after the last
+    tick.  prepacked = (host batches, SvcBatch, VsBatch, oracle answers) of exactly those notebooks, when the caller has them."""
     host, N = pkg.host, pkg._native
-    b_sts, b_svc, b_vs = fleet.pack(0, per, lean=True)
-    cull = cfleet.pack(0, per)
-    sts_sp, svc_g, vs_g = b_sts.sparse(), b_svc.gen(), b_vs.gen()
+    if prepacked is not None:
+        (sts_sp, svc_g, vs_g, cull), b_svc, b_vs, want = prepacked
+        assert len(cull) == per
+    else:
+        b_sts, b_svc, b_vs = fleet.pack(0, per, lean=True)
+        cull = cfleet.pack(0, per)
+        sts_sp, svc_g, vs_g = b_sts.sparse(), b_svc.gen(), b_vs.gen()
+        th = os.cpu_count() or 1
+        want = {"diff_sts": O.packed_diff_sts_sparse(sts_sp, threads=th), "diff_svc": O.packed_diff_svc(b_svc, threads=th),
+                "diff_vs": O.packed_diff_vs(b_vs, threads=th), "cull": O.packed_cull(cull, now, 1440, 1, 1, threads=th)}
     alg_bytes = sum(b.algorithmic_bytes() for b in (sts_sp, svc_g, vs_g, cull))
-    th = os.cpu_count() or 1
-    want = {"diff_sts": O.packed_diff_sts_sparse(sts_sp, threads=th), "diff_svc": O.packed_diff_svc(b_svc, threads=th),
-            "diff_vs": O.packed_diff_vs(b_vs, threads=th), "cull": O.packed_cull(cull, now, 1440, 1, 1, threads=th)}
     store = pkg.engine.Store(ctx, per)
     t0 = time.perf_counter()
     store.put(np.arange(per, dtype=np.uint64), sts_sp, svc_g, vs_g, cull)
@@ -714,7 +723,7 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak):
     for t in range(6):
         slots = rng.choice(per, size=m, replace=False).astype(np.uint64)
         alt = (per + t * m + np.arange(m)).astype(np.uint64) % np.uint64(fleet.n)
-        a_sts, a_svc, a_vs = fleet.pack(idx=alt)
+        a_sts, a_svc, a_vs = fleet.pack(idx=alt, lean=True)
         a_cf = host.CullFleet(host.SEED_BASE + 900 + t, m)
         a_cull = a_cf.pack()
         rows = (a_sts.sparse(), a_svc.gen(), a_vs.gen(), a_cull)
@@ -737,12 +746,12 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak):
     store.close()
     put_ms = statistics.median(x[0] for x in ticks[1:]) * 1e3
     tick_ms = statistics.median(x[1] for x in ticks[1:]) * 1e3
-    return {"load_seconds": load_s, "load_GBps": (alg_bytes / load_s) / 1e9,
+    return {"notebooks": per, "load_seconds": load_s, "load_GBps": (alg_bytes / load_s) / 1e9,
             "step_ms_fresh": fresh_ms, "step_objects_per_s_fresh": per / (fresh_ms * 1e-3), "step_frac_of_peak_fresh": alg_bytes / (fresh_ms * 1e-3) / 1e9 / peak,
             "step_ms_after_6_ticks": churned_ms, "rows_replaced_per_tick": m,
             "tick_ms": tick_ms, "tick_put_ms": put_ms, "tick_objects_per_s": per / (tick_ms * 1e-3),
             "store": st, "parity": "bit-exact vs packed oracle after the last tick (replaced slots included)",
-            "note": "tick = nbg_store_put of 1 % of the rows (host buffers) + nbg_store_step over all 1.25 M slots with host outputs; "
+            "note": "tick = nbg_store_put of 1 % of the rows (host buffers) + nbg_store_step over all slots with host outputs; "
                     "packing the replaced rows is outside the tick (it happens when the informer delivers the object)"}
 
 
