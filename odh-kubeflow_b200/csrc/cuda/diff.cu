@@ -657,8 +657,11 @@ diff_vs_kernel(nbg_vs_batch in, unsigned long long n, unsigned hf_base, unsigned
 // generateVirtualService NBCTL:558-658; slot layout = csrc/host/pack.cpp).
 struct SvcGenConsts { unsigned long long port_name, proto_tcp, sel_key; };
 
+#ifndef NBG_GEN_MINBLOCKS
+#define NBG_GEN_MINBLOCKS 16
+#endif
 template <bool SPANS>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, NBG_GEN_MINBLOCKS)
 diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
                     unsigned lt_base, unsigned at_base, unsigned st_base,
                     uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
@@ -712,7 +715,7 @@ diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
 }
 
 template <bool SPANS>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, NBG_GEN_MINBLOCKS)
 diff_vs_gen_kernel(nbg_vs_gen_batch in, nbg_vs_gen_consts k, unsigned long long n, unsigned hf_base, unsigned ht_base,
                    uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
   constexpr int VEC = NBG_VS_SLOTS / 2;                // 4 lanes per object
