@@ -34,7 +34,9 @@
 extern "C" {
 #endif
 
-#define NBG_ABI_VERSION 2
+/* 3: additions only (nbg_balance_shards, nbg_check_step_device, nbg_store_check); nbg_store_put now refuses a slot
+ *    named twice (NBG_E_INVAL) instead of leaving the outcome open.  2: spans (end pointers) in the batch structs. */
+#define NBG_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------ */
 #define NBG_OK              0

@@ -35,6 +35,31 @@ int main() {
       nbh_obj_free(m); nbh_obj_free(nb);
     }
     nbh_sts_free(a); nbh_svc_free(b); nbh_vs_free(c);
+    {  // round 2: lean packing, packing of held objects, namespace tables, table-driven shards, Feast / proxy mutations
+      std::vector<uint64_t> nh(100), nsz(100);
+      if (nbh_fleet_ns_table(f, nh.data(), nsz.data()) != 100) return 2;
+      std::vector<uint32_t> table(100);
+      for (int k = 0; k < 100; ++k) table[k] = (uint32_t)(k % 3);
+      const uint64_t cnt = nbh_fleet_shard_indices_by_table(f, table.data(), 1, nullptr, 0);
+      std::vector<uint64_t> idx(cnt);
+      nbh_fleet_shard_indices_by_table(f, table.data(), 1, idx.data(), cnt);
+      if (nbh_fleet_pack_lean(f, idx.data(), 0, cnt, &a, &b, &c)) return 3;
+      nbg_sts_sparse_batch lv; nbh_sts_view_sparse(a, &lv);
+      if (!nbh_sts_is_lean(a)) return 4;
+      nbh_sts_free(a); nbh_svc_free(b); nbh_vs_free(c);
+      std::vector<nbh_obj*> objs(500 * 7);
+      nbh_fleet_objects(f, nullptr, 100, 500, objs.data());
+      if (nbh_pack_objects(objs.data(), 500, 1, &a, &b, &c)) return 5;
+      nbh_sts_free(a); nbh_svc_free(b); nbh_vs_free(c);
+      for (int k = 0; k < 200; ++k) {
+        nbh_obj* m = nbh_obj_clone(objs[k * 7]);
+        nbh_obj_set_str(m, "metadata.labels.opendatahub.io/feast-integration", k % 2 ? "true" : "false");
+        nbh_odh_mutate_proxy(m, 63, "http://p:1", "http://p:2", ".svc");
+        nbh_odh_mutate(m, 32);
+        nbh_obj_free(m);
+      }
+      for (nbh_obj* o : objs) nbh_obj_free(o);
+    }
     nbh_cullfleet* cf = nbh_cullfleet_new(7, 5000, 1767225600, 0, 4.0);
     nbh_cull* cb; nbh_cullfleet_pack(cf, nullptr, 0, 5000, &cb);
     nbh_cull_free(cb); nbh_cullfleet_free(cf);
