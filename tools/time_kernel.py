@@ -9,7 +9,7 @@ host = pkg.host
 kind, n = sys.argv[1], int(sys.argv[2])
 ctx = pkg.Context([0])
 if kind == "cull":
-    cf = host.CullFleet(host.SEED_BASE + 3, n); b = cf.pack(); kw = dict(now=(cf.now_sec, cf.now_nsec))
+    cf = host.CullFleet(host.SEED_BASE + 3, n); b = cf.pack(); kw = dict(now=(int(os.environ.get("NOW_SEC", cf.now_sec)), cf.now_nsec))
 else:
     f = host.Fleet(host.FLEET_KUBEFLOW, host.SEED_BASE + 5, n, max(200, n // 50))
     base = kind.replace("_gen", "").replace("_sparse", "")
