@@ -720,6 +720,7 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak, prepacked=
     rng = np.random.default_rng(7)
     m = max(per // 100, 1)
     ticks = []
+    tick_out = pkg.engine.StepBuffers(per, pinned=True)              # a controller keeps its result buffers
     for t in range(6):
         slots = rng.choice(per, size=m, replace=False).astype(np.uint64)
         alt = (per + t * m + np.arange(m)).astype(np.uint64) % np.uint64(fleet.n)
@@ -730,7 +731,7 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak, prepacked=
         t0 = time.perf_counter()
         store.put(slots, *rows)
         put_s = time.perf_counter() - t0
-        r = store.step(per, consts, now[0], now[1])                      # host outputs: the tick a controller would run
+        r = store.step(per, consts, now[0], now[1], out=tick_out)        # host outputs: the tick a controller would run
         ticks.append((put_s, time.perf_counter() - t0))
         exp["sts"][slots] = O.packed_diff_sts_sparse(rows[0])[0]
         exp["svc"][slots] = O.packed_diff_svc(a_svc)[0]
@@ -743,6 +744,8 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak, prepacked=
         raise SystemExit("bench: the resident store differs from the packed oracle after replacements")
     churned_ms = device_step_ms()
     st = store.stats()
+    r = None
+    tick_out.close()
     store.close()
     put_ms = statistics.median(x[0] for x in ticks[1:]) * 1e3
     tick_ms = statistics.median(x[1] for x in ticks[1:]) * 1e3
@@ -751,7 +754,7 @@ def resident_store(pkg, O, ctx, torch, fleet, cfleet, per, now, peak, prepacked=
             "step_ms_after_6_ticks": churned_ms, "rows_replaced_per_tick": m,
             "tick_ms": tick_ms, "tick_put_ms": put_ms, "tick_objects_per_s": per / (tick_ms * 1e-3),
             "store": st, "parity": "bit-exact vs packed oracle after the last tick (replaced slots included)",
-            "note": "tick = nbg_store_put of 1 % of the rows (host buffers) + nbg_store_step over all slots with host outputs; "
+            "note": "tick = nbg_store_put of 1 % of the rows (host buffers) + nbg_store_step over all slots with host outputs (pinned, kept across ticks); "
                     "packing the replaced rows is outside the tick (it happens when the informer delivers the object)"}
 
 

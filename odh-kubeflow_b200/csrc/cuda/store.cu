@@ -26,6 +26,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "../../../include/nbgraft.h"
@@ -305,11 +306,30 @@ size_t chunk_bytes(uint64_t k0, uint64_t k1, const nbg_sts_sparse_batch* sts, co
   return bytes;
 }
 
-// Copy the listed pieces into the pinned slot.  One thread: measured on the B200 host, three more gather threads
-// (a pool living with the store) cut the gather of a 14 MB put from 1.1 to 0.8 ms but slowed the planning loop
-// and the DMA running beside it by more (2.0 ms per put against 1.45): the host's memory system is the shared limit.
+// Copy the listed pieces into the pinned slot.  Small chunks: one thread — measured on the B200 host, three more
+// gather threads cut the gather of a 14 MB put from 1.1 to 0.8 ms but slowed the planning loop and the DMA running
+// beside it by more (2.0 ms per put against 1.45).  Chunks of 16 MB and more (a put of tens of thousands of rows)
+// are split by bytes over up to four threads started for the chunk: there the copy is the whole cost.
+void gather_part(const std::vector<Gather>& g, size_t total, unsigned who, unsigned parts) {
+  const size_t lo = total * who / parts, hi = total * (who + 1) / parts;
+  size_t at = 0;
+  for (const auto& t : g) {
+    const size_t b = std::max(lo, at), e = std::min(hi, at + t.bytes);
+    if (b < e) memcpy(t.dst + (b - at), t.src + (b - at), e - b);
+    at += t.bytes;
+    if (at >= hi) break;
+  }
+}
 void run_gather(const std::vector<Gather>& g) {
-  for (const auto& t : g) memcpy(t.dst, t.src, t.bytes);
+  size_t total = 0;
+  for (const auto& t : g) total += t.bytes;
+  const unsigned hc = std::thread::hardware_concurrency();
+  const unsigned parts = total >= (16u << 20) ? std::min(4u, std::max(1u, hc / 2)) : 1u;
+  if (parts == 1) { gather_part(g, total, 0, 1); return; }
+  std::vector<std::thread> pool;
+  for (unsigned w = 1; w < parts; ++w) pool.emplace_back(gather_part, std::cref(g), total, w, parts);
+  gather_part(g, total, 0, parts);
+  for (auto& th : pool) th.join();
 }
 
 nbg_kvmap span_map(const Heap& h) {

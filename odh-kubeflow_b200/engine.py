@@ -333,6 +333,44 @@ def bitmap_to_bools(bitmap, n):
     return bits[:n].astype(bool)
 
 
+class StepBuffers:
+    """Host result buffers of one step over n notebooks: {"sts"|"svc"|"vs": (reason, bitmap), "cull": (action, argmax,
+    cull bitmap, period bitmap)}.  pinned=True takes them from nbg_alloc_pinned (the read-back then runs at PCIe speed)."""
+
+    def __init__(self, n, pinned=True):
+        words = (n + 63) // 64
+        self._lib, self._ptrs = N.nbg(), []
+        spec = [("sts_r", n, np.uint8), ("sts_b", words, np.uint64), ("svc_r", n, np.uint8), ("svc_b", words, np.uint64),
+                ("vs_r", n, np.uint8), ("vs_b", words, np.uint64), ("act", n, np.uint8), ("amax", n, np.uint32),
+                ("cb", words, np.uint64), ("pb", words, np.uint64)]
+        a = {}
+        for name, count, dt in spec:
+            if pinned:
+                nbytes = max(count * np.dtype(dt).itemsize, 1)
+                p = self._lib.nbg_alloc_pinned(nbytes)
+                if not p:
+                    raise MemoryError("nbg_alloc_pinned(%d)" % nbytes)
+                self._ptrs.append(p)
+                a[name] = np.frombuffer((C.c_uint8 * nbytes).from_address(p), dtype=np.uint8, count=count * np.dtype(dt).itemsize).view(dt)
+                a[name][...] = 0
+            else:
+                a[name] = np.zeros(count, dt)
+        self.arrays = {"sts": (a["sts_r"], a["sts_b"]), "svc": (a["svc_r"], a["svc_b"]), "vs": (a["vs_r"], a["vs_b"]),
+                       "cull": (a["act"], a["amax"], a["cb"], a["pb"])}
+
+    def close(self):
+        self.arrays = None
+        for p in self._ptrs:
+            self._lib.nbg_free_pinned(p)
+        self._ptrs = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class Store:
     """A resident fleet (nbg_store_*): packed rows live in device memory, put() replaces the rows of given
     slots from host batches of as many objects, step() runs the four predicates over slots [0, n)."""
@@ -362,17 +400,14 @@ class Store:
         _check(self._lib.nbg_store_put(self._h, idx.ctypes.data_as(N.u64p), len(idx),
                                        *[C.byref(v) if v is not None else None for v in views]), "nbg_store_put")
 
-    def step(self, n, vs_consts, now_sec, now_nsec, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE):
-        """-> the same dict as Context.step()."""
-        words = (n + 63) // 64
-        r = {k: (np.zeros(n, np.uint8), np.zeros(words, np.uint64)) for k in ("sts", "svc", "vs")}
-        action, argmax = np.zeros(n, np.uint8), np.zeros(n, np.uint32)
-        cb, pb = np.zeros(words, np.uint64), np.zeros(words, np.uint64)
+    def step(self, n, vs_consts, now_sec, now_nsec, cull_idle_min=1440, check_period_min=1, mode=N.CULL_RECONCILE, out=None):
+        """-> the same dict as Context.step().  out: a StepBuffers to write into (a caller that steps every tick keeps
+        one, pinned, instead of allocating 9 bytes per notebook each time)."""
+        r = out.arrays if out is not None else StepBuffers(n, pinned=False).arrays
         o = N.nbg_step_outputs(*[a.ctypes.data for a in (r["sts"][0], r["sts"][1], r["svc"][0], r["svc"][1], r["vs"][0],
-                                                         r["vs"][1], action, argmax, cb, pb)])
+                                                         r["vs"][1], r["cull"][0], r["cull"][1], r["cull"][2], r["cull"][3])])
         p = N.nbg_cull_params(now_sec, now_nsec, cull_idle_min, check_period_min, mode)
         _check(self._lib.nbg_store_step(self._h, n, C.byref(vs_consts), C.byref(p), C.byref(o)), "nbg_store_step")
-        r["cull"] = (action, argmax, cb, pb)
         return r
 
     def step_device(self, n, vs_consts, params, outputs, stream):

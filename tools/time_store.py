@@ -17,6 +17,7 @@ store = pkg.engine.Store(ctx, n)
 t0 = time.perf_counter(); store.put(np.arange(n, dtype=np.uint64), a.sparse(), b.gen(), c.gen(), cb); load = time.perf_counter() - t0
 nbytes = sum(x.algorithmic_bytes() for x in (a.sparse(), b.gen(), c.gen(), cb))
 consts = host.vs_gen_consts()
+out = pkg.engine.StepBuffers(n, pinned=True)
 rng = np.random.default_rng(7)
 m = max(n // 100, 1)
 puts, ticks = [], []
@@ -27,7 +28,7 @@ for t in range(8):
     s4 = cf.pack(idx=alt)
     rows = (s1.sparse(), s2.gen(), s3.gen(), s4)
     t0 = time.perf_counter(); store.put(slots, *rows); p = time.perf_counter() - t0
-    r = store.step(n, consts, now[0], now[1]); ticks.append(time.perf_counter() - t0); puts.append(p)
+    r = store.step(n, consts, now[0], now[1], out=out); ticks.append(time.perf_counter() - t0); puts.append(p)
 ok = int(r["sts"][0].astype(np.uint64).sum()) + int(r["cull"][0].astype(np.uint64).sum())   # to compare builds; parity is the tests' job
 print("%s n=%d  load %.3f s (%.1f GB/s)  put of %d rows %.2f ms  tick %.2f ms  result-sum=%d  %s" % (
     os.path.basename(os.environ.get("NBGRAFT_LIB", "default")), n, load, nbytes / load / 1e9, m,
