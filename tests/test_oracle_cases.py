@@ -535,3 +535,44 @@ def test_culler_env_parsing_follows_strconv_atoi(monkeypatch):
     assert (culler.CULL_IDLE_TIME, culler.IDLENESS_CHECK_PERIOD) == (1440, 15)
     monkeypatch.delenv("IDLENESS_CHECK_PERIOD")
     culler.initGlobalVars()
+
+
+_SIDECAR = GOLDEN["auth_sidecar_resources_table"]
+
+
+@pytest.mark.parametrize("case", _SIDECAR["cases"], ids=[c["name"] for c in _SIDECAR["cases"]])
+def test_ref_auth_sidecar_resources_table(case):
+    """auth_proxy_resources_test.go:140-418, all 17 rows: the Quantity spellings the reference itself accepts, refuses,
+    trims, compares and prints — reached through InjectKubeRbacProxy, whose proxy container carries the four values."""
+    meta = {"name": "test-notebook", "namespace": "default"}
+    if case["annotations"] is not None:
+        meta["annotations"] = {_SIDECAR["annotation_prefix"] + k: v for k, v in case["annotations"].items()}
+    nb = host.Notebook({"metadata": meta, "spec": {"template": {"spec": {"containers": [{"name": "test-notebook", "image": "test-image"}]}}}})
+    if case["error"]:
+        before = nb.digest()
+        with pytest.raises(host.HostError):
+            host.odh_mutate(nb, 16)
+        assert nb.digest() == before                       # nothing injected (notebook_webhook.go:177-183)
+        return
+    host.odh_mutate(nb, 16)
+    proxy = [c for c in nb.to_python()["spec"]["template"]["spec"]["containers"] if c["name"] == "kube-rbac-proxy"][0]
+    got = {"cpu_request": _quantity_text(proxy["resources"]["requests"]["cpu"]), "memory_request": _quantity_text(proxy["resources"]["requests"]["memory"]),
+           "cpu_limit": _quantity_text(proxy["resources"]["limits"]["cpu"]), "memory_limit": _quantity_text(proxy["resources"]["limits"]["memory"])}
+    assert got == case["expect"]
+
+
+def test_ref_kube_rbac_proxy_replaces_an_existing_container():
+    g = GOLDEN["kube_rbac_proxy_update_existing"]
+    nb = host.Notebook(g["notebook"])
+    host.odh_mutate(nb, 16)
+    pod = nb.to_python()["spec"]["template"]["spec"]
+    e = g["expect"]
+    assert len(pod["containers"]) == e["containers"]
+    c = [x for x in pod["containers"] if x["name"] == "kube-rbac-proxy"][0]
+    assert c["image"] != e["old_image"] and c["imagePullPolicy"] == e["imagePullPolicy"]
+    for side in ("requests", "limits"):
+        assert {k: _quantity_text(v) for k, v in c["resources"][side].items()} == e[side]
+    assert e["args_absent"] not in c["args"] and len(c["args"]) > e["args_more_than"]
+    assert [{"name": p["name"], "containerPort": p["containerPort"]} for p in c["ports"]] == e["ports"]
+    names = {v["name"] for v in pod["volumes"]}
+    assert set(e["volumes_include"]) <= names
