@@ -77,6 +77,16 @@ int nbh_odh_mutate(nbh_obj* notebook, int flags);
  * one keeps its value: the reference's update at :583-585 writes to the range copy). */
 int nbh_odh_mutate_proxy(nbh_obj* notebook, int flags, const char* http_proxy, const char* https_proxy, const char* no_proxy);
 
+/* Desired objects of the ODH controller, the `from` side of its comparators: what = "HTTPRoute"
+ * (NewNotebookHTTPRoute, notebook_route.go:50-131), "NetworkPolicy" / "KubeRbacProxyNetworkPolicy"
+ * (notebook_network.go:132-211), "ReferenceGrant" (notebook_referencegrant.go:39-69) or "RoleBinding"
+ * (NewRoleBinding, notebook_rbac.go:36-59).  central_namespace = the controller's namespace; gateway_* = the
+ * NOTEBOOK_GATEWAY_NAME / NOTEBOOK_GATEWAY_NAMESPACE overrides (NULL or "" = data-science-gateway / openshift-ingress);
+ * the three role strings are read for "RoleBinding" only. */
+int nbh_odh_build(const nbh_obj* notebook, const char* what, const char* central_namespace, const char* gateway_name,
+                  const char* gateway_namespace, const char* rolebinding_name, const char* role_kind,
+                  const char* role_name, nbh_obj** out);
+
 /* The COPY half of CopyStatefulSetFields / CopyServiceFields / CopyVirtualService (COMMON:114-131,173-192,
  * 208-217): what the Go functions write into `to`, given the reason bits the compare kernel returned for the pair
  * (nbg_diff_sts / nbg_diff_svc / nbg_diff_vs).  caller_prestep != 0 also copies the template labels when the

@@ -354,6 +354,7 @@ def _bind_nbh(lib):
         "nbh_generate_virtualservice": ([_vp, P(nbh_env), P(_vp), cp, sz], C.c_int),
         "nbh_odh_mutate": ([_vp, C.c_int], C.c_int),
         "nbh_odh_mutate_proxy": ([_vp, C.c_int, C.c_char_p, C.c_char_p, C.c_char_p], C.c_int),
+        "nbh_odh_build": ([_vp, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, P(_vp)], C.c_int),
         "nbh_apply_sts_fields": ([_vp, _vp, C.c_uint, C.c_int], C.c_int),
         "nbh_apply_svc_fields": ([_vp, _vp], C.c_int),
         "nbh_apply_vs_fields": ([_vp, _vp, C.c_uint], C.c_int),
@@ -410,7 +411,7 @@ def _bind_nbh(lib):
 
 NBH_SYMBOLS = [
     "nbh_obj_from_json", "nbh_obj_free", "nbh_obj_to_json", "nbh_str_free", "nbh_obj_get", "nbh_obj_erase", "nbh_obj_set_str", "nbh_obj_digest",
-    "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate", "nbh_odh_mutate_proxy",
+    "nbh_generate_statefulset", "nbh_generate_service", "nbh_generate_virtualservice", "nbh_odh_mutate", "nbh_odh_mutate_proxy", "nbh_odh_build",
     "nbh_sts_new", "nbh_sts_free", "nbh_sts_add", "nbh_sts_view", "nbh_sts_view_sparse", "nbh_svc_new", "nbh_svc_free", "nbh_svc_add",
     "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",

@@ -519,4 +519,132 @@ bool odh_webhook_mutate(GVal* nb, const OdhInject& what) {
   return true;
 }
 
+// ------------------------------------------------------------- ODH desired objects
+// The desired side of the ODH controller's comparators, restated from the builders it calls before
+// CompareNotebookHTTPRoutes / NetworkPolicies / ReferenceGrants and the RoleBinding check.  Pointer fields that the
+// Go code leaves nil stay absent (group, kind, weight ... are defaults the API server adds to the LIVE object, which
+// is why a freshly created route already differs from the desired one under reflect.DeepEqual).
+bool odh_build(const GVal& nb, const std::string& what, const OdhBuildEnv& env, GVal* out) {
+  const GVal& meta = field(nb, "metadata");
+  const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
+  auto labels_of = [](std::initializer_list<std::pair<const char*, std::string>> kv) {
+    GVal m = GVal::map();
+    for (const auto& e : kv) m.set(e.first, GVal::str(e.second));
+    return m;
+  };
+  auto match_labels = [&](const char* key, const std::string& val) {
+    GVal sel = GVal::strct();
+    sel.set("matchLabels", labels_of({{key, val}}));
+    return sel;
+  };
+  auto str_ptr = [](const std::string& v) { return GVal::ptr(GVal::str(v)); };
+  GVal o = GVal::strct(), m = GVal::strct(), spec = GVal::strct();
+  if (what == "HTTPRoute") {                               // NewNotebookHTTPRoute, notebook_route.go:50-131
+    const std::string route = "nb-" + ns + "-" + name;
+    if (route.size() > 63)                                 // HTTPRouteSubDomainMaxLen: generateName instead (:68-79)
+      m.set("generateName", GVal::str("nb-" + ns.substr(0, 10) + "-" + name.substr(0, 10) + "-"));
+    else
+      m.set("name", GVal::str(route));
+    m.set("namespace", GVal::str(env.central_namespace));
+    m.set("labels", labels_of({{"notebook-name", name}, {"notebook-namespace", ns}}));
+    GVal parent = GVal::strct();
+    parent.set("name", GVal::str(env.gateway_name.empty() ? "data-science-gateway" : env.gateway_name));
+    parent.set("namespace", str_ptr(env.gateway_namespace.empty() ? "openshift-ingress" : env.gateway_namespace));
+    GVal parents = GVal::list();
+    parents.items.push_back(std::move(parent));
+    GVal pathm = GVal::strct();
+    pathm.set("type", str_ptr("PathPrefix"));
+    pathm.set("value", str_ptr("/notebook/" + ns + "/" + name));
+    GVal match = GVal::strct();
+    match.set("path", GVal::ptr(std::move(pathm)));
+    GVal matches = GVal::list();
+    matches.items.push_back(std::move(match));
+    GVal backend = GVal::strct();
+    backend.set("name", GVal::str(name));
+    backend.set("namespace", str_ptr(ns));
+    backend.set("port", GVal::ptr(GVal::integer(8888)));
+    GVal backends = GVal::list();
+    backends.items.push_back(std::move(backend));
+    GVal rule = GVal::strct();
+    rule.set("matches", std::move(matches));
+    rule.set("backendRefs", std::move(backends));
+    GVal rules = GVal::list();
+    rules.items.push_back(std::move(rule));
+    spec.set("parentRefs", std::move(parents));
+    spec.set("rules", std::move(rules));
+  } else if (what == "NetworkPolicy" || what == "KubeRbacProxyNetworkPolicy") {
+    // NewNotebookNetworkPolicy / NewKubeRbacProxyNetworkPolicy, notebook_network.go:132-211
+    const bool proxy = what != "NetworkPolicy";
+    m.set("name", GVal::str(name + (proxy ? "-kube-rbac-proxy-np" : "-ctrl-np")));
+    m.set("namespace", GVal::str(ns));
+    GVal port = GVal::strct();
+    port.set("protocol", str_ptr("TCP"));
+    {
+      GVal ios = GVal::strct();                            // &intstr.IntOrString{IntVal: port}: Type stays Int (0)
+      ios.set("IntVal", GVal::integer(proxy ? 8443 : 8888));
+      port.set("port", GVal::ptr(std::move(ios)));
+    }
+    GVal ports = GVal::list();
+    ports.items.push_back(std::move(port));
+    GVal rule = GVal::strct();
+    rule.set("ports", std::move(ports));
+    if (!proxy) {                                          // only the controller's namespace may reach the notebook port
+      GVal peer = GVal::strct();
+      peer.set("namespaceSelector", GVal::ptr(match_labels("kubernetes.io/metadata.name", env.central_namespace)));
+      GVal from = GVal::list();
+      from.items.push_back(std::move(peer));
+      rule.set("from", std::move(from));
+    }
+    GVal ingress = GVal::list();
+    ingress.items.push_back(std::move(rule));
+    GVal types = GVal::list();
+    types.items.push_back(GVal::str("Ingress"));
+    spec.set("podSelector", match_labels("notebook-name", name));
+    spec.set("ingress", std::move(ingress));
+    spec.set("policyTypes", std::move(types));
+  } else if (what == "ReferenceGrant") {                   // NewNotebookReferenceGrant, notebook_referencegrant.go:39-69
+    m.set("name", GVal::str("notebook-httproute-access"));
+    m.set("namespace", GVal::str(ns));
+    m.set("labels", labels_of({{"app.kubernetes.io/managed-by", "odh-notebook-controller"},
+                               {"opendatahub.io/component", "notebook-controller"}}));
+    GVal from = GVal::strct();
+    from.set("group", GVal::str("gateway.networking.k8s.io"));
+    from.set("kind", GVal::str("HTTPRoute"));
+    from.set("namespace", GVal::str(env.central_namespace));
+    GVal froms = GVal::list();
+    froms.items.push_back(std::move(from));
+    GVal to = GVal::strct();                               // Group "" (core), Name unset: any Service of the namespace
+    to.set("kind", GVal::str("Service"));
+    GVal tos = GVal::list();
+    tos.items.push_back(std::move(to));
+    spec.set("from", std::move(froms));
+    spec.set("to", std::move(tos));
+  } else if (what == "RoleBinding") {                      // NewRoleBinding, notebook_rbac.go:36-59
+    m.set("name", GVal::str(env.rolebinding_name));
+    m.set("namespace", GVal::str(ns));
+    m.set("labels", labels_of({{"notebook-name", name}}));
+    GVal subject = GVal::strct();
+    subject.set("kind", GVal::str("ServiceAccount"));
+    subject.set("name", GVal::str(name));
+    subject.set("namespace", GVal::str(ns));
+    GVal subjects = GVal::list();
+    subjects.items.push_back(std::move(subject));
+    GVal ref = GVal::strct();
+    ref.set("kind", GVal::str(env.role_kind));
+    ref.set("name", GVal::str(env.role_name));
+    ref.set("apiGroup", GVal::str("rbac.authorization.k8s.io"));
+    o.set("metadata", std::move(m));
+    o.set("subjects", std::move(subjects));
+    o.set("roleRef", std::move(ref));
+    *out = std::move(o);
+    return true;
+  } else {
+    return false;
+  }
+  o.set("metadata", std::move(m));
+  o.set("spec", std::move(spec));
+  *out = std::move(o);
+  return true;
+}
+
 }  // namespace nbh

@@ -246,6 +246,19 @@ NBH_API int nbh_odh_mutate(nbh_obj* nb, int flags) {
   inj.elyra_secret = flags & 8; inj.rbac_proxy = flags & 16; inj.feast = flags & 32;
   return odh_webhook_mutate(&nb->v, inj) ? 0 : 1;     // 1: kube-rbac-proxy injection refused (bad resource annotations)
 }
+NBH_API int nbh_odh_build(const nbh_obj* nb, const char* what, const char* central_namespace, const char* gateway_name,
+                          const char* gateway_namespace, const char* rolebinding_name, const char* role_kind,
+                          const char* role_name, nbh_obj** out) {
+  if (!nb || !what || !out) return -1;
+  OdhBuildEnv env;
+  auto s = [](const char* p) { return std::string(p ? p : ""); };
+  env.central_namespace = s(central_namespace); env.gateway_name = s(gateway_name); env.gateway_namespace = s(gateway_namespace);
+  env.rolebinding_name = s(rolebinding_name); env.role_kind = s(role_kind); env.role_name = s(role_name);
+  nbh_obj* o = new nbh_obj();
+  if (!odh_build(nb->v, what, env, &o->v)) { delete o; return -1; }
+  *out = o;
+  return 0;
+}
 NBH_API int nbh_odh_mutate_proxy(nbh_obj* nb, int flags, const char* http_proxy, const char* https_proxy, const char* no_proxy) {
   if (!nb || !http_proxy || !https_proxy || !no_proxy) return -1;
   OdhInject inj;

@@ -49,6 +49,15 @@ struct OdhInject {
 // are still applied; no proxy container, volumes or service account are added — ODHWH:177-183)
 bool odh_webhook_mutate(GVal* notebook, const OdhInject& what);
 
+// Desired objects of the ODH controller (the `from` side of its comparators): `what` is "HTTPRoute",
+// "NetworkPolicy", "KubeRbacProxyNetworkPolicy", "ReferenceGrant" or "RoleBinding".
+struct OdhBuildEnv {
+  std::string central_namespace;                 // the controller's own namespace (routes live there)
+  std::string gateway_name, gateway_namespace;   // NOTEBOOK_GATEWAY_NAME / _NAMESPACE; "" = the defaults
+  std::string rolebinding_name, role_kind, role_name;
+};
+bool odh_build(const GVal& notebook, const std::string& what, const OdhBuildEnv& env, GVal* out);
+
 // ---- the copy half of Copy*Fields (apply.cpp) ------------------------------
 // `reason` = the bits the compare kernel returned for this pair (include/nbgraft.h).
 void apply_statefulset_fields(const GVal& from, GVal* to, unsigned reason, bool caller_prestep);

@@ -147,6 +147,19 @@ def odh_mutate(notebook, flags=2 | 4 | 8 | 16 | 32, proxy=None):
     return notebook
 
 
+def odh_build(notebook, what, central_namespace="redhat-ods-applications", gateway_name="", gateway_namespace="",
+              rolebinding_name="", role_kind="", role_name=""):
+    """The ODH controller's desired object for a Notebook: what = "HTTPRoute" | "NetworkPolicy" |
+    "KubeRbacProxyNetworkPolicy" | "ReferenceGrant" | "RoleBinding" (the `from` side of its comparators)."""
+    out = C.c_void_p()
+    rc = N.nbh().nbh_odh_build(notebook._h, what.encode(), central_namespace.encode(), gateway_name.encode(),
+                               gateway_namespace.encode(), rolebinding_name.encode(), role_kind.encode(), role_name.encode(),
+                               C.byref(out))
+    if rc != 0:
+        raise HostError("odh_build: unknown kind " + what)
+    return Obj(out.value)
+
+
 def _arr(ptr, count, dtype):
     if count == 0:
         return np.empty(0, dtype=dtype)

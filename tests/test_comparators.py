@@ -150,3 +150,128 @@ def test_comparator_fleet_gpu(ctx):
         cm.add(o["sts_from"], o["sts_to"])
     g, w = ctx.diff_generic(cm), O.packed_diff_generic(cm)
     assert np.array_equal(g[0], w[0]) and np.array_equal(g[1], w[1])
+
+
+# ---- the desired side from the restated ODH builders (nbh_odh_build) ---------------------------------------
+TEST_NB = {"metadata": {"name": "test-notebook", "namespace": "default"},
+           "spec": {"template": {"spec": {"containers": [{"name": "test-notebook", "image": "i"}]}}}}
+# notebook_controller_test.go:800-838: the NetworkPolicy the ODH test expects for "test-notebook" (controller pod in
+# redhat-ods-applications, suite_test.go)
+EXPECTED_NETPOL = {"metadata": {"name": "test-notebook-ctrl-np", "namespace": "default"},
+                   "spec": {"podSelector": {"matchLabels": {"notebook-name": "test-notebook"}},
+                            "ingress": [{"ports": [{"protocol": "TCP", "port": 8888}],
+                                         "from": [{"namespaceSelector": {"matchLabels": {"kubernetes.io/metadata.name": "redhat-ods-applications"}}}]}],
+                            "policyTypes": ["Ingress"]}}
+EXPECTED_PROXY_NETPOL = {"metadata": {"name": "test-notebook-kube-rbac-proxy-np", "namespace": "default"},
+                         "spec": {"podSelector": {"matchLabels": {"notebook-name": "test-notebook"}},
+                                  "ingress": [{"ports": [{"protocol": "TCP", "port": 8443}]}], "policyTypes": ["Ingress"]}}
+
+
+def test_odh_builders_give_the_objects_the_reference_tests_expect():
+    nb = host.Notebook(TEST_NB)
+    route = host.odh_build(nb, "HTTPRoute")
+    # the controller's own object (no defaults yet) equals the transcription above; against the object the API server
+    # hands back (group / kind / weight defaulted) the reference's comparator already says "different"
+    assert O.compare_generic(route, host.Obj.from_json("HTTPRoute", DESIRED_HTTPROUTE), "metadata.labels", "spec", 0) == 0
+    assert O.compare_generic(route, host.Obj.from_json("HTTPRoute", EXPECTED_HTTPROUTE), "metadata.labels", "spec", 0) == 2
+    assert route.to_python()["metadata"] == EXPECTED_HTTPROUTE["metadata"]
+    for what, expected in (("NetworkPolicy", EXPECTED_NETPOL), ("KubeRbacProxyNetworkPolicy", EXPECTED_PROXY_NETPOL)):
+        got = host.odh_build(nb, what)
+        assert O.compare_generic(got, host.Obj.from_json("NetworkPolicy", expected), "metadata.labels", "spec", 0) == 0, what
+        assert got.to_python()["metadata"] == expected["metadata"]
+    rg = host.odh_build(nb, "ReferenceGrant")
+    want = {"metadata": {"name": "notebook-httproute-access", "namespace": "default",
+                         "labels": {"app.kubernetes.io/managed-by": "odh-notebook-controller", "opendatahub.io/component": "notebook-controller"}},
+            "spec": {"from": [{"group": "gateway.networking.k8s.io", "kind": "HTTPRoute", "namespace": "redhat-ods-applications"}],
+                     "to": [{"group": "", "kind": "Service"}]}}
+    assert O.compare_generic(rg, host.Obj.from_json("ReferenceGrant", want), "metadata.labels", "spec", 0) == 0
+    rb = host.odh_build(nb, "RoleBinding", rolebinding_name="rb", role_kind="ClusterRole", role_name="r")
+    assert O.compare_generic(rb, host.Obj.from_json("RoleBinding", _e(ROLEBINDING, lambda o: o["subjects"][0].update({"name": "test-notebook"}))),
+                             "metadata.none", "subjects", 0) == 0
+    # a name that does not fit a DNS label switches to generateName (notebook_route.go:68-79)
+    long_nb = host.Notebook(_e(TEST_NB, lambda o: o["metadata"].update({"name": "n" * 40, "namespace": "s" * 30})))
+    meta = host.odh_build(long_nb, "HTTPRoute").to_python()["metadata"]
+    assert "name" not in meta and meta["generateName"] == "nb-" + "s" * 10 + "-" + "n" * 10 + "-"
+    # gateway overrides (NOTEBOOK_GATEWAY_NAME / NOTEBOOK_GATEWAY_NAMESPACE)
+    pr = host.odh_build(nb, "HTTPRoute", gateway_name="gw", gateway_namespace="gwns").to_python()["spec"]["parentRefs"][0]
+    assert pr == {"name": "gw", "namespace": "gwns"}
+    with pytest.raises(host.HostError):
+        host.odh_build(nb, "Ingress")
+
+
+def _api_defaults(kind, obj):
+    """What the API server adds to a freshly created object of the kind (the defaults the reference's expected objects show)."""
+    o = copy.deepcopy(obj)
+    if kind == "HTTPRoute":
+        for p in o["spec"]["parentRefs"]:
+            p.update({"group": "gateway.networking.k8s.io", "kind": "Gateway"})
+        for r in o["spec"]["rules"]:
+            for b in r["backendRefs"]:
+                b.update({"group": "", "kind": "Service", "weight": 1})
+    return o
+
+
+def _odh_pairs(n):
+    """(kind, desired, live) for n ODH fleet notebooks: the builders' objects against live copies that are identical,
+    defaulted by the API server, or edited by hand (the cases the ODH reconcilers exist for)."""
+    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 71, n, max(n // 25, 1))
+    rng = np.random.default_rng(71)
+    out = []
+    for i in range(n):
+        nb = fleet.get(i, "notebook")
+        kind = ("HTTPRoute", "NetworkPolicy", "KubeRbacProxyNetworkPolicy", "ReferenceGrant")[i % 4]
+        typ = "NetworkPolicy" if "NetworkPolicy" in kind else kind
+        desired = host.odh_build(nb, kind)
+        live = _as_api(desired.to_python())
+        u = rng.random()
+        if u < 0.35:
+            pass
+        elif u < 0.6:
+            live = _api_defaults(kind, live)
+        elif u < 0.75:
+            live["metadata"].setdefault("labels", {})["edited-by"] = "someone"
+        elif u < 0.9:
+            if "policyTypes" in live["spec"]:
+                live["spec"]["policyTypes"] = ["Egress"]                  # the manual patch of notebook_controller_test.go:902
+            elif "rules" in live["spec"]:
+                live["spec"]["rules"] = [{"backendRefs": [{"name": "foo", "port": 8888}]}]   # ... and of :134
+            else:
+                live["spec"]["to"].append({"group": "", "kind": "Secret"})
+        else:
+            live["metadata"]["resourceVersion"] = str(int(rng.integers(1, 10 ** 6)))          # not compared
+        out.append((typ, desired, host.Obj.from_json(typ, live)))
+    return out
+
+
+def _as_api(v):
+    if isinstance(v, dict):
+        if v and set(v) <= {"Type", "IntVal", "StrVal"}:
+            return v.get("StrVal", "") if v.get("Type") else v.get("IntVal", 0)
+        return {k: _as_api(x) for k, x in v.items()}
+    if isinstance(v, list):
+        return [_as_api(x) for x in v]
+    return v
+
+
+def test_odh_builder_pairs_packed_equals_semantic():
+    pairs = _odh_pairs(1200)
+    b = host.GenBatch(N.GEN_DEEPEQUAL, "metadata.labels", "spec")
+    for _, d, f in pairs:
+        b.add(d, f)
+    reason = O.packed_diff_generic(b)[0]
+    for i, (_, d, f) in enumerate(pairs):
+        assert O.compare_generic(d, f, "metadata.labels", "spec", 0) == reason[i], i
+    # every outcome occurs: equal, labels only, spec only
+    assert {0, 1, 2} <= set(int(x) for x in reason)
+
+
+@pytest.mark.gpu
+def test_odh_builder_pairs_gpu(ctx):
+    pairs = _odh_pairs(6000)
+    b = host.GenBatch(N.GEN_DEEPEQUAL, "metadata.labels", "spec")
+    for _, d, f in pairs:
+        b.add(d, f)
+    got, want = ctx.diff_generic(b), O.packed_diff_generic(b)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    for i in range(0, 6000, 7):
+        assert O.compare_generic(pairs[i][1], pairs[i][2], "metadata.labels", "spec", 0) == got[0][i]
