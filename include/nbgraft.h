@@ -319,6 +319,41 @@ int nbg_diff_svc_gen(nbg_ctx* ctx, const nbg_svc_gen_batch* in, uint64_t n, uint
 int nbg_diff_vs_gen(nbg_ctx* ctx, const nbg_vs_gen_batch* in, const nbg_vs_gen_consts* consts, uint64_t n,
                     uint8_t* reason, uint64_t* bitmap);
 
+/* ---- desired StatefulSet generated ON THE DEVICE (second half) ---------------------------
+ * generateStatefulSet (NBCTL:433-523) as a patch of the NOTEBOOK's own PodSpec tile.  The desired PodSpec is a deep
+ * copy of the Notebook's with at most four edits — containers[0].workingDir defaulted (NBCTL:495-497), a nil
+ * containers[0].ports replaced by the default port (:498-506), NB_PREFIX appended to containers[0].env unless a
+ * variable of that name exists (:417-431), securityContext {fsGroup: 100} when it is nil and ADD_FSGROUP (:514-521) —
+ * and every one of them lands in named slots of the tile, so the kernel makes the desired tile in registers from
+ * the Notebook's and compares it with the live one.  Spec.Replicas is 0 iff the stop annotation is present (:434-437).
+ * `in` is an nbg_sts_batch (dense tiles) whose `from` side holds what the NOTEBOOK supplies:
+ *     pod_from    = the tile of the Notebook's spec.template.spec (not of the generated StatefulSet)
+ *     labels_from = the Notebook's labels (the desired StatefulSet's labels are a copy of them, NBCTL:474-477)
+ *     tmpl_from   = digest of the desired template labels ({statefulset, notebook-name, workbenches} + labels)
+ *     replicas_from, ann_from: NOT READ (derived from gen->flags / the desired object has no annotations)
+ * Same results as nbg_diff_sts on (pack(generateStatefulSet(notebook)), live), bit for bit.
+ * This is a capability, not the fast path: it needs DENSE tiles (the sparse sweep cannot shift runs at the
+ * insertion points) and saves no byte — the Notebook's tile is as large as the desired one — so nbg_step keeps
+ * taking the desired side from the host. */
+#define NBG_GEN_STOPPED    0x01u /* annotation kubeflow-resource-stopped present: desired replicas 0              */
+#define NBG_GEN_PREPATCHED 0x02u /* pod_from already IS the desired tile: the host generated it (containers[0].env
+                                    has 14 or more entries, more than the tile shows by name)                     */
+typedef struct nbg_sts_gen_inputs {
+  const uint64_t* prefix_hash;   /* n: hash64("/notebook/<namespace>/<name>"), the value of NB_PREFIX */
+  const uint8_t*  flags;         /* n: NBG_GEN_*                                                       */
+} nbg_sts_gen_inputs;
+/* what does not depend on the notebook (nbh_sts_gen_consts computes them with the packer's own functions) */
+typedef struct nbg_sts_gen_consts {
+  uint64_t working_dir;          /* hash64("/home/jovyan")                                   */
+  uint64_t port_name, port_rest; /* hash64("notebook-port"), the packer's digest of the rest of the default port */
+  uint64_t env_name;             /* hash64("NB_PREFIX")                                      */
+  uint32_t add_fsgroup, pad;     /* ADD_FSGROUP unset or "true" (NBCTL:514)                  */
+} nbg_sts_gen_consts;
+int nbg_diff_sts_gen(nbg_ctx* ctx, const nbg_sts_batch* in, const nbg_sts_gen_inputs* gen, const nbg_sts_gen_consts* consts,
+                     uint64_t n, uint8_t* reason, uint64_t* bitmap);
+int nbg_diff_sts_gen_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, const nbg_sts_gen_inputs* gen,
+                            const nbg_sts_gen_consts* consts, uint64_t n, uint8_t* reason, uint64_t* bitmap, void* stream);
+
 /* One reconcile step over n notebooks in ONE call: nbg_diff_sts_sparse + nbg_diff_svc_gen +
  * nbg_diff_vs_gen + nbg_cull (any of the batches may be NULL to skip it), queued as a single
  * copy/compute pipeline so the PCIe link stays busy across the four — the batch analogue of

@@ -101,6 +101,15 @@ void nbh_sts_free(nbh_sts* b);
 int nbh_sts_add(nbh_sts* b, const nbh_obj* from, const nbh_obj* to);
 uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out);   /* returns n; pointers live as long as b is unchanged */
 
+/* generateStatefulSet on the device (nbg_diff_sts_gen): append a pair whose `from` side is taken from the NOTEBOOK
+ * (its own PodSpec tile, its labels, the digest of the desired template labels) instead of from a generated
+ * StatefulSet; nbh_sts_view gives the nbg_sts_batch, nbh_sts_view_gen the per-notebook generator inputs (0 when
+ * the batch was not filled with nbh_sts_add_gen alone), nbh_sts_gen_consts the constants.  -1 when
+ * generateStatefulSet would fail or leave its common path (no containers; name longer than 52 characters). */
+int nbh_sts_add_gen(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* to, const nbh_env* env /*NULL = defaults*/);
+uint64_t nbh_sts_view_gen(const nbh_sts* b, nbg_sts_gen_inputs* out);
+int nbh_sts_gen_consts(const nbh_env* env /*NULL = defaults*/, nbg_sts_gen_consts* out);
+
 /* the same pairs with sparsely stored PodSpec tiles (nbg_diff_sts_sparse) */
 uint64_t nbh_sts_view_sparse(const nbh_sts* b, nbg_sts_sparse_batch* out);
 

@@ -149,6 +149,8 @@ SVC_LABELS, SVC_ANNOTATIONS, SVC_SELECTOR, SVC_PORTS = 1, 2, 4, 8
 VS_SPEC_DIFFERS, VS_TO_MISSING, VS_FROM_MISSING = 1, 2, 4
 ACT_SRC_MASK, ACT_PERIOD, ACT_CULL, ACT_STOPPED, ACT_INIT, ACT_NOPOD = 3, 4, 8, 16, 32, 64
 CULL_PREDICATES, CULL_RECONCILE = 0, 1
+GEN_STOPPED, GEN_PREPATCHED = 1, 2
+STS_UPDATE_MASK = 0x0F
 
 # ---- one place that knows which array goes into which field of which batch struct -----------------
 # Array names are those of host.*Batch.arrays(): "<map>.off/.ent[/.end]" for string maps,
@@ -158,12 +160,15 @@ CULL_PREDICATES, CULL_RECONCILE = 0, 1
 _KV_FIELDS = {"StsBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
               "StsSparseBatch": ("labels_from", "labels_to", "ann_from", "ann_to"),
               "SvcBatch": ("labels_from", "labels_to", "ann_from", "ann_to", "sel_from", "sel_to"),
+              "sts_gen": ("labels_from", "labels_to", "ann_to"),
               "VsBatch": ("hdr_from", "hdr_to"), "svc_gen": ("labels_to", "ann_to", "sel_to"), "vs_gen": ("hdr_from", "hdr_to"),
               "GenBatch": ("labels_a", "labels_b", "spec_a", "spec_b"), "RestartBatch": (), "CullBatch": ()}
 _SPARSE_FIELDS = {"StsSparseBatch": ("pod_from", "pod_to"), "RestartBatch": ("old_spec", "updated_spec", "mutated_spec")}
 _PLAIN_FIELDS = {
     "StsBatch": (("replicas_from", C.c_int32), ("replicas_to", C.c_int32), ("tmpl_from", C.c_uint64), ("tmpl_to", C.c_uint64),
                  ("pod_from", C.c_uint64), ("pod_to", C.c_uint64)),
+    "sts_gen": (("replicas_to", C.c_int32), ("tmpl_from", C.c_uint64), ("tmpl_to", C.c_uint64), ("pod_from", C.c_uint64),
+                ("pod_to", C.c_uint64)),
     "StsSparseBatch": (("replicas_from", C.c_int32), ("replicas_to", C.c_int32), ("tmpl_from", C.c_uint64), ("tmpl_to", C.c_uint64)),
     "SvcBatch": (("flags", C.c_uint8), ("ports_from", C.c_uint64), ("ports_to", C.c_uint64)),
     "VsBatch": (("flags", C.c_uint8), ("spec_from", C.c_uint64), ("spec_to", C.c_uint64)),
@@ -178,7 +183,7 @@ _PLAIN_FIELDS = {
 
 
 def batch_struct(kind, ptr, has=lambda name: False):
-    cls = {"StsBatch": nbg_sts_batch, "StsSparseBatch": nbg_sts_sparse_batch, "SvcBatch": nbg_svc_batch, "VsBatch": nbg_vs_batch,
+    cls = {"StsBatch": nbg_sts_batch, "sts_gen": nbg_sts_batch, "StsSparseBatch": nbg_sts_sparse_batch, "SvcBatch": nbg_svc_batch, "VsBatch": nbg_vs_batch,
            "svc_gen": nbg_svc_gen_batch, "vs_gen": nbg_vs_gen_batch, "GenBatch": nbg_generic_batch,
            "RestartBatch": nbg_restart_batch, "CullBatch": nbg_cull_batch}[kind]
     s = cls()
@@ -213,10 +218,19 @@ NBG_SYMBOLS = [
     "nbg_step", "nbg_step_device", "nbg_store_create", "nbg_store_destroy", "nbg_store_put", "nbg_store_step",
     "nbg_store_step_device", "nbg_store_get_stats", "nbg_store_check", "nbg_device_id", "nbg_diff_svc_gen", "nbg_diff_svc_gen_device", "nbg_diff_vs_gen", "nbg_diff_vs_gen_device",
     "nbg_count_running", "nbg_count_running_device", "nbg_diff_generic", "nbg_diff_generic_device", "nbg_restart_block", "nbg_restart_block_device",
-    "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device", "nbg_check_step_device",
+    "nbg_cull_text", "nbg_parse_records", "nbg_parse_records_device", "nbg_hash_strings", "nbg_hash_strings_device", "nbg_check_step_device", "nbg_diff_sts_gen", "nbg_diff_sts_gen_device",
 ]
 
 _vp = C.c_void_p
+
+
+class nbg_sts_gen_inputs(C.Structure):
+    _fields_ = [("prefix_hash", u64p), ("flags", u8p)]
+
+
+class nbg_sts_gen_consts(C.Structure):
+    _fields_ = [("working_dir", C.c_uint64), ("port_name", C.c_uint64), ("port_rest", C.c_uint64), ("env_name", C.c_uint64),
+                ("add_fsgroup", C.c_uint32), ("pad", C.c_uint32)]
 
 
 class nbg_step_extents(C.Structure):
@@ -248,6 +262,12 @@ def _bind_nbg(lib):
     lib.nbg_check_step_device.argtypes = [_vp, C.c_int, _vp, _vp, _vp, _vp, C.c_uint64, C.POINTER(nbg_step_extents), _vp,
                                           C.POINTER(C.c_uint)]
     lib.nbg_check_step_device.restype = C.c_int
+    lib.nbg_diff_sts_gen.argtypes = [_vp, C.POINTER(nbg_sts_batch), C.POINTER(nbg_sts_gen_inputs), C.POINTER(nbg_sts_gen_consts),
+                                     C.c_uint64, _vp, _vp]
+    lib.nbg_diff_sts_gen.restype = C.c_int
+    lib.nbg_diff_sts_gen_device.argtypes = [_vp, C.c_int, C.POINTER(nbg_sts_batch), C.POINTER(nbg_sts_gen_inputs),
+                                            C.POINTER(nbg_sts_gen_consts), C.c_uint64, _vp, _vp, _vp]
+    lib.nbg_diff_sts_gen_device.restype = C.c_int
     lib.nbg_store_check.argtypes = [_vp, C.c_uint64, C.POINTER(C.c_uint)]
     lib.nbg_store_check.restype = C.c_int
     for name, bt in (("nbg_diff_sts", nbg_sts_batch), ("nbg_diff_svc", nbg_svc_batch), ("nbg_diff_vs", nbg_vs_batch),
@@ -387,6 +407,9 @@ def _bind_nbh(lib):
         "nbh_fleet_pack": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
         "nbh_fleet_pack_lean": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
         "nbh_sts_is_lean": ([_vp], C.c_int),
+        "nbh_sts_add_gen": ([_vp, _vp, _vp, _vp], C.c_int),
+        "nbh_sts_view_gen": ([_vp, P(nbg_sts_gen_inputs)], C.c_uint64),
+        "nbh_sts_gen_consts": ([_vp, P(nbg_sts_gen_consts)], C.c_int),
         "nbh_pack_objects": ([P(_vp), C.c_uint64, C.c_int, P(_vp), P(_vp), P(_vp)], C.c_int),
         "nbh_fleet_ns_table": ([_vp, u64p, u64p], C.c_uint32),
         "nbh_fleet_shard_indices_by_table": ([_vp, u32p, C.c_uint32, u64p, C.c_uint64], C.c_uint64),
@@ -416,7 +439,7 @@ NBH_SYMBOLS = [
     "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
-    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_lean", "nbh_sts_is_lean", "nbh_pack_objects", "nbh_fleet_ns_table", "nbh_fleet_shard_indices_by_table", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
+    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_lean", "nbh_sts_is_lean", "nbh_pack_objects", "nbh_sts_add_gen", "nbh_sts_view_gen", "nbh_sts_gen_consts", "nbh_fleet_ns_table", "nbh_fleet_shard_indices_by_table", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
     "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",
 ]

@@ -29,6 +29,8 @@ cudaError_t nbg_launch_diff_sts(const nbg_sts_batch*, unsigned long long, const 
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_sts_sparse(const nbg_sts_sparse_batch*, unsigned long long, const unsigned*, uint8_t*,
                                        uint64_t*, cudaStream_t);
+cudaError_t nbg_launch_diff_sts_gen(const nbg_sts_batch*, const uint64_t*, const uint8_t*, const nbg_sts_gen_consts*,
+                                    unsigned long long, const unsigned*, uint8_t*, uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_svc(const nbg_svc_batch*, unsigned long long, const unsigned*, uint8_t*,
                                 uint64_t*, cudaStream_t);
 cudaError_t nbg_launch_diff_vs(const nbg_vs_batch*, unsigned long long, const unsigned*, uint8_t*,
@@ -431,6 +433,19 @@ int nbg_diff_sts_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, uint6
   cudaStream_t s = (cudaStream_t)stream;
   const unsigned bases[4] = {0, 0, 0, 0};
   CU(nbg_launch_diff_sts(in, n, bases, tl_deployment ? 1 : 0, reason, bitmap, s));
+  ctx->launches++;
+  return NBG_OK;
+}
+
+int nbg_diff_sts_gen_device(nbg_ctx* ctx, int device, const nbg_sts_batch* in, const nbg_sts_gen_inputs* gen,
+                            const nbg_sts_gen_consts* consts, uint64_t n, uint8_t* reason, uint64_t* bitmap, void* stream) {
+  if (int rc = check_dev(ctx, device)) return rc;
+  if (!in || !gen || !consts) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !gen->prefix_hash || !gen->flags) return NBG_E_INVAL;
+  CU(cudaSetDevice(ctx->devs[device]->id));
+  const unsigned bases[3] = {0, 0, 0};
+  CU(nbg_launch_diff_sts_gen(in, gen->prefix_hash, gen->flags, consts, n, bases, reason, bitmap, (cudaStream_t)stream));
   ctx->launches++;
   return NBG_OK;
 }
@@ -1109,6 +1124,50 @@ int nbg_diff_sts(nbg_ctx* ctx, const nbg_sts_batch* in, uint64_t n, uint8_t* rea
       b.ann_from = csr_ptr(sl, af); b.ann_to = csr_ptr(sl, at);
       const unsigned bases[4] = {lf.base, lt.base, af.base, at.base};
       CU(nbg_launch_diff_sts(&b, m, bases, tl_deployment ? 1 : 0, (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
+      ctx->launches++;
+      if (int r = slot_download(d, sl, lay)) return r;
+    }
+    return NBG_OK;
+  });
+  if (rc != NBG_OK) return rc;
+  unsigned any = 0;
+  for (uint64_t i = 0; i < n; ++i) any |= reason[i];
+  return (any & NBG_STS_NILREPLICAS) ? NBG_E_NILREPLICAS : NBG_OK;
+}
+
+int nbg_diff_sts_gen(nbg_ctx* ctx, const nbg_sts_batch* in, const nbg_sts_gen_inputs* gen, const nbg_sts_gen_consts* consts,
+                     uint64_t n, uint8_t* reason, uint64_t* bitmap) {
+  if (!ctx || !in || !gen || !consts) return NBG_E_INVAL;
+  if (n == 0) return NBG_OK;
+  if (!reason || !bitmap || !in->replicas_to || !in->tmpl_from || !in->tmpl_to || !in->pod_from || !in->pod_to ||
+      !gen->prefix_hash || !gen->flags)
+    return NBG_E_INVAL;
+  if (!csr_ptrs_ok(in->labels_from, n) || !csr_ptrs_ok(in->labels_to, n) || !csr_ptrs_ok(in->ann_to, n)) return NBG_E_INVAL;
+  int rc = for_each_device(ctx, n, [&](Dev& d, uint64_t lo, uint64_t hi) -> int {
+    uint64_t c = 0;
+    for (uint64_t i0 = lo; i0 < hi; i0 += kStsChunk, ++c) {
+      const uint64_t i1 = i0 + kStsChunk < hi ? i0 + kStsChunk : hi, m = i1 - i0;
+      if (!csr_ok(in->labels_from, i0, i1) || !csr_ok(in->labels_to, i0, i1) || !csr_ok(in->ann_to, i0, i1)) return NBG_E_RANGE;
+      Slot& sl = d.slot[c & 1];
+      Layout lay;
+      const size_t a_rt = lay.in(in->replicas_to + i0, m * 4);
+      const size_t a_tf = lay.in(in->tmpl_from + i0, m * 8), a_tt = lay.in(in->tmpl_to + i0, m * 8);
+      const size_t a_pf = lay.in(in->pod_from + i0 * NBG_POD_SLOTS, m * NBG_POD_SLOTS * 8);
+      const size_t a_pt = lay.in(in->pod_to + i0 * NBG_POD_SLOTS, m * NBG_POD_SLOTS * 8);
+      const size_t a_ph = lay.in(gen->prefix_hash + i0, m * 8), a_gf = lay.in(gen->flags + i0, m);
+      const CsrDev lf = csr_in(lay, in->labels_from, i0, i1), lt = csr_in(lay, in->labels_to, i0, i1);
+      const CsrDev at = csr_in(lay, in->ann_to, i0, i1);
+      const size_t o_reason = lay.out(reason + i0, m);
+      const size_t o_bits = lay.out(bitmap + i0 / 64, (m + 63) / 64 * 8);
+      if (int r = slot_upload(d, sl, lay)) return r;
+      nbg_sts_batch b{};
+      b.replicas_to = (const int32_t*)(sl.dev + a_rt);
+      b.tmpl_from = (const uint64_t*)(sl.dev + a_tf); b.tmpl_to = (const uint64_t*)(sl.dev + a_tt);
+      b.pod_from = (const uint64_t*)(sl.dev + a_pf); b.pod_to = (const uint64_t*)(sl.dev + a_pt);
+      b.labels_from = csr_ptr(sl, lf); b.labels_to = csr_ptr(sl, lt); b.ann_to = csr_ptr(sl, at);
+      const unsigned bases[3] = {lf.base, lt.base, at.base};
+      CU(nbg_launch_diff_sts_gen(&b, (const uint64_t*)(sl.dev + a_ph), (const uint8_t*)(sl.dev + a_gf), consts, m, bases,
+                                 (uint8_t*)(sl.dev + o_reason), (uint64_t*)(sl.dev + o_bits), d.s_run));
       ctx->launches++;
       if (int r = slot_download(d, sl, lay)) return r;
     }

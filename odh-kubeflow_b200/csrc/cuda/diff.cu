@@ -109,6 +109,111 @@ diff_sts_kernel(nbg_sts_batch in, unsigned long long n,
   store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
 }
 
+// ------------------------------------------------ StatefulSet, desired side generated on the device
+// generateStatefulSet (NBCTL:433-523) as a patch of the NOTEBOOK's own PodSpec tile: the desired PodSpec is a deep
+// copy of the Notebook's with at most four edits, all of which land in named slots of the tile (csrc/host/pack.cpp):
+//   containers[0].workingDir   "" -> "/home/jovyan"                          slot 42          NBCTL:495-497
+//   containers[0].ports        nil -> [{8888, "notebook-port", "TCP"}]       slots 52, 53; tag in 46   NBCTL:498-506
+//   containers[0].env          + {NB_PREFIX, /notebook/<ns>/<name>} unless a variable of that name is there
+//                                                                            slots 56+2e, 57+2e; tag in 46   NBCTL:417-431
+//   securityContext            nil -> {fsGroup: 100} when ADD_FSGROUP         slot 7; presence bits in 14     NBCTL:514-521
+// Vector v of a tile holds slots 2v and 2v+1, and lane l of the warp holds vectors l, l+32, l+64 of the object, so
+// every edit belongs to one known lane; the two words the edits depend on (the count tags in slot 46, the presence
+// bits in slot 14) travel by shuffle, "is NB_PREFIX there" is one ballot over the lanes that hold the env names.
+// An object whose env list is too long for the tile to show all its names (14 or more entries) cannot be decided
+// here: the host generates its tile and marks it NBG_GEN_PREPATCHED.
+struct StsGenConsts { unsigned long long working_dir, port_name, port_rest, env_name; unsigned add_fsgroup; };
+
+__device__ __forceinline__ unsigned long long lo64(const uint4& v) { return (unsigned long long)v.x | ((unsigned long long)v.y << 32); }
+__device__ __forceinline__ unsigned long long hi64(const uint4& v) { return (unsigned long long)v.z | ((unsigned long long)v.w << 32); }
+__device__ __forceinline__ void set_lo64(uint4& v, unsigned long long x) { v.x = (unsigned)x; v.y = (unsigned)(x >> 32); }
+__device__ __forceinline__ void set_hi64(uint4& v, unsigned long long x) { v.z = (unsigned)x; v.w = (unsigned)(x >> 32); }
+
+// a[0..2] = this lane's three vectors of ONE object's Notebook tile; on return, of its desired StatefulSet tile
+__device__ __forceinline__ void generate_sts_tile(uint4* a, unsigned lane, unsigned flags, unsigned long long prefix_hash,
+                                                  const StsGenConsts& k) {
+  // every lane takes part in the shuffles, whatever its object's flags say
+  const unsigned long long tag = __shfl_sync(FULL, lo64(a[0]), 23);       // slot 46: ports | env << 16 | mounts << 32 | envFrom << 48
+  const unsigned long long presence = __shfl_sync(FULL, lo64(a[0]), 7);   // slot 14
+  const unsigned ports_tag = (unsigned)(tag & 0xFFFFu), env_tag = (unsigned)((tag >> 16) & 0xFFFFu);
+  const unsigned env_n = env_tag == 0xFFFFu ? 0u : env_tag;               // a nil list has no elements
+  const unsigned shown = env_n < 14u ? env_n : 14u;
+  bool mine = false;
+  if (lane >= 28u) mine = (lane - 28u) < shown && lo64(a[0]) == k.env_name;          // env 0..3: vectors 28..31
+  if (lane <= 9u) mine |= (lane + 4u) < shown && lo64(a[1]) == k.env_name;           // env 4..13: vectors 32..41
+  const bool has_prefix = __ballot_sync(FULL, mine) != 0u;
+  if (flags & NBG_GEN_PREPATCHED) return;
+  const bool append = !has_prefix && env_n < 14u;
+  if (lane == 21u && lo64(a[0]) == 0ull) set_lo64(a[0], k.working_dir);
+  if (lane == 26u && ports_tag == 0xFFFFu) { set_lo64(a[0], k.port_name); set_hi64(a[0], k.port_rest); }
+  if (append) {
+    const unsigned v = 28u + env_n;
+    if (lane == (v & 31u)) {                                             // env 0..3 in the lane's first vector, 4..13 in its second
+      if (v < 32u) { set_lo64(a[0], k.env_name); set_hi64(a[0], prefix_hash); }
+      else { set_lo64(a[1], k.env_name); set_hi64(a[1], prefix_hash); }
+    }
+  }
+  if (lane == 23u) {
+    const unsigned long long ports_new = ports_tag == 0xFFFFu ? 1ull : ports_tag;
+    const unsigned long long env_new = append ? env_n + 1ull : env_tag;
+    set_lo64(a[0], (tag & ~0xFFFFFFFFull) | ports_new | (env_new << 16));
+  }
+  if (k.add_fsgroup && !(presence & 2ull)) {                               // securityContext == nil
+    if (lane == 3u) set_hi64(a[0], 100ull);                                // slot 7: *fsGroup
+    if (lane == 4u) set_hi64(a[0], 0ull);                                  // slot 9: what the struct holds besides fsGroup/runAsUser - nothing (was: the nil marker)
+    if (lane == 7u) set_lo64(a[0], presence | 6ull);                       // slot 14: securityContext and fsGroup are pointers now
+  }
+}
+
+__global__ void __launch_bounds__(128)
+diff_sts_gen_kernel(nbg_sts_batch in, const unsigned long long* __restrict__ prefix_hash, const uint8_t* __restrict__ gen_flags,
+                    StsGenConsts k, unsigned long long n, unsigned lf_base, unsigned lt_base, unsigned at_base,
+                    uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long base = warp * 32ull;
+  if (base >= n) return;
+  const unsigned long long i = base + lane;
+  const unsigned cnt = (unsigned)min(32ull, n - base);
+  unsigned reason = 0, my_flags = 0;
+  unsigned long long my_prefix = 0;
+  if (i < n) {
+    my_flags = __ldg(gen_flags + i);
+    my_prefix = __ldg(prefix_hash + i);
+    const int rf = (my_flags & NBG_GEN_STOPPED) ? 0 : 1, rt = __ldg(in.replicas_to + i);     // NBCTL:434-437
+    if (rt == NBG_REPLICAS_NIL) {
+      reason |= NBG_STS_NILREPLICAS;
+    } else if (rf != rt) {
+      reason |= NBG_STS_REPLICAS;
+      if (__ldg(in.tmpl_from + i) != __ldg(in.tmpl_to + i)) reason |= NBG_STS_TMPL_LABELS;
+    }
+    if (live_map_differs(in.labels_from.ent, __ldg(in.labels_from.off + i) - lf_base, end_at(in.labels_from, i) - lf_base,
+                         in.labels_to.ent, __ldg(in.labels_to.off + i) - lt_base, end_at(in.labels_to, i) - lt_base))
+      reason |= NBG_STS_LABELS;
+    // the desired StatefulSet has no annotations (NBCTL:439-443): any live one with a non-empty value differs
+    for (unsigned t = __ldg(in.ann_to.off + i) - at_base, e = end_at(in.ann_to, i) - at_base; t < e; ++t)
+      if (ld_kv(in.ann_to.ent + t).val != 0ull) reason |= NBG_STS_ANNOTATIONS;
+  }
+  const uint4* pf = reinterpret_cast<const uint4*>(in.pod_from) + base * kPodVec + lane;
+  const uint4* pt = reinterpret_cast<const uint4*>(in.pod_to) + base * kPodVec + lane;
+  unsigned pod_bits = 0;
+  for (unsigned o = 0; o < cnt; ++o) {
+    uint4 a[kPodVecPerLane], b[kPodVecPerLane];
+#pragma unroll
+    for (int v = 0; v < kPodVecPerLane; ++v) {
+      a[v] = ld_stream(pf + (o * kPodVec) + v * 32);
+      b[v] = ld_stream(pt + (o * kPodVec) + v * 32);
+    }
+    generate_sts_tile(a, lane, __shfl_sync(FULL, my_flags, o), __shfl_sync(FULL, my_prefix, o), k);
+    unsigned d = 0;
+#pragma unroll
+    for (int v = 0; v < kPodVecPerLane; ++v) d |= diff4(a[v], b[v]);
+    if (__any_sync(FULL, d != 0)) pod_bits |= 1u << o;
+  }
+  if ((pod_bits >> lane) & 1u) reason |= NBG_STS_PODSPEC;
+  store_results(base, n, lane, reason, (reason & NBG_STS_UPDATE_MASK) != 0, reason_out, bitmap_half);
+}
+
 // ------------------------------------------------ StatefulSet, sparse tiles
 // Same predicate, PodSpec tiles stored as (192-bit mask, packed non-zero slots).
 // Lane j compares object j's masks itself (2 x 24 B); objects whose masks agree
@@ -819,6 +924,21 @@ extern "C" cudaError_t nbg_launch_diff_sts(const nbg_sts_batch* in, unsigned lon
   const unsigned long long grid = (n + block - 1) / block;
   nbg::diff_sts_kernel<<<(unsigned)grid, block, 0, stream>>>(
       *in, n, bases[0], bases[1], bases[2], bases[3], deployment ? 1u : 0u, reason, reinterpret_cast<uint32_t*>(bitmap));
+  return cudaGetLastError();
+}
+
+extern "C" cudaError_t nbg_launch_diff_sts_gen(const nbg_sts_batch* in, const uint64_t* prefix_hash, const uint8_t* gen_flags,
+                                               const nbg_sts_gen_consts* consts, unsigned long long n,
+                                               const unsigned* bases /*3: labels_from, labels_to, ann_to*/, uint8_t* reason,
+                                               uint64_t* bitmap, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  nbg::StsGenConsts k;
+  k.working_dir = consts->working_dir; k.port_name = consts->port_name; k.port_rest = consts->port_rest;
+  k.env_name = consts->env_name; k.add_fsgroup = consts->add_fsgroup;
+  const unsigned block = 128;
+  nbg::diff_sts_gen_kernel<<<(unsigned)((n + block - 1) / block), block, 0, stream>>>(
+      *in, reinterpret_cast<const unsigned long long*>(prefix_hash), gen_flags, k, n, bases[0], bases[1], bases[2], reason,
+      reinterpret_cast<uint32_t*>(bitmap));
   return cudaGetLastError();
 }
 

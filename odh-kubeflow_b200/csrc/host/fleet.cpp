@@ -94,6 +94,53 @@ void StsBatch::add(const GVal& from, const GVal& to) {
   sparsify_tile(tile_to, mask_to, val_to, voff_to);
   ++n;
 }
+bool StsBatch::add_gen(const GVal& nb, const GVal& to, const BuilderEnv& env) {
+  const GVal& meta = field(nb, "metadata");
+  const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
+  const GVal& pod = path(nb, {"spec", "template", "spec"});
+  const GVal& conts = field(pod, "containers");
+  if (name.size() > 52 || conts.kind != GVal::List || conts.items.empty()) return false;
+  if (lean) return false;                                  // the generator works on dense tiles
+  const GVal& nb_ann = field(meta, "annotations");
+  const bool stopped = nb_ann.kind == GVal::Map && nb_ann.has("kubeflow-resource-stopped");   // NBCTL:434-437
+  const GVal& nb_labels = field(meta, "labels");
+  GVal tmpl = GVal::map();                                 // NBCTL:462-466,480-483
+  tmpl.set("statefulset", GVal::str(name));
+  tmpl.set("notebook-name", GVal::str(name));
+  tmpl.set("opendatahub.io/workbenches", GVal::str("true"));
+  GVal labels = GVal::map();                               // NBCTL:442,474-477: a copy, non-nil even when empty
+  if (nb_labels.kind == GVal::Map)
+    for (const auto& e : nb_labels.kv) { tmpl.set(e.first, e.second); labels.set(e.first, e.second); }
+  const GVal& env0 = field(conts.items[0], "env");
+  const bool too_long = env0.kind == GVal::List && env0.items.size() >= 14;   // the tile names 14 variables at most
+  uint64_t tile_from[NBG_POD_SLOTS], tile_to[NBG_POD_SLOTS];
+  if (too_long) {
+    GVal ss;
+    std::string err;
+    if (!generate_statefulset(nb, env, &ss, &err)) return false;
+    pack_podspec(path(ss, {"spec", "template", "spec"}), tile_from);
+  } else {
+    pack_podspec(pod, tile_from);
+  }
+  pack_podspec(path(to, {"spec", "template", "spec"}), tile_to);
+  const GVal& rt = path(to, {"spec", "replicas"});
+  replicas_from.push_back(stopped ? 0 : 1);
+  replicas_to.push_back((rt.kind == GVal::Ptr && !rt.items.empty()) ? (int32_t)rt.items[0].i : NBG_REPLICAS_NIL);
+  tmpl_from.push_back(digest_string_map(tmpl));
+  tmpl_to.push_back(digest_string_map(path(to, {"spec", "template", "metadata", "labels"})));
+  pod_from.insert(pod_from.end(), tile_from, tile_from + NBG_POD_SLOTS);
+  pod_to.insert(pod_to.end(), tile_to, tile_to + NBG_POD_SLOTS);
+  labels_from.add(labels);
+  labels_to.add(path(to, {"metadata", "labels"}));
+  ann_from.add(GVal());                                    // the desired StatefulSet has no annotations (NBCTL:439-443)
+  ann_to.add(path(to, {"metadata", "annotations"}));
+  sparsify_tile(tile_from, mask_from, val_from, voff_from);   // kept consistent; the sparse form of a gen batch is the Notebook's tile too
+  sparsify_tile(tile_to, mask_to, val_to, voff_to);
+  prefix_hash.push_back(hash_str("/notebook/" + ns + "/" + name));
+  gen_flags.push_back((uint8_t)((stopped ? NBG_GEN_STOPPED : 0) | (too_long ? NBG_GEN_PREPATCHED : 0)));
+  ++n;
+  return true;
+}
 void StsBatch::append(const StsBatch& o) {
   {
     const uint32_t bf = (uint32_t)val_from.size(), bt = (uint32_t)val_to.size();

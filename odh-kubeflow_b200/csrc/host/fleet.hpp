@@ -51,7 +51,13 @@ struct StsBatch {
   // lean: keep only the sparse form of the PodSpec tiles (what the step reads).  A 10 M-notebook batch then
   // costs 0.78 KB per pair on the host instead of 3.9 KB; view() of a lean batch has no dense tiles.
   bool lean = false;
+  // generateStatefulSet on the device (nbg_diff_sts_gen): per-notebook inputs of the generator; filled by add_gen only
+  std::vector<uint64_t> prefix_hash;
+  std::vector<uint8_t> gen_flags;
   void add(const GVal& from, const GVal& to);
+  // the `from` side taken from the NOTEBOOK (its own PodSpec tile, its labels); false when generateStatefulSet would
+  // fail or take its generateName branch (no containers, name longer than 52 characters)
+  bool add_gen(const GVal& notebook, const GVal& to, const BuilderEnv& env);
   void append(const StsBatch& o);
   nbg_sts_batch view() const;
   nbg_sts_sparse_batch view_sparse() const;

@@ -683,6 +683,49 @@ NBH_API int nbh_pack_objects(const nbh_obj* const* objs, uint64_t m, int lean, n
   if (vs) { nbh_vs* o = new nbh_vs(); for (auto& b : pw) { o->b.append(b); b = VsBatch(); } *vs = o; }
   return 0;
 }
+// ---- generateStatefulSet on the device: the batch's `from` side from the Notebook itself (nbg_diff_sts_gen)
+NBH_API int nbh_sts_add_gen(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* to, const nbh_env* env) {
+  if (!b || !notebook || !to) return -1;
+  BuilderEnv e;
+  if (env) {
+    e.add_fsgroup = env->add_fsgroup != 0;
+    if (env->cluster_domain) e.cluster_domain = env->cluster_domain;
+    if (env->istio_host && *env->istio_host) e.istio_host = env->istio_host;
+    if (env->istio_gateway && *env->istio_gateway) e.istio_gateway = env->istio_gateway;
+  }
+  return b->b.add_gen(notebook->v, to->v, e) ? 0 : -1;
+}
+NBH_API uint64_t nbh_sts_view_gen(const nbh_sts* b, nbg_sts_gen_inputs* out) {
+  if (!b || !out || b->b.prefix_hash.size() != b->b.n) return 0;
+  out->prefix_hash = b->b.prefix_hash.data();
+  out->flags = b->b.gen_flags.data();
+  return b->b.n;
+}
+NBH_API int nbh_sts_gen_consts(const nbh_env* env, nbg_sts_gen_consts* out) {
+  if (!out) return -1;
+  // the default port exactly as generateStatefulSet builds it (NBCTL:499-505), through the packer itself
+  GVal port = GVal::strct();
+  port.set("containerPort", GVal::integer(8888));
+  port.set("name", GVal::str("notebook-port"));
+  port.set("protocol", GVal::str("TCP"));
+  GVal ports = GVal::list();
+  ports.items.push_back(std::move(port));
+  GVal c = GVal::strct();
+  c.set("ports", std::move(ports));
+  GVal conts = GVal::list();
+  conts.items.push_back(std::move(c));
+  GVal pod = GVal::strct();
+  pod.set("containers", std::move(conts));
+  uint64_t tile[NBG_POD_SLOTS];
+  pack_podspec(pod, tile);
+  out->working_dir = nbg_hash_bytes("/home/jovyan", 12);
+  out->port_name = tile[52];                               // containers[0].ports[0]: name, then the digest of the rest
+  out->port_rest = tile[53];
+  out->env_name = nbg_hash_bytes("NB_PREFIX", 9);
+  out->add_fsgroup = (!env || env->add_fsgroup) ? 1u : 0u;
+  out->pad = 0;
+  return 0;
+}
 NBH_API int nbh_sts_is_lean(const nbh_sts* b) { return b && b->b.lean ? 1 : 0; }
 
 // Namespace table of the fleet: ns_hash[k] = nbg_hash64 of namespace k's name, ns_size[k] = notebooks in it.

@@ -86,6 +86,13 @@ class DeviceBatch:
                 self._consts = _host.vs_gen_consts()
             rc = lib.nbg_diff_vs_gen_device(ctx.handle, di, C.byref(self._struct), C.byref(self._consts), self.n, o[0], o[1],
                                             C.c_void_p(stream))
+        elif self.kind == "sts_gen":
+            if not hasattr(self, "_consts"):
+                self._consts = host.sts_gen_consts()
+                self._gen = N.nbg_sts_gen_inputs(C.cast(self.tensors["gen.prefix_hash"].data_ptr(), N.u64p),
+                                                 C.cast(self.tensors["gen.flags"].data_ptr(), N.u8p))
+            rc = lib.nbg_diff_sts_gen_device(ctx.handle, di, C.byref(self._struct), C.byref(self._gen), C.byref(self._consts),
+                                             self.n, o[0], o[1], C.c_void_p(stream))
         elif self.kind == "GenBatch":
             rc = lib.nbg_diff_generic_device(ctx.handle, di, C.byref(self._struct), self.n, self.mode, o[0], o[1], C.c_void_p(stream))
         elif self.kind == "RestartBatch":

@@ -94,6 +94,19 @@ class Context:
         """Batched CopyStatefulSetFields (COMMON:107-134) + NBCTL:188-194."""
         return self._diff(self._lib.nbg_diff_sts, batch, allow_nil)
 
+    def diff_sts_gen(self, batch, consts, allow_nil=False):
+        """CopyStatefulSetFields against a desired StatefulSet generated on the device from the Notebook
+        (batch = a host.StsBatch filled with add_gen; consts = host.sts_gen_consts())."""
+        view, gen = batch.view, batch.gen_inputs
+        n = batch.n
+        reason = np.zeros(n, dtype=np.uint8)
+        bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+        rc = self._lib.nbg_diff_sts_gen(self._h, C.byref(view), C.byref(gen), C.byref(consts), n,
+                                        reason.ctypes.data_as(C.c_void_p), bitmap.ctypes.data_as(C.c_void_p))
+        if not (allow_nil and rc == N.NBG_E_NILREPLICAS):
+            _check(rc, "nbg_diff_sts_gen")
+        return reason, bitmap
+
     def diff_deploy(self, batch):
         """Batched CopyDeploymentSetFields (COMMON:136-163) on a StsBatch of Deployment pairs: Replicas compared as
         pointers (different unless both nil), no panic, no template-label pre-step."""

@@ -246,6 +246,54 @@ class StsBatch(_Batch):
         """The same pairs with sparsely stored PodSpec tiles (include/nbgraft.h: nbg_sts_sparse_batch)."""
         return StsSparseBatch(self)
 
+    def add_gen(self, notebook, to, env=None):
+        """Append a pair whose desired side will be generated ON THE DEVICE from the Notebook (nbg_diff_sts_gen):
+        the batch then holds the Notebook's own PodSpec tile and labels instead of a generated StatefulSet's."""
+        if N.nbh().nbh_sts_add_gen(self._h, notebook._h, to._h, _env(env)) != 0:
+            raise HostError("add_gen: generateStatefulSet would fail or leave its common path for this Notebook")
+        return self
+
+    @property
+    def gen_inputs(self):
+        g = N.nbg_sts_gen_inputs()
+        n = int(N.nbh().nbh_sts_view_gen(self._h, C.byref(g)))
+        if n != len(self):
+            raise HostError("not a batch filled with add_gen")
+        return g
+
+
+class StsGenView:
+    """Non-owning view of a StsBatch filled with add_gen: the arrays nbg_diff_sts_gen reads (the Notebook's tile and
+    labels, the live side, one hash and one flag byte per Notebook)."""
+    kind = "sts_gen"
+
+    def __init__(self, parent):
+        self.parent = parent
+        parent.gen_inputs                                   # raises unless it is a gen batch
+
+    def __len__(self):
+        return len(self.parent)
+
+    def arrays(self):
+        a = self.parent.arrays()
+        out = {k: v for k, v in a.items() if k != "replicas_from" and not k.startswith("ann_from")}
+        g, n = self.parent.gen_inputs, len(self.parent)
+        out["gen.prefix_hash"] = _arr(g.prefix_hash, n, np.uint64)
+        out["gen.flags"] = _arr(g.flags, n, np.uint8)
+        return out
+
+    output_bytes = staticmethod(StsBatch.output_bytes)
+
+    def algorithmic_bytes(self):
+        return sum(a.nbytes for a in self.arrays().values()) + self.output_bytes(len(self))
+
+
+def sts_gen_consts(env=None):
+    c = N.nbg_sts_gen_consts()
+    if N.nbh().nbh_sts_gen_consts(_env(env), C.byref(c)) != 0:
+        raise HostError("sts_gen_consts")
+    return c
+
 
 class StsSparseBatch:
     """Non-owning sparse view of a StsBatch (keeps the parent alive)."""

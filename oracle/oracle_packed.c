@@ -265,6 +265,52 @@ ORC_API void orc2_diff_deploy(const nbg_sts_batch* in, uint64_t n, uint8_t* reas
     set_bit(bitmap, i, (r & NBG_STS_UPDATE_MASK) != 0);
   }
 }
+/* generateStatefulSet as a patch of the Notebook's dense PodSpec tile (notebook_controller.go:433-523; slot layout of
+ * csrc/host/pack.cpp: pod-level slots 0..15, containers[0] at 40: workingDir 42, count tags 46, ports 52.., env 56..).
+ * Written for the tile as a plain array, one slot at a time — not the way the kernel splits it over lanes. */
+ORC_API void orc2_generate_sts_tile(const uint64_t* nb_tile, uint64_t prefix_hash, unsigned flags,
+                                    const nbg_sts_gen_consts* k, uint64_t* out) {
+  memcpy(out, nb_tile, NBG_POD_SLOTS * 8);
+  if (flags & NBG_GEN_PREPATCHED) return;                     /* the host generated it */
+  if (out[42] == 0) out[42] = k->working_dir;                  /* :495-497 */
+  uint64_t tag = out[46];
+  unsigned ports = (unsigned)(tag & 0xFFFF), env = (unsigned)((tag >> 16) & 0xFFFF);
+  if (ports == 0xFFFF) {                                       /* :498-506: nil, not merely empty */
+    out[52] = k->port_name; out[53] = k->port_rest;
+    ports = 1;
+  }
+  const unsigned env_n = env == 0xFFFF ? 0 : env;
+  int found = 0;                                               /* :417-431: an existing NB_PREFIX is left alone */
+  for (unsigned e = 0; e < env_n && e < 14; ++e) found |= out[56 + 2 * e] == k->env_name;
+  if (!found && env_n < 14) {
+    out[56 + 2 * env_n] = k->env_name;
+    out[57 + 2 * env_n] = prefix_hash;
+    env = env_n + 1;
+  }
+  out[46] = (tag & ~0xFFFFFFFFull) | ports | ((uint64_t)env << 16);
+  if (k->add_fsgroup && !(out[14] & 2)) {                      /* :514-521: securityContext == nil */
+    out[7] = 100;
+    out[9] = 0;                                                /* the rest of &PodSecurityContext{FSGroup: &g}: empty (a nil pointer has a marker there) */
+    out[14] |= 6;
+  }
+}
+ORC_API void orc2_diff_sts_gen(const nbg_sts_batch* in, const nbg_sts_gen_inputs* gen, const nbg_sts_gen_consts* k, uint64_t n,
+                               uint8_t* reason, uint64_t* bitmap) {
+  uint64_t want[NBG_POD_SLOTS];
+  for (uint64_t i = 0; i < n; ++i) {
+    unsigned r = 0;
+    const int rf = (gen->flags[i] & NBG_GEN_STOPPED) ? 0 : 1, rt = in->replicas_to[i];
+    if (rt == NBG_REPLICAS_NIL) r |= NBG_STS_NILREPLICAS;
+    else if (rf != rt) { r |= NBG_STS_REPLICAS; if (in->tmpl_from[i] != in->tmpl_to[i]) r |= NBG_STS_TMPL_LABELS; }
+    if (live_differs(&in->labels_from, &in->labels_to, i)) r |= NBG_STS_LABELS;
+    for (uint32_t t = in->ann_to.off[i]; t < in->ann_to.off[i + 1]; ++t)
+      if (in->ann_to.ent[t].val != 0) r |= NBG_STS_ANNOTATIONS;           /* desired has none */
+    orc2_generate_sts_tile(in->pod_from + i * NBG_POD_SLOTS, gen->prefix_hash[i], gen->flags[i], k, want);
+    if (memcmp(want, in->pod_to + i * NBG_POD_SLOTS, NBG_POD_SLOTS * 8) != 0) r |= NBG_STS_PODSPEC;
+    reason[i] = (uint8_t)r;
+    set_bit(bitmap, i, (r & NBG_STS_UPDATE_MASK) != 0);
+  }
+}
 ORC_API double orc2_diff_sts_sparse(const nbg_sts_sparse_batch* in, uint64_t n, int threads, uint8_t* reason, uint64_t* bitmap) {
   return run(4, in, NULL, n, threads, reason, NULL, bitmap, NULL);
 }

@@ -54,6 +54,11 @@ def lib():
             f = getattr(L, name)
             f.argtypes = [C.POINTER(bt), C.c_uint64, C.c_int, vp, vp]
             f.restype = C.c_double
+        L.orc2_generate_sts_tile.argtypes = [vp, C.c_uint64, C.c_uint, C.POINTER(N.nbg_sts_gen_consts), vp]
+        L.orc2_generate_sts_tile.restype = None
+        L.orc2_diff_sts_gen.argtypes = [C.POINTER(N.nbg_sts_batch), C.POINTER(N.nbg_sts_gen_inputs), C.POINTER(N.nbg_sts_gen_consts),
+                                        C.c_uint64, vp, vp]
+        L.orc2_diff_sts_gen.restype = None
         L.orc_counts_as_running.argtypes = [vp]
         L.orc_semantic_equal.argtypes = [vp, vp]
         L.orc_restart_block.argtypes = [vp, vp, vp, C.c_int]
@@ -196,6 +201,25 @@ def packed_diff_sts(batch, threads=1):
 
 def packed_diff_sts_sparse(batch, threads=1):
     return _diff2(lib().orc2_diff_sts_sparse, batch, threads)
+
+
+def generate_sts_tile(nb_tile, prefix_hash, flags, consts):
+    """The packed oracle's generateStatefulSet: the Notebook's dense PodSpec tile -> the desired StatefulSet's."""
+    nb_tile = np.ascontiguousarray(nb_tile, dtype=np.uint64)
+    out = np.zeros(N.NBG_POD_SLOTS, np.uint64)
+    lib().orc2_generate_sts_tile(nb_tile.ctypes.data_as(C.c_void_p), int(prefix_hash), int(flags), C.byref(consts),
+                                 out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def packed_diff_sts_gen(batch, consts):
+    view, gen = batch.view, batch.gen_inputs
+    n = batch.n
+    reason = np.zeros(n, dtype=np.uint8)
+    bitmap = np.zeros((n + 63) // 64, dtype=np.uint64)
+    lib().orc2_diff_sts_gen(C.byref(view), C.byref(gen), C.byref(consts), n, reason.ctypes.data_as(C.c_void_p),
+                            bitmap.ctypes.data_as(C.c_void_p))
+    return reason, bitmap
 
 
 def packed_diff_svc(batch, threads=1):
