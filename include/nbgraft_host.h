@@ -109,6 +109,11 @@ uint64_t nbh_sts_view(const nbh_sts* b, nbg_sts_batch* out);   /* returns n; poi
 int nbh_sts_add_gen(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* to, const nbh_env* env /*NULL = defaults*/);
 uint64_t nbh_sts_view_gen(const nbh_sts* b, nbg_sts_gen_inputs* out);
 int nbh_sts_gen_consts(const nbh_env* env /*NULL = defaults*/, nbg_sts_gen_consts* out);
+/* For the sparse step (nbg_diff_sts_sparse, nbg_step): the pair nbh_sts_add(generateStatefulSet(notebook), to) would
+ * append, array for array, WITHOUT building the StatefulSet - the Notebook's PodSpec is packed once and the desired
+ * tile made from it on the host with the same few slot edits the kernel above makes (notebook_controller.go:495-521).
+ * Works on lean batches; not to be mixed with nbh_sts_add_gen in one batch.  -1 as nbh_sts_add_gen. */
+int nbh_sts_add_notebook(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* to, const nbh_env* env /*NULL = defaults*/);
 
 /* the same pairs with sparsely stored PodSpec tiles (nbg_diff_sts_sparse) */
 uint64_t nbh_sts_view_sparse(const nbh_sts* b, nbg_sts_sparse_batch* out);

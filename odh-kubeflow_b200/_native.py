@@ -408,6 +408,7 @@ def _bind_nbh(lib):
         "nbh_fleet_pack_lean": ([_vp, u64p, C.c_uint64, C.c_uint64, P(_vp), P(_vp), P(_vp)], C.c_int),
         "nbh_sts_is_lean": ([_vp], C.c_int),
         "nbh_sts_add_gen": ([_vp, _vp, _vp, _vp], C.c_int),
+        "nbh_sts_add_notebook": ([_vp, _vp, _vp, _vp], C.c_int),
         "nbh_sts_view_gen": ([_vp, P(nbg_sts_gen_inputs)], C.c_uint64),
         "nbh_sts_gen_consts": ([_vp, P(nbg_sts_gen_consts)], C.c_int),
         "nbh_pack_objects": ([P(_vp), C.c_uint64, C.c_int, P(_vp), P(_vp), P(_vp)], C.c_int),
@@ -439,7 +440,7 @@ NBH_SYMBOLS = [
     "nbh_svc_view", "nbh_svc_view_gen", "nbh_vs_view_gen", "nbh_vs_gen_consts", "nbh_vs_new", "nbh_vs_free", "nbh_vs_add", "nbh_vs_view", "nbh_gen_new", "nbh_gen_free", "nbh_gen_add", "nbh_gen_view", "nbh_rb_new", "nbh_rb_free", "nbh_rb_add", "nbh_rb_view", "nbh_obj_clone", "nbh_cull_new", "nbh_cull_free",
     "nbh_cull_add_json", "nbh_cull_view", "nbh_cull_records", "nbh_cull_new_last_activity", "nbh_parse_rfc3339",
     "nbh_format_rfc3339", "nbh_parse_records", "nbh_fleet_new", "nbh_fleet_free", "nbh_fleet_get", "nbh_fleet_drift_class",
-    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_lean", "nbh_sts_is_lean", "nbh_pack_objects", "nbh_sts_add_gen", "nbh_sts_view_gen", "nbh_sts_gen_consts", "nbh_fleet_ns_table", "nbh_fleet_shard_indices_by_table", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
+    "nbh_apply_sts_fields", "nbh_apply_svc_fields", "nbh_apply_vs_fields", "nbh_fleet_ns_hash", "nbh_fleet_pack", "nbh_fleet_pack_lean", "nbh_sts_is_lean", "nbh_pack_objects", "nbh_sts_add_gen", "nbh_sts_add_notebook", "nbh_sts_view_gen", "nbh_sts_gen_consts", "nbh_fleet_ns_table", "nbh_fleet_shard_indices_by_table", "nbh_fleet_pack_timing", "nbh_cullfleet_new", "nbh_cullfleet_free", "nbh_cullfleet_json",
     "nbh_cullfleet_pack", "nbh_threads", "nbh_fleet_shard_indices", "nbh_fleet_objects",
     "nbh_join_key_owner", "nbh_join_key_controlled", "nbh_fleet_join_lists",
 ]

@@ -94,25 +94,42 @@ void StsBatch::add(const GVal& from, const GVal& to) {
   sparsify_tile(tile_to, mask_to, val_to, voff_to);
   ++n;
 }
-bool StsBatch::add_gen(const GVal& nb, const GVal& to, const BuilderEnv& env) {
+// The part of generateStatefulSet that is not the PodSpec (NBCTL:434-437,442,462-483), from the Notebook alone.
+namespace {
+struct NotebookSide {
+  bool ok = false, stopped = false;
+  const GVal* pod = nullptr;
+  const GVal* env0 = nullptr;
+  std::string prefix;
+  GVal labels = GVal::map(), tmpl = GVal::map();
+};
+NotebookSide notebook_side(const GVal& nb) {
+  NotebookSide r;
   const GVal& meta = field(nb, "metadata");
   const std::string name = meta.get_str("name"), ns = meta.get_str("namespace");
-  const GVal& pod = path(nb, {"spec", "template", "spec"});
-  const GVal& conts = field(pod, "containers");
-  if (name.size() > 52 || conts.kind != GVal::List || conts.items.empty()) return false;
-  if (lean) return false;                                  // the generator works on dense tiles
+  r.pod = &path(nb, {"spec", "template", "spec"});
+  const GVal& conts = field(*r.pod, "containers");
+  if (name.size() > 52 || conts.kind != GVal::List || conts.items.empty()) return r;
+  r.env0 = &field(conts.items[0], "env");
   const GVal& nb_ann = field(meta, "annotations");
-  const bool stopped = nb_ann.kind == GVal::Map && nb_ann.has("kubeflow-resource-stopped");   // NBCTL:434-437
-  const GVal& nb_labels = field(meta, "labels");
-  GVal tmpl = GVal::map();                                 // NBCTL:462-466,480-483
-  tmpl.set("statefulset", GVal::str(name));
-  tmpl.set("notebook-name", GVal::str(name));
-  tmpl.set("opendatahub.io/workbenches", GVal::str("true"));
-  GVal labels = GVal::map();                               // NBCTL:442,474-477: a copy, non-nil even when empty
+  r.stopped = nb_ann.kind == GVal::Map && nb_ann.has("kubeflow-resource-stopped");   // NBCTL:434-437
+  r.tmpl.set("statefulset", GVal::str(name));                                        // NBCTL:462-466,480-483
+  r.tmpl.set("notebook-name", GVal::str(name));
+  r.tmpl.set("opendatahub.io/workbenches", GVal::str("true"));
+  const GVal& nb_labels = field(meta, "labels");                                     // NBCTL:442,474-477: a copy, non-nil even when empty
   if (nb_labels.kind == GVal::Map)
-    for (const auto& e : nb_labels.kv) { tmpl.set(e.first, e.second); labels.set(e.first, e.second); }
-  const GVal& env0 = field(conts.items[0], "env");
-  const bool too_long = env0.kind == GVal::List && env0.items.size() >= 14;   // the tile names 14 variables at most
+    for (const auto& e : nb_labels.kv) { r.tmpl.set(e.first, e.second); r.labels.set(e.first, e.second); }
+  r.prefix = "/notebook/" + ns + "/" + name;
+  r.ok = true;
+  return r;
+}
+}  // namespace
+
+bool StsBatch::add_gen(const GVal& nb, const GVal& to, const BuilderEnv& env) {
+  if (lean) return false;                                  // the generator works on dense tiles
+  const NotebookSide side = notebook_side(nb);
+  if (!side.ok) return false;
+  const bool too_long = side.env0->kind == GVal::List && side.env0->items.size() >= 14;   // the tile names 14 variables at most
   uint64_t tile_from[NBG_POD_SLOTS], tile_to[NBG_POD_SLOTS];
   if (too_long) {
     GVal ss;
@@ -120,24 +137,55 @@ bool StsBatch::add_gen(const GVal& nb, const GVal& to, const BuilderEnv& env) {
     if (!generate_statefulset(nb, env, &ss, &err)) return false;
     pack_podspec(path(ss, {"spec", "template", "spec"}), tile_from);
   } else {
-    pack_podspec(pod, tile_from);
+    pack_podspec(*side.pod, tile_from);
   }
   pack_podspec(path(to, {"spec", "template", "spec"}), tile_to);
   const GVal& rt = path(to, {"spec", "replicas"});
-  replicas_from.push_back(stopped ? 0 : 1);
+  replicas_from.push_back(side.stopped ? 0 : 1);
   replicas_to.push_back((rt.kind == GVal::Ptr && !rt.items.empty()) ? (int32_t)rt.items[0].i : NBG_REPLICAS_NIL);
-  tmpl_from.push_back(digest_string_map(tmpl));
+  tmpl_from.push_back(digest_string_map(side.tmpl));
   tmpl_to.push_back(digest_string_map(path(to, {"spec", "template", "metadata", "labels"})));
   pod_from.insert(pod_from.end(), tile_from, tile_from + NBG_POD_SLOTS);
   pod_to.insert(pod_to.end(), tile_to, tile_to + NBG_POD_SLOTS);
-  labels_from.add(labels);
+  labels_from.add(side.labels);
   labels_to.add(path(to, {"metadata", "labels"}));
   ann_from.add(GVal());                                    // the desired StatefulSet has no annotations (NBCTL:439-443)
   ann_to.add(path(to, {"metadata", "annotations"}));
   sparsify_tile(tile_from, mask_from, val_from, voff_from);   // kept consistent; the sparse form of a gen batch is the Notebook's tile too
   sparsify_tile(tile_to, mask_to, val_to, voff_to);
-  prefix_hash.push_back(hash_str("/notebook/" + ns + "/" + name));
-  gen_flags.push_back((uint8_t)((stopped ? NBG_GEN_STOPPED : 0) | (too_long ? NBG_GEN_PREPATCHED : 0)));
+  prefix_hash.push_back(hash_str(side.prefix));
+  gen_flags.push_back((uint8_t)((side.stopped ? NBG_GEN_STOPPED : 0) | (too_long ? NBG_GEN_PREPATCHED : 0)));
+  ++n;
+  return true;
+}
+bool StsBatch::add_notebook(const GVal& nb, const GVal& to, const BuilderEnv& env) {
+  if (!prefix_hash.empty()) return false;                  // not into a batch add_gen has filled
+  const NotebookSide side = notebook_side(nb);
+  if (!side.ok) return false;
+  uint64_t tile_from[NBG_POD_SLOTS], tile_to[NBG_POD_SLOTS];
+  pack_podspec(*side.pod, tile_from);
+  if (!patch_statefulset_tile(tile_from, hash_str(side.prefix), env.add_fsgroup)) {
+    GVal ss;                                               // an env the tile cannot decide: build the object after all
+    std::string err;
+    if (!generate_statefulset(nb, env, &ss, &err)) return false;
+    pack_podspec(path(ss, {"spec", "template", "spec"}), tile_from);
+  }
+  pack_podspec(path(to, {"spec", "template", "spec"}), tile_to);
+  const GVal& rt = path(to, {"spec", "replicas"});
+  replicas_from.push_back(side.stopped ? 0 : 1);
+  replicas_to.push_back((rt.kind == GVal::Ptr && !rt.items.empty()) ? (int32_t)rt.items[0].i : NBG_REPLICAS_NIL);
+  tmpl_from.push_back(digest_string_map(side.tmpl));
+  tmpl_to.push_back(digest_string_map(path(to, {"spec", "template", "metadata", "labels"})));
+  if (!lean) {
+    pod_from.insert(pod_from.end(), tile_from, tile_from + NBG_POD_SLOTS);
+    pod_to.insert(pod_to.end(), tile_to, tile_to + NBG_POD_SLOTS);
+  }
+  labels_from.add(side.labels);
+  labels_to.add(path(to, {"metadata", "labels"}));
+  ann_from.add(GVal());
+  ann_to.add(path(to, {"metadata", "annotations"}));
+  sparsify_tile(tile_from, mask_from, val_from, voff_from);
+  sparsify_tile(tile_to, mask_to, val_to, voff_to);
   ++n;
   return true;
 }

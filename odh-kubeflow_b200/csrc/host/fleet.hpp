@@ -58,6 +58,9 @@ struct StsBatch {
   // the `from` side taken from the NOTEBOOK (its own PodSpec tile, its labels); false when generateStatefulSet would
   // fail or take its generateName branch (no containers, name longer than 52 characters)
   bool add_gen(const GVal& notebook, const GVal& to, const BuilderEnv& env);
+  // the same pair as add(generate_statefulset(notebook), to), array for array, without building the StatefulSet:
+  // the desired tile is the Notebook's tile patched on the host (patch_statefulset_tile).  Works on lean batches.
+  bool add_notebook(const GVal& notebook, const GVal& to, const BuilderEnv& env);
   void append(const StsBatch& o);
   nbg_sts_batch view() const;
   nbg_sts_sparse_batch view_sparse() const;

@@ -695,6 +695,12 @@ NBH_API int nbh_sts_add_gen(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* 
   }
   return b->b.add_gen(notebook->v, to->v, e) ? 0 : -1;
 }
+NBH_API int nbh_sts_add_notebook(nbh_sts* b, const nbh_obj* notebook, const nbh_obj* to, const nbh_env* env) {
+  if (!b || !notebook || !to) return -1;
+  BuilderEnv e;
+  if (env) e.add_fsgroup = env->add_fsgroup != 0;
+  return b->b.add_notebook(notebook->v, to->v, e) ? 0 : -1;
+}
 NBH_API uint64_t nbh_sts_view_gen(const nbh_sts* b, nbg_sts_gen_inputs* out) {
   if (!b || !out || b->b.prefix_hash.size() != b->b.n) return 0;
   out->prefix_hash = b->b.prefix_hash.data();

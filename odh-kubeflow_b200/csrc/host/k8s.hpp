@@ -73,6 +73,8 @@ void pack_kvmap(const GVal& m, std::vector<nbg_kv>* out);   // sorted by key has
 // two flattened vectors are equal  <=>  reflect.DeepEqual of the trees (NBG_GEN_DEEPEQUAL).
 void flatten_tree(const GVal& v, std::vector<nbg_kv>* out);
 void pack_podspec(const GVal& podspec, uint64_t* slots /*NBG_POD_SLOTS*/);
+// the Notebook's PodSpec tile -> the tile of the StatefulSet generateStatefulSet makes from it (NBCTL:495-521)
+bool patch_statefulset_tile(uint64_t* slots, uint64_t prefix_hash, bool add_fsgroup);
 // The tree as apimachinery's equality.Semantic.DeepEqual sees it: nil and empty slices/maps are
 // the same, a Quantity is its number.  pack_podspec(semantic_canon(x)) tiles are equal
 // <=> equality.Semantic.DeepEqual(x, y)  (ODHWH:547-563).

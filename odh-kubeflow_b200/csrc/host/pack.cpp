@@ -352,6 +352,41 @@ void pack_podspec(const GVal& pod, uint64_t* s) {
   s[15] = h;
 }
 
+// generateStatefulSet's edits of the PodSpec (NBCTL:495-521), applied to the Notebook's own tile: what the desired
+// StatefulSet's tile is, without building the StatefulSet.  False when the tile cannot tell (env longer than the
+// tile names, so an NB_PREFIX beyond it would go unseen) - the caller then builds and packs the object.
+bool patch_statefulset_tile(uint64_t* s, uint64_t prefix_hash, bool add_fsgroup) {
+  static const uint64_t kWorkingDir = hash_str("/home/jovyan"), kEnvName = hash_str("NB_PREFIX");
+  static const struct DefaultPort { uint64_t name, rest; DefaultPort() {
+    GVal port = GVal::strct();
+    port.set("containerPort", GVal::integer(8888));
+    port.set("name", GVal::str("notebook-port"));
+    port.set("protocol", GVal::str("TCP"));
+    name = str_of(port, "name");
+    rest = digest_without(port, {"name"});
+  } } kPort;
+  uint64_t* c = s + kContBase;                    // containers[0]
+  uint64_t* ports = c + 12;
+  uint64_t* env = ports + 2 * kMaxPorts;
+  const uint64_t tags = c[6];
+  uint64_t n_ports = tags & 0xFFFF, n_env = (tags >> 16) & 0xFFFF;
+  const bool env_nil = n_env == 0xFFFF;
+  const uint64_t have = env_nil ? 0 : n_env;
+  if (have >= (uint64_t)kMaxEnv) return false;
+  if (c[2] == 0) c[2] = kWorkingDir;
+  if (n_ports == 0xFFFF) { ports[0] = kPort.name; ports[1] = kPort.rest; n_ports = 1; }
+  bool there = false;
+  for (uint64_t e = 0; e < have; ++e) there = there || env[2 * e] == kEnvName;
+  if (!there) { env[2 * have] = kEnvName; env[2 * have + 1] = prefix_hash; n_env = have + 1; }
+  c[6] = (tags & ~0xFFFFFFFFull) | n_ports | (n_env << 16);
+  if (add_fsgroup && !(s[14] & 2)) {              // no securityContext: &PodSecurityContext{FSGroup: &100}
+    s[7] = 100;
+    s[9] = 0;                                     // nothing else in it
+    s[14] |= 2 | 4;
+  }
+  return true;
+}
+
 void pack_service_ports(const GVal& ports, uint64_t* s) {
   memset(s, 0, NBG_SVC_SLOTS * sizeof(uint64_t));
   for (int k = 0; k < 2; ++k) {

@@ -253,6 +253,13 @@ class StsBatch(_Batch):
             raise HostError("add_gen: generateStatefulSet would fail or leave its common path for this Notebook")
         return self
 
+    def add_notebook(self, notebook, to, env=None):
+        """Append the pair add(generate_statefulset(notebook), to) would, without building the StatefulSet: the
+        desired tile is made on the host from the Notebook's own (nbh_sts_add_notebook).  For the sparse step."""
+        if N.nbh().nbh_sts_add_notebook(self._h, notebook._h, to._h, _env(env)) != 0:
+            raise HostError("add_notebook: generateStatefulSet would fail or leave its common path for this Notebook")
+        return self
+
     @property
     def gen_inputs(self):
         g = N.nbg_sts_gen_inputs()

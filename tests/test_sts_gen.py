@@ -96,6 +96,44 @@ def test_oracle_patch_of_the_notebook_tile_is_the_generated_statefulsets_tile(na
         assert np.array_equal(g.arrays()[k], h.arrays()[k]), k
 
 
+@pytest.mark.parametrize("env", ENVS, ids=["default", "no-fsgroup", "fsgroup"])
+def test_host_patched_pairs_are_the_generated_pairs_array_for_array(env):
+    """nbh_sts_add_notebook (the same edits made by the host packer, for the sparse step) against
+    add(generate_statefulset(nb), live): every dense and every sparse array, bit for bit."""
+    a, b = host.StsBatch(), host.StsBatch()
+    other = host.generate_statefulset(host.Notebook(_nb(lambda o: _c0(o).update(image="img:2"))), env)
+    for name, edit in NOTEBOOKS:
+        nb = host.Notebook(_nb(edit))
+        desired = host.generate_statefulset(nb, env)
+        for live in (desired, other):
+            a.add_notebook(nb, live, env)
+            b.add(desired, live)
+    for x, y in ((a, b), (a.sparse(), b.sparse())):
+        xa, ya = x.arrays(), y.arrays()
+        assert xa.keys() == ya.keys()
+        for k in xa:
+            assert np.array_equal(xa[k], ya[k]), k
+    with pytest.raises(host.HostError):
+        host.StsBatch().add_notebook(host.Notebook(_nb(lambda o: _pod(o).update(containers=[]))), other, env)
+    with pytest.raises(host.HostError):                           # one batch, one kind of `from` side
+        host.StsBatch().add_gen(host.Notebook(_nb()), other).add_notebook(host.Notebook(_nb()), other)
+
+
+def test_host_patched_fleet_pairs_in_a_lean_batch():
+    n = 1500
+    fleet = host.Fleet(host.FLEET_ODH, host.SEED_BASE + 49, n, 40)
+    a, b = host.pack_objects([], lean=True)[0], host.StsBatch()
+    assert a.lean and len(a) == 0
+    for i in range(n):
+        nb, live = fleet.get(i, "notebook"), fleet.get(i, "sts_to")
+        a.add_notebook(nb, live)
+        b.add(host.generate_statefulset(nb), live)
+    xa, ya = a.sparse().arrays(), b.sparse().arrays()
+    for k in xa:
+        assert np.array_equal(xa[k], ya[k]), k
+    assert np.array_equal(O.packed_diff_sts_sparse(a.sparse())[0], O.packed_diff_sts(b)[0])
+
+
 def test_flags_say_what_the_host_did():
     g = host.StsBatch()
     for name in ("base", "stopped", "env of 13: the appended one is the tile's last", "env of 14: prepatched on the host"):
