@@ -36,7 +36,7 @@ extern "C" {
 
 /* 3: additions only (nbg_balance_shards, nbg_check_step_device, nbg_store_check); nbg_store_put now refuses a slot
  *    named twice (NBG_E_INVAL) instead of leaving the outcome open.  2: spans (end pointers) in the batch structs. */
-#define NBG_ABI_VERSION 3
+#define NBG_ABI_VERSION 4
 
 /* ---- status codes ------------------------------------------------------ */
 #define NBG_OK              0
@@ -52,7 +52,9 @@ extern "C" {
 
 /* ---- schema constants (frozen; tests/test_abi.py checks them) ---------- */
 #define NBG_POD_SLOTS   192u  /* u64 slots per PodSpec tile  (1536 B per side)   */
-#define NBG_SVC_SLOTS    16u  /* u64 slots per Service ports tile (128 B)        */
+#define NBG_SVC_SLOTS     8u  /* u64 slots per Service ports tile (64 B): ports[0] as six fields (name, protocol,
+                               * appProtocol, port|nodePort<<32, targetPort int|type<<32, digest of the rest), the
+                               * length of the list (0xFFFFFFFF = nil) and one digest of ports[1:] (0 = none) */
 #define NBG_VS_SLOTS      8u  /* u64 slots per VirtualService spec tile (64 B)   */
 #define NBG_REPLICAS_NIL INT32_MIN /* marks a nil *int32 Replicas pointer        */
 #define NBG_ARGMAX_NONE 0xFFFFFFFFu
@@ -294,7 +296,7 @@ uint64_t nbg_join_key(uint64_t ns_hash, uint64_t uid_hash);
  * of a handful of Notebook fields, so their outputs need not be packed and shipped: these two
  * entry points take only those fields for the desired side, synthesise the desired tile in
  * registers and compare it with the live object — identical results to nbg_diff_svc /
- * nbg_diff_vs on (generate*(notebook), live), ~45 % / ~30 % fewer bytes per object.
+ * nbg_diff_vs on (generate*(notebook), live), ~43 % / ~29 % fewer bytes per object.
  * (generateStatefulSet is NOT done this way: its PodSpec is the Notebook's own.) */
 typedef struct nbg_svc_gen_batch {
   const uint64_t* name_hash;     /* n: hash64(notebook name) — selector {"statefulset": name}      */

@@ -140,7 +140,7 @@ class nbh_env(C.Structure):
 # constants of include/nbgraft.h
 NBG_OK, NBG_E_NODEVICE, NBG_E_INVAL, NBG_E_NOMEM, NBG_E_CUDA = 0, -1, -2, -3, -4
 NBG_E_NILREPLICAS, NBG_E_RANGE, NBG_E_TOOBIG = -5, -6, -7
-NBG_POD_SLOTS, NBG_SVC_SLOTS, NBG_VS_SLOTS = 192, 16, 8
+NBG_POD_SLOTS, NBG_SVC_SLOTS, NBG_VS_SLOTS = 192, 8, 8
 NBG_REPLICAS_NIL = -(2 ** 31)
 NBG_JOIN_STATIC_MAX_STS = 131072
 NBG_ARGMAX_NONE = 0xFFFFFFFF

@@ -770,7 +770,8 @@ __global__ void __launch_bounds__(128, NBG_GEN_MINBLOCKS)
 diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
                     unsigned lt_base, unsigned at_base, unsigned st_base,
                     uint8_t* __restrict__ reason_out, uint32_t* __restrict__ bitmap_half) {
-  constexpr int VEC = NBG_SVC_SLOTS / 2;               // 8 lanes per object
+  constexpr int VEC = NBG_SVC_SLOTS / 2;               // 4 lanes per object
+  static_assert(VEC == 4, "the desired tile below is written for the 8-slot layout of csrc/host/pack.cpp");
   const unsigned lane = threadIdx.x & 31;
   const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const unsigned long long base = warp * 32ull;
@@ -781,33 +782,35 @@ diff_svc_gen_kernel(nbg_svc_gen_batch in, SvcGenConsts k, unsigned long long n,
   unsigned port_bits = 0;
 #pragma unroll
   for (int r = 0; r < VEC; ++r) {
-    const unsigned idx = r * 32 + lane, part = lane & 7u;
-    const unsigned long long obj = base + (idx >> 3);
+    const unsigned idx = r * 32 + lane, part = lane & 3u;
+    const unsigned long long obj = base + (idx >> 2);
     unsigned d = 0;
     if (idx < limit) {
       unsigned long long a = 0, b = 0;                 // desired slots 2*part, 2*part+1
       if (part == 0) { a = k.port_name; b = k.proto_tcp; }                    // Name, Protocol
       else if (part == 1) { b = 80ull; }                                      // AppProtocol nil; Port 80, NodePort 0
       else if (part == 2) { a = (unsigned long long)(unsigned)__ldg(in.target_port + obj); }   // TargetPort Int
-      else if (part == 6) { a = 1ull; }                                       // one port, no overflow
+      else if (part == 3) { a = 1ull; }                                       // one port, nothing after it
       const uint4 want = make_uint4((unsigned)a, (unsigned)(a >> 32), (unsigned)b, (unsigned)(b >> 32));
       d = diff4(want, ld_stream(pt + idx));
     }
     const unsigned ballot = __ballot_sync(FULL, d != 0);
 #pragma unroll
-    for (int g = 0; g < 4; ++g)
-      if ((ballot >> (g * 8)) & 0xFFu) port_bits |= 1u << (r * 4 + g);
+    for (int g = 0; g < 8; ++g)
+      if ((ballot >> (g * 4)) & 0xFu) port_bits |= 1u << (r * 8 + g);
   }
   unsigned reason = 0;
   if (i < n) {
     const unsigned fl = __ldg(in.flags + i);
+    const unsigned l0 = __ldg(in.labels_to.off + i) - lt_base, l1 = end_at<SPANS>(in.labels_to, i) - lt_base;
+    const unsigned a0 = __ldg(in.ann_to.off + i) - at_base, a1 = end_at<SPANS>(in.ann_to, i) - at_base;
+    const unsigned s0 = __ldg(in.sel_to.off + i) - st_base, s1 = end_at<SPANS>(in.sel_to, i) - st_base;
     // desired has no labels and no annotations: any live entry with a non-empty value differs
-    for (unsigned t = __ldg(in.labels_to.off + i) - lt_base, e = end_at<SPANS>(in.labels_to, i) - lt_base; t < e; ++t)
+    for (unsigned t = l0; t < l1; ++t)
       if (ld_kv(in.labels_to.ent + t).val != 0ull) reason |= NBG_SVC_LABELS;
-    for (unsigned t = __ldg(in.ann_to.off + i) - at_base, e = end_at<SPANS>(in.ann_to, i) - at_base; t < e; ++t)
+    for (unsigned t = a0; t < a1; ++t)
       if (ld_kv(in.ann_to.ent + t).val != 0ull) reason |= NBG_SVC_ANNOTATIONS;
     // desired selector = {"statefulset": name}, non-nil
-    const unsigned s0 = __ldg(in.sel_to.off + i) - st_base, s1 = end_at<SPANS>(in.sel_to, i) - st_base;
     bool sel_ne = (fl & NBG_F_TO_SEL_NIL) != 0 || (s1 - s0) != 1u;
     if (!sel_ne) {
       const nbg_kv e = ld_kv(in.sel_to.ent + s0);

@@ -70,16 +70,26 @@ uint64_t digest_without(const GVal& s, std::initializer_list<const char*> skip) 
   return n ? nbg_combine(h, n) : 0;
 }
 
+// A resource.Quantity in three slots.  Nearly every quantity is a small int64Amount in one of the three formats, and
+// that case takes ONE non-zero slot: value (40 bits, two's complement) | scale (8 bits) << 40 | format << 48 | 1 << 56.
+// Anything larger keeps the value in slot 0 and scale / format / presence in slot 1, which is then non-zero - so the
+// two spellings cannot be confused, and each is injective on (value, scale, format).  Slot 2: whatever else the
+// struct holds (the cached string, inf.Dec, odd formats, extra fields).
 void pack_quantity(const GVal& q, bool present, uint64_t* s3) {
   s3[0] = s3[1] = s3[2] = 0;
   if (!present) return;
   const GVal& i = field(q, "i");
-  s3[0] = (uint64_t)field(i, "value").i;
-  const uint32_t scale = (uint32_t)(int32_t)field(i, "scale").i;
+  const int64_t value = field(i, "value").i;
+  const int64_t scale = (int32_t)field(i, "scale").i;
   const std::string fmt = field(q, "Format").kind == GVal::Str ? field(q, "Format").s : std::string();
   uint64_t code = fmt.empty() ? 0 : fmt == "DecimalSI" ? 1 : fmt == "BinarySI" ? 2 : fmt == "DecimalExponent" ? 3 : 255;
-  s3[1] = (uint64_t)scale | (code << 32) | (1ull << 40);
-  // everything else the struct holds: cached string, inf.Dec, odd formats, extra fields
+  const int64_t lim = (int64_t)1 << 39;
+  if (code != 255 && value >= -lim && value < lim && scale >= -128 && scale <= 127) {
+    s3[0] = ((uint64_t)value & ((1ull << 40) - 1)) | ((uint64_t)(uint8_t)(int8_t)scale << 40) | (code << 48) | (1ull << 56);
+  } else {
+    s3[0] = (uint64_t)value;
+    s3[1] = (uint64_t)(uint32_t)scale | (code << 32) | (1ull << 40);
+  }
   s3[2] = code != 255 ? digest_without(q, {"i", "Format"}) : digest_without(q, {"i"});
 }
 
@@ -333,7 +343,10 @@ void pack_podspec(const GVal& pod, uint64_t* s) {
       GVal* src = rest.find(kn.src);
       if (!src || src->kind != GVal::Ptr || src->items.empty() || src->items[0].kind != GVal::Struct) continue;
       p[1] = nbg_combine(hash_str(kn.src), str_of(src->items[0], kn.ref));
-      src->items[0].erase(kn.ref);   // the pointer itself stays: &T{} != nil
+      src->items[0].erase(kn.ref);
+      // p[1] != 0 already says "this source, non-nil": when nothing else is set in it (the usual volume) it leaves
+      // the rest, so that slot 2 stays zero; otherwise the pointer stays, &T{...} with what is left of it
+      if (src->items[0].is_zero()) rest.erase(kn.src);
       break;
     }
     p[2] = rest.kv.empty() ? 0 : digest(rest);
@@ -388,26 +401,26 @@ bool patch_statefulset_tile(uint64_t* s, uint64_t prefix_hash, bool add_fsgroup)
 }
 
 void pack_service_ports(const GVal& ports, uint64_t* s) {
+  // ports[0] field by field (generateService builds exactly one port, NBCTL:538-548, and that is what drifts);
+  // every further port is folded into ONE digest: equal lists <=> equal tiles either way, in half the bytes.
   memset(s, 0, NBG_SVC_SLOTS * sizeof(uint64_t));
-  for (int k = 0; k < 2; ++k) {
-    if (ports.kind != GVal::List || (size_t)k >= ports.items.size()) continue;
-    const GVal& sp = ports.items[k];
-    uint64_t* p = s + k * 6;
-    p[0] = str_of(sp, "name");
-    p[1] = str_of(sp, "protocol");
+  if (ports.kind == GVal::List && !ports.items.empty()) {
+    const GVal& sp = ports.items[0];
+    s[0] = str_of(sp, "name");
+    s[1] = str_of(sp, "protocol");
     const GVal& ap = field(sp, "appProtocol");
-    p[2] = ap.kind == GVal::Ptr ? nbg_combine(K_PTR, ap.items.empty() ? 0 : hash_str(ap.items[0].s)) : 0;
-    p[3] = (uint64_t)(uint32_t)field(sp, "port").i | ((uint64_t)(uint32_t)field(sp, "nodePort").i << 32);
+    s[2] = ap.kind == GVal::Ptr ? nbg_combine(K_PTR, ap.items.empty() ? 0 : hash_str(ap.items[0].s)) : 0;
+    s[3] = (uint64_t)(uint32_t)field(sp, "port").i | ((uint64_t)(uint32_t)field(sp, "nodePort").i << 32);
     const GVal& tp = field(sp, "targetPort");
-    p[4] = (uint64_t)(uint32_t)field(tp, "IntVal").i | ((uint64_t)field(tp, "Type").i << 32);
+    s[4] = (uint64_t)(uint32_t)field(tp, "IntVal").i | ((uint64_t)field(tp, "Type").i << 32);
     GVal rest = sp.kind == GVal::Struct ? sp : GVal::strct();
     for (const char* n : {"name", "protocol", "appProtocol", "port", "nodePort"}) rest.erase(n);
     if (GVal* t = rest.find("targetPort")) { t->erase("IntVal"); t->erase("Type"); }
     rest.canon();
-    p[5] = rest.kv.empty() ? 0 : digest(rest);   // targetPort.StrVal and anything unexpected
+    s[5] = rest.kv.empty() ? 0 : digest(rest);   // targetPort.StrVal and anything unexpected
   }
-  s[12] = ports.kind == GVal::List ? ports.items.size() : 0xFFFFFFFFull;
-  s[13] = overflow_digest(ports, 2);
+  s[6] = ports.kind == GVal::List ? ports.items.size() : 0xFFFFFFFFull;
+  s[7] = overflow_digest(ports, 1);
 }
 
 bool pack_vs_spec(const GVal& obj, uint64_t* s, std::vector<nbg_kv>* headers, bool* headers_nil) {

@@ -68,6 +68,52 @@ STS_CASES = [
 ]
 
 
+def _vols(d):
+    return d["spec"]["template"]["spec"]["volumes"]
+
+
+def _req(d):
+    return _c0(d)["resources"]["requests"]
+
+
+# Cases that edit BOTH sides: (name, edit of desired, edit of live, expected reason).  They sit on the two places where
+# the packer spends fewer slots on the usual value than on the general one (csrc/host/pack.cpp: a small Quantity in one
+# slot, a volume whose source holds nothing but its reference in two) - the short and the long spelling of a tile
+# must never compare equal to each other, and each must stay injective.
+STS_BOTH_CASES = [
+    ("pvc readOnly on live only", None, lambda d: _vols(d)[0]["persistentVolumeClaim"].update({"readOnly": True}), 8),
+    ("pvc readOnly on both", lambda d: _vols(d)[0]["persistentVolumeClaim"].update({"readOnly": True}),
+     lambda d: _vols(d)[0]["persistentVolumeClaim"].update({"readOnly": True}), 0),
+    ("pvc readOnly false is the zero value", None, lambda d: _vols(d)[0]["persistentVolumeClaim"].update({"readOnly": False}), 0),
+    ("volume without a source vs emptyDir {}", lambda d: _vols(d).append({"name": "x"}), lambda d: _vols(d).append({"name": "x", "emptyDir": {}}), 8),
+    ("emptyDir {} vs emptyDir {medium: ''}", lambda d: _vols(d).append({"name": "x", "emptyDir": {}}),
+     lambda d: _vols(d).append({"name": "x", "emptyDir": {"medium": ""}}), 0),
+    ("emptyDir {} vs emptyDir {sizeLimit}", lambda d: _vols(d).append({"name": "x", "emptyDir": {}}),
+     lambda d: _vols(d).append({"name": "x", "emptyDir": {"sizeLimit": "1Gi"}}), 8),
+    ("same claim name under another source kind", lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}),
+     lambda d: _vols(d).append({"name": "x", "configMap": {"name": "n"}}), 8),
+    ("two sources in one volume vs one", lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}),
+     lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}, "emptyDir": {}}), 8),
+    ("configMap optional pointer false vs absent (a *bool)", lambda d: _vols(d).append({"name": "x", "configMap": {"name": "n"}}),
+     lambda d: _vols(d).append({"name": "x", "configMap": {"name": "n", "optional": False}}), 8),
+    ("memory 511Gi on both (one-slot spelling)", lambda d: _req(d).update({"memory": "511Gi"}), lambda d: _req(d).update({"memory": "511Gi"}), 0),
+    ("memory 512Gi on both (2^39: the long spelling)", lambda d: _req(d).update({"memory": "512Gi"}), lambda d: _req(d).update({"memory": "512Gi"}), 0),
+    ("memory 512Gi vs 511Gi", lambda d: _req(d).update({"memory": "512Gi"}), lambda d: _req(d).update({"memory": "511Gi"}), 8),
+    ("memory 512Gi vs 549755813888 (same bytes, DecimalSI)", lambda d: _req(d).update({"memory": "512Gi"}),
+     lambda d: _req(d).update({"memory": "549755813888"}), 8),
+    ("memory 1Gi vs 1073741824 (same bytes, DecimalSI)", None, lambda d: _req(d).update({"memory": "1073741824"}), 8),
+    ("cpu 1 vs 1000m", lambda d: _req(d).update({"cpu": "1"}), lambda d: _req(d).update({"cpu": "1000m"}), 8),
+    ("cpu -1 vs 1", lambda d: _req(d).update({"cpu": "-1"}), lambda d: _req(d).update({"cpu": "1"}), 8),
+    ("cpu -1 on both", lambda d: _req(d).update({"cpu": "-1"}), lambda d: _req(d).update({"cpu": "-1"}), 0),
+    ("cpu 1e3 vs 1k (DecimalExponent vs DecimalSI)", lambda d: _req(d).update({"cpu": "1e3"}), lambda d: _req(d).update({"cpu": "1k"}), 8),
+    ("cpu 8E on both (near the int64 edge)", lambda d: _req(d).update({"cpu": "8E"}), lambda d: _req(d).update({"cpu": "8E"}), 0),
+    ("cpu 8E vs 8P", lambda d: _req(d).update({"cpu": "8E"}), lambda d: _req(d).update({"cpu": "8P"}), 8),
+    ("cpu 100n vs 100u (scales -9 and -6)", lambda d: _req(d).update({"cpu": "100n"}), lambda d: _req(d).update({"cpu": "100u"}), 8),
+    ("a quantity present with value 0 vs absent", lambda d: _req(d).update({"cpu": "0"}), lambda d: _req(d).pop("cpu"), 8),
+    ("value 0 on both", lambda d: _req(d).update({"cpu": "0"}), lambda d: _req(d).update({"cpu": "0"}), 0),
+]
+
+
 def _env_nil_vs_empty(d):
     # desired has env [NB_PREFIX] (appended by setPrefixEnvVar); make live's second container carry env: []
     d["spec"]["template"]["spec"]["containers"].append({"name": "side", "env": []})
@@ -82,6 +128,8 @@ def sts_case_pairs(generate):
             yield name, d2, _edit(desired, _env_nil_vs_empty), want
             continue
         yield name, desired, _edit(desired, edit), want
+    for name, edit_from, edit_to, want in STS_BOTH_CASES:
+        yield name, _edit(desired, edit_from or (lambda d: None)), _edit(desired, edit_to or (lambda d: None)), want
 
 
 # Service: L=1 A=2 S=4 Pt=8
@@ -101,6 +149,30 @@ SVC_CASES = [
     ("live label with empty value", lambda d: d["metadata"].update({"labels": {"a": ""}}), 0),
     ("live annotation", lambda d: d["metadata"].update({"annotations": {"a": "b"}}), 2),
 ]
+
+# Services whose port lists are longer than the one port the tile spells out: ports[1:] are folded into one digest
+# (csrc/host/pack.cpp: pack_service_ports), which must still make equal lists equal and everything else different.
+# (name, desired ports, live ports, expected reason)
+_P = lambda name, port, **kw: dict({"name": name, "port": port, "protocol": "TCP", "targetPort": port}, **kw)
+SVC_PORT_LISTS = [
+    ("two equal ports", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("b", 81)], 0),
+    ("three equal ports", [_P("a", 80), _P("b", 81), _P("c", 82)], [_P("a", 80), _P("b", 81), _P("c", 82)], 0),
+    ("second port: other name", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("x", 81)], 8),
+    ("second port: other number", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("b", 82)], 8),
+    ("second port: nodePort set", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("b", 81, nodePort=30081)], 8),
+    ("second port: targetPort as a string", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("b", 81, targetPort="81")], 8),
+    ("second port: appProtocol", [_P("a", 80), _P("b", 81)], [_P("a", 80), _P("b", 81, appProtocol="http")], 8),
+    ("third port differs", [_P("a", 80), _P("b", 81), _P("c", 82)], [_P("a", 80), _P("b", 81), _P("c", 83)], 8),
+    ("third port missing", [_P("a", 80), _P("b", 81), _P("c", 82)], [_P("a", 80), _P("b", 81)], 8),
+    ("same ports, other order", [_P("a", 80), _P("b", 81)], [_P("b", 81), _P("a", 80)], 8),
+    ("first port differs, rest equal", [_P("a", 80), _P("b", 81)], [_P("a", 90), _P("b", 81)], 8),
+    ("one port against the same port twice", [_P("a", 80)], [_P("a", 80), _P("a", 80)], 8),
+    ("second port equal to the first on both sides", [_P("a", 80), _P("a", 80)], [_P("a", 80), _P("a", 80)], 0),
+    ("nil against empty", None, [], 8),
+    ("nil against nil", None, None, 0),
+    ("empty against empty", [], [], 0),
+]
+
 
 # VirtualService: 1 differs (true), 2 to.spec missing (true), 4 from.spec missing (false)
 VS_CASES = [

@@ -40,7 +40,7 @@ def test_schema_constants_match_header():
     def const(name):
         return int(re.search(r"#define\s+%s\s+\(?(-?\w+)u?\)?" % name, text).group(1).rstrip("u"), 0)
     assert const("NBG_POD_SLOTS") == N.NBG_POD_SLOTS == 192
-    assert const("NBG_SVC_SLOTS") == N.NBG_SVC_SLOTS == 16
+    assert const("NBG_SVC_SLOTS") == N.NBG_SVC_SLOTS == 8
     assert const("NBG_VS_SLOTS") == N.NBG_VS_SLOTS == 8
     assert N.nbg().nbg_abi_version() == const("NBG_ABI_VERSION")
     assert C.sizeof(N.nbg_kv) == 16 and C.sizeof(N.nbg_cull_params) == 24

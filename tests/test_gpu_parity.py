@@ -11,7 +11,7 @@ import pytest
 
 import cases
 import oracle as O
-from test_oracle_cases import GOLDEN, STS_PAIRS, SVC_PAIRS, VS_PAIRS, _resolve_now, check_cull_expectation
+from test_oracle_cases import GOLDEN, STS_PAIRS, SVC_PAIRS, SVC_PORT_PAIRS, VS_PAIRS, _resolve_now, check_cull_expectation
 
 pytestmark = pytest.mark.gpu
 
@@ -102,6 +102,15 @@ def test_derived_svc(ctx, name, frm, to, want):
     to = json.loads(json.dumps(to))
     assert rh.CopyServiceFields(frm, to, ctx) == (want != 0)
     assert rh.CopyServiceFields(frm, to, ctx) is False
+
+
+def test_service_port_lists_longer_than_the_tile_spells_out(ctx):
+    b = host.SvcBatch()
+    for name, frm, to, want in SVC_PORT_PAIRS:
+        b.add(host.Service(frm), host.Service(to))
+    reason, bm = ctx.diff_svc(b)
+    assert reason.tolist() == [p[3] for p in SVC_PORT_PAIRS]
+    assert bits(bm, len(b)).tolist() == [p[3] != 0 for p in SVC_PORT_PAIRS]
 
 
 @pytest.mark.parametrize("name,frm,to,want", VS_PAIRS, ids=[p[0][:60] for p in VS_PAIRS])

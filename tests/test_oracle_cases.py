@@ -150,6 +150,28 @@ def test_derived_svc(name, frm, to, want):
     assert O.copy_service_fields(f, t) == 0
 
 
+def _svc_port_pairs():
+    desired = host.generate_service(host.Notebook(cases.BASE_NOTEBOOK)).to_python()
+    for name, fp, tp, want in cases.SVC_PORT_LISTS:
+        f, t = json.loads(json.dumps(desired)), json.loads(json.dumps(desired))
+        for side, ports in ((f, fp), (t, tp)):
+            if ports is None:
+                side["spec"].pop("ports")
+            else:
+                side["spec"]["ports"] = json.loads(json.dumps(ports))
+        yield name, f, t, want
+
+
+SVC_PORT_PAIRS = list(_svc_port_pairs())
+
+
+@pytest.mark.parametrize("name,frm,to,want", SVC_PORT_PAIRS, ids=[p[0] for p in SVC_PORT_PAIRS])
+def test_service_port_lists_longer_than_the_tile_spells_out(name, frm, to, want):
+    f, t = host.Service(frm), host.Service(to)
+    assert O.copy_service_fields(f, host.Service(to)) == want          # the object-level port decides
+    assert int(O.packed_diff_svc(host.SvcBatch().add(f, t))[0][0]) == want
+
+
 def _vs_pairs():
     desired = host.generate_virtualservice(host.Notebook(cases.BASE_NOTEBOOK)).to_python()
     for name, edit, want in cases.VS_CASES:
