@@ -70,33 +70,27 @@ uint64_t digest_without(const GVal& s, std::initializer_list<const char*> skip) 
   return n ? nbg_combine(h, n) : 0;
 }
 
-// A resource.Quantity in three slots.  Nearly every quantity is a small int64Amount in one of the three formats, and
-// that case takes ONE non-zero slot: value (40 bits, two's complement) | scale (8 bits) << 40 | format << 48 | 1 << 56.
-// Anything larger keeps the value in slot 0 and scale / format / presence in slot 1, which is then non-zero - so the
-// two spellings cannot be confused, and each is injective on (value, scale, format).  Slot 2: whatever else the
-// struct holds (the cached string, inf.Dec, odd formats, extra fields).
+// A resource.Quantity: ONE word, the digest of the struct reflect.DeepEqual walks - int64Amount{value, scale}, the
+// inf.Dec, the cached string s and the Format - so "1" != "1000m" and "1Gi" != "1024Mi" (COMMON:128).  The other two
+// slots of the triple stay zero (the sparse form pays per non-zero slot).  An absent entry is 0; a present one is not,
+// whatever its value: digest() of a struct never returns 0.
 void pack_quantity(const GVal& q, bool present, uint64_t* s3) {
   s3[0] = s3[1] = s3[2] = 0;
-  if (!present) return;
-  const GVal& i = field(q, "i");
-  const int64_t value = field(i, "value").i;
-  const int64_t scale = (int32_t)field(i, "scale").i;
-  const std::string fmt = field(q, "Format").kind == GVal::Str ? field(q, "Format").s : std::string();
-  uint64_t code = fmt.empty() ? 0 : fmt == "DecimalSI" ? 1 : fmt == "BinarySI" ? 2 : fmt == "DecimalExponent" ? 3 : 255;
-  const int64_t lim = (int64_t)1 << 39;
-  if (code != 255 && value >= -lim && value < lim && scale >= -128 && scale <= 127) {
-    s3[0] = ((uint64_t)value & ((1ull << 40) - 1)) | ((uint64_t)(uint8_t)(int8_t)scale << 40) | (code << 48) | (1ull << 56);
-  } else {
-    s3[0] = (uint64_t)value;
-    s3[1] = (uint64_t)(uint32_t)scale | (code << 32) | (1ull << 40);
-  }
-  s3[2] = code != 255 ? digest_without(q, {"i", "Format"}) : digest_without(q, {"i"});
+  if (present) s3[0] = digest(q);
 }
 
 constexpr int kPodLevel = 16, kVolSlots = 3, kMaxVol = 8, kContBase = kPodLevel + kVolSlots * kMaxVol,
               kContSlots = 76, kMaxCont = 2;
 constexpr int kMaxPorts = 2, kMaxEnv = 14, kMaxMounts = 10;
 static_assert(kContBase + kContSlots * kMaxCont == (int)NBG_POD_SLOTS, "PodSpec tile layout");
+
+// A list element that has a name (container port, volume mount) in its two slots: ONE word for the whole element,
+// name and everything else folded together, the second slot zero - an element is what drifts, and the sparse form
+// pays per non-zero slot.  (Env variables keep name and value apart: setPrefixEnvVar looks names up, NBCTL:417-431.)
+void pack_named_element(const GVal& e, uint64_t* p) {
+  p[0] = nbg_combine(str_of(e, "name"), digest_without(e, {"name"}));
+  p[1] = 0;
+}
 
 void pack_container(const GVal& c, uint64_t* s) {
   s[0] = str_of(c, "name");
@@ -119,8 +113,7 @@ void pack_container(const GVal& c, uint64_t* s) {
   for (int k = 0; k < kMaxPorts; ++k, p += 2) {
     p[0] = p[1] = 0;
     if (ports.kind == GVal::List && (size_t)k < ports.items.size()) {
-      p[0] = str_of(ports.items[k], "name");
-      p[1] = digest_without(ports.items[k], {"name"});
+      pack_named_element(ports.items[k], p);
     }
   }
   for (int k = 0; k < kMaxEnv; ++k, p += 2) {
@@ -146,8 +139,7 @@ void pack_container(const GVal& c, uint64_t* s) {
   for (int k = 0; k < kMaxMounts; ++k, p += 2) {
     p[0] = p[1] = 0;
     if (mounts.kind == GVal::List && (size_t)k < mounts.items.size()) {
-      p[0] = str_of(mounts.items[k], "name");
-      p[1] = digest_without(mounts.items[k], {"name"});
+      pack_named_element(mounts.items[k], p);
     }
   }
   // residual: the container minus everything slotted above; nil-ness and emptiness of the
@@ -350,6 +342,9 @@ void pack_podspec(const GVal& pod, uint64_t* s) {
       break;
     }
     p[2] = rest.kv.empty() ? 0 : digest(rest);
+    // the usual volume - a name and one plain source - is ONE word; with anything else in it the three slots stay
+    // apart and the third is non-zero, so the two spellings cannot meet
+    if (p[2] == 0 && p[1] != 0) { p[0] = nbg_combine(p[0], p[1]); p[1] = 0; }
   }
   for (int k = 0; k < kMaxCont; ++k)
     if (conts.kind == GVal::List && (size_t)k < conts.items.size())
@@ -375,8 +370,10 @@ bool patch_statefulset_tile(uint64_t* s, uint64_t prefix_hash, bool add_fsgroup)
     port.set("containerPort", GVal::integer(8888));
     port.set("name", GVal::str("notebook-port"));
     port.set("protocol", GVal::str("TCP"));
-    name = str_of(port, "name");
-    rest = digest_without(port, {"name"});
+    uint64_t p[2];
+    pack_named_element(port, p);
+    name = p[0];
+    rest = p[1];
   } } kPort;
   uint64_t* c = s + kContBase;                    // containers[0]
   uint64_t* ports = c + 12;

@@ -96,6 +96,31 @@ STS_BOTH_CASES = [
      lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}, "emptyDir": {}}), 8),
     ("configMap optional pointer false vs absent (a *bool)", lambda d: _vols(d).append({"name": "x", "configMap": {"name": "n"}}),
      lambda d: _vols(d).append({"name": "x", "configMap": {"name": "n", "optional": False}}), 8),
+    ("volume: same source under another name", lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}),
+     lambda d: _vols(d).append({"name": "y", "secret": {"secretName": "n"}}), 8),
+    ("volume: same name, other secret", lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}),
+     lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "m"}}), 8),
+    ("volume: plain source on both", lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}),
+     lambda d: _vols(d).append({"name": "x", "secret": {"secretName": "n"}}), 0),
+    ("volume: a source the packer has no short form for, on both", lambda d: _vols(d).append({"name": "x", "hostPath": {"path": "/p"}}),
+     lambda d: _vols(d).append({"name": "x", "hostPath": {"path": "/p"}}), 0),
+    ("volume: hostPath path differs", lambda d: _vols(d).append({"name": "x", "hostPath": {"path": "/p"}}),
+     lambda d: _vols(d).append({"name": "x", "hostPath": {"path": "/q"}}), 8),
+    ("mount: same name, other path", None, lambda d: _c0(d)["volumeMounts"][0].update({"mountPath": "/elsewhere"}), 8),
+    ("mount: other name, same path", None, lambda d: _c0(d)["volumeMounts"][0].update({"name": "other"}), 8),
+    ("mount: readOnly set", None, lambda d: _c0(d)["volumeMounts"][0].update({"readOnly": True}), 8),
+    ("mounts: names swapped between two mounts",
+     lambda d: _c0(d).update({"volumeMounts": [{"name": "a", "mountPath": "/x"}, {"name": "b", "mountPath": "/y"}]}),
+     lambda d: _c0(d).update({"volumeMounts": [{"name": "b", "mountPath": "/x"}, {"name": "a", "mountPath": "/y"}]}), 8),
+    ("mounts: same two mounts, other order",
+     lambda d: _c0(d).update({"volumeMounts": [{"name": "a", "mountPath": "/x"}, {"name": "b", "mountPath": "/y"}]}),
+     lambda d: _c0(d).update({"volumeMounts": [{"name": "b", "mountPath": "/y"}, {"name": "a", "mountPath": "/x"}]}), 8),
+    ("mount: an empty element against none", lambda d: _c0(d)["volumeMounts"].append({}), None, 8),
+    ("container port: other name", None, lambda d: _c0(d)["ports"][0].update({"name": "other"}), 8),
+    ("container port: other number", None, lambda d: _c0(d)["ports"][0].update({"containerPort": 9999}), 8),
+    ("container port: hostPort set", None, lambda d: _c0(d)["ports"][0].update({"hostPort": 80}), 8),
+    ("container ports: a second one on both", lambda d: _c0(d)["ports"].append({"containerPort": 1, "name": "z"}),
+     lambda d: _c0(d)["ports"].append({"containerPort": 1, "name": "z"}), 0),
     ("memory 511Gi on both (one-slot spelling)", lambda d: _req(d).update({"memory": "511Gi"}), lambda d: _req(d).update({"memory": "511Gi"}), 0),
     ("memory 512Gi on both (2^39: the long spelling)", lambda d: _req(d).update({"memory": "512Gi"}), lambda d: _req(d).update({"memory": "512Gi"}), 0),
     ("memory 512Gi vs 511Gi", lambda d: _req(d).update({"memory": "512Gi"}), lambda d: _req(d).update({"memory": "511Gi"}), 8),
