@@ -34,7 +34,11 @@
 extern "C" {
 #endif
 
-/* 3: additions only (nbg_balance_shards, nbg_check_step_device, nbg_store_check); nbg_store_put now refuses a slot
+/* 4: the Service ports tile is 8 slots (was 16: ports[1:] are one digest now), and the packer of libnbgraft_host.so
+ *    spends one word on a Quantity, a container port, a volume mount and a plain volume (the tiles of version 3 and
+ *    version 4 packers do not compare with each other; nothing on the device side changed but NBG_SVC_SLOTS);
+ *    nbg_diff_sts_gen added.
+ * 3: additions only (nbg_balance_shards, nbg_check_step_device, nbg_store_check); nbg_store_put now refuses a slot
  *    named twice (NBG_E_INVAL) instead of leaving the outcome open.  2: spans (end pointers) in the batch structs. */
 #define NBG_ABI_VERSION 4
 
@@ -115,7 +119,7 @@ typedef struct nbg_sts_batch {
 } nbg_sts_batch;
 
 /* The same StatefulSet pairs with the PodSpec tile stored sparsely.  A synthetic
- * Kubeflow PodSpec fills ~35 of the 192 slots, an ODH one ~90, so the dense tile is
+ * Kubeflow PodSpec fills ~24 of the 192 slots, an ODH one ~68, so the dense tile is
  * mostly zeros; here each side keeps a 192-bit presence mask (bit s = slot s is
  * non-zero) and only the non-zero slots, in slot order:
  *     mask[3*i .. 3*i+3), val[off[i] .. off[i+1])

@@ -194,7 +194,7 @@ int nbh_fleet_pack(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_
                    nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
 /* The same, keeping only what the reconcile step reads of the StatefulSet pairs: the SPARSE PodSpec tiles
  * (nbh_sts_view_sparse); the dense tiles are not stored and nbh_sts_view returns NULL for pod_from / pod_to.
- * 0.8 KB instead of 3.9 KB per pair: what lets the 10 M-notebook fleet of BASELINE config #5 sit in host memory. */
+ * 0.6 KB instead of 3.7 KB per pair: what lets the 10 M-notebook fleet of BASELINE config #5 sit in host memory. */
 int nbh_fleet_pack_lean(const nbh_fleet* f, const uint64_t* idx, uint64_t i0, uint64_t m,
                         nbh_sts** sts /*nullable*/, nbh_svc** svc /*nullable*/, nbh_vs** vs /*nullable*/);
 int nbh_sts_is_lean(const nbh_sts* b);

@@ -49,7 +49,7 @@ struct StsBatch {
   std::vector<uint32_t> voff_from{0}, voff_to{0};
   uint64_t n = 0;
   // lean: keep only the sparse form of the PodSpec tiles (what the step reads).  A 10 M-notebook batch then
-  // costs 0.78 KB per pair on the host instead of 3.9 KB; view() of a lean batch has no dense tiles.
+  // costs 0.59 KB per pair on the host instead of 3.7 KB; view() of a lean batch has no dense tiles.
   bool lean = false;
   // generateStatefulSet on the device (nbg_diff_sts_gen): per-notebook inputs of the generator; filled by add_gen only
   std::vector<uint64_t> prefix_hash;
