@@ -90,6 +90,8 @@ def _is_quantity(v):
 def _quantity_text(v):
     if v.get("s"):
         return v["s"]
+    if "d" in v:
+        raise ValueError("an inf.Dec quantity has no text this helper can write: build the JSON from the original string")
     val, scale = v.get("i", {}).get("value", 0), v.get("i", {}).get("scale", 0)
     fmt = v.get("Format", "")
     if fmt == "BinarySI":
