@@ -20,6 +20,7 @@
 #pragma once
 #include <algorithm>
 #include <cstdint>
+#include <cstring>
 #include <string>
 #include <string_view>
 #include <utility>
@@ -69,6 +70,13 @@ struct GVal {
   // ---- Map / Struct access (sorted by name)
   // (string_view: looking a field up by a literal name builds no temporary std::string)
   const GVal* find(std::string_view name) const {
+    if (kv.size() <= 32) {
+      // API objects have a handful of fields: a scan that looks at lengths first beats a binary search whose every
+      // step is a lexicographic compare (a quarter of the packer's time went into those)
+      for (const auto& e : kv)
+        if (e.first.size() == name.size() && memcmp(e.first.data(), name.data(), name.size()) == 0) return &e.second;
+      return nullptr;
+    }
     auto it = std::lower_bound(kv.begin(), kv.end(), name,
                                [](const std::pair<std::string, GVal>& e, std::string_view n) { return std::string_view(e.first) < n; });
     return (it != kv.end() && std::string_view(it->first) == name) ? &it->second : nullptr;

@@ -38,8 +38,7 @@ uint64_t str_of(const GVal& s, const char* name) {
   const GVal& f = field(s, name);
   return f.kind == GVal::Str ? hash_str(f.s) : 0;
 }
-// marker node: a Ptr without pointee cannot be produced by any decoder
-GVal marker() { GVal g; g.kind = GVal::Ptr; return g; }
+// (a marker node is a Ptr without pointee, which no decoder can produce: digest K_PTR over K_MARK)
 
 // count tag of a slice field: 0xFFFF nil, else min(len, 0xFFFE)
 uint64_t count_tag(const GVal& l) {
@@ -327,21 +326,44 @@ void pack_podspec(const GVal& pod, uint64_t* s) {
     const GVal& v = vols.items[k];
     p[0] = str_of(v, "name");
     // the usual sources: kind + the one string that names the backing object
-    static const struct { const char* src; const char* ref; } known[] = {
-        {"persistentVolumeClaim", "claimName"}, {"configMap", "name"}, {"secret", "secretName"}, {"emptyDir", "medium"}};
-    GVal rest = v.kind == GVal::Struct ? v : GVal::strct();
-    rest.erase("name");
-    for (const auto& kn : known) {
-      GVal* src = rest.find(kn.src);
-      if (!src || src->kind != GVal::Ptr || src->items.empty() || src->items[0].kind != GVal::Struct) continue;
-      p[1] = nbg_combine(hash_str(kn.src), str_of(src->items[0], kn.ref));
-      src->items[0].erase(kn.ref);
-      // p[1] != 0 already says "this source, non-nil": when nothing else is set in it (the usual volume) it leaves
-      // the rest, so that slot 2 stays zero; otherwise the pointer stays, &T{...} with what is left of it
-      if (src->items[0].is_zero()) rest.erase(kn.src);
-      break;
-    }
-    p[2] = rest.kv.empty() ? 0 : digest(rest);
+    static const struct Known { const char* src; const char* ref; uint64_t src_hash; } known[] = {
+        {"persistentVolumeClaim", "claimName", hash_str("persistentVolumeClaim")}, {"configMap", "name", hash_str("configMap")},
+        {"secret", "secretName", hash_str("secret")}, {"emptyDir", "medium", hash_str("emptyDir")}};
+    // p[1] != 0 says "this source, non-nil": when nothing else is set in it (the usual volume) the source leaves the
+    // rest, so that slot 2 stays zero; otherwise the pointer stays in the rest, &T{...} with what is left of it.
+    // The rest is digested in place - the value digest() gives for a copy of the volume with the name, the reference
+    // and (when nothing else is in it) the source erased - without building that copy.
+    const GVal* chosen = nullptr;
+    const char* chosen_ref = nullptr;
+    bool drop_source = false;
+    if (v.kind == GVal::Struct)
+      for (const auto& kn : known) {
+        const GVal* src = v.find(kn.src);
+        if (!src || src->kind != GVal::Ptr || src->items.empty() || src->items[0].kind != GVal::Struct) continue;
+        p[1] = nbg_combine(kn.src_hash, str_of(src->items[0], kn.ref));
+        chosen = src; chosen_ref = kn.ref;
+        drop_source = true;
+        for (const auto& f : src->items[0].kv)
+          if (f.first != kn.ref && !f.second.is_zero()) { drop_source = false; break; }
+        break;
+      }
+    size_t left = 0, counted = 0;
+    uint64_t hr = K_STRUCT;
+    if (v.kind == GVal::Struct)
+      for (const auto& e : v.kv) {
+        if (e.first == "name") continue;
+        if (&e.second == chosen) {
+          if (drop_source) continue;
+          ++left; ++counted;
+          hr = nbg_combine(nbg_combine(hr, hash_str(e.first)), nbg_combine(K_PTR, digest_without(chosen->items[0], {chosen_ref})));
+          continue;
+        }
+        ++left;
+        if (e.second.is_zero()) continue;
+        hr = nbg_combine(nbg_combine(hr, hash_str(e.first)), digest(e.second));
+        ++counted;
+      }
+    p[2] = left == 0 ? 0 : nbg_combine(hr, counted);
     // the usual volume - a name and one plain source - is ONE word; with anything else in it the three slots stay
     // apart and the third is non-zero, so the two spellings cannot meet
     if (p[2] == 0 && p[1] != 0) { p[0] = nbg_combine(p[0], p[1]); p[1] = 0; }
@@ -410,15 +432,60 @@ void pack_service_ports(const GVal& ports, uint64_t* s) {
     s[3] = (uint64_t)(uint32_t)field(sp, "port").i | ((uint64_t)(uint32_t)field(sp, "nodePort").i << 32);
     const GVal& tp = field(sp, "targetPort");
     s[4] = (uint64_t)(uint32_t)field(tp, "IntVal").i | ((uint64_t)field(tp, "Type").i << 32);
-    GVal rest = sp.kind == GVal::Struct ? sp : GVal::strct();
-    for (const char* n : {"name", "protocol", "appProtocol", "port", "nodePort"}) rest.erase(n);
-    if (GVal* t = rest.find("targetPort")) { t->erase("IntVal"); t->erase("Type"); }
-    rest.canon();
-    s[5] = rest.kv.empty() ? 0 : digest(rest);   // targetPort.StrVal and anything unexpected
+    // targetPort.StrVal and anything unexpected: the digest of the port without the fields slotted above, taken in
+    // place (what digest() gives for a canonical copy with those fields erased; 0 when nothing is left)
+    uint64_t hr = K_STRUCT;
+    size_t counted = 0;
+    if (sp.kind == GVal::Struct)
+      for (const auto& e : sp.kv) {
+        const std::string& f = e.first;
+        if (f == "name" || f == "protocol" || f == "appProtocol" || f == "port" || f == "nodePort") continue;
+        uint64_t d;
+        if (f == "targetPort" && e.second.kind == GVal::Struct) {
+          d = digest_without(e.second, {"IntVal", "Type"});
+          if (d == 0) continue;                  // nothing but the slotted int and type
+        } else {
+          if (e.second.is_zero()) continue;
+          d = digest(e.second);
+        }
+        hr = nbg_combine(nbg_combine(hr, hash_str(f)), d);
+        ++counted;
+      }
+    s[5] = counted ? nbg_combine(hr, counted) : 0;
   }
   s[6] = ports.kind == GVal::List ? ports.items.size() : 0xFFFFFFFFull;
   s[7] = overflow_digest(ports, 1);
 }
+
+namespace {
+// digest(v) with some nodes of the tree read as marker(): what digest() gives for a copy of v in which those nodes
+// were replaced by a marker - the slotted leaves are taken OUT of the residual that way, the shape around them stays.
+uint64_t digest_marked(const GVal& v, const GVal* const* marks, int n_marks) {
+  for (int k = 0; k < n_marks; ++k)
+    if (marks[k] == &v) return nbg_combine(K_PTR, K_MARK);       // == digest(marker())
+  switch (v.kind) {
+    case GVal::List: {
+      uint64_t h = nbg_combine(K_LIST, v.items.size());
+      for (const auto& e : v.items) h = nbg_combine(h, digest_marked(e, marks, n_marks));
+      return h;
+    }
+    case GVal::Map: case GVal::Struct: {
+      uint64_t h = v.kind == GVal::Map ? K_MAP : K_STRUCT;
+      size_t n = 0;
+      for (const auto& e : v.kv) {
+        bool marked = false;
+        for (int k = 0; k < n_marks; ++k) marked |= marks[k] == &e.second;
+        if (v.kind == GVal::Struct && !marked && e.second.is_zero()) continue;
+        h = nbg_combine(nbg_combine(h, hash_str(e.first)), digest_marked(e.second, marks, n_marks));
+        ++n;
+      }
+      return nbg_combine(h, n);
+    }
+    case GVal::Ptr: return nbg_combine(K_PTR, v.items.empty() ? K_MARK : digest_marked(v.items[0], marks, n_marks));
+    default: return digest(v);
+  }
+}
+}  // namespace
 
 bool pack_vs_spec(const GVal& obj, uint64_t* s, std::vector<nbg_kv>* headers, bool* headers_nil) {
   memset(s, 0, NBG_VS_SLOTS * sizeof(uint64_t));
@@ -426,31 +493,33 @@ bool pack_vs_spec(const GVal& obj, uint64_t* s, std::vector<nbg_kv>* headers, bo
   // unstructured.NestedMap(obj, "spec"): found only if present, ok only if a map (COMMON:200,208)
   const GVal* specp = obj.kind == GVal::Map ? obj.find("spec") : nullptr;
   if (!specp || specp->kind != GVal::Map) return false;
-  GVal spec = *specp;  // leaves taken out below are replaced by a marker, so shape is kept
+  const GVal& spec = *specp;
+  const GVal* marks[8];                  // leaves with a slot of their own: read as a marker by the residual digest
+  int n_marks = 0;
 
-  auto take_str = [](GVal* holder, uint64_t* slot) {
-    if (holder && holder->kind == GVal::Str) { *slot = hash_str(holder->s); *holder = marker(); }
+  auto take_str = [&](const GVal* holder, uint64_t* slot) {
+    if (holder && holder->kind == GVal::Str) { *slot = hash_str(holder->s); marks[n_marks++] = holder; }
   };
-  auto first = [](GVal* l) -> GVal* { return (l && l->kind == GVal::List && !l->items.empty()) ? &l->items[0] : nullptr; };
-  auto child = [](GVal* m, const char* k) -> GVal* { return (m && m->kind == GVal::Map) ? m->find(k) : nullptr; };
+  auto first = [](const GVal* l) -> const GVal* { return (l && l->kind == GVal::List && !l->items.empty()) ? &l->items[0] : nullptr; };
+  auto child = [](const GVal* m, const char* k) -> const GVal* { return (m && m->kind == GVal::Map) ? m->find(k) : nullptr; };
 
   take_str(first(child(&spec, "hosts")), &s[0]);
   take_str(first(child(&spec, "gateways")), &s[1]);
-  GVal* http0 = first(child(&spec, "http"));
+  const GVal* http0 = first(child(&spec, "http"));
   take_str(child(child(first(child(http0, "match")), "uri"), "prefix"), &s[2]);
   take_str(child(child(http0, "rewrite"), "uri"), &s[3]);
-  GVal* dest = child(first(child(http0, "route")), "destination");
+  const GVal* dest = child(first(child(http0, "route")), "destination");
   take_str(child(dest, "host"), &s[4]);
-  if (GVal* num = child(child(dest, "port"), "number")) {
-    if (num->kind == GVal::Int) { s[5] = (uint64_t)num->i; s[6] = 1; *num = marker(); }
-    else if (num->kind == GVal::Float) { memcpy(&s[5], &num->f, 8); if (num->f == 0.0) s[5] = 0; s[6] = 2; *num = marker(); }
+  if (const GVal* num = child(child(dest, "port"), "number")) {
+    if (num->kind == GVal::Int) { s[5] = (uint64_t)num->i; s[6] = 1; marks[n_marks++] = num; }
+    else if (num->kind == GVal::Float) { memcpy(&s[5], &num->f, 8); if (num->f == 0.0) s[5] = 0; s[6] = 2; marks[n_marks++] = num; }
   }
-  if (GVal* set = child(child(child(http0, "headers"), "request"), "set")) {
+  if (const GVal* set = child(child(child(http0, "headers"), "request"), "set")) {
     bool all_str = set->kind == GVal::Map;
     if (all_str) for (const auto& e : set->kv) if (e.second.kind != GVal::Str) all_str = false;
-    if (all_str) { pack_kvmap(*set, headers); *headers_nil = false; *set = marker(); }
+    if (all_str) { pack_kvmap(*set, headers); *headers_nil = false; marks[n_marks++] = set; }
   }
-  s[7] = digest(spec);
+  s[7] = digest_marked(spec, marks, n_marks);
   return true;
 }
 

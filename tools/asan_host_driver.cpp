@@ -51,6 +51,19 @@ int main() {
       nbh_fleet_objects(f, nullptr, 100, 500, objs.data());
       if (nbh_pack_objects(objs.data(), 500, 1, &a, &b, &c)) return 5;
       nbh_sts_free(a); nbh_svc_free(b); nbh_vs_free(c);
+      {  // the desired StatefulSet tile made from the Notebook's: for the device (add_gen) and on the host (add_notebook)
+        nbh_sts* g = nbh_sts_new();
+        nbh_sts* h = nbh_sts_new();
+        for (int k = 0; k < 500; ++k) {
+          if (nbh_sts_add_gen(g, objs[k * 7], objs[k * 7 + 2], nullptr)) return 6;
+          if (nbh_sts_add_notebook(h, objs[k * 7], objs[k * 7 + 2], nullptr)) return 7;
+        }
+        nbg_sts_gen_inputs gi; nbg_sts_gen_consts gc; nbg_sts_batch gb;
+        if (nbh_sts_view_gen(g, &gi) != 500 || nbh_sts_view_gen(h, &gi) != 0) return 8;
+        if (nbh_sts_gen_consts(nullptr, &gc) || nbh_sts_view(h, &gb) != 500) return 9;
+        if (nbh_sts_add_notebook(g, objs[0], objs[2], nullptr) == 0) return 10;   // one kind of `from` side per batch
+        nbh_sts_free(g); nbh_sts_free(h);
+      }
       for (int k = 0; k < 200; ++k) {
         nbh_obj* m = nbh_obj_clone(objs[k * 7]);
         nbh_obj_set_str(m, "metadata.labels.opendatahub.io/feast-integration", k % 2 ? "true" : "false");
