@@ -41,7 +41,7 @@ func outputs(n int) ([]byte, []uint64) { return make([]byte, n), make([]uint64, 
 // ---- CopyServiceFields (util.go:166-195) --------------------------------------------------------------
 type SvcBatch struct {
 	Flags              []uint8  // n
-	PortsFrom, PortsTo []uint64 // n * 16
+	PortsFrom, PortsTo []uint64 // n * NBG_SVC_SLOTS (8)
 	LabelsFrom, LabelsTo, AnnFrom, AnnTo, SelFrom, SelTo KvMap
 }
 
@@ -174,7 +174,7 @@ type SvcGenBatch struct {
 	NameHash   []uint64 // hash64(notebook name)
 	TargetPort []int32
 	Flags      []uint8
-	PortsTo    []uint64 // n * 16
+	PortsTo    []uint64 // n * NBG_SVC_SLOTS (8)
 	LabelsTo, AnnTo, SelTo KvMap
 }
 
